@@ -1,0 +1,176 @@
+/*
+ * magicsoup_b200 -- C ABI of the B200 (sm_100a) implementation of magicsoup's
+ * per-step world math.  One shared library: magicsoup_b200/libmagicsoup_b200.so.
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer owned by the caller unless its name ends
+ *     in `_host`.  The library allocates nothing and frees nothing; scratch
+ *     memory is passed in (sizes from the ms_*_scratch_bytes queries).
+ *   - Tensors are row-major and shaped exactly like the reference's torch tensors
+ *     (reference = mRcSchwering/magic-soup 1.0.5, paths below are relative to its
+ *     python/magicsoup/): X (c,s) f32; N,Nf,Nb,A (c,p,s) int32; Kmr (c,p,s) f32;
+ *     Ke,Kmf,Kmb,Vmax (c,p) f32; molecule_map (m,H,W) f32; cell_molecules (c,m)
+ *     f32; cell_positions (c,2) int32.  s = 2*m, intracellular signals first.
+ *   - `stream` is a cudaStream_t (NULL = default stream).  Calls only enqueue
+ *     work; nothing synchronises the device.
+ *   - Return value: 0 = ok, negative = error (ms_error_string).  No C++ exceptions
+ *     cross this boundary, NaN/Inf in the data never trap (the reference lets them
+ *     propagate, docs/tutorials.md:408).
+ *   - Arithmetic: float32, no FMA contraction, sums in ascending index order,
+ *     integer powers by repeated multiplication -- bit-identical to
+ *     oracle/ms_oracle.c (the "spec order").
+ */
+#ifndef MAGICSOUP_B200_H
+#define MAGICSOUP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MS_OK 0
+#define MS_ERR_INVALID_ARGUMENT (-1)
+#define MS_ERR_CUDA (-2)
+#define MS_ERR_SCRATCH_TOO_SMALL (-3)
+#define MS_ERR_NO_DEVICE (-4)
+#define MS_ERR_TOO_LARGE (-5)
+
+/* Number of uint32 words in a flags buffer (see ms_integrate_signals). */
+#define MS_N_FLAGS 24
+
+/* The nine Kinetics parameter tensors, kinetics.py:399-409. */
+typedef struct ms_kinetics_params {
+  const int32_t *N, *Nf, *Nb, *A; /* (c,p,s) */
+  const float *Kmr;               /* (c,p,s) */
+  const float *Ke, *Kmf, *Kmb, *Vmax; /* (c,p) */
+  int64_t c, p, s;
+} ms_kinetics_params;
+
+int ms_version(void);
+const char *ms_error_string(int code);
+/* message of the last CUDA error seen by this thread's failing call ("" if none) */
+const char *ms_last_cuda_error(void);
+int ms_device_count(void);
+
+/* ------------------------------------------------------------------ kinetics */
+
+/*
+ * Kinetics.integrate_signals(X) -> X'          kinetics.py:725-751
+ * Three trimmed parts (0.7, 0.2, 0.1), each: velocities, substrate trimming,
+ * equilibrium trimming; fused per cell, every parameter read once.
+ *
+ * eq_iters_host[3]: how many equilibrium-adjustment iterations to APPLY in each
+ *   part (0..4).  The reference stops a part's iterations as soon as NO cell in
+ *   the whole batch has an adjustable protein with |V| > 0.1 (kinetics.py:846, a
+ *   global torch.any).  Pass {4,4,4} first, then inspect `flags`:
+ *     flags[q*4+k]      != 0  <=> some cell had such a protein at iteration k of part q
+ *     flags[12+q*4+k]   != 0  <=> some cell had ANY adjustable protein there
+ *   If flags[q*4+k]==0 while flags[12+q*4+k]!=0 for some k < eq_iters[q], the
+ *   reference would have stopped part q at k: call again with eq_iters[q] = k
+ *   (later parts' flags are only meaningful once earlier parts are settled).
+ *   magicsoup_b200.kinetics.Kinetics.integrate_signals runs this protocol.
+ * flags: MS_N_FLAGS uint32, zeroed by this call before the kernel runs.
+ * scratch: ms_kinetics_scratch_bytes(p, s) bytes (used only by cells whose
+ *   proteomes do not fit the in-shared-memory sparse lists).
+ * X_out must not alias X_in.
+ */
+int ms_integrate_signals(const ms_kinetics_params *params, const float *X_in, float *X_out,
+                         const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
+                         size_t scratch_bytes, void *stream);
+
+/*
+ * Kinetics._integrate_signals_part(adj_vmax, X0) -> X1      kinetics.py:753-769
+ * One part with the caller's already trimmed velocities adj_vmax (c,p).
+ * max_eq_iters as eq_iters above (0 = no equilibrium adjustment, which is what the
+ * reference's tests mock, tests/fast/test_kinetics.py:87-96).  flags: MS_N_FLAGS
+ * words, entries [k] and [12+k] are written.  V_out (c,p) optional (NULL).
+ */
+int ms_integrate_signals_part(const ms_kinetics_params *params, const float *adj_vmax,
+                              const float *X0, float *X1, int32_t max_eq_iters,
+                              uint32_t *flags, float *V_out, void *scratch,
+                              size_t scratch_bytes, void *stream);
+
+size_t ms_kinetics_scratch_bytes(int64_t p, int64_t s);
+
+/* Kinetics._multiply_signals(X, N) -> (xx (c,p), involved (c,p) as uint8)  kinetics.py:894-918 */
+int ms_multiply_signals(const float *X, const int32_t *K, int64_t c, int64_t p, int64_t s,
+                        float *xx, uint8_t *involved, void *stream);
+
+/* Kinetics._get_quotient(X) -> Q (c,p)                                      kinetics.py:881-892 */
+int ms_get_quotient(const float *X, const int32_t *Nf, const int32_t *Nb, int64_t c, int64_t p,
+                    int64_t s, float *Q, void *stream);
+
+/* Kinetics._get_velocities(X, Vmax) -> V (c,p); Vmax is adj_vmax           kinetics.py:771-806 */
+int ms_get_velocities(const ms_kinetics_params *params, const float *X, const float *adj_vmax,
+                      float *V, void *stream);
+
+/* Kinetics._get_negative_adjusted_nv(NV, X) -> NV_adj (c,p,s)              kinetics.py:861-879
+ * Fsig_scratch: (c,s) floats of caller scratch.  NV_adj must not alias NV. */
+int ms_get_negative_adjusted_nv(const float *NV, const float *X, int64_t c, int64_t p, int64_t s,
+                                float *NV_adj, float *Fsig_scratch, void *stream);
+
+/* X1 = max(X0 + sum over proteins of NV, 0)                                  kinetics.py:763-764
+ * NV dense (c,p,s); F_scratch: (c,p) floats of caller scratch. */
+int ms_add_protein_rates(const float *X0, const float *NV, int64_t c, int64_t p, int64_t s,
+                         float *X1, float *F_scratch, void *stream);
+
+/*
+ * Kinetics._get_equilibrium_adjusted_x(X0, X1, NV, V) -> X1'               kinetics.py:808-859
+ * Dense NV (c,p,s).  F (c,p) is caller scratch (float).  max_iters / flags as in
+ * ms_integrate_signals_part.  X1_out may alias X1_in.
+ */
+int ms_get_equilibrium_adjusted_x(const float *X0, const float *X1_in, const float *NV,
+                                  const float *V, const int32_t *Nf, const int32_t *Nb,
+                                  const float *Ke, int64_t c, int64_t p, int64_t s, float *X1_out,
+                                  float *F_scratch, int32_t max_iters, uint32_t *flags,
+                                  void *stream);
+
+/* --------------------------------------------------------------------- world */
+
+/*
+ * World.enzymatic_activity(), compute half                     world.py:610-622
+ * Gathers X0 = [cell_molecules | molecule_map at the cell's pixel] inside the
+ * kinetics kernel and writes the integrated signals to X_out (c,s).  Nothing is
+ * modified in place so that the eq_iters protocol can re-run; commit the result
+ * with ms_scatter_signals once `flags` are settled.
+ */
+int ms_enzymatic_activity(const ms_kinetics_params *params, const int32_t *cell_positions,
+                          const float *cell_molecules, const float *molecule_map, int64_t m,
+                          int64_t H, int64_t W, float *X_out, const int32_t *eq_iters_host,
+                          uint32_t *flags, void *scratch, size_t scratch_bytes, void *stream);
+
+/*
+ * World.enzymatic_activity(), write-back half                  world.py:624-625
+ * molecule_map[:, x, y] = X[:, m:], cell_molecules_out = X[:, :m].
+ */
+int ms_scatter_signals(const float *X, const int32_t *cell_positions, int64_t c, int64_t m,
+                       int64_t H, int64_t W, float *cell_molecules_out, float *molecule_map,
+                       void *stream);
+
+/*
+ * World.diffuse_molecules(), diffusion half                    world.py:638-649
+ * Per molecule k: 3x3 circular stencil with weights a[k] (8 neighbours) and b[k]
+ * (centre) from World._get_diffuse (world.py:948-972), then the mass correction
+ * += (sum_before - sum_after) / (H*W) and clamp(0).  In place on molecule_map.
+ * scratch: ms_diffuse_scratch_bytes(m,H,W) bytes (stencil output + plane sums).
+ */
+int ms_diffuse_molecules(float *molecule_map, const float *a, const float *b, int64_t m, int64_t H,
+                         int64_t W, void *scratch, size_t scratch_bytes, void *stream);
+
+size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W);
+
+/*
+ * World.diffuse_molecules(), permeation half                   world.py:651-665
+ * perm[k] from World._get_permeate (world.py:935-946).  cell_molecules_out may
+ * alias cell_molecules_in; molecule_map is updated at the cells' pixels.
+ */
+int ms_permeate(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
+                const int32_t *cell_positions, const float *perm, int64_t c, int64_t m, int64_t H,
+                int64_t W, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MAGICSOUP_B200_H */

@@ -1,0 +1,9 @@
+"""
+magicsoup_b200: B200-native (sm_100a) implementation of magicsoup's per-step world
+math behind the reference's own `Kinetics` / `World` API:
+`Kinetics.integrate_signals`, `World.enzymatic_activity`, `World.diffuse_molecules`.
+"""
+from magicsoup_b200.kinetics import Kinetics  # noqa: F401
+from magicsoup_b200.world import World, Molecule, Chemistry  # noqa: F401
+
+__version__ = "0.1.0"

@@ -1,0 +1,286 @@
+// World.diffuse_molecules for sm_100a (reference python/magicsoup/world.py:627-665,
+// weights from World._get_diffuse :948-972 and World._get_permeate :935-946), and the
+// write-back half of World.enzymatic_activity (:624-625).
+//
+//   pass 1  stencil      shared-memory tiled circular 3x3 stencil of every molecule plane
+//                        into scratch + exact fixed-point plane sums before/after
+//   pass 2  correct      out += (sum_before - sum_after) / (H*W); clamp(0); back in place
+//   pass 3  permeate     per cell and molecule: symmetric exchange with its pixel
+//
+// Spec order (bit-identical to oracle/ms_oracle.c): top=(nw+n)+ne, mid=w+e,
+// bot=(sw+s)+se, nb=(top+mid)+bot, out=b*c+a*nb without FMA; plane sums are exact
+// integers of 2^-32 (order independent, so atomics are deterministic), rounded once
+// to float32 where the reference has torch.sum's float32 scalars (world.py:640-648).
+#include "ms_common.cuh"
+
+namespace ms {
+
+constexpr int TW = 128;      // tile width  (32 lanes x float4)
+constexpr int TH = 32;       // tile height (8 warps x 4 rows)
+constexpr int TSTRIDE = 136; // smem row stride in floats; interior starts at column 4
+constexpr int DTHREADS = 256;
+
+struct FixSum {
+  long long hi, lo;
+  __device__ __forceinline__ void add(float x) {
+    const long long q = __double2ll_rn((double)x * 4294967296.0);
+    hi += q >> 32;
+    lo += q & 0xffffffffLL;
+  }
+};
+
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+__device__ __forceinline__ float stencil_point(float nw, float n, float ne, float wv, float c,
+                                               float e, float sw, float sv, float se, float a,
+                                               float b) {
+  const float top = (nw + n) + ne;
+  const float mid = wv + e;
+  const float bot = (sw + sv) + se;
+  const float nb = (top + mid) + bot;
+  return b * c + a * nb;
+}
+
+// block-level reduction of the four fixed-point accumulators + one atomic each
+__device__ void block_commit_sums(FixSum in, FixSum out, unsigned long long *sums /* 4 per plane */) {
+  __shared__ long long red[4][DTHREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long v0 = warp_sum_ll(in.hi), v1 = warp_sum_ll(in.lo), v2 = warp_sum_ll(out.hi),
+            v3 = warp_sum_ll(out.lo);
+  if (lane == 0) { red[0][warp] = v0; red[1][warp] = v1; red[2][warp] = v2; red[3][warp] = v3; }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    long long t = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += red[threadIdx.x][w];
+    atomicAdd(&sums[threadIdx.x], (unsigned long long)t);
+  }
+}
+
+// fast path: W % 128 == 0, H % 32 == 0.  grid = (W/TW, H/TH, m)
+__global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__restrict__ map,
+                                                                 float *__restrict__ out,
+                                                                 const float *__restrict__ wa,
+                                                                 const float *__restrict__ wb, int H,
+                                                                 int W, unsigned long long *sums) {
+  __shared__ __align__(16) float tile[(TH + 2) * TSTRIDE];
+  const int k = blockIdx.z;
+  const int x0 = blockIdx.y * TH, y0 = blockIdx.x * TW;
+  const float *plane = map + (size_t)k * H * W;
+  float *oplane = out + (size_t)k * H * W;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  // interior columns of rows -1..TH: one float4 per lane per row
+  for (int r = warp; r < TH + 2; r += DTHREADS / 32) {
+    int gx = x0 + r - 1;
+    gx = gx < 0 ? gx + H : (gx >= H ? gx - H : gx);
+    const float4 v = *reinterpret_cast<const float4 *>(plane + (size_t)gx * W + y0 + 4 * lane);
+    *reinterpret_cast<float4 *>(&tile[r * TSTRIDE + 4 + 4 * lane]) = v;
+  }
+  // halo columns -1 and TW
+  for (int t = threadIdx.x; t < 2 * (TH + 2); t += DTHREADS) {
+    const int r = t >> 1, side = t & 1;
+    int gx = x0 + r - 1;
+    gx = gx < 0 ? gx + H : (gx >= H ? gx - H : gx);
+    int gy = side ? y0 + TW : y0 - 1;
+    gy = gy < 0 ? gy + W : (gy >= W ? gy - W : gy);
+    tile[r * TSTRIDE + (side ? 4 + TW : 3)] = plane[(size_t)gx * W + gy];
+  }
+  __syncthreads();
+
+  const float a = wa[k], b = wb[k];
+  FixSum sin = {0, 0}, sout = {0, 0};
+  const int c0 = 4 + 4 * lane;
+  // rolling 3-row window: rows r-1, r, r+1 of the tile; each row = left, 4 centre, right
+  float prev[6], cur[6], nxt[6];
+  auto load_row = [&](int r, float *dst) {
+    const float4 v = *reinterpret_cast<const float4 *>(&tile[r * TSTRIDE + c0]);
+    dst[0] = tile[r * TSTRIDE + c0 - 1];
+    dst[1] = v.x; dst[2] = v.y; dst[3] = v.z; dst[4] = v.w;
+    dst[5] = tile[r * TSTRIDE + c0 + 4];
+  };
+  const int r0 = 4 * warp;  // first output row of this warp (tile row index r0+1)
+  load_row(r0, prev);
+  load_row(r0 + 1, cur);
+#pragma unroll
+  for (int rr = 0; rr < 4; rr++) {
+    load_row(r0 + rr + 2, nxt);
+    float o[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      o[q] = stencil_point(prev[q], prev[q + 1], prev[q + 2], cur[q], cur[q + 1], cur[q + 2], nxt[q],
+                           nxt[q + 1], nxt[q + 2], a, b);
+      sin.add(cur[q + 1]);
+      sout.add(o[q]);
+    }
+    *reinterpret_cast<float4 *>(oplane + (size_t)(x0 + r0 + rr) * W + y0 + 4 * lane) =
+        make_float4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+    for (int q = 0; q < 6; q++) { prev[q] = cur[q]; cur[q] = nxt[q]; }
+  }
+  block_commit_sums(sin, sout, sums + 4 * k);
+}
+
+// generic path: any H, W (e.g. the 5x5 map of the reference's test).  grid = (blocks, 1, m)
+__global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *__restrict__ map,
+                                                                   float *__restrict__ out,
+                                                                   const float *__restrict__ wa,
+                                                                   const float *__restrict__ wb, int H,
+                                                                   int W, unsigned long long *sums) {
+  const int k = blockIdx.z;
+  const float *plane = map + (size_t)k * H * W;
+  float *oplane = out + (size_t)k * H * W;
+  const float a = wa[k], b = wb[k];
+  FixSum sin = {0, 0}, sout = {0, 0};
+  const long long n = (long long)H * W;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n;
+       t += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(t / W), y = (int)(t % W);
+    const int xm = x == 0 ? H - 1 : x - 1, xp = x == H - 1 ? 0 : x + 1;
+    const int ym = y == 0 ? W - 1 : y - 1, yp = y == W - 1 ? 0 : y + 1;
+    const float *rm = plane + (size_t)xm * W, *r0 = plane + (size_t)x * W, *rp = plane + (size_t)xp * W;
+    const float c = r0[y];
+    const float o = stencil_point(rm[ym], rm[y], rm[yp], r0[ym], c, r0[yp], rp[ym], rp[y], rp[yp], a, b);
+    oplane[t] = o;
+    sin.add(c);
+    sout.add(o);
+  }
+  block_commit_sums(sin, sout, sums + 4 * k);
+}
+
+// pass 2: world.py:648-649.  grid = (blocks, 1, m)
+__global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restrict__ out,
+                                                           float *__restrict__ map, long long n_pxls,
+                                                           const unsigned long long *sums) {
+  const int k = blockIdx.z;
+  const long long *sk = reinterpret_cast<const long long *>(sums) + 4 * k;
+  const float s0 = (float)((double)sk[0] + (double)sk[1] * 2.3283064365386963e-10);
+  const float s1 = (float)((double)sk[2] + (double)sk[3] * 2.3283064365386963e-10);
+  const float corr = (s0 - s1) / (float)n_pxls;
+  const float *src = out + (size_t)k * n_pxls;
+  float *dst = map + (size_t)k * n_pxls;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if ((n_pxls & 3) == 0) {
+    const float4 *s4 = reinterpret_cast<const float4 *>(src);
+    float4 *d4 = reinterpret_cast<float4 *>(dst);
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < (n_pxls >> 2); t += stride) {
+      float4 v = s4[t];
+      v.x = clamp0(v.x + corr); v.y = clamp0(v.y + corr);
+      v.z = clamp0(v.z + corr); v.w = clamp0(v.w + corr);
+      d4[t] = v;
+    }
+  } else {
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n_pxls; t += stride)
+      dst[t] = clamp0(src[t] + corr);
+  }
+}
+
+// pass 3: world.py:654-665, one thread per (cell, molecule)
+__global__ void permeate_kernel(const float *cm_in, float *cm_out, float *map, const int *pos,
+                                const float *perm, long long c, int m, int H, int W) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * m) return;
+  const long long cell = r / m;
+  const int k = (int)(r % m);
+  const int x = pos[2 * cell], y = pos[2 * cell + 1];
+  const size_t mi = ((size_t)k * H + x) * W + y;
+  const float xi = cm_in[r], xe = map[mi], q = perm[k];
+  const float di = xi * q, de = xe * q;
+  cm_out[r] = xi + (de - di);
+  map[mi] = xe + (di - de);
+}
+
+// world.py:624-625, one thread per (cell, signal)
+__global__ void scatter_kernel(const float *X, const int *pos, long long c, int m, int H, int W,
+                               float *cm_out, float *map) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = 2 * m;
+  if (r >= c * s) return;
+  const long long cell = r / s;
+  const int i = (int)(r % s);
+  const float v = X[r];
+  if (i < m) {
+    cm_out[cell * m + i] = v;
+  } else {
+    const int x = pos[2 * cell], y = pos[2 * cell + 1];
+    map[((size_t)(i - m) * H + x) * W + y] = v;
+  }
+}
+
+}  // namespace ms
+
+using namespace ms;
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+extern "C" size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W) {
+  if (m <= 0 || H <= 0 || W <= 0) return 256;
+  return align256((size_t)m * H * W * sizeof(float)) + align256((size_t)m * 4 * sizeof(long long));
+}
+
+// shared by ms_diffuse_molecules and the no-scratch-argument variants
+int ms_diffuse_launch_(float *molecule_map, const float *a, const float *b, int64_t m, int64_t H,
+                       int64_t W, float *tmp, unsigned long long *sums, cudaStream_t st) {
+  MS_CUDA_CHECK(cudaMemsetAsync(sums, 0, (size_t)m * 4 * sizeof(long long), st));
+  const long long n = (long long)H * W;
+  if (W % TW == 0 && H % TH == 0) {
+    dim3 grid((unsigned)(W / TW), (unsigned)(H / TH), (unsigned)m);
+    stencil_tiled_kernel<<<grid, DTHREADS, 0, st>>>(molecule_map, tmp, a, b, (int)H, (int)W, sums);
+  } else {
+    unsigned blocks = (unsigned)((n + DTHREADS - 1) / DTHREADS);
+    if (blocks > 1024) blocks = 1024;
+    dim3 grid(blocks, 1, (unsigned)m);
+    stencil_generic_kernel<<<grid, DTHREADS, 0, st>>>(molecule_map, tmp, a, b, (int)H, (int)W, sums);
+  }
+  MS_CUDA_CHECK(cudaGetLastError());
+  long long work = (n & 3) == 0 ? n / 4 : n;
+  unsigned blocks = (unsigned)((work + DTHREADS - 1) / DTHREADS);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, molecule_map, n, sums);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_diffuse_molecules(float *molecule_map, const float *a, const float *b, int64_t m,
+                                    int64_t H, int64_t W, void *scratch, size_t scratch_bytes,
+                                    void *stream) {
+  if (m < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX || m > 65535)
+    return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!molecule_map || !a || !b) return MS_ERR_INVALID_ARGUMENT;
+  if (!scratch || scratch_bytes < ms_diffuse_scratch_bytes(m, H, W)) return MS_ERR_SCRATCH_TOO_SMALL;
+  float *tmp = (float *)scratch;
+  unsigned long long *sums =
+      (unsigned long long *)((char *)scratch + align256((size_t)m * H * W * sizeof(float)));
+  return ms_diffuse_launch_(molecule_map, a, b, m, H, W, tmp, sums, (cudaStream_t)stream);
+}
+
+extern "C" int ms_permeate(const float *cell_molecules_in, float *cell_molecules_out,
+                           float *molecule_map, const int32_t *cell_positions, const float *perm,
+                           int64_t c, int64_t m, int64_t H, int64_t W, void *stream) {
+  if (c < 0 || m < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX) return MS_ERR_INVALID_ARGUMENT;
+  if (c * m == 0) return MS_OK;
+  if (!cell_molecules_in || !cell_molecules_out || !molecule_map || !cell_positions || !perm)
+    return MS_ERR_INVALID_ARGUMENT;
+  const long long n = c * m;
+  permeate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, c, (int)m, (int)H, (int)W);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_scatter_signals(const float *X, const int32_t *cell_positions, int64_t c, int64_t m,
+                                  int64_t H, int64_t W, float *cell_molecules_out, float *molecule_map,
+                                  void *stream) {
+  if (c < 0 || m < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX) return MS_ERR_INVALID_ARGUMENT;
+  if (c * m == 0) return MS_OK;
+  if (!X || !cell_positions || !cell_molecules_out || !molecule_map) return MS_ERR_INVALID_ARGUMENT;
+  const long long n = c * 2 * m;
+  scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      X, cell_positions, c, (int)m, (int)H, (int)W, cell_molecules_out, molecule_map);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}

@@ -1,0 +1,878 @@
+// Fused per-cell kinetics for sm_100a: Kinetics.integrate_signals
+// (reference python/magicsoup/kinetics.py:725-918) and the gather half of
+// World.enzymatic_activity (python/magicsoup/world.py:619-622).
+//
+// One warp integrates one cell.  The cell's dense (p,s) parameter tile is streamed
+// from HBM exactly once with coalesced loads (one 128 B row segment per load
+// instruction) and compressed on the fly into sparse lists in shared memory:
+//   cat  : per protein, ascending signal: (signal, Nf, Nb, N)      -> products X^N
+//   reg  : per protein, ascending signal: (signal, A) + Kmr        -> allosteric term
+//   csc  : per signal, ascending protein: (protein, N)             -> sums over proteins
+// All 3 parts x (velocities, substrate trimming, <=4 equilibrium iterations) then run
+// on those lists out of shared memory.  Cells whose tiles do not fit the lists or the
+// 8-bit packing take a dense path straight from global memory with identical
+// arithmetic.  See DESIGN.md for the layout, the spec order and the roofline.
+#include "ms_common.cuh"
+
+namespace ms {
+
+constexpr int WARPS_PER_CTA = 8;
+constexpr int THREADS = WARPS_PER_CTA * 32;
+constexpr int MAX_ST = 4;  // signals per lane in the sparse path (s <= 128)
+constexpr unsigned FULL = 0xffffffffu;
+
+struct KinArgs {
+  const int *N, *Nf, *Nb, *A;
+  const float *Kmr, *Ke, *Kmf, *Kmb, *Vmax;
+  long long c;
+  int p, s;
+  // signal source: X_in (c,s), or gather from cell_molecules / molecule_map
+  const float *X_in;
+  const float *cell_mols;
+  const float *mol_map;
+  const int *pos;
+  int m, H, W;
+  float *X_out;
+  unsigned *flags;
+  int n_parts;            // 3 = integrate_signals, 1 = one part with adj_vmax
+  int eq_iters[3];
+  float trims[3];
+  const float *adj_vmax;  // (c,p) when n_parts == 1
+  float *V_out;           // optional (c,p), n_parts == 1 only
+  int e_cat, e_reg;       // list capacities (entries)
+  int words_per_warp;     // shared memory words per warp
+  int sparse_enabled;     // 0 forces the dense path (p > 256 or s > 128)
+};
+
+// per-warp shared memory carve-up (32-bit words)
+struct WarpMem {
+  float *X0, *X1, *Fsig;            // s32 each
+  unsigned *colptr;                 // s32 + 4
+  float *V, *Fmin, *F;              // p32 each
+  float *Ke, *Kmf, *Kmb, *Vmax;     // p32 each
+  unsigned *act;                    // p32: indices of proteins with cat entries
+  unsigned *rowptr;                 // p32 + 4: (cat offset) | (reg offset << 16)
+  unsigned *cat;                    // e_cat
+  unsigned *csc;                    // e_cat
+  float *nvs;                       // e_cat (aliases the link list during the scan)
+  unsigned *reg;                    // e_reg
+  float *regk;                      // e_reg
+};
+
+__host__ __device__ inline int round32(int x) { return (x + 31) & ~31; }
+
+__host__ __device__ inline int warp_words(int p, int s, int e_cat, int e_reg) {
+  const int s32 = round32(s), p32 = round32(p);
+  return 3 * s32 + (s32 + 4) + 8 * p32 + (p32 + 4) + 3 * e_cat + 2 * e_reg;
+}
+
+__device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_cat, int e_reg) {
+  const int s32 = round32(s), p32 = round32(p);
+  WarpMem m;
+  m.X0 = (float *)w;            w += s32;
+  m.X1 = (float *)w;            w += s32;
+  m.Fsig = (float *)w;          w += s32;
+  m.colptr = w;                 w += s32 + 4;
+  m.V = (float *)w;             w += p32;
+  m.Fmin = (float *)w;          w += p32;
+  m.F = (float *)w;             w += p32;
+  m.Ke = (float *)w;            w += p32;
+  m.Kmf = (float *)w;           w += p32;
+  m.Kmb = (float *)w;           w += p32;
+  m.Vmax = (float *)w;          w += p32;
+  m.act = w;                    w += p32;
+  m.rowptr = w;                 w += p32 + 4;
+  m.cat = w;                    w += e_cat;
+  m.csc = w;                    w += e_cat;
+  m.nvs = (float *)w;           w += e_cat;
+  m.reg = w;                    w += e_reg;
+  m.regk = (float *)w;
+  return m;
+}
+
+// ---------------------------------------------------------------------------
+// scan: stream the cell's dense tile once and build the sparse lists.
+// Lane l owns signals l, l+32, ...; rows (proteins) are visited in ascending order,
+// so row lists come out in ascending signal order and column lists in ascending
+// protein order without any sorting or atomics.
+// Returns false if the cell needs the dense path.
+// ---------------------------------------------------------------------------
+template <int ST>
+__device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, int lane,
+                          int &n_act_out) {
+  const int p = a.p, s = a.s;
+  const long long tile = cell * (long long)p * s;
+  const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
+  const unsigned lt = (1u << lane) - 1u;
+  unsigned *link = (unsigned *)w.nvs;
+
+  int head[ST], cnt[ST];
+#pragma unroll
+  for (int t = 0; t < ST; t++) { head[t] = 0; cnt[t] = 0; }
+  int cat_total = 0, reg_total = 0, n_act = 0;
+  bool bad = false;
+  if (lane == 0) w.rowptr[0] = 0;
+
+  constexpr int RU = (ST == 1) ? 4 : (ST == 2 ? 2 : 1);  // rows in flight per lane
+  for (int j0 = 0; j0 < p; j0 += RU) {
+    int vn[RU][ST], vf[RU][ST], vb[RU][ST], va[RU][ST];
+#pragma unroll
+    for (int r = 0; r < RU; r++) {
+#pragma unroll
+      for (int t = 0; t < ST; t++) {
+        const int i = lane + 32 * t;
+        const bool ok = (j0 + r < p) && (i < s);
+        const int off = (j0 + r) * s + i;
+        vf[r][t] = ok ? ldg_stream(gNf + off) : 0;
+        vb[r][t] = ok ? ldg_stream(gNb + off) : 0;
+        vn[r][t] = ok ? ldg_stream(gN + off) : 0;
+        va[r][t] = ok ? ldg_stream(gA + off) : 0;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RU; r++) {
+      const int j = j0 + r;
+      if (j >= p) break;
+      unsigned row_any = 0;
+#pragma unroll
+      for (int t = 0; t < ST; t++) row_any |= (unsigned)(vf[r][t] | vb[r][t] | vn[r][t] | va[r][t]);
+      if (__ballot_sync(FULL, row_any != 0) != 0) {
+        bool row_cat = false;
+#pragma unroll
+        for (int t = 0; t < ST; t++) {
+          const int i = lane + 32 * t;
+          const int nf = vf[r][t], nb = vb[r][t], n = vn[r][t], av = va[r][t];
+          const bool catnz = (nf | nb | n) != 0;
+          const bool regnz = av != 0;
+          bad |= ((unsigned)nf > 255u) | ((unsigned)nb > 255u) | (n < -128) | (n > 127) |
+                 (av < -128) | (av > 127);
+          const unsigned bc = __ballot_sync(FULL, catnz);
+          const unsigned br = __ballot_sync(FULL, regnz);
+          if (catnz) {
+            const int pos = cat_total + __popc(bc & lt);
+            if (pos < a.e_cat) {
+              w.cat[pos] = (unsigned)i | ((unsigned)nf << 8) | ((unsigned)nb << 16) |
+                           ((unsigned)(n & 0xff) << 24);
+              if (n != 0) {  // column list, newest first: (protein, N, previous entry + 1)
+                link[pos] = (unsigned)j | ((unsigned)(n & 0xff) << 8) | ((unsigned)head[t] << 16);
+                head[t] = pos + 1;
+                cnt[t]++;
+              }
+            }
+          }
+          if (regnz) {
+            const int pos = reg_total + __popc(br & lt);
+            if (pos < a.e_reg)
+              w.reg[pos] = (unsigned)i | ((unsigned)(av & 0xff) << 8) | ((unsigned)j << 16);
+          }
+          cat_total += __popc(bc);
+          reg_total += __popc(br);
+          row_cat |= (bc != 0);
+        }
+        if (row_cat) {
+          if (lane == 0) w.act[n_act] = (unsigned)j;
+          n_act++;
+        }
+      }
+      if (lane == 0)
+        w.rowptr[j + 1] = (unsigned)min(cat_total, 0xffff) | ((unsigned)min(reg_total, 0xffff) << 16);
+    }
+  }
+  n_act_out = n_act;
+  if (__any_sync(FULL, bad) || cat_total > a.e_cat || reg_total > a.e_reg) return false;
+  __syncwarp();
+
+  // column pointers: exclusive scan of the per-signal counts in signal order
+  int base = 0;
+#pragma unroll
+  for (int t = 0; t < ST; t++) {
+    int x = cnt[t];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int y = __shfl_up_sync(FULL, x, d);
+      if (lane >= d) x += y;
+    }
+    const int excl = base + x - cnt[t];
+    const int i = lane + 32 * t;
+    if (i < s) w.colptr[i] = (unsigned)excl;
+    // walk the (newest first) column list and lay it out ascending
+    int e = head[t], k = excl + cnt[t] - 1;
+    while (e) {
+      const unsigned wd = link[e - 1];
+      w.csc[k--] = wd & 0xffffu;
+      e = (int)(wd >> 16);
+    }
+    base += __shfl_sync(FULL, x, 31);
+  }
+  if (lane == 0) w.colptr[s] = (unsigned)base;
+
+  // per-protein scalars, and the Kmr values of the (few) regulatory entries
+  const long long row = cell * (long long)p;
+  for (int j = lane; j < p; j += 32) {
+    w.Ke[j] = ldg_stream(a.Ke + row + j);
+    w.Kmf[j] = ldg_stream(a.Kmf + row + j);
+    w.Kmb[j] = ldg_stream(a.Kmb + row + j);
+    w.Vmax[j] = a.adj_vmax ? ldg_stream(a.adj_vmax + row + j) : ldg_stream(a.Vmax + row + j);
+  }
+  for (int e = lane; e < reg_total; e += 32) {
+    const unsigned wd = w.reg[e];
+    w.regk[e] = ldg_stream(a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
+  }
+  __syncwarp();
+  return true;
+}
+
+// ---------------------------------------------------------------------------
+// sparse path: all parts of one cell on the shared-memory lists
+// ---------------------------------------------------------------------------
+template <int ST>
+__device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, int lane, int n_act,
+                           unsigned *sflags) {
+  const int p = a.p, s = a.s;
+  for (int q = 0; q < a.n_parts; q++) {
+    const float trim = a.trims[q];
+    // ---- velocities (kinetics.py:771-806) on the active proteins
+    bool poison = false;
+    for (int t = lane; t < n_act; t += 32) {
+      const int j = (int)w.act[t];
+      const unsigned rp0 = w.rowptr[j], rp1 = w.rowptr[j + 1];
+      float xf = 1.0f, xb = 1.0f;
+      bool invf = false, invb = false;
+      for (unsigned e = rp0 & 0xffffu; e < (rp1 & 0xffffu); e++) {
+        const unsigned wd = w.cat[e];
+        const float x = w.X0[wd & 0xffu];
+        const int nf = (wd >> 8) & 0xff, nb = (wd >> 16) & 0xff;
+        if (nf) { invf = true; xf = xf * (nf == 1 ? x : powi(x, nf)); }
+        if (nb) { invb = true; xb = xb * (nb == 1 ? x : powi(x, nb)); }
+      }
+      float kf = fix_product(xf) / w.Kmf[j];
+      if (!invf) kf = 0.0f;
+      if (isinf(kf)) kf = V_MAX;
+      float kb = fix_product(xb) / w.Kmb[j];
+      if (!invb) kb = 0.0f;
+      if (isinf(kb)) kb = V_MAX;
+      float a_reg = 1.0f;
+      for (unsigned e = rp0 >> 16; e < (rp1 >> 16); e++) {
+        const unsigned wd = w.reg[e];
+        const int av = (int)(int8_t)((wd >> 8) & 0xff);
+        a_reg = a_reg * reg_factor(w.X0[wd & 0xffu], av, w.regk[e]);
+      }
+      float vmax = w.Vmax[j];
+      if (!a.adj_vmax) vmax = clamp0(vmax * trim);  // kinetics.py:749
+      const float v = velocity_from(kf, kb, a_reg, vmax);
+      w.V[j] = v;
+      poison |= isnan(v);
+    }
+    poison = __any_sync(FULL, poison);  // 0 * NaN of the dense reference reaches every signal
+    __syncwarp();
+
+    // ---- substrate trimming (kinetics.py:861-879): per signal D_i and F_i
+#pragma unroll
+    for (int t = 0; t < ST; t++) {
+      const int i = lane + 32 * t;
+      if (i < s) {
+        float d = 0.0f;
+        for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++) {
+          const unsigned wd = w.csc[e];
+          const float nv = (float)(int)(int8_t)(wd >> 8) * w.V[wd & 0xffu];  // kinetics.py:759
+          w.nvs[e] = nv;
+          float neg = -nv;
+          neg = neg < 0.0f ? 0.0f : neg;
+          d = d + neg;
+        }
+        float f = w.X0[i] / d;
+        if (f > 1.0f) f = 1.0f;
+        w.Fsig[i] = f;
+      }
+    }
+    __syncwarp();
+    // per protein: the most limiting substrate
+    for (int t = lane; t < n_act; t += 32) {
+      const int j = (int)w.act[t];
+      const float v = w.V[j];
+      float fm = 1.0f;
+      for (unsigned e = w.rowptr[j] & 0xffffu; e < (w.rowptr[j + 1] & 0xffffu); e++) {
+        const unsigned wd = w.cat[e];
+        const int n = (int)(int8_t)(wd >> 24);
+        const bool removes = n > 0 ? (v < 0.0f) : (n < 0 ? (v > 0.0f) : false);
+        if (removes) fm = nanmin(fm, w.Fsig[wd & 0xffu]);
+      }
+      w.Fmin[j] = fm;
+      w.F[j] = 1.0f;
+    }
+    __syncwarp();
+    // X1 = max(X0 + sum_j NV'_ji, 0)   (kinetics.py:763-764)
+#pragma unroll
+    for (int t = 0; t < ST; t++) {
+      const int i = lane + 32 * t;
+      if (i < s) {
+        float acc = 0.0f;
+        for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++) {
+          const float nvp = w.nvs[e] * w.Fmin[w.csc[e] & 0xffu];
+          w.nvs[e] = nvp;
+          acc = acc + nvp;
+        }
+        float x = clamp0(w.X0[i] + acc);
+        if (poison) x = __int_as_float(0x7fc00000);
+        w.X1[i] = x;
+      }
+    }
+    __syncwarp();
+
+    // ---- equilibrium trimming (kinetics.py:808-859)
+    const int iters = a.eq_iters[q];
+    for (int k = 0; k < iters; k++) {
+      const float inc = eq_increment(k);
+      unsigned mine = 0;
+      for (int t = lane; t < n_act; t += 32) {
+        const int j = (int)w.act[t];
+        float xf = 1.0f, xb = 1.0f;
+        bool invf = false, invb = false;
+        for (unsigned e = w.rowptr[j] & 0xffffu; e < (w.rowptr[j + 1] & 0xffffu); e++) {
+          const unsigned wd = w.cat[e];
+          const float x = w.X1[wd & 0xffu];
+          const int nf = (wd >> 8) & 0xff, nb = (wd >> 16) & 0xff;
+          if (nf) { invf = true; xf = xf * (nf == 1 ? x : powi(x, nf)); }
+          if (nb) { invb = true; xb = xb * (nb == 1 ? x : powi(x, nb)); }
+        }
+        xf = invf ? fix_product(xf) : 0.0f;
+        xb = invb ? fix_product(xb) : 0.0f;
+        const float F = w.F[j];
+        const unsigned dec = eq_decide(w.V[j], quotient_from(xb, xf), w.Ke[j], F);
+        if (dec & 3u) {
+          mine |= (dec & 4u) ? 3u : 2u;
+          w.F[j] = eq_update(F, dec, inc);
+        }
+      }
+      const unsigned any = __reduce_or_sync(FULL, mine);
+      if (lane == 0 && any) {
+        if (any & 1u) sflags[q * 4 + k] = 1u;
+        sflags[12 + q * 4 + k] = 1u;
+      }
+      if (!any) break;  // no adjustable protein: F, X1 and every later iteration are unchanged
+      __syncwarp();
+#pragma unroll
+      for (int t = 0; t < ST; t++) {
+        const int i = lane + 32 * t;
+        if (i < s) {
+          float acc = 0.0f;
+          for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++)
+            acc = acc + w.nvs[e] * w.F[w.csc[e] & 0xffu];
+          float x = clamp0(w.X0[i] + acc);
+          if (poison) x = __int_as_float(0x7fc00000);
+          w.X1[i] = x;
+        }
+      }
+      __syncwarp();
+    }
+
+    if (a.V_out) {
+      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = 0.0f;
+      __syncwarp();
+      for (int t = lane; t < n_act; t += 32) {
+        const int j = (int)w.act[t];
+        a.V_out[cell * (long long)p + j] = w.V[j];
+      }
+    }
+    // next part starts from this part's result
+#pragma unroll
+    for (int t = 0; t < ST; t++) {
+      const int i = lane + 32 * t;
+      if (i < s) w.X0[i] = w.X1[i];
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// dense path: same arithmetic straight from global memory (any p, s, any int32)
+// F, V, Fmin live in `scr` (global, 3*p floats per warp) when p is too large for
+// the shared arrays; X0/X1/Fsig always fit (s32 words are reserved per warp).
+// ---------------------------------------------------------------------------
+__device__ float dense_product(const float *X, const int *K, int s, bool &involved) {
+  float xx = 1.0f;
+  bool any = false;
+  for (int i = 0; i < s; i++) {
+    const int k = K[i];
+    if (k > 0) {
+      any = true;
+      xx = xx * powi(X[i], k);
+    } else if (k < 0) {
+      xx = xx * __int_as_float(0x7f800000);
+    }
+  }
+  involved = any;
+  return fix_product(xx);
+}
+
+__device__ void run_dense(const KinArgs &a, float *X0, float *X1, float *Fsig, float *V, float *Fmin,
+                          float *F, long long cell, int lane, unsigned *sflags) {
+  const int p = a.p, s = a.s;
+  const long long row = cell * (long long)p;
+  const long long tile = row * s;
+  const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
+  const float *gKmr = a.Kmr + tile;
+  for (int q = 0; q < a.n_parts; q++) {
+    const float trim = a.trims[q];
+    bool poison = false;
+    for (int j = lane; j < p; j += 32) {
+      bool inv;
+      float kf = dense_product(X0, gNf + j * s, s, inv) / a.Kmf[row + j];
+      if (!inv) kf = 0.0f;
+      if (isinf(kf)) kf = V_MAX;
+      float kb = dense_product(X0, gNb + j * s, s, inv) / a.Kmb[row + j];
+      if (!inv) kb = 0.0f;
+      if (isinf(kb)) kb = V_MAX;
+      float a_reg = 1.0f;
+      for (int i = 0; i < s; i++) {
+        const int av = gA[j * s + i];
+        if (av != 0) a_reg = a_reg * reg_factor(X0[i], av, gKmr[j * s + i]);
+      }
+      float vmax = a.adj_vmax ? a.adj_vmax[row + j] : clamp0(a.Vmax[row + j] * trim);
+      const float v = velocity_from(kf, kb, a_reg, vmax);
+      V[j] = v;
+      poison |= isnan(v);
+    }
+    poison = __any_sync(FULL, poison);
+    __syncwarp();
+    for (int i = lane; i < s; i += 32) {
+      float d = 0.0f;
+      for (int j = 0; j < p; j++) {
+        float neg = -((float)gN[j * s + i] * V[j]);
+        neg = neg < 0.0f ? 0.0f : neg;
+        d = d + neg;
+      }
+      float f = X0[i] / d;
+      if (f > 1.0f) f = 1.0f;
+      Fsig[i] = f;
+    }
+    __syncwarp();
+    for (int j = lane; j < p; j += 32) {
+      const float v = V[j];
+      float fm = 1.0f;
+      for (int i = 0; i < s; i++)
+        if ((float)gN[j * s + i] * v < 0.0f) fm = nanmin(fm, Fsig[i]);
+      Fmin[j] = fm;
+      F[j] = 1.0f;
+    }
+    __syncwarp();
+    for (int i = lane; i < s; i += 32) {
+      float acc = 0.0f;
+      for (int j = 0; j < p; j++) acc = acc + ((float)gN[j * s + i] * V[j]) * Fmin[j];
+      X1[i] = clamp0(X0[i] + acc);
+    }
+    __syncwarp();
+    const int iters = a.eq_iters[q];
+    for (int k = 0; k < iters; k++) {
+      const float inc = eq_increment(k);
+      unsigned mine = 0;
+      for (int j = lane; j < p; j += 32) {
+        bool invb, invf;
+        float xb = dense_product(X1, gNb + j * s, s, invb);
+        if (!invb) xb = 0.0f;
+        float xf = dense_product(X1, gNf + j * s, s, invf);
+        if (!invf) xf = 0.0f;
+        const float Fj = F[j];
+        const unsigned dec = eq_decide(V[j], quotient_from(xb, xf), a.Ke[row + j], Fj);
+        if (dec & 3u) {
+          mine |= (dec & 4u) ? 3u : 2u;
+          F[j] = eq_update(Fj, dec, inc);
+        }
+      }
+      const unsigned any = __reduce_or_sync(FULL, mine);
+      if (lane == 0 && any) {
+        if (any & 1u) sflags[q * 4 + k] = 1u;
+        sflags[12 + q * 4 + k] = 1u;
+      }
+      if (!any) break;
+      __syncwarp();
+      for (int i = lane; i < s; i += 32) {
+        float acc = 0.0f;
+        for (int j = 0; j < p; j++)
+          acc = acc + (((float)gN[j * s + i] * V[j]) * Fmin[j]) * F[j];
+        X1[i] = clamp0(X0[i] + acc);
+      }
+      __syncwarp();
+    }
+    (void)poison;  // dense sums include 0 * NaN terms themselves
+    if (a.V_out)
+      for (int j = lane; j < p; j += 32) a.V_out[row + j] = V[j];
+    for (int i = lane; i < s; i += 32) X0[i] = X1[i];
+    __syncwarp();
+  }
+}
+
+template <int ST>
+__global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, float *dense_scratch) {
+  extern __shared__ __align__(16) unsigned smem[];
+  __shared__ unsigned sflags[MS_N_FLAGS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < MS_N_FLAGS) sflags[threadIdx.x] = 0;
+  __syncthreads();
+  unsigned *wbase = smem + (size_t)warp * a.words_per_warp;
+  const int p = a.p, s = a.s, s32 = round32(s);
+  const long long gw = (long long)blockIdx.x * WARPS_PER_CTA + warp;
+  const long long nw = (long long)gridDim.x * WARPS_PER_CTA;
+  float *dscr = dense_scratch + gw * (size_t)(3 * round32(p));
+
+  for (long long cell = gw; cell < a.c; cell += nw) {
+    float *X0 = (float *)wbase, *X1 = X0 + s32, *Fsig = X1 + s32;
+    // gather X0 (world.py:619-621) or read it
+    for (int i = lane; i < s; i += 32) {
+      float x;
+      if (a.X_in) {
+        x = a.X_in[cell * s + i];
+      } else if (i < a.m) {
+        x = a.cell_mols[cell * a.m + i];
+      } else {
+        const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
+        x = a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
+      }
+      X0[i] = x;
+    }
+    __syncwarp();
+    bool sparse = false;
+    int n_act = 0;
+    WarpMem w;
+    if (a.sparse_enabled) {
+      w = carve(wbase, p, s, a.e_cat, a.e_reg);
+      sparse = scan_cell<ST>(a, w, cell, lane, n_act);
+    }
+    if (sparse) {
+      run_sparse<ST>(a, w, cell, lane, n_act, sflags);
+    } else {
+      __syncwarp();
+      run_dense(a, X0, X1, Fsig, dscr, dscr + round32(p), dscr + 2 * round32(p), cell, lane, sflags);
+    }
+    for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
+    __syncwarp();
+  }
+  __syncthreads();
+  if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
+}
+
+// ---------------------------------------------------------------------------
+// staged kernels (dense tensors, one thread per (cell, protein) or (cell, signal))
+// ---------------------------------------------------------------------------
+__global__ void multiply_signals_kernel(const float *X, const int *K, long long c, int p, int s,
+                                        float *xx, uint8_t *involved) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * p) return;
+  bool inv;
+  xx[r] = dense_product(X + (r / p) * s, K + r * s, s, inv);
+  involved[r] = inv ? 1 : 0;
+}
+
+__global__ void quotient_kernel(const float *X, const int *Nf, const int *Nb, long long c, int p,
+                                int s, float *Q) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * p) return;
+  bool invb, invf;
+  float xb = dense_product(X + (r / p) * s, Nb + r * s, s, invb);
+  if (!invb) xb = 0.0f;
+  float xf = dense_product(X + (r / p) * s, Nf + r * s, s, invf);
+  if (!invf) xf = 0.0f;
+  Q[r] = quotient_from(xb, xf);
+}
+
+__global__ void velocities_kernel(KinArgs a, const float *X, const float *vmax, float *V) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.c * a.p) return;
+  const int s = a.s;
+  const float *x = X + (r / a.p) * s;
+  bool inv;
+  float kf = dense_product(x, a.Nf + r * s, s, inv) / a.Kmf[r];
+  if (!inv) kf = 0.0f;
+  if (isinf(kf)) kf = V_MAX;
+  float kb = dense_product(x, a.Nb + r * s, s, inv) / a.Kmb[r];
+  if (!inv) kb = 0.0f;
+  if (isinf(kb)) kb = V_MAX;
+  float a_reg = 1.0f;
+  for (int i = 0; i < s; i++) {
+    const int av = a.A[r * s + i];
+    if (av != 0) a_reg = a_reg * reg_factor(x[i], av, a.Kmr[r * s + i]);
+  }
+  V[r] = velocity_from(kf, kb, a_reg, vmax[r]);
+}
+
+// F_i = min(X_i / sum_j max(-NV_ji, 0), 1), one thread per (cell, signal); Fsig (c,s) scratch
+__global__ void neg_adjust_fsig_kernel(const float *NV, const float *X, long long c, int p, int s,
+                                       float *Fsig) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * s) return;
+  const long long cell = r / s;
+  const int i = (int)(r % s);
+  float d = 0.0f;
+  for (int j = 0; j < p; j++) {
+    float neg = -NV[(cell * p + j) * s + i];
+    neg = neg < 0.0f ? 0.0f : neg;
+    d = d + neg;
+  }
+  float f = X[r] / d;
+  if (f > 1.0f) f = 1.0f;
+  Fsig[r] = f;
+}
+
+__global__ void neg_adjust_apply_kernel(const float *NV, const float *Fsig, long long c, int p,
+                                        int s, float *NV_adj) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * p) return;
+  const long long cell = r / p;
+  float fm = 1.0f;
+  for (int i = 0; i < s; i++)
+    if (NV[r * s + i] < 0.0f) fm = nanmin(fm, Fsig[cell * s + i]);
+  for (int i = 0; i < s; i++) NV_adj[r * s + i] = NV[r * s + i] * fm;
+}
+
+// one equilibrium iteration, decision half: one thread per (cell, protein)
+__global__ void eq_decide_kernel(const float *X1, const float *V, const int *Nf, const int *Nb,
+                                 const float *Ke, long long c, int p, int s, float *F, float inc,
+                                 unsigned *flag_imp, unsigned *flag_any) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * p) return;
+  const float *x = X1 + (r / p) * s;
+  bool invb, invf;
+  float xb = dense_product(x, Nb + r * s, s, invb);
+  if (!invb) xb = 0.0f;
+  float xf = dense_product(x, Nf + r * s, s, invf);
+  if (!invf) xf = 0.0f;
+  const float Fr = F[r];
+  const unsigned dec = eq_decide(V[r], quotient_from(xb, xf), Ke[r], Fr);
+  if (dec & 3u) {
+    F[r] = eq_update(Fr, dec, inc);
+    *flag_any = 1u;
+    if (dec & 4u) *flag_imp = 1u;
+  }
+}
+
+// X1_i = max(X0_i + sum_j NV_ji * F_j, 0), one thread per (cell, signal)
+__global__ void eq_apply_kernel(const float *X0, const float *NV, const float *F, long long c, int p,
+                                int s, float *X1) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= c * s) return;
+  const long long cell = r / s;
+  const int i = (int)(r % s);
+  float acc = 0.0f;
+  for (int j = 0; j < p; j++) acc = acc + NV[(cell * p + j) * s + i] * F[cell * p + j];
+  X1[r] = clamp0(X0[r] + acc);
+}
+
+__global__ void fill_kernel(float *x, long long n, float v) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n) x[r] = v;
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+struct LaunchPlan {
+  int e_cat, e_reg, words_per_warp, st, sparse_enabled, grid;
+  size_t smem_bytes;
+};
+
+static int g_sm_count = 0;
+
+static int sm_count() {
+  if (g_sm_count == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 148;
+    g_sm_count = n > 0 ? n : 148;
+  }
+  return g_sm_count;
+}
+
+static LaunchPlan make_plan(int64_t p, int64_t s) {
+  LaunchPlan pl;
+  pl.sparse_enabled = (p <= 256 && s <= 32 * MAX_ST) ? 1 : 0;
+  pl.st = s <= 32 ? 1 : (s <= 64 ? 2 : 4);
+  // list capacities: 4 entries per protein on average, at least 64; regulatory 1 per protein
+  int e_cat = (int)(4 * p < 64 ? 64 : 4 * p);
+  if (e_cat > (int)(p * s)) e_cat = (int)(p * s);
+  e_cat = round32(e_cat);
+  int e_reg = round32((int)(p < 32 ? 32 : p));
+  if (!pl.sparse_enabled) { e_cat = 0; e_reg = 0; }
+  pl.e_cat = e_cat;
+  pl.e_reg = e_reg;
+  pl.words_per_warp = pl.sparse_enabled ? warp_words((int)p, (int)s, e_cat, e_reg) : 3 * round32((int)s);
+  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * WARPS_PER_CTA;
+  pl.grid = sm_count() * 4;
+  return pl;
+}
+
+}  // namespace ms
+
+using namespace ms;
+
+extern "C" size_t ms_kinetics_scratch_bytes(int64_t p, int64_t s) {
+  (void)s;
+  // 3 float arrays of round32(p) per resident warp of the largest grid we launch
+  return (size_t)148 * 8 * WARPS_PER_CTA * 3 * (size_t)round32((int)p) * sizeof(float) + 256;
+}
+
+static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, size_t scratch_bytes,
+                        cudaStream_t st) {
+  if (!P || P->c < 0 || P->p < 0 || P->s < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (P->p > 65535 || P->s > 8192) return MS_ERR_TOO_LARGE;
+  a.N = P->N; a.Nf = P->Nf; a.Nb = P->Nb; a.A = P->A;
+  a.Kmr = P->Kmr; a.Ke = P->Ke; a.Kmf = P->Kmf; a.Kmb = P->Kmb; a.Vmax = P->Vmax;
+  a.c = P->c; a.p = (int)P->p; a.s = (int)P->s;
+  MS_CUDA_CHECK(cudaMemsetAsync(a.flags, 0, MS_N_FLAGS * sizeof(unsigned), st));
+  if (P->c == 0 || P->s == 0) return MS_OK;
+  LaunchPlan pl = make_plan(P->p, P->s);
+  if (pl.smem_bytes > 200 * 1024) {  // huge p or s: dense path with minimal shared memory
+    pl.sparse_enabled = 0;
+    pl.words_per_warp = 3 * round32(a.s);
+    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * WARPS_PER_CTA;
+  }
+  int64_t ctas_needed = ceil_div(P->c, WARPS_PER_CTA);
+  if (pl.grid > ctas_needed) pl.grid = (int)ctas_needed;
+  const size_t need = (size_t)pl.grid * WARPS_PER_CTA * 3 * (size_t)round32(a.p) * sizeof(float);
+  if (scratch_bytes < need || !scratch) return MS_ERR_SCRATCH_TOO_SMALL;
+  a.e_cat = pl.e_cat; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
+  a.sparse_enabled = pl.sparse_enabled;
+  auto kern = pl.st == 1 ? kinetics_fused_kernel<1> : (pl.st == 2 ? kinetics_fused_kernel<2> : kinetics_fused_kernel<4>);
+  MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+  kern<<<pl.grid, THREADS, pl.smem_bytes, st>>>(a, (float *)scratch);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+static int fill_eq(KinArgs &a, const int32_t *eq_iters_host) {
+  for (int q = 0; q < 3; q++) {
+    int v = eq_iters_host ? eq_iters_host[q] : 4;
+    if (v < 0 || v > 4) return MS_ERR_INVALID_ARGUMENT;
+    a.eq_iters[q] = v;
+  }
+  a.trims[0] = 0.7f; a.trims[1] = 0.2f; a.trims[2] = 0.1f;  // kinetics.py:746
+  a.n_parts = 3;
+  return MS_OK;
+}
+
+extern "C" int ms_integrate_signals(const ms_kinetics_params *params, const float *X_in, float *X_out,
+                                    const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
+                                    size_t scratch_bytes, void *stream) {
+  if (!params || !flags || (params->c > 0 && (!X_in || !X_out)) || X_in == X_out)
+    return MS_ERR_INVALID_ARGUMENT;
+  KinArgs a = {};
+  int rc = fill_eq(a, eq_iters_host);
+  if (rc) return rc;
+  a.X_in = X_in; a.X_out = X_out; a.flags = flags;
+  return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int ms_integrate_signals_part(const ms_kinetics_params *params, const float *adj_vmax,
+                                         const float *X0, float *X1, int32_t max_eq_iters,
+                                         uint32_t *flags, float *V_out, void *scratch,
+                                         size_t scratch_bytes, void *stream) {
+  if (!params || !flags || (params->c > 0 && (!X0 || !X1 || !adj_vmax)) || X0 == X1 ||
+      max_eq_iters < 0 || max_eq_iters > 4)
+    return MS_ERR_INVALID_ARGUMENT;
+  KinArgs a = {};
+  a.n_parts = 1;
+  a.eq_iters[0] = max_eq_iters;
+  a.trims[0] = 1.0f;
+  a.adj_vmax = adj_vmax;
+  a.V_out = V_out;
+  a.X_in = X0; a.X_out = X1; a.flags = flags;
+  return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int ms_enzymatic_activity(const ms_kinetics_params *params, const int32_t *cell_positions,
+                                     const float *cell_molecules, const float *molecule_map,
+                                     int64_t m, int64_t H, int64_t W, float *X_out,
+                                     const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
+                                     size_t scratch_bytes, void *stream) {
+  if (!params || !flags || params->s != 2 * m || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX ||
+      (params->c > 0 && (!cell_positions || !cell_molecules || !molecule_map || !X_out)))
+    return MS_ERR_INVALID_ARGUMENT;
+  KinArgs a = {};
+  int rc = fill_eq(a, eq_iters_host);
+  if (rc) return rc;
+  a.X_in = nullptr; a.cell_mols = cell_molecules; a.mol_map = molecule_map; a.pos = cell_positions;
+  a.m = (int)m; a.H = (int)H; a.W = (int)W;
+  a.X_out = X_out; a.flags = flags;
+  return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+extern "C" int ms_multiply_signals(const float *X, const int32_t *K, int64_t c, int64_t p, int64_t s,
+                                   float *xx, uint8_t *involved, void *stream) {
+  if (c < 0 || p < 0 || s < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (c * p == 0) return MS_OK;
+  multiply_signals_kernel<<<blocks_for(c * p, 128), 128, 0, (cudaStream_t)stream>>>(X, K, c, (int)p, (int)s, xx, involved);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_get_quotient(const float *X, const int32_t *Nf, const int32_t *Nb, int64_t c,
+                               int64_t p, int64_t s, float *Q, void *stream) {
+  if (c < 0 || p < 0 || s < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (c * p == 0) return MS_OK;
+  quotient_kernel<<<blocks_for(c * p, 128), 128, 0, (cudaStream_t)stream>>>(X, Nf, Nb, c, (int)p, (int)s, Q);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_get_velocities(const ms_kinetics_params *P, const float *X, const float *adj_vmax,
+                                 float *V, void *stream) {
+  if (!P) return MS_ERR_INVALID_ARGUMENT;
+  if (P->c * P->p == 0) return MS_OK;
+  KinArgs a = {};
+  a.Nf = P->Nf; a.Nb = P->Nb; a.A = P->A; a.Kmr = P->Kmr; a.Kmf = P->Kmf; a.Kmb = P->Kmb;
+  a.c = P->c; a.p = (int)P->p; a.s = (int)P->s;
+  velocities_kernel<<<blocks_for(P->c * P->p, 128), 128, 0, (cudaStream_t)stream>>>(a, X, adj_vmax, V);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_get_negative_adjusted_nv(const float *NV, const float *X, int64_t c, int64_t p,
+                                           int64_t s, float *NV_adj, float *Fsig_scratch,
+                                           void *stream) {
+  if (c < 0 || p < 0 || s < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (c * p * s == 0) return MS_OK;
+  if (!Fsig_scratch || NV == NV_adj) return MS_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  neg_adjust_fsig_kernel<<<blocks_for(c * s, 128), 128, 0, st>>>(NV, X, c, (int)p, (int)s, Fsig_scratch);
+  MS_CUDA_CHECK(cudaGetLastError());
+  neg_adjust_apply_kernel<<<blocks_for(c * p, 128), 128, 0, st>>>(NV, Fsig_scratch, c, (int)p, (int)s, NV_adj);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_get_equilibrium_adjusted_x(const float *X0, const float *X1_in, const float *NV,
+                                             const float *V, const int32_t *Nf, const int32_t *Nb,
+                                             const float *Ke, int64_t c, int64_t p, int64_t s,
+                                             float *X1_out, float *F_scratch, int32_t max_iters,
+                                             uint32_t *flags, void *stream) {
+  if (c < 0 || p < 0 || s < 0 || max_iters < 0 || max_iters > 4 || !flags) return MS_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  MS_CUDA_CHECK(cudaMemsetAsync(flags, 0, MS_N_FLAGS * sizeof(unsigned), st));
+  if (c * s == 0) return MS_OK;
+  if (X1_out != X1_in)
+    MS_CUDA_CHECK(cudaMemcpyAsync(X1_out, X1_in, sizeof(float) * (size_t)(c * s), cudaMemcpyDeviceToDevice, st));
+  if (c * p == 0) return MS_OK;
+  if (!F_scratch) return MS_ERR_INVALID_ARGUMENT;
+  fill_kernel<<<blocks_for(c * p, 256), 256, 0, st>>>(F_scratch, c * p, 1.0f);
+  for (int k = 0; k < max_iters; k++) {
+    eq_decide_kernel<<<blocks_for(c * p, 128), 128, 0, st>>>(X1_out, V, Nf, Nb, Ke, c, (int)p, (int)s, F_scratch,
+                                                             k == 0 ? 0.5f : (k == 1 ? 0.25f : (k == 2 ? 0.125f : 0.0625f)),
+                                                             flags + k, flags + 12 + k);
+    eq_apply_kernel<<<blocks_for(c * s, 128), 128, 0, st>>>(X0, NV, F_scratch, c, (int)p, (int)s, X1_out);
+  }
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_add_protein_rates(const float *X0, const float *NV, int64_t c, int64_t p, int64_t s,
+                                    float *X1, float *F_scratch, void *stream) {
+  if (c < 0 || p < 0 || s < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (c * s == 0) return MS_OK;
+  if (!X0 || !X1 || (c * p > 0 && (!NV || !F_scratch))) return MS_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c * p > 0) fill_kernel<<<blocks_for(c * p, 256), 256, 0, st>>>(F_scratch, c * p, 1.0f);
+  eq_apply_kernel<<<blocks_for(c * s, 128), 128, 0, st>>>(X0, NV, F_scratch, c, (int)p, (int)s, X1);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}

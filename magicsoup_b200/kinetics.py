@@ -1,0 +1,359 @@
+"""
+`Kinetics` with the reference's interface (mRcSchwering/magic-soup 1.0.5,
+python/magicsoup/kinetics.py:292-992) whose numeric core runs as hand-written sm_100a
+CUDA kernels through the C ABI of include/magicsoup_b200.h.
+
+Mirrored from the reference (same names, argument meaning, dtypes, error behaviour):
+  parameter tensors  Ke, Kmf, Kmb, Vmax (c,p) f32; Kmr (c,p,s) f32; N, Nf, Nb, A (c,p,s) i32
+                     (kinetics.py:399-409)
+  integrate_signals(X)                                  kinetics.py:725
+  _integrate_signals_part / _get_velocities / _multiply_signals / _get_quotient /
+  _get_negative_adjusted_nv / _get_equilibrium_adjusted_x   kinetics.py:753-918
+  unset_cell_params / copy_cell_params / remove_cell_params /
+  increase_max_cells / increase_max_proteins            kinetics.py:627-723
+
+The parameter tensors are plain attributes that users and tests overwrite
+(`kinetics.N = tensor`), possibly with CPU tensors: every call reads the current
+attributes and normalises them (device, dtype, contiguity) at the boundary.
+
+There is no CPU fallback: the numeric methods raise without a CUDA device.
+`set_cell_params` / `get_proteome` (genome -> parameters, kinetics.py:462-625) are host
+side genetics and not part of this hot path; populations are installed with
+`set_cell_params_from_tensors`.
+"""
+from __future__ import annotations
+
+from typing import Any, Sequence
+
+import torch
+
+from magicsoup_b200 import _native as nat
+
+_EPS = 1e-36
+_MAX = 1e36
+_MIN = -1e36
+_TRIMS = (0.7, 0.2, 0.1)  # kinetics.py:746
+_INT_PARAMS = ("N", "Nf", "Nb", "A")
+_CPS_PARAMS = ("N", "Nf", "Nb", "A", "Kmr")
+_ALL_PARAMS = ("N", "Nf", "Nb", "A", "Kmr", "Ke", "Kmf", "Kmb", "Vmax")
+_STAGE_METHODS = ("_integrate_signals_part", "_get_velocities", "_multiply_signals", "_get_quotient",
+                  "_get_negative_adjusted_nv", "_get_equilibrium_adjusted_x")
+
+
+def _settle_early_exit(flags: list[int], eq: list[int], n_parts: int) -> bool:
+    """
+    kinetics.py:846-847: the reference leaves a part's adjustment loop at the first
+    iteration where NO cell has an adjustable protein with |V| > 0.1.  `flags` come from
+    a launch that applied eq[q] iterations in part q.  Returns True if eq was lowered
+    (the launch must be repeated), False if the launch already equals the reference.
+    """
+    for q in range(n_parts):
+        for k in range(eq[q]):
+            if flags[q * 4 + k] == 0:
+                if flags[12 + q * 4 + k] != 0:
+                    eq[q] = k  # some low-impact protein kept adjusting: not what the reference does
+                    return True
+                break  # nothing adjustable anywhere: later iterations were no-ops
+    return False
+
+
+class Kinetics:
+    """see module docstring; constructor signature of kinetics.py:380-389"""
+
+    def __init__(
+        self,
+        chemistry: Any,
+        abs_temp: float = 310.0,
+        km_range: tuple[float, float] = (1e-2, 100.0),
+        vmax_range: tuple[float, float] = (1e-3, 100.0),
+        device: str = "cpu",
+        scalar_enc_size: int = 64 - 3,
+        vector_enc_size: int = 4096 - 3 * 64,
+    ):
+        self.abs_temp = abs_temp
+        self.device = device
+        self.km_range = km_range
+        self.vmax_range = vmax_range
+        self.scalar_enc_size = scalar_enc_size
+        self.vector_enc_size = vector_enc_size
+        molecules = list(chemistry.molecules)
+        self.mol_names = [d.name for d in molecules]
+        self.mol_energies = torch.tensor([d.energy for d in molecules] * 2, dtype=torch.float32, device=device)
+        n_signals = 2 * len(molecules)
+        self.Ke = self._zeros_f32_tensor(0, 0)
+        self.Kmf = self._zeros_f32_tensor(0, 0)
+        self.Kmb = self._zeros_f32_tensor(0, 0)
+        self.Kmr = self._zeros_f32_tensor(0, 0, n_signals)
+        self.Vmax = self._zeros_f32_tensor(0, 0)
+        self.N = self._zeros_i32_tensor(0, 0, n_signals)
+        self.Nf = self._zeros_i32_tensor(0, 0, n_signals)
+        self.Nb = self._zeros_i32_tensor(0, 0, n_signals)
+        self.A = self._zeros_i32_tensor(0, 0, n_signals)
+        self._scratch: dict[str, torch.Tensor] = {}
+
+    # ------------------------------------------------------------------ pickling
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        state["_scratch"] = {}  # device scratch is rebuilt lazily (world.py:747-793 pickles the object)
+        return state
+
+    # ------------------------------------------------------------------ device plumbing
+    def _cuda(self) -> torch.device:
+        nat.require_cuda()
+        dev = torch.device(self.device)
+        if dev.type != "cuda":
+            dev = torch.device("cuda", torch.cuda.current_device())
+        return dev
+
+    def _f32(self, t: Any, dev: torch.device) -> torch.Tensor:
+        if not isinstance(t, torch.Tensor):
+            t = torch.as_tensor(t)
+        return t.to(device=dev, dtype=torch.float32).contiguous()
+
+    def _i32(self, t: Any, dev: torch.device) -> torch.Tensor:
+        if not isinstance(t, torch.Tensor):
+            t = torch.as_tensor(t)
+        return t.to(device=dev, dtype=torch.int32).contiguous()
+
+    def _buffer(self, key: str, nbytes: int, dev: torch.device) -> torch.Tensor:
+        buf = self._scratch.get(key)
+        if buf is None or buf.numel() < nbytes or buf.device != dev:
+            buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
+            self._scratch[key] = buf
+        return buf
+
+    def _params(self, dev: torch.device, c: int, s: int, need: Sequence[str] = _ALL_PARAMS):
+        """
+        Normalised views of the current attributes + the C struct.  Tensors a call does
+        not read may be left at their initial (0,0[,s]) shape, as the reference's tests do.
+        """
+        p = None
+        for k in need:
+            t = getattr(self, k)
+            if t.dim() >= 2 and t.shape[0] == c:
+                p = int(t.shape[1])
+                break
+        if p is None:
+            p = int(getattr(self, need[0]).shape[1])
+        keep = {}
+        for k in _ALL_PARAMS:
+            t = getattr(self, k)
+            want = (c, p, s) if k in _CPS_PARAMS else (c, p)
+            if k in need:
+                if tuple(t.shape) != want:
+                    raise ValueError(f"Kinetics.{k} has shape {tuple(t.shape)}, expected {want}")
+                keep[k] = self._i32(t, dev) if k in _INT_PARAMS else self._f32(t, dev)
+            else:
+                keep[k] = None
+        st = nat.KineticsParams(**{k: nat.ptr(v) for k, v in keep.items()}, c=c, p=p, s=s)
+        return st, keep, p
+
+    def _kin_scratch(self, dev: torch.device, p: int, s: int):
+        n = int(nat.lib().ms_kinetics_scratch_bytes(p, s))
+        return self._buffer("kin", n, dev), n
+
+    def _flags(self, dev: torch.device) -> torch.Tensor:
+        return self._buffer("flags", nat.N_FLAGS * 4, dev)
+
+    def _read_flags(self, flags: torch.Tensor) -> list[int]:
+        return flags[: nat.N_FLAGS * 4].view(torch.int32).tolist()  # device -> host sync
+
+    def _overrides(self, name: str) -> bool:
+        return getattr(type(self), name) is not getattr(Kinetics, name)
+
+    # ------------------------------------------------------------------ hot path
+    def integrate_signals(self, X: torch.Tensor) -> torch.Tensor:
+        """
+        kinetics.py:725-751.  X (c,s) >= 0 -> new (c,s) tensor.  One fused kernel launch
+        (plus, only if the reference's global early exit would have fired, a repeat).
+        Subclasses that override a stage method get the staged composition instead.
+        """
+        if any(self._overrides(m) for m in _STAGE_METHODS):
+            for trim in _TRIMS:
+                X = self._integrate_signals_part(adj_vmax=(self.Vmax * trim).clamp(0.0), X0=X)
+            return X
+        dev = self._cuda()
+        Xd = self._f32(X, dev)
+        c, s = Xd.shape
+        out = torch.empty_like(Xd)
+        if c == 0 or s == 0:
+            return out
+        st, keep, p = self._params(dev, c, s)
+        scratch, nbytes = self._kin_scratch(dev, p, s)
+        flags = self._flags(dev)
+        eq = [4, 4, 4]
+        while True:
+            nat.check(nat.lib().ms_integrate_signals(
+                st, nat.ptr(Xd), nat.ptr(out), nat.eq_array(eq), nat.ptr(flags), nat.ptr(scratch),
+                nbytes, nat.stream_ptr(dev)))
+            if not _settle_early_exit(self._read_flags(flags), eq, 3):
+                return out
+
+    def _integrate_signals_part(self, adj_vmax: torch.Tensor, X0: torch.Tensor) -> torch.Tensor:
+        """kinetics.py:753-769"""
+        dev = self._cuda()
+        X0d = self._f32(X0, dev)
+        c, s = X0d.shape
+        if c == 0 or s == 0:
+            return X0d.clone()
+        staged = any(self._overrides(m) for m in _STAGE_METHODS if m != "_integrate_signals_part")
+        if staged:
+            # composition through the (possibly overridden) stage methods
+            V = self._get_velocities(X=X0d, Vmax=adj_vmax)
+            NV = self._i32(self.N, dev).float() * V[:, :, None]  # kinetics.py:759, one rounding
+            NV_adj = self._get_negative_adjusted_nv(NV=NV, X=X0d)
+            X1 = self._sum_over_proteins(X0d, NV_adj)
+            return self._get_equilibrium_adjusted_x(X0=X0d, X1=X1, NV=NV_adj, V=V)
+        X1, _ = self._part_kernel(adj_vmax, X0d, dev)
+        return X1
+
+    def _part_kernel(self, adj_vmax, X0d, dev, want_v: bool = False):
+        c, s = X0d.shape
+        st, keep, p = self._params(dev, c, s)
+        adj = self._f32(adj_vmax, dev)
+        if tuple(adj.shape) != (c, p):
+            raise ValueError(f"adj_vmax has shape {tuple(adj.shape)}, expected {(c, p)}")
+        scratch, nbytes = self._kin_scratch(dev, p, s)
+        flags = self._flags(dev)
+        X1 = torch.empty_like(X0d)
+        V = torch.empty(c, p, dtype=torch.float32, device=dev) if want_v else None
+        eq = [4, 0, 0]
+        while True:
+            nat.check(nat.lib().ms_integrate_signals_part(
+                st, nat.ptr(adj), nat.ptr(X0d), nat.ptr(X1), eq[0], nat.ptr(flags), nat.ptr(V),
+                nat.ptr(scratch), nbytes, nat.stream_ptr(dev)))
+            if not _settle_early_exit(self._read_flags(flags), eq, 1):
+                return X1, V
+
+    def _sum_over_proteins(self, X0: torch.Tensor, NV: torch.Tensor) -> torch.Tensor:
+        """X1 = max(X0 + sum_p NV, 0) in spec order (kinetics.py:763-764)"""
+        dev = X0.device
+        c, p, s = NV.shape
+        X1 = torch.empty_like(X0)
+        F = torch.empty(c, p, dtype=torch.float32, device=dev)
+        nat.check(nat.lib().ms_add_protein_rates(nat.ptr(X0), nat.ptr(NV), c, p, s, nat.ptr(X1), nat.ptr(F),
+                                                 nat.stream_ptr(dev)))
+        return X1
+
+    def _get_velocities(self, X: torch.Tensor, Vmax: torch.Tensor) -> torch.Tensor:
+        """kinetics.py:771-806"""
+        dev = self._cuda()
+        Xd = self._f32(X, dev)
+        c, s = Xd.shape
+        st, keep, p = self._params(dev, c, s, need=("Nf", "Nb", "A", "Kmr", "Kmf", "Kmb"))
+        vmax = self._f32(Vmax, dev)
+        V = torch.empty(c, p, dtype=torch.float32, device=dev)
+        nat.check(nat.lib().ms_get_velocities(st, nat.ptr(Xd), nat.ptr(vmax), nat.ptr(V), nat.stream_ptr(dev)))
+        return V
+
+    def _multiply_signals(self, X: torch.Tensor, N: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+        """kinetics.py:894-918 -> (xx (c,p) f32, involved (c,p) bool)"""
+        dev = self._cuda()
+        Xd, Nd = self._f32(X, dev), self._i32(N, dev)
+        c, p, s = Nd.shape
+        xx = torch.empty(c, p, dtype=torch.float32, device=dev)
+        inv = torch.empty(c, p, dtype=torch.uint8, device=dev)
+        nat.check(nat.lib().ms_multiply_signals(nat.ptr(Xd), nat.ptr(Nd), c, p, s, nat.ptr(xx), nat.ptr(inv),
+                                                nat.stream_ptr(dev)))
+        return xx, inv.bool()
+
+    def _get_quotient(self, X: torch.Tensor) -> torch.Tensor:
+        """kinetics.py:881-892"""
+        dev = self._cuda()
+        Xd = self._f32(X, dev)
+        Nf, Nb = self._i32(self.Nf, dev), self._i32(self.Nb, dev)
+        c, p, s = Nf.shape
+        Q = torch.empty(c, p, dtype=torch.float32, device=dev)
+        nat.check(nat.lib().ms_get_quotient(nat.ptr(Xd), nat.ptr(Nf), nat.ptr(Nb), c, p, s, nat.ptr(Q),
+                                            nat.stream_ptr(dev)))
+        return Q
+
+    def _get_negative_adjusted_nv(self, NV: torch.Tensor, X: torch.Tensor) -> torch.Tensor:
+        """kinetics.py:861-879 (the reference's test passes an int32 NV; result is float32)"""
+        dev = self._cuda()
+        NVd, Xd = self._f32(NV, dev), self._f32(X, dev)
+        c, p, s = NVd.shape
+        out = torch.empty_like(NVd)
+        fsig = torch.empty(c, s, dtype=torch.float32, device=dev)
+        nat.check(nat.lib().ms_get_negative_adjusted_nv(nat.ptr(NVd), nat.ptr(Xd), c, p, s, nat.ptr(out),
+                                                        nat.ptr(fsig), nat.stream_ptr(dev)))
+        return out
+
+    def _get_equilibrium_adjusted_x(self, X0: torch.Tensor, X1: torch.Tensor, NV: torch.Tensor,
+                                    V: torch.Tensor) -> torch.Tensor:
+        """kinetics.py:808-859 on dense NV (c,p,s)"""
+        dev = self._cuda()
+        X0d, X1d, NVd, Vd = (self._f32(t, dev) for t in (X0, X1, NV, V))
+        c, p, s = NVd.shape
+        Nf, Nb, Ke = self._i32(self.Nf, dev), self._i32(self.Nb, dev), self._f32(self.Ke, dev)
+        out = torch.empty_like(X1d)
+        F = torch.empty(c, p, dtype=torch.float32, device=dev)
+        flags = self._flags(dev)
+        eq = [4, 0, 0]
+        while True:
+            nat.check(nat.lib().ms_get_equilibrium_adjusted_x(
+                nat.ptr(X0d), nat.ptr(X1d), nat.ptr(NVd), nat.ptr(Vd), nat.ptr(Nf), nat.ptr(Nb), nat.ptr(Ke),
+                c, p, s, nat.ptr(out), nat.ptr(F), eq[0], nat.ptr(flags), nat.stream_ptr(dev)))
+            if not _settle_early_exit(self._read_flags(flags), eq, 1):
+                return out
+
+    # ------------------------------------------------------------------ parameter store
+    def set_cell_params_from_tensors(self, cell_idxs: list[int] | torch.Tensor, **tensors: torch.Tensor):
+        """
+        Install ready-made parameters for `cell_idxs` (what set_cell_params derives from
+        proteomes, kinetics.py:571-625).  Keyword names are the attribute names.
+        """
+        p_new = int(tensors["N"].shape[1])
+        self.increase_max_proteins(max_n=p_new)
+        p = int(self.N.shape[1])
+        for k in _ALL_PARAMS:
+            src = tensors[k].to(device=self.device, dtype=getattr(self, k).dtype)
+            if p_new < p:  # pad like unset proteins
+                pad_shape = list(src.shape)
+                pad_shape[1] = p - p_new
+                src = torch.cat([src, torch.zeros(pad_shape, dtype=src.dtype, device=src.device)], dim=1)
+            getattr(self, k)[cell_idxs] = src
+
+    def set_cell_params(self, cell_idxs, proteomes):
+        raise NotImplementedError(
+            "genome -> parameter translation (reference kinetics.py:521-625) is host-side genetics "
+            "outside this package's hot path; use set_cell_params_from_tensors")
+
+    def unset_cell_params(self, cell_idxs: list[int]):
+        """kinetics.py:627-644"""
+        for k in _ALL_PARAMS:
+            getattr(self, k)[cell_idxs] = 0
+
+    def copy_cell_params(self, from_idxs: list[int], to_idxs: list[int]):
+        """kinetics.py:646-665"""
+        for k in _ALL_PARAMS:
+            t = getattr(self, k)
+            t[to_idxs] = t[from_idxs]
+
+    def remove_cell_params(self, keep: torch.Tensor):
+        """kinetics.py:667-686: order-preserving compaction of the cell dimension"""
+        for k in _ALL_PARAMS:
+            setattr(self, k, getattr(self, k)[keep])
+
+    def increase_max_cells(self, by_n: int):
+        """kinetics.py:688-703"""
+        for k in _ALL_PARAMS:
+            setattr(self, k, self._expand(getattr(self, k), dim=0, n=by_n))
+
+    def increase_max_proteins(self, max_n: int):
+        """kinetics.py:705-723: the protein dimension only ever grows"""
+        n_prots = int(self.N.size(1))
+        if max_n > n_prots:
+            for k in _ALL_PARAMS:
+                setattr(self, k, self._expand(getattr(self, k), dim=1, n=max_n - n_prots))
+
+    def _expand(self, t: torch.Tensor, dim: int, n: int) -> torch.Tensor:
+        shape = list(t.shape)
+        shape[dim] = n
+        return torch.cat([t, torch.zeros(shape, dtype=t.dtype, device=t.device)], dim=dim)
+
+    def _zeros_i32_tensor(self, *args) -> torch.Tensor:
+        return torch.zeros(*args, device=self.device, dtype=torch.int32)
+
+    def _zeros_f32_tensor(self, *args) -> torch.Tensor:
+        return torch.zeros(*args, device=self.device, dtype=torch.float32)

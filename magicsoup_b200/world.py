@@ -1,0 +1,336 @@
+"""
+`World` with the reference's step interface (mRcSchwering/magic-soup 1.0.5,
+python/magicsoup/world.py:36-1004) for the per-step world math:
+
+  enzymatic_activity()        world.py:610-625   fused kinetics kernel + write-back
+  diffuse_molecules()         world.py:627-665   tiled stencil, mass correction, permeation
+  degrade_molecules()         world.py:667-678
+  increment_cell_lifetimes()  world.py:680-687
+  kill_cells / divide_cells_at / add_cells_from_params   index-consistent bookkeeping of
+                              world.py:406-540 for the tensors the kernels read
+
+State attributes keep the reference's names, shapes and dtypes (world.py:192-204):
+cell_map (H,W) bool, cell_positions (c,2) i32, cell_lifetimes/cell_divisions (c,) i32,
+cell_molecules (c,m) f32, molecule_map (m,H,W) f32.  As in the reference,
+enzymatic_activity/diffuse_molecules update molecule_map in place and REBIND
+cell_molecules to a new tensor.
+
+Genomes, translation and mutation (genetics.py, mutations.py, the Rust `_lib`) keep
+their host role in the reference and are not part of this package; cells enter through
+`add_cells_from_params` with ready parameter tensors.  No CPU fallback: the step methods
+raise without a CUDA device.
+"""
+from __future__ import annotations
+
+import math
+import random
+from dataclasses import dataclass
+from typing import Any
+
+import torch
+
+from magicsoup_b200 import _native as nat
+from magicsoup_b200.kinetics import Kinetics, _settle_early_exit, _ALL_PARAMS
+
+
+@dataclass(frozen=True)
+class Molecule:
+    """the attributes of the reference's Molecule that the world math reads (containers.py:91-132)"""
+
+    name: str
+    energy: float
+    half_life: int = 100_000
+    diffusivity: float = 0.1
+    permeability: float = 0.0
+
+
+@dataclass
+class Chemistry:
+    """molecules (ordered) + reactions, as containers.py's Chemistry"""
+
+    molecules: list
+    reactions: list
+
+
+def permeation_factor(mol_perm_rate: float) -> float:
+    """world.py:935-946 _get_permeate"""
+    rate = min(abs(mol_perm_rate), 1.0)
+    if rate == 0.0:
+        return 0.0
+    return 1 / (1 / rate + 1)
+
+
+def diffusion_weights(mol_diff_rate: float) -> tuple[float, float]:
+    """world.py:948-964 _get_diffuse: (neighbour weight a, centre weight b) of the 3x3 kernel"""
+    rate = min(abs(mol_diff_rate), 1.0)
+    if rate == 0.0:
+        return 0.0, 1.0
+    d = 1 / rate
+    a = 1 / (d + 8)
+    b = d * a
+    b = b + 1.0 - (8 * a + b)
+    return a, b
+
+
+class World:
+    """see module docstring; constructor signature of world.py:147-157"""
+
+    def __init__(
+        self,
+        chemistry: Any,
+        map_size: int = 128,
+        abs_temp: float = 310.0,
+        mol_map_init: str = "randn",
+        start_codons: tuple[str, ...] = ("TTG", "GTG", "ATG"),
+        stop_codons: tuple[str, ...] = ("TGA", "TAG", "TAA"),
+        device: str = "cpu",
+        batch_size: int | None = None,
+    ):
+        self.device = device
+        self.batch_size = batch_size
+        self.map_size = map_size
+        self.abs_temp = abs_temp
+        self.chemistry = chemistry
+        self.start_codons = start_codons
+        self.stop_codons = stop_codons
+        self.kinetics = Kinetics(chemistry=chemistry, abs_temp=abs_temp, device=device)
+
+        molecules = list(chemistry.molecules)
+        self.n_molecules = len(molecules)
+        self._int_mol_idxs = list(range(self.n_molecules))
+        self._ext_mol_idxs = list(range(self.n_molecules, self.n_molecules * 2))
+        self._mol_degrads = [math.exp(-math.log(2) / d.half_life) for d in molecules]
+        self._diffusion = [diffusion_weights(d.diffusivity) for d in molecules]
+        self._permeation = [permeation_factor(d.permeability) for d in molecules]
+
+        self.n_cells = 0
+        self.cell_genomes: list[str] = []
+        self.cell_labels: list[str] = []
+        self.cell_map = torch.zeros(map_size, map_size, dtype=torch.bool, device=device)
+        self.cell_positions = torch.zeros(0, 2, dtype=torch.int32, device=device)
+        self.cell_lifetimes = torch.zeros(0, dtype=torch.int32, device=device)
+        self.cell_divisions = torch.zeros(0, dtype=torch.int32, device=device)
+        self.cell_molecules = torch.zeros(0, self.n_molecules, dtype=torch.float32, device=device)
+        self.molecule_map = self._get_molecule_map(n=self.n_molecules, size=map_size, init=mol_map_init)
+        self._scratch: dict[str, torch.Tensor] = {}
+        # when set to a list, (start, end) CUDA event pairs around each kinetics kernel
+        # launch are appended to it (used by bench.py for the roofline of that kernel)
+        self._kernel_events: list | None = None
+
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        state["_scratch"] = {}
+        state["_kernel_events"] = None
+        return state
+
+    # ------------------------------------------------------------------ plumbing
+    def _cuda(self) -> torch.device:
+        nat.require_cuda()
+        dev = torch.device(self.device)
+        if dev.type != "cuda":
+            dev = torch.device("cuda", torch.cuda.current_device())
+        return dev
+
+    def _buffer(self, key: str, nbytes: int, dev: torch.device) -> torch.Tensor:
+        buf = self._scratch.get(key)
+        if buf is None or buf.numel() < nbytes or buf.device != dev:
+            buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
+            self._scratch[key] = buf
+        return buf
+
+    def _const_f32(self, key: str, values: list[float], dev: torch.device) -> torch.Tensor:
+        """per-molecule factors as float32 device vectors, refreshed when the lists change"""
+        cached = self._scratch.get(key)
+        stamp = self._scratch.get(key + "_src")
+        if cached is None or stamp != tuple(values) or cached.device != dev:
+            cached = torch.tensor(values, dtype=torch.float32, device=dev)
+            self._scratch[key] = cached
+            self._scratch[key + "_src"] = tuple(values)  # type: ignore[assignment]
+        return cached
+
+    def _state_on_device(self, dev: torch.device):
+        """normalise user-assigned state tensors (tests assign CPU tensors, world.py H5)"""
+        mm = self.molecule_map
+        if mm.device != dev or mm.dtype != torch.float32 or not mm.is_contiguous():
+            mm = mm.to(device=dev, dtype=torch.float32).contiguous()
+            self.molecule_map = mm
+        cm = self.cell_molecules.to(device=dev, dtype=torch.float32).contiguous()
+        pos = self.cell_positions.to(device=dev, dtype=torch.int32).contiguous()
+        return mm, cm, pos
+
+    # ------------------------------------------------------------------ step methods
+    def enzymatic_activity(self):
+        """world.py:610-625"""
+        if self.n_cells == 0:
+            return
+        dev = self._cuda()
+        kin = self.kinetics
+        mm, cm, pos = self._state_on_device(dev)
+        m = self.n_molecules
+        _, H, W = mm.shape
+        c, s = self.n_cells, 2 * m
+        if any(kin._overrides(k) for k in ("integrate_signals",)) or any(
+                kin._overrides(k) for k in ("_integrate_signals_part", "_get_velocities", "_multiply_signals",
+                                            "_get_quotient", "_get_negative_adjusted_nv",
+                                            "_get_equilibrium_adjusted_x")):
+            xs, ys = pos[:, 0].long(), pos[:, 1].long()
+            X = kin.integrate_signals(X=torch.cat([cm, mm[:, xs, ys].T], dim=1))
+        else:
+            st, keep, p = kin._params(dev, c, s)
+            scratch, nbytes = kin._kin_scratch(dev, p, s)
+            flags = kin._flags(dev)
+            X = torch.empty(c, s, dtype=torch.float32, device=dev)
+            eq = [4, 4, 4]
+            while True:
+                if self._kernel_events is not None:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record(torch.cuda.current_stream(dev))
+                nat.check(nat.lib().ms_enzymatic_activity(
+                    st, nat.ptr(pos), nat.ptr(cm), nat.ptr(mm), m, H, W, nat.ptr(X), nat.eq_array(eq),
+                    nat.ptr(flags), nat.ptr(scratch), nbytes, nat.stream_ptr(dev)))
+                if self._kernel_events is not None:
+                    ev[1].record(torch.cuda.current_stream(dev))
+                    self._kernel_events.append(ev)
+                if not _settle_early_exit(kin._read_flags(flags), eq, 3):
+                    break
+        new_cm = torch.empty(c, m, dtype=torch.float32, device=dev)
+        nat.check(nat.lib().ms_scatter_signals(nat.ptr(X), nat.ptr(pos), c, m, H, W, nat.ptr(new_cm), nat.ptr(mm),
+                                               nat.stream_ptr(dev)))
+        self.cell_molecules = new_cm
+
+    @torch.no_grad()
+    def diffuse_molecules(self):
+        """world.py:627-665"""
+        dev = self._cuda()
+        mm, cm, pos = self._state_on_device(dev)
+        m, H, W = mm.shape
+        if m == 0:
+            return
+        a = self._const_f32("diff_a", [w[0] for w in self._diffusion], dev)
+        b = self._const_f32("diff_b", [w[1] for w in self._diffusion], dev)
+        nbytes = int(nat.lib().ms_diffuse_scratch_bytes(m, H, W))
+        scratch = self._buffer("diffuse", nbytes, dev)
+        nat.check(nat.lib().ms_diffuse_molecules(nat.ptr(mm), nat.ptr(a), nat.ptr(b), m, H, W, nat.ptr(scratch),
+                                                 nbytes, nat.stream_ptr(dev)))
+        if self.n_cells == 0:
+            return
+        perm = self._const_f32("perm", list(self._permeation), dev)
+        new_cm = torch.empty_like(cm)
+        nat.check(nat.lib().ms_permeate(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pos), nat.ptr(perm),
+                                        self.n_cells, m, H, W, nat.stream_ptr(dev)))
+        self.cell_molecules = new_cm
+
+    def degrade_molecules(self):
+        """world.py:667-678 (per-molecule scalar decay; plain tensor ops, not a kernel of this package)"""
+        dev = self.molecule_map.device
+        f = torch.tensor(self._mol_degrads, dtype=torch.float32, device=dev)
+        self.molecule_map *= f[:, None, None]
+        self.cell_molecules *= f.to(self.cell_molecules.device)[None, :]
+
+    def increment_cell_lifetimes(self):
+        """world.py:680-687"""
+        self.cell_lifetimes += 1
+
+    # ------------------------------------------------------------------ cell bookkeeping
+    def add_cells_from_params(self, positions: torch.Tensor, cell_molecules: torch.Tensor | None = None,
+                              **params: torch.Tensor) -> list[int]:
+        """
+        Append cells at the given free pixels with ready-made kinetic parameters (what
+        spawn_cells + set_cell_params produce, world.py:287-341).  Without `cell_molecules`
+        each new cell takes half of its pixel's molecules (world.py:335-338).
+        """
+        n = int(positions.shape[0])
+        if n == 0:
+            return []
+        dev = self.device
+        pos = positions.to(device=dev, dtype=torch.int32)
+        xs, ys = pos[:, 0].long(), pos[:, 1].long()
+        if bool(self.cell_map[xs, ys].any()):
+            raise ValueError("some positions are already occupied")
+        new_idxs = list(range(self.n_cells, self.n_cells + n))
+        self.n_cells += n
+        self.cell_genomes.extend("" for _ in range(n))
+        self.cell_labels.extend("".join(random.choices("abcdefghijklmnopqrstuvwxyz", k=12)) for _ in range(n))
+        self.cell_lifetimes = self._expand_c(self.cell_lifetimes, n)
+        self.cell_positions = self._expand_c(self.cell_positions, n)
+        self.cell_divisions = self._expand_c(self.cell_divisions, n)
+        self.cell_molecules = self._expand_c(self.cell_molecules, n)
+        self.kinetics.increase_max_cells(by_n=n)
+        self.cell_map[xs, ys] = True
+        self.cell_positions[new_idxs] = pos
+        if cell_molecules is None:
+            pickup = self.molecule_map[:, xs, ys] * 0.5
+            self.cell_molecules[new_idxs, :] += pickup.T
+            self.molecule_map[:, xs, ys] -= pickup
+        else:
+            self.cell_molecules[new_idxs, :] = cell_molecules.to(device=dev, dtype=torch.float32)
+        self.kinetics.set_cell_params_from_tensors(new_idxs, **params)
+        return new_idxs
+
+    def kill_cells(self, cell_idxs: list[int] | None = None):
+        """world.py:495-540: spill molecules, compact every per-cell tensor order-preservingly"""
+        if cell_idxs is None:
+            cell_idxs = list(range(self.n_cells))
+        if len(cell_idxs) == 0:
+            return
+        cell_idxs = list(set(cell_idxs))
+        xs = self.cell_positions[cell_idxs, 0].long()
+        ys = self.cell_positions[cell_idxs, 1].long()
+        self.cell_map[xs, ys] = False
+        self.molecule_map[:, xs, ys] += self.cell_molecules[cell_idxs, :].T
+        keep = torch.ones(self.cell_lifetimes.size(0), dtype=torch.bool, device=self.cell_lifetimes.device)
+        keep[cell_idxs] = False
+        self.cell_lifetimes = self.cell_lifetimes[keep]
+        self.cell_positions = self.cell_positions[keep]
+        self.cell_divisions = self.cell_divisions[keep]
+        self.cell_molecules = self.cell_molecules[keep]
+        self.kinetics.remove_cell_params(keep=keep)
+        for idx in sorted(cell_idxs, reverse=True):
+            self.cell_genomes.pop(idx)
+            self.cell_labels.pop(idx)
+        self.n_cells -= len(cell_idxs)
+
+    def divide_cells_at(self, parent_idxs: list[int], child_positions: torch.Tensor) -> list[tuple[int, int]]:
+        """
+        world.py:446-475 after the reference's Rust helper has picked the children's pixels:
+        children are appended, inherit the parents' parameters and half of their molecules.
+        """
+        n = len(parent_idxs)
+        if n == 0:
+            return []
+        child_idxs = list(range(self.n_cells, self.n_cells + n))
+        self.n_cells += n
+        self.cell_genomes.extend(self.cell_genomes[d] for d in parent_idxs)
+        self.cell_labels.extend(self.cell_labels[d] for d in parent_idxs)
+        self.cell_lifetimes = self._expand_c(self.cell_lifetimes, n)
+        self.cell_positions = self._expand_c(self.cell_positions, n)
+        self.cell_divisions = self._expand_c(self.cell_divisions, n)
+        self.cell_molecules = self._expand_c(self.cell_molecules, n)
+        self.kinetics.increase_max_cells(by_n=n)
+        self.kinetics.copy_cell_params(from_idxs=parent_idxs, to_idxs=child_idxs)
+        pos = child_positions.to(device=self.cell_positions.device, dtype=torch.int32)
+        self.cell_map[pos[:, 0].long(), pos[:, 1].long()] = True
+        self.cell_positions[child_idxs] = pos
+        descendants = parent_idxs + child_idxs
+        self.cell_molecules[child_idxs] = self.cell_molecules[parent_idxs]
+        self.cell_molecules[descendants] *= 0.5
+        self.cell_divisions[child_idxs] = self.cell_divisions[parent_idxs]
+        self.cell_divisions[descendants] += 1
+        self.cell_lifetimes[descendants] = 0
+        return list(zip(parent_idxs, child_idxs))
+
+    # ------------------------------------------------------------------ helpers
+    def _get_molecule_map(self, n: int, size: int, init: str) -> torch.Tensor:
+        """world.py:922-933"""
+        if init == "zeros":
+            return torch.zeros(n, size, size, device=self.device, dtype=torch.float32)
+        if init == "randn":
+            return (torch.randn(n, size, size, dtype=torch.float32, device=self.device) + 10.0).abs()
+        raise ValueError(f"Didnt recognize mol_map_init={init}. Should be one of: 'zeros', 'randn'.")
+
+    def _expand_c(self, t: torch.Tensor, n: int) -> torch.Tensor:
+        zeros = torch.zeros(n, *t.shape[1:], dtype=t.dtype, device=t.device)
+        return torch.cat([t, zeros], dim=0)
+
+    def __repr__(self) -> str:
+        return f"{type(self).__name__}(map_size:{self.map_size!r},abs_temp:{self.abs_temp!r},device:{self.device!r})"

@@ -1,0 +1,141 @@
+"""
+CPU-only tests: the C-ABI library loads and exports every symbol include/magicsoup_b200.h
+declares, the host-side logic (early-exit protocol, parameter store, cell bookkeeping)
+and the no-CPU-fallback rule.  No kernel is launched here.
+"""
+import ctypes
+import re
+from pathlib import Path
+
+import pytest
+import torch
+
+import magicsoup_b200 as ms
+from magicsoup_b200 import _native as nat
+from magicsoup_b200.kinetics import _settle_early_exit, _ALL_PARAMS
+from magicsoup_b200.synthetic import make_population
+from magicsoup_b200.world import diffusion_weights, permeation_factor
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def test_library_exports_every_declared_symbol():
+    header = (ROOT / "include" / "magicsoup_b200.h").read_text()
+    declared = set(re.findall(r"\b(ms_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 18
+    lib = nat.lib()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert declared <= set(nat.exported_symbols()) | {"ms_diffuse_molecules_static"}
+    assert lib.ms_version() >= 100
+    assert lib.ms_error_string(-3).decode().startswith("scratch")
+    assert lib.ms_kinetics_scratch_bytes(64, 32) > 0
+    assert lib.ms_diffuse_scratch_bytes(16, 1024, 1024) >= 16 * 1024 * 1024 * 4
+
+
+def test_no_cpu_fallback():
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    pop = make_population(4, 3, 2, 4, seed=0)
+    kin = ms.Kinetics(chemistry=ms.Chemistry([ms.Molecule("a", 1.0), ms.Molecule("b", 2.0)], []))
+    for k in _ALL_PARAMS:
+        setattr(kin, k, getattr(pop, k))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        kin.integrate_signals(pop.X0())
+    w = ms.World(chemistry=ms.Chemistry([ms.Molecule("a", 1.0)], []), map_size=4)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        w.diffuse_molecules()
+
+
+def test_settle_early_exit_protocol():
+    full = [1] * 24
+    eq = [4, 4, 4]
+    assert _settle_early_exit(full, eq, 3) is False and eq == [4, 4, 4]
+    # nothing adjustable anywhere from iteration 2 of part 0 on: later iterations were no-ops
+    f = list(full)
+    f[2] = f[3] = f[14] = f[15] = 0
+    eq = [4, 4, 4]
+    assert _settle_early_exit(f, eq, 3) is False and eq == [4, 4, 4]
+    # part 1, iteration 1: only low-impact proteins still adjustable -> the reference stops there
+    f = list(full)
+    f[4 + 1] = 0
+    eq = [4, 4, 4]
+    assert _settle_early_exit(f, eq, 3) is True and eq == [4, 1, 4]
+    # after the repeat the same flags settle
+    assert _settle_early_exit(f, eq, 3) is False
+    # single-part calls only look at part 0
+    f = [0] * 24
+    f[12] = 1
+    eq = [4, 0, 0]
+    assert _settle_early_exit(f, eq, 1) is True and eq == [0, 0, 0]
+
+
+def test_weights_match_reference_formulas():
+    assert diffusion_weights(0.0) == (0.0, 1.0)
+    a, b = diffusion_weights(0.5)
+    assert abs(a - 0.1) < 1e-12 and abs(8 * a + b - 1.0) < 1e-12
+    assert diffusion_weights(-3.0) == diffusion_weights(1.0)
+    assert permeation_factor(0.0) == 0.0 and permeation_factor(1.0) == 0.5 and permeation_factor(-7.0) == 0.5
+
+
+def _kin(m=2):
+    return ms.Kinetics(chemistry=ms.Chemistry([ms.Molecule(f"hk{i}", 1.0) for i in range(m)], []))
+
+
+def test_parameter_store_grow_copy_remove():
+    kin = _kin()
+    assert kin.N.shape == (0, 0, 4) and kin.N.dtype is torch.int32 and kin.Ke.dtype is torch.float32
+    kin.increase_max_cells(by_n=3)
+    kin.increase_max_proteins(max_n=2)
+    kin.increase_max_proteins(max_n=1)  # never shrinks (kinetics.py:705-723)
+    assert kin.N.shape == (3, 2, 4) and kin.Vmax.shape == (3, 2)
+    pop = make_population(3, 2, 2, 4, seed=3)
+    kin.set_cell_params_from_tensors([0, 1, 2], **{k: getattr(pop, k) for k in _ALL_PARAMS})
+    kin.copy_cell_params(from_idxs=[0], to_idxs=[2])
+    assert torch.equal(kin.Kmr[2], kin.Kmr[0]) and torch.equal(kin.N[2], pop.N[0])
+    kin.unset_cell_params(cell_idxs=[1])
+    assert kin.Ke[1].abs().sum() == 0 and kin.A[1].abs().sum() == 0
+    kin.remove_cell_params(keep=torch.tensor([True, False, True]))
+    assert kin.N.shape == (2, 2, 4) and torch.equal(kin.N[1], pop.N[0])
+    # fewer proteins than the store: padded with zeros
+    kin.increase_max_cells(by_n=1)
+    small = make_population(1, 1, 2, 4, seed=4)
+    kin.set_cell_params_from_tensors([2], **{k: getattr(small, k) for k in _ALL_PARAMS})
+    assert torch.equal(kin.N[2, 0], small.N[0, 0]) and kin.N[2, 1].abs().sum() == 0
+
+
+def test_world_bookkeeping_on_cpu():
+    mols = [ms.Molecule("wa", 1.0, half_life=10), ms.Molecule("wb", 2.0, diffusivity=1.0, permeability=0.5)]
+    w = ms.World(chemistry=ms.Chemistry(mols, []), map_size=8)
+    assert w.molecule_map.shape == (2, 8, 8) and w.cell_map.dtype is torch.bool
+    assert w.cell_positions.dtype is torch.int32 and w.cell_molecules.shape == (0, 2)
+    pop = make_population(5, 3, 2, 8, seed=5)
+    before = w.molecule_map.sum()
+    idxs = w.add_cells_from_params(pop.cell_positions, **{k: getattr(pop, k) for k in _ALL_PARAMS})
+    assert idxs == [0, 1, 2, 3, 4] and w.n_cells == 5 and int(w.cell_map.sum()) == 5
+    assert abs(float(before - w.molecule_map.sum() - w.cell_molecules.sum())) < 1e-3
+    with pytest.raises(ValueError):
+        w.add_cells_from_params(pop.cell_positions[:1], **{k: getattr(pop, k)[:1] for k in _ALL_PARAMS})
+    w.kill_cells([1, 3])
+    assert w.n_cells == 3 and w.kinetics.N.shape[0] == 3 and len(w.cell_labels) == 3
+    assert torch.equal(w.cell_positions, pop.cell_positions[[0, 2, 4]])
+    free = torch.nonzero(~w.cell_map)[:1].int()
+    assert w.divide_cells_at([0], free) == [(0, 3)]
+    assert w.n_cells == 4 and int(w.cell_divisions[0]) == 1 and int(w.cell_divisions[3]) == 1
+    w.degrade_molecules()
+    w.increment_cell_lifetimes()
+    assert int(w.cell_lifetimes[1]) == 1
+    with pytest.raises(ValueError):
+        ms.World(chemistry=ms.Chemistry(mols, []), map_size=4, mol_map_init="nope")
+
+
+def test_synthetic_population_invariants():
+    pop = make_population(64, 16, 6, 16, seed=9)
+    assert pop.N.shape == (64, 16, 12) and pop.N.dtype is torch.int32
+    assert (pop.Nf >= 0).all() and (pop.Nb >= 0).all()
+    assert torch.equal(pop.N, pop.Nb - pop.Nf)
+    assert ((pop.Kmr == 1.0) | (pop.A != 0)).all()
+    assert (pop.Ke >= 1e-36).all() and (pop.Ke <= 1e36).all()
+    assert len({(int(x), int(y)) for x, y in pop.cell_positions.tolist()}) == 64
+    again = make_population(64, 16, 6, 16, seed=9)
+    assert torch.equal(pop.N, again.N) and torch.equal(pop.Kmr, again.Kmr)

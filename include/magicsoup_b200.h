@@ -72,8 +72,9 @@ int ms_device_count(void);
  *   (later parts' flags are only meaningful once earlier parts are settled).
  *   magicsoup_b200.kinetics.Kinetics.integrate_signals runs this protocol.
  * flags: MS_N_FLAGS uint32, zeroed by this call before the kernel runs.
- * scratch: ms_kinetics_scratch_bytes(p, s) bytes (used only by cells whose
- *   proteomes do not fit the in-shared-memory sparse lists).
+ * scratch: ms_kinetics_scratch_bytes(c, p, s) bytes: the list of cells whose tiles do not
+ *   fit the small in-shared-memory lists (they are integrated by a second launch of the
+ *   same kernel with large lists) and the per-warp arrays of the dense path.
  * X_out must not alias X_in.
  */
 int ms_integrate_signals(const ms_kinetics_params *params, const float *X_in, float *X_out,
@@ -92,7 +93,7 @@ int ms_integrate_signals_part(const ms_kinetics_params *params, const float *adj
                               uint32_t *flags, float *V_out, void *scratch,
                               size_t scratch_bytes, void *stream);
 
-size_t ms_kinetics_scratch_bytes(int64_t p, int64_t s);
+size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s);
 
 /* Kinetics._multiply_signals(X, N) -> (xx (c,p), involved (c,p) as uint8)  kinetics.py:894-918 */
 int ms_multiply_signals(const float *X, const int32_t *K, int64_t c, int64_t p, int64_t s,

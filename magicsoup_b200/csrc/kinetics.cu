@@ -42,6 +42,13 @@ struct KinArgs {
   int e_cat, e_reg;       // list capacities (entries)
   int words_per_warp;     // shared memory words per warp
   int sparse_enabled;     // 0 forces the dense path (p > 256 or s > 128)
+  // Two tiers.  Tier 1 (small lists, 32 warps/SM) defers cells whose tile does not fit to
+  // defer_list; tier 2 (lists sized for a full tile, few warps/SM) integrates exactly those
+  // cells, and only what cannot be packed at all takes the dense path.
+  int tier;               // 1 or 2
+  int defer_enabled;      // tier 1: a tier-2 launch follows
+  int *defer_count;       // device counter (zeroed before tier 1)
+  int *defer_list;        // device list of deferred cell indices (capacity c)
 };
 
 // per-warp shared memory carve-up (32-bit words)
@@ -507,15 +514,18 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, f
   extern __shared__ __align__(16) unsigned smem[];
   __shared__ unsigned sflags[MS_N_FLAGS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warps_per_cta = blockDim.x >> 5;
   if (threadIdx.x < MS_N_FLAGS) sflags[threadIdx.x] = 0;
   __syncthreads();
   unsigned *wbase = smem + (size_t)warp * a.words_per_warp;
   const int p = a.p, s = a.s, s32 = round32(s);
-  const long long gw = (long long)blockIdx.x * WARPS_PER_CTA + warp;
-  const long long nw = (long long)gridDim.x * WARPS_PER_CTA;
+  const long long gw = (long long)blockIdx.x * warps_per_cta + warp;
+  const long long nw = (long long)gridDim.x * warps_per_cta;
   float *dscr = dense_scratch + gw * (size_t)(3 * round32(p));
+  const long long n_items = a.tier == 2 ? (long long)*a.defer_count : a.c;
 
-  for (long long cell = gw; cell < a.c; cell += nw) {
+  for (long long item = gw; item < n_items; item += nw) {
+    const long long cell = a.tier == 2 ? (long long)a.defer_list[item] : item;
     float *X0 = (float *)wbase, *X1 = X0 + s32, *Fsig = X1 + s32;
     // gather X0 (world.py:619-621) or read it
     for (int i = lane; i < s; i += 32) {
@@ -540,6 +550,9 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, f
     }
     if (sparse) {
       run_sparse<ST>(a, w, cell, lane, n_act, sflags);
+    } else if (a.tier == 1 && a.defer_enabled) {
+      if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
+      continue;  // integrated by the tier-2 launch
     } else {
       __syncwarp();
       run_dense(a, X0, X1, Fsig, dscr, dscr + round32(p), dscr + 2 * round32(p), cell, lane, sflags);
@@ -666,7 +679,7 @@ __global__ void fill_kernel(float *x, long long n, float v) {
 // host side
 // ---------------------------------------------------------------------------
 struct LaunchPlan {
-  int e_cat, e_reg, words_per_warp, st, sparse_enabled, grid;
+  int e_cat, e_reg, words_per_warp, st, sparse_enabled, grid, warps_per_cta;
   size_t smem_bytes;
 };
 
@@ -682,60 +695,120 @@ static int sm_count() {
   return g_sm_count;
 }
 
-static LaunchPlan make_plan(int64_t p, int64_t s) {
-  LaunchPlan pl;
+constexpr size_t SMEM_PER_SM = 220 * 1024;   // usable per SM (227 KB max per CTA on sm_100a)
+constexpr size_t SMEM_PER_CTA_MAX = 200 * 1024;
+
+// tier 1: lists for a typical proteome (4 entries per protein row on average)
+static LaunchPlan plan_tier1(int64_t p, int64_t s) {
+  LaunchPlan pl = {};
   pl.sparse_enabled = (p <= 256 && s <= 32 * MAX_ST) ? 1 : 0;
   pl.st = s <= 32 ? 1 : (s <= 64 ? 2 : 4);
-  // list capacities: 4 entries per protein on average, at least 64; regulatory 1 per protein
   int e_cat = (int)(4 * p < 64 ? 64 : 4 * p);
   if (e_cat > (int)(p * s)) e_cat = (int)(p * s);
-  e_cat = round32(e_cat);
-  int e_reg = round32((int)(p < 32 ? 32 : p));
-  if (!pl.sparse_enabled) { e_cat = 0; e_reg = 0; }
-  pl.e_cat = e_cat;
-  pl.e_reg = e_reg;
-  pl.words_per_warp = pl.sparse_enabled ? warp_words((int)p, (int)s, e_cat, e_reg) : 3 * round32((int)s);
-  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * WARPS_PER_CTA;
-  pl.grid = sm_count() * 4;
+  pl.e_cat = round32(e_cat);
+  int e_reg = (int)(p < 32 ? 32 : p);
+  if (e_reg > (int)(p * s)) e_reg = (int)(p * s);
+  pl.e_reg = round32(e_reg);
+  pl.warps_per_cta = WARPS_PER_CTA;
+  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_cat, pl.e_reg);
+  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
+  if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
+    pl.sparse_enabled = 0;
+    pl.e_cat = pl.e_reg = 0;
+    pl.words_per_warp = 3 * round32((int)s);
+    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
+  }
+  size_t per_sm = SMEM_PER_SM / (pl.smem_bytes + 1024);
+  if (per_sm > 4) per_sm = 4;
+  if (per_sm < 1) per_sm = 1;
+  pl.grid = sm_count() * (int)per_sm;
   return pl;
+}
+
+// tier 2: lists that hold a completely dense tile; as many warps per CTA as fit
+static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
+  pl = {};
+  if (!(p <= 256 && s <= 32 * MAX_ST)) return false;
+  pl.sparse_enabled = 1;
+  pl.st = s <= 32 ? 1 : (s <= 64 ? 2 : 4);
+  pl.e_cat = round32((int)(p * s));
+  pl.e_reg = round32((int)(p * s));
+  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_cat, pl.e_reg);
+  const size_t per_warp = (size_t)pl.words_per_warp * 4;
+  if (per_warp > SMEM_PER_CTA_MAX) return false;
+  int w = (int)((SMEM_PER_SM / 2) / per_warp);
+  if (w < 1) w = 1;
+  if (w > WARPS_PER_CTA) w = WARPS_PER_CTA;
+  pl.warps_per_cta = w;
+  pl.smem_bytes = per_warp * w;
+  size_t per_sm = SMEM_PER_SM / (pl.smem_bytes + 1024);
+  if (per_sm > 4) per_sm = 4;
+  if (per_sm < 1) per_sm = 1;
+  pl.grid = sm_count() * (int)per_sm;
+  return true;
+}
+
+static size_t align256k(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// scratch layout: [dense arrays: max_warps x 3 x round32(p) floats][defer counter][defer list: c ints]
+static size_t dense_scratch_bytes(int64_t p) {
+  return align256k((size_t)148 * 8 * WARPS_PER_CTA * 3 * (size_t)round32((int)p) * sizeof(float));
 }
 
 }  // namespace ms
 
 using namespace ms;
 
-extern "C" size_t ms_kinetics_scratch_bytes(int64_t p, int64_t s) {
+extern "C" size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s) {
   (void)s;
-  // 3 float arrays of round32(p) per resident warp of the largest grid we launch
-  return (size_t)148 * 8 * WARPS_PER_CTA * 3 * (size_t)round32((int)p) * sizeof(float) + 256;
+  if (c < 0) c = 0;
+  return dense_scratch_bytes(p) + 256 + align256k((size_t)c * sizeof(int));
+}
+
+template <typename K>
+static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
+  MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+  a.e_cat = pl.e_cat; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
+  a.sparse_enabled = pl.sparse_enabled;
+  kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+static int launch_plan(const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
+  if (pl.st == 1) return launch_one(kinetics_fused_kernel<1>, pl, a, dense, st);
+  if (pl.st == 2) return launch_one(kinetics_fused_kernel<2>, pl, a, dense, st);
+  return launch_one(kinetics_fused_kernel<4>, pl, a, dense, st);
 }
 
 static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, size_t scratch_bytes,
                         cudaStream_t st) {
   if (!P || P->c < 0 || P->p < 0 || P->s < 0) return MS_ERR_INVALID_ARGUMENT;
-  if (P->p > 65535 || P->s > 8192) return MS_ERR_TOO_LARGE;
+  if (P->p > 65535 || P->s > 8192 || P->c > INT32_MAX) return MS_ERR_TOO_LARGE;
   a.N = P->N; a.Nf = P->Nf; a.Nb = P->Nb; a.A = P->A;
   a.Kmr = P->Kmr; a.Ke = P->Ke; a.Kmf = P->Kmf; a.Kmb = P->Kmb; a.Vmax = P->Vmax;
   a.c = P->c; a.p = (int)P->p; a.s = (int)P->s;
   MS_CUDA_CHECK(cudaMemsetAsync(a.flags, 0, MS_N_FLAGS * sizeof(unsigned), st));
   if (P->c == 0 || P->s == 0) return MS_OK;
-  LaunchPlan pl = make_plan(P->p, P->s);
-  if (pl.smem_bytes > 200 * 1024) {  // huge p or s: dense path with minimal shared memory
-    pl.sparse_enabled = 0;
-    pl.words_per_warp = 3 * round32(a.s);
-    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * WARPS_PER_CTA;
-  }
-  int64_t ctas_needed = ceil_div(P->c, WARPS_PER_CTA);
-  if (pl.grid > ctas_needed) pl.grid = (int)ctas_needed;
-  const size_t need = (size_t)pl.grid * WARPS_PER_CTA * 3 * (size_t)round32(a.p) * sizeof(float);
-  if (scratch_bytes < need || !scratch) return MS_ERR_SCRATCH_TOO_SMALL;
-  a.e_cat = pl.e_cat; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
-  a.sparse_enabled = pl.sparse_enabled;
-  auto kern = pl.st == 1 ? kinetics_fused_kernel<1> : (pl.st == 2 ? kinetics_fused_kernel<2> : kinetics_fused_kernel<4>);
-  MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
-  kern<<<pl.grid, THREADS, pl.smem_bytes, st>>>(a, (float *)scratch);
-  MS_CUDA_CHECK(cudaGetLastError());
-  return MS_OK;
+  if (!scratch || scratch_bytes < ms_kinetics_scratch_bytes(P->c, P->p, P->s)) return MS_ERR_SCRATCH_TOO_SMALL;
+  float *dense = (float *)scratch;
+  a.defer_count = (int *)((char *)scratch + dense_scratch_bytes(P->p));
+  a.defer_list = a.defer_count + 64;
+
+  LaunchPlan p1 = plan_tier1(P->p, P->s), p2;
+  const bool two_tiers = p1.sparse_enabled && plan_tier2(P->p, P->s, p2) && p2.e_cat > p1.e_cat;
+  const int64_t ctas_needed = ceil_div(P->c, p1.warps_per_cta);
+  if (p1.grid > ctas_needed) p1.grid = (int)ctas_needed;
+  a.tier = 1;
+  a.defer_enabled = two_tiers ? 1 : 0;
+  if (two_tiers) MS_CUDA_CHECK(cudaMemsetAsync(a.defer_count, 0, sizeof(int), st));
+  int rc = launch_plan(p1, a, dense, st);
+  if (rc != MS_OK || !two_tiers) return rc;
+  a.tier = 2;
+  a.defer_enabled = 0;
+  const int64_t ctas2 = ceil_div(P->c, p2.warps_per_cta);
+  if (p2.grid > ctas2) p2.grid = (int)ctas2;
+  return launch_plan(p2, a, dense, st);
 }
 
 static int fill_eq(KinArgs &a, const int32_t *eq_iters_host) {

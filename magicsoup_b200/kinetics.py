@@ -148,8 +148,8 @@ class Kinetics:
         st = nat.KineticsParams(**{k: nat.ptr(v) for k, v in keep.items()}, c=c, p=p, s=s)
         return st, keep, p
 
-    def _kin_scratch(self, dev: torch.device, p: int, s: int):
-        n = int(nat.lib().ms_kinetics_scratch_bytes(p, s))
+    def _kin_scratch(self, dev: torch.device, c: int, p: int, s: int):
+        n = int(nat.lib().ms_kinetics_scratch_bytes(c, p, s))
         return self._buffer("kin", n, dev), n
 
     def _flags(self, dev: torch.device) -> torch.Tensor:
@@ -179,7 +179,7 @@ class Kinetics:
         if c == 0 or s == 0:
             return out
         st, keep, p = self._params(dev, c, s)
-        scratch, nbytes = self._kin_scratch(dev, p, s)
+        scratch, nbytes = self._kin_scratch(dev, c, p, s)
         flags = self._flags(dev)
         eq = [4, 4, 4]
         while True:
@@ -213,7 +213,7 @@ class Kinetics:
         adj = self._f32(adj_vmax, dev)
         if tuple(adj.shape) != (c, p):
             raise ValueError(f"adj_vmax has shape {tuple(adj.shape)}, expected {(c, p)}")
-        scratch, nbytes = self._kin_scratch(dev, p, s)
+        scratch, nbytes = self._kin_scratch(dev, c, p, s)
         flags = self._flags(dev)
         X1 = torch.empty_like(X0d)
         V = torch.empty(c, p, dtype=torch.float32, device=dev) if want_v else None

@@ -94,15 +94,16 @@ def _fill_chunk(c: int, p: int, m: int, gen, device, energies: torch.Tensor, abs
     def rint(lo, hi, *shape):
         return torch.randint(lo, hi, shape, generator=gen, device=dev)
 
-    # up to 3 work domains per protein: 0 = none, 1 = catalytic, 2 = transporter
-    n_dom = rint(1, 4, c, p)
+    # 1-3 work domains per protein, 1.38 on average (1.35-1.41 for random genomes)
+    u = rnd(c, p)
+    n_dom = 1 + (u > 0.70).int() + (u > 0.92).int()
     for d in range(3):
         has = active & (n_dom > d)
         kind = torch.where(rnd(c, p) < 0.6, 1, 2)  # catalytic more likely
         sign = torch.where(rnd(c, p) < 0.5, 1, -1).int()
         Nd = torch.zeros(c, p, s, dtype=torch.int32, device=dev)
         # catalytic: <=4 intracellular signals with coefficients in {-2..2}
-        for _ in range(4):
+        for _ in range(2):
             sig = rint(0, m, c, p)
             coef = rint(-2, 3, c, p).int()
             use = (has & (kind == 1)).int()

@@ -177,7 +177,7 @@ class World:
             X = kin.integrate_signals(X=torch.cat([cm, mm[:, xs, ys].T], dim=1))
         else:
             st, keep, p = kin._params(dev, c, s)
-            scratch, nbytes = kin._kin_scratch(dev, p, s)
+            scratch, nbytes = kin._kin_scratch(dev, c, p, s)
             flags = kin._flags(dev)
             X = torch.empty(c, s, dtype=torch.float32, device=dev)
             eq = [4, 4, 4]

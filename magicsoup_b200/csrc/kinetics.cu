@@ -18,7 +18,7 @@ namespace ms {
 
 constexpr int WARPS_PER_CTA = 8;
 constexpr int THREADS = WARPS_PER_CTA * 32;
-constexpr int MAX_ST = 4;  // signals per lane in the sparse path (s <= 128)
+constexpr int MAX_S_SPARSE = 256;  // 8-bit signal / protein indices in the packed lists
 constexpr unsigned FULL = 0xffffffffu;
 
 struct KinArgs {
@@ -39,7 +39,7 @@ struct KinArgs {
   float trims[3];
   const float *adj_vmax;  // (c,p) when n_parts == 1
   float *V_out;           // optional (c,p), n_parts == 1 only
-  int e_cat, e_reg;       // list capacities (entries)
+  int e_sub, e_nnz, e_reg;  // list capacities (entries)
   int words_per_warp;     // shared memory words per warp
   int sparse_enabled;     // 0 forces the dense path (p > 256 or s > 128)
   // Two tiers.  Tier 1 (small lists, 32 warps/SM) defers cells whose tile does not fit to
@@ -53,27 +53,28 @@ struct KinArgs {
 
 // per-warp shared memory carve-up (32-bit words)
 struct WarpMem {
-  float *X0, *X1, *Fsig;            // s32 each
-  unsigned *colptr;                 // s32 + 4
-  float *V, *Fmin, *F;              // p32 each
-  float *Ke, *Kmf, *Kmb, *Vmax;     // p32 each
-  unsigned *act;                    // p32: indices of proteins with cat entries
-  unsigned *rowptr;                 // p32 + 4: (cat offset) | (reg offset << 16)
-  unsigned *cat;                    // e_cat
-  unsigned *csc;                    // e_cat
-  float *nvs;                       // e_cat (aliases the link list during the scan)
-  unsigned *reg;                    // e_reg
-  float *regk;                      // e_reg
+  float *X0, *X1, *Fsig;         // s32 each (Fsig doubles as the counting-sort cursor in the scan)
+  unsigned *colptr;              // s32 + 4
+  float *V, *F;                  // p32 each
+  unsigned *FminKey;             // p32: order-preserving key of F_min (atomicMin target)
+  float *Ke, *Kmf, *Kmb, *Vmax;  // p32 each
+  unsigned *act;                 // p32: proteins that have substrate or product entries
+  unsigned *rowA, *rowB;         // p32 + 4 each: rowA = sub offset | prd offset << 16, rowB = reg offset
+  unsigned *sub, *prd;           // e_sub each: signal | exponent << 8, per protein, ascending signal
+  unsigned *csc;                 // e_nnz: protein | N << 8, per signal, ascending protein
+  float *nvs;                    // e_nnz: rate per csc entry (holds the unsorted N list during the scan)
+  unsigned *reg;                 // e_reg: signal | (A & 0xff) << 8 | protein << 16
+  float *regk;                   // e_reg: Kmr of that entry
 };
 
 __host__ __device__ inline int round32(int x) { return (x + 31) & ~31; }
 
-__host__ __device__ inline int warp_words(int p, int s, int e_cat, int e_reg) {
+__host__ __device__ inline int warp_words(int p, int s, int e_sub, int e_nnz, int e_reg) {
   const int s32 = round32(s), p32 = round32(p);
-  return 3 * s32 + (s32 + 4) + 8 * p32 + (p32 + 4) + 3 * e_cat + 2 * e_reg;
+  return 3 * s32 + (s32 + 4) + 8 * p32 + 2 * (p32 + 4) + 2 * e_sub + 2 * e_nnz + 2 * e_reg;
 }
 
-__device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_cat, int e_reg) {
+__device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_sub, int e_nnz, int e_reg) {
   const int s32 = round32(s), p32 = round32(p);
   WarpMem m;
   m.X0 = (float *)w;            w += s32;
@@ -81,188 +82,327 @@ __device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_cat, i
   m.Fsig = (float *)w;          w += s32;
   m.colptr = w;                 w += s32 + 4;
   m.V = (float *)w;             w += p32;
-  m.Fmin = (float *)w;          w += p32;
   m.F = (float *)w;             w += p32;
+  m.FminKey = w;                w += p32;
   m.Ke = (float *)w;            w += p32;
   m.Kmf = (float *)w;           w += p32;
   m.Kmb = (float *)w;           w += p32;
   m.Vmax = (float *)w;          w += p32;
   m.act = w;                    w += p32;
-  m.rowptr = w;                 w += p32 + 4;
-  m.cat = w;                    w += e_cat;
-  m.csc = w;                    w += e_cat;
-  m.nvs = (float *)w;           w += e_cat;
+  m.rowA = w;                   w += p32 + 4;
+  m.rowB = w;                   w += p32 + 4;
+  m.sub = w;                    w += e_sub;
+  m.prd = w;                    w += e_sub;
+  m.csc = w;                    w += e_nnz;
+  m.nvs = (float *)w;           w += e_nnz;
   m.reg = w;                    w += e_reg;
   m.regk = (float *)w;
   return m;
 }
 
+// order-preserving unsigned key of a float; NaN maps to 0 so that it wins atomicMin
+// (torch.min propagates NaN, kinetics.py:877)
+__device__ __forceinline__ unsigned fkey(float f) {
+  if (isnan(f)) return 0u;
+  const unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float fkey_decode(unsigned k) {
+  if (k == 0u) return __int_as_float(0x7fc00000);
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+constexpr unsigned KEY_ONE = 0xbf800000u;  // fkey(1.0f)
+
+// x^k for a list entry, k >= 1; same multiplication order as powi()
+__device__ __forceinline__ float pow_entry(float x, unsigned k) {
+  float r = (k & 1u) ? x : 1.0f;
+  if (k > 1u) {
+    float b = x * x;
+    if (k & 2u) r = r * b;
+    unsigned n = k >> 2;
+    while (n) {
+      b = b * b;
+      if (n & 1u) r = r * b;
+      n >>= 1;
+    }
+  }
+  return r;
+}
+
+template <int VEC>
+__device__ __forceinline__ void load_vec(const int *ptr, bool ok, int (&v)[VEC]) {
+  if (!ok) {
+#pragma unroll
+    for (int e = 0; e < VEC; e++) v[e] = 0;
+    return;
+  }
+  if constexpr (VEC == 4) {
+    const int4 t = __ldcs(reinterpret_cast<const int4 *>(ptr));
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  } else if constexpr (VEC == 2) {
+    const int2 t = __ldcs(reinterpret_cast<const int2 *>(ptr));
+    v[0] = t.x; v[1] = t.y;
+  } else {
+    v[0] = __ldcs(ptr);
+  }
+}
+
 // ---------------------------------------------------------------------------
-// scan: stream the cell's dense tile once and build the sparse lists.
-// Lane l owns signals l, l+32, ...; rows (proteins) are visited in ascending order,
-// so row lists come out in ascending signal order and column lists in ascending
-// protein order without any sorting or atomics.
-// Returns false if the cell needs the dense path.
+// scan: stream the cell's dense tile once (32*VEC consecutive elements per load
+// instruction, row-major) and compress it into the sparse lists.  Elements are visited
+// in row-major order, so every per-protein list comes out in ascending signal order;
+// the per-signal lists are produced from the row-major N list by a stable counting sort
+// (warp match), i.e. in ascending protein order.  No atomics, no sorting networks.
+// Returns false if the tile does not fit the lists or the packing.
 // ---------------------------------------------------------------------------
-template <int ST>
-__device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, int lane,
-                          int &n_act_out) {
-  const int p = a.p, s = a.s;
-  const long long tile = cell * (long long)p * s;
+template <int VEC>
+__device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, int lane, int &n_act_out) {
+  const int p = a.p, s = a.s, total = p * s;
+  const long long tile = cell * (long long)total;
   const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
   const unsigned lt = (1u << lane) - 1u;
-  unsigned *link = (unsigned *)w.nvs;
+  unsigned *tmp = (unsigned *)w.nvs;
+  constexpr int STEP = 32 * VEC;
+  const int drow = STEP / s, dsig = STEP - drow * s;
 
-  int head[ST], cnt[ST];
-#pragma unroll
-  for (int t = 0; t < ST; t++) { head[t] = 0; cnt[t] = 0; }
-  int cat_total = 0, reg_total = 0, n_act = 0;
-  bool bad = false;
-  if (lane == 0) w.rowptr[0] = 0;
+  int q0 = lane * VEC;
+  int row = q0 / s, sig0 = q0 - row * s;
+  int sub_tot = 0, prd_tot = 0, nnz_tot = 0, reg_tot = 0;
+  int chk = 0;
 
-  constexpr int RU = (ST == 1) ? 4 : (ST == 2 ? 2 : 1);  // rows in flight per lane
-  for (int j0 = 0; j0 < p; j0 += RU) {
-    int vn[RU][ST], vf[RU][ST], vb[RU][ST], va[RU][ST];
+  constexpr int U = VEC == 4 ? 1 : (VEC == 2 ? 2 : 4);  // iterations of loads in flight per lane
+  int nf[U][VEC], nb[U][VEC], nn[U][VEC], na[U][VEC];
+  for (int base = 0; base < total; base += U * STEP) {
 #pragma unroll
-    for (int r = 0; r < RU; r++) {
-#pragma unroll
-      for (int t = 0; t < ST; t++) {
-        const int i = lane + 32 * t;
-        const bool ok = (j0 + r < p) && (i < s);
-        const int off = (j0 + r) * s + i;
-        vf[r][t] = ok ? ldg_stream(gNf + off) : 0;
-        vb[r][t] = ok ? ldg_stream(gNb + off) : 0;
-        vn[r][t] = ok ? ldg_stream(gN + off) : 0;
-        va[r][t] = ok ? ldg_stream(gA + off) : 0;
-      }
+    for (int u = 0; u < U; u++) {
+      const int q = q0 + u * STEP;
+      const bool ok = q < total;
+      load_vec<VEC>(gNf + q, ok, nf[u]);
+      load_vec<VEC>(gNb + q, ok, nb[u]);
+      load_vec<VEC>(gN + q, ok, nn[u]);
+      load_vec<VEC>(gA + q, ok, na[u]);
     }
 #pragma unroll
-    for (int r = 0; r < RU; r++) {
-      const int j = j0 + r;
-      if (j >= p) break;
-      unsigned row_any = 0;
+    for (int u = 0; u < U; u++) {
+      if (base + u * STEP < total) {
+        const bool ok = q0 < total;
+        unsigned msub = 0, mprd = 0, mnnz = 0, mreg = 0;
 #pragma unroll
-      for (int t = 0; t < ST; t++) row_any |= (unsigned)(vf[r][t] | vb[r][t] | vn[r][t] | va[r][t]);
-      if (__ballot_sync(FULL, row_any != 0) != 0) {
-        bool row_cat = false;
+        for (int e = 0; e < VEC; e++) {
+          msub |= (nf[u][e] != 0 ? 1u : 0u) << e;
+          mprd |= (nb[u][e] != 0 ? 1u : 0u) << e;
+          mnnz |= (nn[u][e] != 0 ? 1u : 0u) << e;
+          mreg |= (na[u][e] != 0 ? 1u : 0u) << e;
+        }
+        const unsigned many = msub | mprd | mnnz | mreg;
+        int psub = sub_tot, pprd = prd_tot, pnnz = nnz_tot, preg = reg_tot;
+        if (__ballot_sync(FULL, many != 0) != 0) {
+          // exclusive prefix of the three list counts in one packed shuffle scan
+          const unsigned pk = __popc(msub) | (__popc(mprd) << 10) | (__popc(mnnz) << 20);
+          unsigned incl = pk;
 #pragma unroll
-        for (int t = 0; t < ST; t++) {
-          const int i = lane + 32 * t;
-          const int nf = vf[r][t], nb = vb[r][t], n = vn[r][t], av = va[r][t];
-          const bool catnz = (nf | nb | n) != 0;
-          const bool regnz = av != 0;
-          bad |= ((unsigned)nf > 255u) | ((unsigned)nb > 255u) | (n < -128) | (n > 127) |
-                 (av < -128) | (av > 127);
-          const unsigned bc = __ballot_sync(FULL, catnz);
-          const unsigned br = __ballot_sync(FULL, regnz);
-          if (catnz) {
-            const int pos = cat_total + __popc(bc & lt);
-            if (pos < a.e_cat) {
-              w.cat[pos] = (unsigned)i | ((unsigned)nf << 8) | ((unsigned)nb << 16) |
-                           ((unsigned)(n & 0xff) << 24);
-              if (n != 0) {  // column list, newest first: (protein, N, previous entry + 1)
-                link[pos] = (unsigned)j | ((unsigned)(n & 0xff) << 8) | ((unsigned)head[t] << 16);
-                head[t] = pos + 1;
-                cnt[t]++;
+          for (int d = 1; d < 32; d <<= 1) {
+            const unsigned y = __shfl_up_sync(FULL, incl, d);
+            if (lane >= d) incl += y;
+          }
+          const unsigned excl = incl - pk;
+          const unsigned tot = __shfl_sync(FULL, incl, 31);
+          psub += (int)(excl & 0x3ffu);
+          pprd += (int)((excl >> 10) & 0x3ffu);
+          pnnz += (int)(excl >> 20);
+          sub_tot += (int)(tot & 0x3ffu);
+          prd_tot += (int)((tot >> 10) & 0x3ffu);
+          nnz_tot += (int)(tot >> 20);
+          const unsigned breg = __ballot_sync(FULL, mreg != 0);
+          if (breg) {  // regulatory entries are rare: only then a second scan
+            unsigned ri = __popc(mreg);
+            const unsigned rown = ri;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+              const unsigned y = __shfl_up_sync(FULL, ri, d);
+              if (lane >= d) ri += y;
+            }
+            preg += (int)(ri - rown);
+            reg_tot += (int)__shfl_sync(FULL, ri, 31);
+          }
+          if (ok && sig0 == 0) {
+            w.rowA[row] = (unsigned)min(psub, 0xffff) | ((unsigned)min(pprd, 0xffff) << 16);
+            w.rowB[row] = (unsigned)preg;
+          }
+          if (many) {
+#pragma unroll
+            for (int e = 0; e < VEC; e++) {
+              const int sg = sig0 + e;
+              // range of the packing: exponents < 2^24 and >= 0, |N| < 2^15, |A| < 2^7
+              chk |= ((nf[u][e] | nb[u][e]) & 0xff000000) | ((nn[u][e] + 32768) & 0xffff0000) |
+                     ((na[u][e] + 128) & 0xffffff00);
+              if ((msub >> e) & 1u) {
+                if (psub < a.e_sub) w.sub[psub] = (unsigned)sg | ((unsigned)nf[u][e] << 8);
+                psub++;
+              }
+              if ((mprd >> e) & 1u) {
+                if (pprd < a.e_sub) w.prd[pprd] = (unsigned)sg | ((unsigned)nb[u][e] << 8);
+                pprd++;
+              }
+              if ((mnnz >> e) & 1u) {
+                if (pnnz < a.e_nnz)
+                  tmp[pnnz] = (unsigned)sg | ((unsigned)row << 8) | ((unsigned)nn[u][e] << 16);
+                pnnz++;
+              }
+              if ((mreg >> e) & 1u) {
+                if (preg < a.e_reg)
+                  w.reg[preg] = (unsigned)sg | ((unsigned)(na[u][e] & 0xff) << 8) | ((unsigned)row << 16);
+                preg++;
               }
             }
           }
-          if (regnz) {
-            const int pos = reg_total + __popc(br & lt);
-            if (pos < a.e_reg)
-              w.reg[pos] = (unsigned)i | ((unsigned)(av & 0xff) << 8) | ((unsigned)j << 16);
-          }
-          cat_total += __popc(bc);
-          reg_total += __popc(br);
-          row_cat |= (bc != 0);
+        } else if (ok && sig0 == 0) {
+          w.rowA[row] = (unsigned)min(psub, 0xffff) | ((unsigned)min(pprd, 0xffff) << 16);
+          w.rowB[row] = (unsigned)preg;
         }
-        if (row_cat) {
-          if (lane == 0) w.act[n_act] = (unsigned)j;
-          n_act++;
-        }
+        q0 += STEP;
+        row += drow;
+        sig0 += dsig;
+        if (sig0 >= s) { sig0 -= s; row++; }
       }
-      if (lane == 0)
-        w.rowptr[j + 1] = (unsigned)min(cat_total, 0xffff) | ((unsigned)min(reg_total, 0xffff) << 16);
     }
   }
-  n_act_out = n_act;
-  if (__any_sync(FULL, bad) || cat_total > a.e_cat || reg_total > a.e_reg) return false;
+  if (lane == 0) {
+    w.rowA[p] = (unsigned)min(sub_tot, 0xffff) | ((unsigned)min(prd_tot, 0xffff) << 16);
+    w.rowB[p] = (unsigned)reg_tot;
+  }
+  if (__any_sync(FULL, chk != 0) || sub_tot > a.e_sub || prd_tot > a.e_sub || nnz_tot > a.e_nnz ||
+      reg_tot > a.e_reg) {
+    n_act_out = 0;
+    return false;
+  }
   __syncwarp();
 
-  // column pointers: exclusive scan of the per-signal counts in signal order
-  int base = 0;
-#pragma unroll
-  for (int t = 0; t < ST; t++) {
-    int x = cnt[t];
+  // proteins with substrate/product entries, in ascending order
+  int n_act = 0;
+  for (int j0 = 0; j0 < p; j0 += 32) {
+    const int j = j0 + lane;
+    const bool has = j < p && w.rowA[j + 1] != w.rowA[j];
+    const unsigned b = __ballot_sync(FULL, has);
+    if (has) w.act[n_act + __popc(b & lt)] = (unsigned)j;
+    n_act += __popc(b);
+  }
+  n_act_out = n_act;
+
+  // stable counting sort of the N list by signal -> csc
+  unsigned *cursor = (unsigned *)w.Fsig;
+  for (int i = lane; i < s; i += 32) cursor[i] = 0;
+  __syncwarp();
+  for (int base = 0; base < nnz_tot; base += 32) {
+    const int e = base + lane;
+    const bool v = e < nnz_tot;
+    const unsigned sg = v ? (tmp[e] & 0xffu) : (0x100u + lane);
+    const unsigned peers = __match_any_sync(FULL, sg);
+    if (v && lane == 31 - __clz(peers)) cursor[sg] += __popc(peers);
+    __syncwarp();
+  }
+  unsigned carry = 0;
+  for (int i0 = 0; i0 < s; i0 += 32) {
+    const int i = i0 + lane;
+    const unsigned cnt = i < s ? cursor[i] : 0u;
+    unsigned incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const int y = __shfl_up_sync(FULL, x, d);
-      if (lane >= d) x += y;
+      const unsigned y = __shfl_up_sync(FULL, incl, d);
+      if (lane >= d) incl += y;
     }
-    const int excl = base + x - cnt[t];
-    const int i = lane + 32 * t;
-    if (i < s) w.colptr[i] = (unsigned)excl;
-    // walk the (newest first) column list and lay it out ascending
-    int e = head[t], k = excl + cnt[t] - 1;
-    while (e) {
-      const unsigned wd = link[e - 1];
-      w.csc[k--] = wd & 0xffffu;
-      e = (int)(wd >> 16);
+    if (i < s) {
+      w.colptr[i] = carry + incl - cnt;
+      cursor[i] = carry + incl - cnt;
     }
-    base += __shfl_sync(FULL, x, 31);
+    carry += __shfl_sync(FULL, incl, 31);
   }
-  if (lane == 0) w.colptr[s] = (unsigned)base;
+  if (lane == 0) w.colptr[s] = carry;
+  __syncwarp();
+  for (int base = 0; base < nnz_tot; base += 32) {
+    const int e = base + lane;
+    const bool v = e < nnz_tot;
+    const unsigned wd = v ? tmp[e] : 0u;
+    const unsigned sg = v ? (wd & 0xffu) : (0x100u + lane);
+    const unsigned peers = __match_any_sync(FULL, sg);
+    if (v) {
+      const unsigned pos = cursor[sg] + __popc(peers & lt);
+      w.csc[pos] = ((wd >> 8) & 0xffu) | ((unsigned)((int)wd >> 16) << 8);
+    }
+    __syncwarp();
+    if (v && lane == 31 - __clz(peers)) cursor[sg] += __popc(peers);
+    __syncwarp();
+  }
 
   // per-protein scalars, and the Kmr values of the (few) regulatory entries
-  const long long row = cell * (long long)p;
+  const long long prow = cell * (long long)p;
   for (int j = lane; j < p; j += 32) {
-    w.Ke[j] = ldg_stream(a.Ke + row + j);
-    w.Kmf[j] = ldg_stream(a.Kmf + row + j);
-    w.Kmb[j] = ldg_stream(a.Kmb + row + j);
-    w.Vmax[j] = a.adj_vmax ? ldg_stream(a.adj_vmax + row + j) : ldg_stream(a.Vmax + row + j);
+    w.Ke[j] = __ldcs(a.Ke + prow + j);
+    w.Kmf[j] = __ldcs(a.Kmf + prow + j);
+    w.Kmb[j] = __ldcs(a.Kmb + prow + j);
+    w.Vmax[j] = a.adj_vmax ? __ldcs(a.adj_vmax + prow + j) : __ldcs(a.Vmax + prow + j);
   }
-  for (int e = lane; e < reg_total; e += 32) {
+  for (int e = lane; e < reg_tot; e += 32) {
     const unsigned wd = w.reg[e];
-    w.regk[e] = ldg_stream(a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
+    w.regk[e] = __ldcs(a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
   }
   __syncwarp();
   return true;
 }
 
+// products over a protein's substrate and product lists (kinetics.py:894-918)
+__device__ __forceinline__ void list_products(const WarpMem &w, const float *X, int j, float &xf,
+                                              float &xb, bool &invf, bool &invb) {
+  const unsigned r0 = w.rowA[j], r1 = w.rowA[j + 1];
+  xf = 1.0f;
+  xb = 1.0f;
+  const unsigned f0 = r0 & 0xffffu, f1 = r1 & 0xffffu, b0 = r0 >> 16, b1 = r1 >> 16;
+  for (unsigned e = f0; e < f1; e++) {
+    const unsigned wd = w.sub[e];
+    xf = xf * pow_entry(X[wd & 0xffu], wd >> 8);
+  }
+  for (unsigned e = b0; e < b1; e++) {
+    const unsigned wd = w.prd[e];
+    xb = xb * pow_entry(X[wd & 0xffu], wd >> 8);
+  }
+  invf = f1 > f0;
+  invb = b1 > b0;
+  xf = fix_product(xf);
+  xb = fix_product(xb);
+}
+
 // ---------------------------------------------------------------------------
 // sparse path: all parts of one cell on the shared-memory lists
 // ---------------------------------------------------------------------------
-template <int ST>
 __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, int lane, int n_act,
                            unsigned *sflags) {
   const int p = a.p, s = a.s;
+  const float qnan = __int_as_float(0x7fc00000);
   for (int q = 0; q < a.n_parts; q++) {
     const float trim = a.trims[q];
+    for (int j = lane; j < p; j += 32) {
+      w.V[j] = 0.0f;  // proteins without substrate/product entries have V = 0
+      w.F[j] = 1.0f;
+      w.FminKey[j] = KEY_ONE;
+    }
+    __syncwarp();
     // ---- velocities (kinetics.py:771-806) on the active proteins
     bool poison = false;
     for (int t = lane; t < n_act; t += 32) {
       const int j = (int)w.act[t];
-      const unsigned rp0 = w.rowptr[j], rp1 = w.rowptr[j + 1];
-      float xf = 1.0f, xb = 1.0f;
-      bool invf = false, invb = false;
-      for (unsigned e = rp0 & 0xffffu; e < (rp1 & 0xffffu); e++) {
-        const unsigned wd = w.cat[e];
-        const float x = w.X0[wd & 0xffu];
-        const int nf = (wd >> 8) & 0xff, nb = (wd >> 16) & 0xff;
-        if (nf) { invf = true; xf = xf * (nf == 1 ? x : powi(x, nf)); }
-        if (nb) { invb = true; xb = xb * (nb == 1 ? x : powi(x, nb)); }
-      }
-      float kf = fix_product(xf) / w.Kmf[j];
+      float xf, xb;
+      bool invf, invb;
+      list_products(w, w.X0, j, xf, xb, invf, invb);
+      float kf = xf / w.Kmf[j];
       if (!invf) kf = 0.0f;
       if (isinf(kf)) kf = V_MAX;
-      float kb = fix_product(xb) / w.Kmb[j];
+      float kb = xb / w.Kmb[j];
       if (!invb) kb = 0.0f;
       if (isinf(kb)) kb = V_MAX;
       float a_reg = 1.0f;
-      for (unsigned e = rp0 >> 16; e < (rp1 >> 16); e++) {
+      for (unsigned e = w.rowB[j]; e < w.rowB[j + 1]; e++) {
         const unsigned wd = w.reg[e];
-        const int av = (int)(int8_t)((wd >> 8) & 0xff);
-        a_reg = a_reg * reg_factor(w.X0[wd & 0xffu], av, w.regk[e]);
+        a_reg = a_reg * reg_factor(w.X0[wd & 0xffu], (int)(int8_t)((wd >> 8) & 0xff), w.regk[e]);
       }
       float vmax = w.Vmax[j];
       if (!a.adj_vmax) vmax = clamp0(vmax * trim);  // kinetics.py:749
@@ -273,56 +413,36 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     poison = __any_sync(FULL, poison);  // 0 * NaN of the dense reference reaches every signal
     __syncwarp();
 
-    // ---- substrate trimming (kinetics.py:861-879): per signal D_i and F_i
-#pragma unroll
-    for (int t = 0; t < ST; t++) {
-      const int i = lane + 32 * t;
-      if (i < s) {
-        float d = 0.0f;
-        for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++) {
-          const unsigned wd = w.csc[e];
-          const float nv = (float)(int)(int8_t)(wd >> 8) * w.V[wd & 0xffu];  // kinetics.py:759
-          w.nvs[e] = nv;
-          float neg = -nv;
-          neg = neg < 0.0f ? 0.0f : neg;
-          d = d + neg;
-        }
-        float f = w.X0[i] / d;
-        if (f > 1.0f) f = 1.0f;
-        w.Fsig[i] = f;
+    // ---- substrate trimming (kinetics.py:861-879)
+    for (int i = lane; i < s; i += 32) {
+      const unsigned c0 = w.colptr[i], c1 = w.colptr[i + 1];
+      float d = 0.0f;
+      for (unsigned e = c0; e < c1; e++) {
+        const unsigned wd = w.csc[e];
+        const float nv = (float)((int)wd >> 8) * w.V[wd & 0xffu];  // kinetics.py:759
+        w.nvs[e] = nv;
+        float neg = -nv;
+        neg = neg < 0.0f ? 0.0f : neg;
+        d = d + neg;
       }
-    }
-    __syncwarp();
-    // per protein: the most limiting substrate
-    for (int t = lane; t < n_act; t += 32) {
-      const int j = (int)w.act[t];
-      const float v = w.V[j];
-      float fm = 1.0f;
-      for (unsigned e = w.rowptr[j] & 0xffffu; e < (w.rowptr[j + 1] & 0xffffu); e++) {
-        const unsigned wd = w.cat[e];
-        const int n = (int)(int8_t)(wd >> 24);
-        const bool removes = n > 0 ? (v < 0.0f) : (n < 0 ? (v > 0.0f) : false);
-        if (removes) fm = nanmin(fm, w.Fsig[wd & 0xffu]);
-      }
-      w.Fmin[j] = fm;
-      w.F[j] = 1.0f;
+      float f = w.X0[i] / d;
+      if (f > 1.0f) f = 1.0f;
+      const unsigned key = fkey(f);
+      for (unsigned e = c0; e < c1; e++)  // every protein that removes signal i is limited by F_i
+        if (w.nvs[e] < 0.0f) atomicMin(&w.FminKey[w.csc[e] & 0xffu], key);
     }
     __syncwarp();
     // X1 = max(X0 + sum_j NV'_ji, 0)   (kinetics.py:763-764)
-#pragma unroll
-    for (int t = 0; t < ST; t++) {
-      const int i = lane + 32 * t;
-      if (i < s) {
-        float acc = 0.0f;
-        for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++) {
-          const float nvp = w.nvs[e] * w.Fmin[w.csc[e] & 0xffu];
-          w.nvs[e] = nvp;
-          acc = acc + nvp;
-        }
-        float x = clamp0(w.X0[i] + acc);
-        if (poison) x = __int_as_float(0x7fc00000);
-        w.X1[i] = x;
+    for (int i = lane; i < s; i += 32) {
+      float acc = 0.0f;
+      for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++) {
+        const float nvp = w.nvs[e] * fkey_decode(w.FminKey[w.csc[e] & 0xffu]);
+        w.nvs[e] = nvp;
+        acc = acc + nvp;
       }
+      float x = clamp0(w.X0[i] + acc);
+      if (poison) x = qnan;
+      w.X1[i] = x;
     }
     __syncwarp();
 
@@ -333,17 +453,11 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       unsigned mine = 0;
       for (int t = lane; t < n_act; t += 32) {
         const int j = (int)w.act[t];
-        float xf = 1.0f, xb = 1.0f;
-        bool invf = false, invb = false;
-        for (unsigned e = w.rowptr[j] & 0xffffu; e < (w.rowptr[j + 1] & 0xffffu); e++) {
-          const unsigned wd = w.cat[e];
-          const float x = w.X1[wd & 0xffu];
-          const int nf = (wd >> 8) & 0xff, nb = (wd >> 16) & 0xff;
-          if (nf) { invf = true; xf = xf * (nf == 1 ? x : powi(x, nf)); }
-          if (nb) { invb = true; xb = xb * (nb == 1 ? x : powi(x, nb)); }
-        }
-        xf = invf ? fix_product(xf) : 0.0f;
-        xb = invb ? fix_product(xb) : 0.0f;
+        float xf, xb;
+        bool invf, invb;
+        list_products(w, w.X1, j, xf, xb, invf, invb);
+        if (!invf) xf = 0.0f;
+        if (!invb) xb = 0.0f;
         const float F = w.F[j];
         const unsigned dec = eq_decide(w.V[j], quotient_from(xb, xf), w.Ke[j], F);
         if (dec & 3u) {
@@ -358,35 +472,21 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       }
       if (!any) break;  // no adjustable protein: F, X1 and every later iteration are unchanged
       __syncwarp();
-#pragma unroll
-      for (int t = 0; t < ST; t++) {
-        const int i = lane + 32 * t;
-        if (i < s) {
-          float acc = 0.0f;
-          for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++)
-            acc = acc + w.nvs[e] * w.F[w.csc[e] & 0xffu];
-          float x = clamp0(w.X0[i] + acc);
-          if (poison) x = __int_as_float(0x7fc00000);
-          w.X1[i] = x;
-        }
+      for (int i = lane; i < s; i += 32) {
+        float acc = 0.0f;
+        for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++)
+          acc = acc + w.nvs[e] * w.F[w.csc[e] & 0xffu];
+        float x = clamp0(w.X0[i] + acc);
+        if (poison) x = qnan;
+        w.X1[i] = x;
       }
       __syncwarp();
     }
 
-    if (a.V_out) {
-      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = 0.0f;
-      __syncwarp();
-      for (int t = lane; t < n_act; t += 32) {
-        const int j = (int)w.act[t];
-        a.V_out[cell * (long long)p + j] = w.V[j];
-      }
-    }
+    if (a.V_out)
+      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = w.V[j];
     // next part starts from this part's result
-#pragma unroll
-    for (int t = 0; t < ST; t++) {
-      const int i = lane + 32 * t;
-      if (i < s) w.X0[i] = w.X1[i];
-    }
+    for (int i = lane; i < s; i += 32) w.X0[i] = w.X1[i];
     __syncwarp();
   }
 }
@@ -509,7 +609,7 @@ __device__ void run_dense(const KinArgs &a, float *X0, float *X1, float *Fsig, f
   }
 }
 
-template <int ST>
+template <int VEC>
 __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, float *dense_scratch) {
   extern __shared__ __align__(16) unsigned smem[];
   __shared__ unsigned sflags[MS_N_FLAGS];
@@ -545,11 +645,11 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, f
     int n_act = 0;
     WarpMem w;
     if (a.sparse_enabled) {
-      w = carve(wbase, p, s, a.e_cat, a.e_reg);
-      sparse = scan_cell<ST>(a, w, cell, lane, n_act);
+      w = carve(wbase, p, s, a.e_sub, a.e_nnz, a.e_reg);
+      sparse = scan_cell<VEC>(a, w, cell, lane, n_act);
     }
     if (sparse) {
-      run_sparse<ST>(a, w, cell, lane, n_act, sflags);
+      run_sparse(a, w, cell, lane, n_act, sflags);
     } else if (a.tier == 1 && a.defer_enabled) {
       if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
       continue;  // integrated by the tier-2 launch
@@ -679,7 +779,7 @@ __global__ void fill_kernel(float *x, long long n, float v) {
 // host side
 // ---------------------------------------------------------------------------
 struct LaunchPlan {
-  int e_cat, e_reg, words_per_warp, st, sparse_enabled, grid, warps_per_cta;
+  int e_sub, e_nnz, e_reg, words_per_warp, sparse_enabled, grid, warps_per_cta;
   size_t smem_bytes;
 };
 
@@ -695,45 +795,51 @@ static int sm_count() {
   return g_sm_count;
 }
 
-constexpr size_t SMEM_PER_SM = 220 * 1024;   // usable per SM (227 KB max per CTA on sm_100a)
+constexpr size_t SMEM_PER_SM = 222 * 1024;   // usable per SM (227 KB max per CTA on sm_100a)
 constexpr size_t SMEM_PER_CTA_MAX = 200 * 1024;
 
-// tier 1: lists for a typical proteome (4 entries per protein row on average)
-static LaunchPlan plan_tier1(int64_t p, int64_t s) {
-  LaunchPlan pl = {};
-  pl.sparse_enabled = (p <= 256 && s <= 32 * MAX_ST) ? 1 : 0;
-  pl.st = s <= 32 ? 1 : (s <= 64 ? 2 : 4);
-  int e_cat = (int)(4 * p < 64 ? 64 : 4 * p);
-  if (e_cat > (int)(p * s)) e_cat = (int)(p * s);
-  pl.e_cat = round32(e_cat);
-  int e_reg = (int)(p < 32 ? 32 : p);
-  if (e_reg > (int)(p * s)) e_reg = (int)(p * s);
-  pl.e_reg = round32(e_reg);
-  pl.warps_per_cta = WARPS_PER_CTA;
-  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_cat, pl.e_reg);
-  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
-  if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
-    pl.sparse_enabled = 0;
-    pl.e_cat = pl.e_reg = 0;
-    pl.words_per_warp = 3 * round32((int)s);
-    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
-  }
+static bool sparse_possible(int64_t p, int64_t s) { return p >= 1 && p <= 256 && s >= 1 && s <= MAX_S_SPARSE; }
+
+static void finish_plan(LaunchPlan &pl) {
   size_t per_sm = SMEM_PER_SM / (pl.smem_bytes + 1024);
   if (per_sm > 4) per_sm = 4;
   if (per_sm < 1) per_sm = 1;
   pl.grid = sm_count() * (int)per_sm;
+}
+
+// tier 1: lists for a typical proteome (2-6 non-zeros per protein row)
+static LaunchPlan plan_tier1(int64_t p, int64_t s) {
+  LaunchPlan pl = {};
+  pl.sparse_enabled = sparse_possible(p, s) ? 1 : 0;
+  const int full = (int)(p * s);
+  int e_sub = (int)((5 * p + 1) / 2), e_nnz = (int)((7 * p + 1) / 2), e_reg = (int)p;
+  if (e_sub < 32) e_sub = 32;
+  if (e_nnz < 32) e_nnz = 32;
+  if (e_reg < 32) e_reg = 32;
+  pl.e_sub = round32(e_sub < full ? e_sub : full);
+  pl.e_nnz = round32(e_nnz < full ? e_nnz : full);
+  pl.e_reg = round32(e_reg < full ? e_reg : full);
+  pl.warps_per_cta = WARPS_PER_CTA;
+  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_sub, pl.e_nnz, pl.e_reg);
+  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
+  if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
+    pl.sparse_enabled = 0;
+    pl.e_sub = pl.e_nnz = pl.e_reg = 0;
+    pl.words_per_warp = 3 * round32((int)s);
+    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
+  }
+  finish_plan(pl);
   return pl;
 }
 
 // tier 2: lists that hold a completely dense tile; as many warps per CTA as fit
 static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
   pl = {};
-  if (!(p <= 256 && s <= 32 * MAX_ST)) return false;
+  if (!sparse_possible(p, s)) return false;
   pl.sparse_enabled = 1;
-  pl.st = s <= 32 ? 1 : (s <= 64 ? 2 : 4);
-  pl.e_cat = round32((int)(p * s));
-  pl.e_reg = round32((int)(p * s));
-  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_cat, pl.e_reg);
+  pl.e_sub = pl.e_nnz = pl.e_reg = round32((int)(p * s));
+  if (pl.e_sub > 0xffff) return false;  // 16-bit list offsets
+  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_sub, pl.e_nnz, pl.e_reg);
   const size_t per_warp = (size_t)pl.words_per_warp * 4;
   if (per_warp > SMEM_PER_CTA_MAX) return false;
   int w = (int)((SMEM_PER_SM / 2) / per_warp);
@@ -741,10 +847,7 @@ static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
   if (w > WARPS_PER_CTA) w = WARPS_PER_CTA;
   pl.warps_per_cta = w;
   pl.smem_bytes = per_warp * w;
-  size_t per_sm = SMEM_PER_SM / (pl.smem_bytes + 1024);
-  if (per_sm > 4) per_sm = 4;
-  if (per_sm < 1) per_sm = 1;
-  pl.grid = sm_count() * (int)per_sm;
+  finish_plan(pl);
   return true;
 }
 
@@ -768,17 +871,26 @@ extern "C" size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s) {
 template <typename K>
 static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
   MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
-  a.e_cat = pl.e_cat; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
+  a.e_sub = pl.e_sub; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
   a.sparse_enabled = pl.sparse_enabled;
   kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
 
+// widest vector load the tile geometry and the pointers allow
+static int pick_vec(const KinArgs &a) {
+  const uintptr_t bits = (uintptr_t)a.N | (uintptr_t)a.Nf | (uintptr_t)a.Nb | (uintptr_t)a.A;
+  if (a.s % 4 == 0 && (bits & 15) == 0) return 4;
+  if (a.s % 2 == 0 && (bits & 7) == 0) return 2;
+  return 1;
+}
+
 static int launch_plan(const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
-  if (pl.st == 1) return launch_one(kinetics_fused_kernel<1>, pl, a, dense, st);
-  if (pl.st == 2) return launch_one(kinetics_fused_kernel<2>, pl, a, dense, st);
-  return launch_one(kinetics_fused_kernel<4>, pl, a, dense, st);
+  const int vec = pick_vec(a);
+  if (vec == 4) return launch_one(kinetics_fused_kernel<4>, pl, a, dense, st);
+  if (vec == 2) return launch_one(kinetics_fused_kernel<2>, pl, a, dense, st);
+  return launch_one(kinetics_fused_kernel<1>, pl, a, dense, st);
 }
 
 static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, size_t scratch_bytes,
@@ -796,7 +908,7 @@ static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, 
   a.defer_list = a.defer_count + 64;
 
   LaunchPlan p1 = plan_tier1(P->p, P->s), p2;
-  const bool two_tiers = p1.sparse_enabled && plan_tier2(P->p, P->s, p2) && p2.e_cat > p1.e_cat;
+  const bool two_tiers = p1.sparse_enabled && plan_tier2(P->p, P->s, p2) && p2.e_nnz > p1.e_nnz;
   const int64_t ctas_needed = ceil_div(P->c, p1.warps_per_cta);
   if (p1.grid > ctas_needed) p1.grid = (int)ctas_needed;
   a.tier = 1;

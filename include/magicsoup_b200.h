@@ -163,6 +163,24 @@ int ms_diffuse_molecules(float *molecule_map, const float *a, const float *b, in
 size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W);
 
 /*
+ * The two passes of ms_diffuse_molecules for a ROW SLAB of a map that is split over
+ * several GPUs (no counterpart in the single-device reference; same arithmetic as
+ * world.py:638-649 on the whole map).
+ * ms_diffuse_stencil: stencil of the slab (m,H,W) into `out` (m,H,W); the rows above
+ *   row 0 and below row H-1 come from halo_top / halo_bottom (m,W) (the neighbouring
+ *   slabs' edge rows; NULL = wrap around inside the slab); sums (4*m int64, zeroed by
+ *   the call) receive the slab's exact plane sums before/after as 2^-32 fixed point
+ *   {hi_before, lo_before, hi_after, lo_after}: add them over all slabs (integers, so
+ *   the order does not matter) before the second pass.
+ * ms_diffuse_correct: map_slab = clamp(out + (sum_before - sum_after)/n_pxls_total, 0).
+ */
+int ms_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
+                       const float *a, const float *b, int64_t m, int64_t H, int64_t W, float *out,
+                       int64_t *sums, void *stream);
+int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, int64_t m, int64_t H,
+                       int64_t W, int64_t n_pxls_total, void *stream);
+
+/*
  * World.diffuse_molecules(), permeation half                   world.py:651-665
  * perm[k] from World._get_permeate (world.py:935-946).  cell_molecules_out may
  * alias cell_molecules_in; molecule_map is updated at the cells' pixels.

@@ -44,6 +44,8 @@ _SIGNATURES = {
     "ms_scatter_signals": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "ms_diffuse_molecules": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _sz, _vp]),
     "ms_diffuse_scratch_bytes": (_sz, [_i64, _i64, _i64]),
+    "ms_diffuse_stencil": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "ms_diffuse_correct": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
     "ms_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
 }
 

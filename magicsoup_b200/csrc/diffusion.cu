@@ -60,8 +60,19 @@ __device__ void block_commit_sums(FixSum in, FixSum out, unsigned long long *sum
   }
 }
 
+// Row `gx` of plane k of a slab: rows -1 and H come from the neighbours' halo rows
+// (m,W) when given (multi-GPU row slabs), else they wrap around inside the plane.
+__device__ __forceinline__ const float *slab_row(const float *plane, const float *halo_top,
+                                                 const float *halo_bot, int k, int gx, int H, int W) {
+  if (gx < 0) return halo_top ? halo_top + (size_t)k * W : plane + (size_t)(H - 1) * W;
+  if (gx >= H) return halo_bot ? halo_bot + (size_t)k * W : plane;
+  return plane + (size_t)gx * W;
+}
+
 // fast path: W % 128 == 0, H % 32 == 0.  grid = (W/TW, H/TH, m)
 __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__restrict__ map,
+                                                                 const float *__restrict__ halo_top,
+                                                                 const float *__restrict__ halo_bot,
                                                                  float *__restrict__ out,
                                                                  const float *__restrict__ wa,
                                                                  const float *__restrict__ wb, int H,
@@ -75,19 +86,17 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
 
   // interior columns of rows -1..TH: one float4 per lane per row
   for (int r = warp; r < TH + 2; r += DTHREADS / 32) {
-    int gx = x0 + r - 1;
-    gx = gx < 0 ? gx + H : (gx >= H ? gx - H : gx);
-    const float4 v = *reinterpret_cast<const float4 *>(plane + (size_t)gx * W + y0 + 4 * lane);
+    const float *src = slab_row(plane, halo_top, halo_bot, k, x0 + r - 1, H, W);
+    const float4 v = *reinterpret_cast<const float4 *>(src + y0 + 4 * lane);
     *reinterpret_cast<float4 *>(&tile[r * TSTRIDE + 4 + 4 * lane]) = v;
   }
   // halo columns -1 and TW
   for (int t = threadIdx.x; t < 2 * (TH + 2); t += DTHREADS) {
     const int r = t >> 1, side = t & 1;
-    int gx = x0 + r - 1;
-    gx = gx < 0 ? gx + H : (gx >= H ? gx - H : gx);
+    const float *src = slab_row(plane, halo_top, halo_bot, k, x0 + r - 1, H, W);
     int gy = side ? y0 + TW : y0 - 1;
     gy = gy < 0 ? gy + W : (gy >= W ? gy - W : gy);
-    tile[r * TSTRIDE + (side ? 4 + TW : 3)] = plane[(size_t)gx * W + gy];
+    tile[r * TSTRIDE + (side ? 4 + TW : 3)] = src[gy];
   }
   __syncthreads();
 
@@ -126,6 +135,8 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
 
 // generic path: any H, W (e.g. the 5x5 map of the reference's test).  grid = (blocks, 1, m)
 __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *__restrict__ map,
+                                                                   const float *__restrict__ halo_top,
+                                                                   const float *__restrict__ halo_bot,
                                                                    float *__restrict__ out,
                                                                    const float *__restrict__ wa,
                                                                    const float *__restrict__ wb, int H,
@@ -139,9 +150,10 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n;
        t += (long long)gridDim.x * blockDim.x) {
     const int x = (int)(t / W), y = (int)(t % W);
-    const int xm = x == 0 ? H - 1 : x - 1, xp = x == H - 1 ? 0 : x + 1;
     const int ym = y == 0 ? W - 1 : y - 1, yp = y == W - 1 ? 0 : y + 1;
-    const float *rm = plane + (size_t)xm * W, *r0 = plane + (size_t)x * W, *rp = plane + (size_t)xp * W;
+    const float *rm = slab_row(plane, halo_top, halo_bot, k, x - 1, H, W);
+    const float *r0 = plane + (size_t)x * W;
+    const float *rp = slab_row(plane, halo_top, halo_bot, k, x + 1, H, W);
     const float c = r0[y];
     const float o = stencil_point(rm[ym], rm[y], rm[yp], r0[ym], c, r0[yp], rp[ym], rp[y], rp[yp], a, b);
     oplane[t] = o;
@@ -154,12 +166,13 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
 // pass 2: world.py:648-649.  grid = (blocks, 1, m)
 __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restrict__ out,
                                                            float *__restrict__ map, long long n_pxls,
+                                                           long long n_pxls_total,
                                                            const unsigned long long *sums) {
   const int k = blockIdx.z;
   const long long *sk = reinterpret_cast<const long long *>(sums) + 4 * k;
   const float s0 = (float)((double)sk[0] + (double)sk[1] * 2.3283064365386963e-10);
   const float s1 = (float)((double)sk[2] + (double)sk[3] * 2.3283064365386963e-10);
-  const float corr = (s0 - s1) / (float)n_pxls;
+  const float corr = (s0 - s1) / (float)n_pxls_total;
   const float *src = out + (size_t)k * n_pxls;
   float *dst = map + (size_t)k * n_pxls;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -221,41 +234,71 @@ extern "C" size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W) {
   return align256((size_t)m * H * W * sizeof(float)) + align256((size_t)m * 4 * sizeof(long long));
 }
 
-// shared by ms_diffuse_molecules and the no-scratch-argument variants
-int ms_diffuse_launch_(float *molecule_map, const float *a, const float *b, int64_t m, int64_t H,
-                       int64_t W, float *tmp, unsigned long long *sums, cudaStream_t st) {
+static int stencil_launch(const float *map, const float *halo_top, const float *halo_bot,
+                          const float *a, const float *b, int64_t m, int64_t H, int64_t W, float *tmp,
+                          unsigned long long *sums, cudaStream_t st) {
   MS_CUDA_CHECK(cudaMemsetAsync(sums, 0, (size_t)m * 4 * sizeof(long long), st));
   const long long n = (long long)H * W;
   if (W % TW == 0 && H % TH == 0) {
     dim3 grid((unsigned)(W / TW), (unsigned)(H / TH), (unsigned)m);
-    stencil_tiled_kernel<<<grid, DTHREADS, 0, st>>>(molecule_map, tmp, a, b, (int)H, (int)W, sums);
+    stencil_tiled_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums);
   } else {
     unsigned blocks = (unsigned)((n + DTHREADS - 1) / DTHREADS);
     if (blocks > 1024) blocks = 1024;
     dim3 grid(blocks, 1, (unsigned)m);
-    stencil_generic_kernel<<<grid, DTHREADS, 0, st>>>(molecule_map, tmp, a, b, (int)H, (int)W, sums);
+    stencil_generic_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums);
   }
   MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+static int correct_launch(const float *tmp, float *map, int64_t m, int64_t H, int64_t W,
+                          long long n_pxls_total, const unsigned long long *sums, cudaStream_t st) {
+  const long long n = (long long)H * W;
   long long work = (n & 3) == 0 ? n / 4 : n;
   unsigned blocks = (unsigned)((work + DTHREADS - 1) / DTHREADS);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, molecule_map, n, sums);
+  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, map, n, n_pxls_total, sums);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
+}
+
+static bool bad_map(int64_t m, int64_t H, int64_t W) {
+  return m < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX || m > 65535;
 }
 
 extern "C" int ms_diffuse_molecules(float *molecule_map, const float *a, const float *b, int64_t m,
                                     int64_t H, int64_t W, void *scratch, size_t scratch_bytes,
                                     void *stream) {
-  if (m < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX || m > 65535)
-    return MS_ERR_INVALID_ARGUMENT;
+  if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
   if (m == 0) return MS_OK;
   if (!molecule_map || !a || !b) return MS_ERR_INVALID_ARGUMENT;
   if (!scratch || scratch_bytes < ms_diffuse_scratch_bytes(m, H, W)) return MS_ERR_SCRATCH_TOO_SMALL;
   float *tmp = (float *)scratch;
   unsigned long long *sums =
       (unsigned long long *)((char *)scratch + align256((size_t)m * H * W * sizeof(float)));
-  return ms_diffuse_launch_(molecule_map, a, b, m, H, W, tmp, sums, (cudaStream_t)stream);
+  int rc = stencil_launch(molecule_map, nullptr, nullptr, a, b, m, H, W, tmp, sums, (cudaStream_t)stream);
+  if (rc != MS_OK) return rc;
+  return correct_launch(tmp, molecule_map, m, H, W, (long long)H * W, sums, (cudaStream_t)stream);
+}
+
+extern "C" int ms_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
+                                  const float *a, const float *b, int64_t m, int64_t H, int64_t W,
+                                  float *out, int64_t *sums, void *stream) {
+  if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!map_slab || !a || !b || !out || !sums || out == map_slab) return MS_ERR_INVALID_ARGUMENT;
+  return stencil_launch(map_slab, halo_top, halo_bottom, a, b, m, H, W, out, (unsigned long long *)sums,
+                        (cudaStream_t)stream);
+}
+
+extern "C" int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, int64_t m,
+                                  int64_t H, int64_t W, int64_t n_pxls_total, void *stream) {
+  if (bad_map(m, H, W) || n_pxls_total <= 0) return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!out || !map_slab || !sums) return MS_ERR_INVALID_ARGUMENT;
+  return correct_launch(out, map_slab, m, H, W, n_pxls_total, (const unsigned long long *)sums,
+                        (cudaStream_t)stream);
 }
 
 extern "C" int ms_permeate(const float *cell_molecules_in, float *cell_molecules_out,

@@ -39,7 +39,7 @@ struct KinArgs {
   float trims[3];
   const float *adj_vmax;  // (c,p) when n_parts == 1
   float *V_out;           // optional (c,p), n_parts == 1 only
-  int e_sub, e_nnz, e_reg;  // list capacities (entries)
+  int e_ent, e_nnz, e_reg;  // list capacities (entries)
   int words_per_warp;     // shared memory words per warp
   int sparse_enabled;     // 0 forces the dense path (p > 256 or s > 128)
   // Two tiers.  Tier 1 (small lists, 32 warps/SM) defers cells whose tile does not fit to
@@ -51,52 +51,57 @@ struct KinArgs {
   int *defer_list;        // device list of deferred cell indices (capacity c)
 };
 
-// per-warp shared memory carve-up (32-bit words)
+// per-warp shared memory carve-up (32-bit words).  Only the base pointer and a few word
+// offsets are kept in registers; the arrays are addressed as base + offset.
 struct WarpMem {
-  float *X0, *X1, *Fsig;         // s32 each (Fsig doubles as the counting-sort cursor in the scan)
-  unsigned *colptr;              // s32 + 4
-  float *V, *F;                  // p32 each
-  unsigned *FminKey;             // p32: order-preserving key of F_min (atomicMin target)
-  float *Ke, *Kmf, *Kmb, *Vmax;  // p32 each
-  unsigned *act;                 // p32: proteins that have substrate or product entries
-  unsigned *rowA, *rowB;         // p32 + 4 each: rowA = sub offset | prd offset << 16, rowB = reg offset
-  unsigned *sub, *prd;           // e_sub each: signal | exponent << 8, per protein, ascending signal
-  unsigned *csc;                 // e_nnz: protein | N << 8, per signal, ascending protein
-  float *nvs;                    // e_nnz: rate per csc entry (holds the unsorted N list during the scan)
-  unsigned *reg;                 // e_reg: signal | (A & 0xff) << 8 | protein << 16
-  float *regk;                   // e_reg: Kmr of that entry
+  unsigned *b;
+  int s32, p32, o_ent, o_nvs, o_csc, o_reg, o_regk;
+  // s32 each (Fsig doubles as the counting-sort cursor in the scan)
+  __device__ __forceinline__ float *X0() const { return (float *)b; }
+  __device__ __forceinline__ float *X1() const { return (float *)(b + s32); }
+  __device__ __forceinline__ float *Fsig() const { return (float *)(b + 2 * s32); }
+  __device__ __forceinline__ unsigned *colptr() const { return b + 3 * s32; }  // s32 + 4
+  // p32 each
+  __device__ __forceinline__ float *V() const { return (float *)(b + 4 * s32 + 4); }
+  __device__ __forceinline__ float *F() const { return (float *)(b + 4 * s32 + 4 + p32); }
+  // order-preserving key of F_min (atomicMin target)
+  __device__ __forceinline__ unsigned *FminKey() const { return b + 4 * s32 + 4 + 2 * p32; }
+  __device__ __forceinline__ float *Ke() const { return (float *)(b + 4 * s32 + 4 + 3 * p32); }
+  __device__ __forceinline__ float *Kmf() const { return (float *)(b + 4 * s32 + 4 + 4 * p32); }
+  __device__ __forceinline__ float *Kmb() const { return (float *)(b + 4 * s32 + 4 + 5 * p32); }
+  __device__ __forceinline__ float *Vmax() const { return (float *)(b + 4 * s32 + 4 + 6 * p32); }
+  // proteins that have substrate or product entries
+  __device__ __forceinline__ unsigned *act() const { return b + 4 * s32 + 4 + 7 * p32; }
+  // p32 + 4: ent offset | reg offset << 16
+  __device__ __forceinline__ unsigned *rowptr() const { return b + 4 * s32 + 4 + 8 * p32; }
+  // e_ent: signal | exponent << 8 | (1 << 31 if product side), per protein, ascending signal
+  __device__ __forceinline__ unsigned *ent() const { return b + o_ent; }
+  // e_nnz: rate per csc entry (nvs + csc hold the element queue during the scan)
+  __device__ __forceinline__ float *nvs() const { return (float *)(b + o_nvs); }
+  // e_nnz: protein | N << 8, per signal, ascending protein
+  __device__ __forceinline__ unsigned *csc() const { return b + o_csc; }
+  // e_reg: signal | (A & 0xff) << 8 | protein << 16 ; Kmr of that entry
+  __device__ __forceinline__ unsigned *reg() const { return b + o_reg; }
+  __device__ __forceinline__ float *regk() const { return (float *)(b + o_regk); }
 };
 
 __host__ __device__ inline int round32(int x) { return (x + 31) & ~31; }
 
-__host__ __device__ inline int warp_words(int p, int s, int e_sub, int e_nnz, int e_reg) {
+__host__ __device__ inline int warp_words(int p, int s, int e_ent, int e_nnz, int e_reg) {
   const int s32 = round32(s), p32 = round32(p);
-  return 3 * s32 + (s32 + 4) + 8 * p32 + 2 * (p32 + 4) + 2 * e_sub + 2 * e_nnz + 2 * e_reg;
+  return 3 * s32 + (s32 + 4) + 8 * p32 + (p32 + 4) + e_ent + 2 * e_nnz + 2 * e_reg;
 }
 
-__device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_sub, int e_nnz, int e_reg) {
-  const int s32 = round32(s), p32 = round32(p);
+__device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_ent, int e_nnz, int e_reg) {
   WarpMem m;
-  m.X0 = (float *)w;            w += s32;
-  m.X1 = (float *)w;            w += s32;
-  m.Fsig = (float *)w;          w += s32;
-  m.colptr = w;                 w += s32 + 4;
-  m.V = (float *)w;             w += p32;
-  m.F = (float *)w;             w += p32;
-  m.FminKey = w;                w += p32;
-  m.Ke = (float *)w;            w += p32;
-  m.Kmf = (float *)w;           w += p32;
-  m.Kmb = (float *)w;           w += p32;
-  m.Vmax = (float *)w;          w += p32;
-  m.act = w;                    w += p32;
-  m.rowA = w;                   w += p32 + 4;
-  m.rowB = w;                   w += p32 + 4;
-  m.sub = w;                    w += e_sub;
-  m.prd = w;                    w += e_sub;
-  m.csc = w;                    w += e_nnz;
-  m.nvs = (float *)w;           w += e_nnz;
-  m.reg = w;                    w += e_reg;
-  m.regk = (float *)w;
+  m.b = w;
+  m.s32 = round32(s);
+  m.p32 = round32(p);
+  m.o_ent = 4 * m.s32 + 4 + 9 * m.p32 + 4;
+  m.o_nvs = m.o_ent + e_ent;
+  m.o_csc = m.o_nvs + e_nnz;
+  m.o_reg = m.o_csc + e_nnz;
+  m.o_regk = m.o_reg + e_reg;
   return m;
 }
 
@@ -113,18 +118,23 @@ __device__ __forceinline__ float fkey_decode(unsigned k) {
 }
 constexpr unsigned KEY_ONE = 0xbf800000u;  // fkey(1.0f)
 
+// exponents >= 4 are rare: keep their loop out of the hot instruction stream
+__device__ __noinline__ float pow_tail(float r, float b, unsigned n) {
+  while (n) {
+    b = b * b;
+    if (n & 1u) r = r * b;
+    n >>= 1;
+  }
+  return r;
+}
+
 // x^k for a list entry, k >= 1; same multiplication order as powi()
 __device__ __forceinline__ float pow_entry(float x, unsigned k) {
   float r = (k & 1u) ? x : 1.0f;
   if (k > 1u) {
-    float b = x * x;
+    const float b = x * x;
     if (k & 2u) r = r * b;
-    unsigned n = k >> 2;
-    while (n) {
-      b = b * b;
-      if (n & 1u) r = r * b;
-      n >>= 1;
-    }
+    if (k > 3u) r = pow_tail(r, b, k >> 2);
   }
   return r;
 }
@@ -148,151 +158,139 @@ __device__ __forceinline__ void load_vec(const int *ptr, bool ok, int (&v)[VEC])
 }
 
 // ---------------------------------------------------------------------------
-// scan: stream the cell's dense tile once (32*VEC consecutive elements per load
-// instruction, row-major) and compress it into the sparse lists.  Elements are visited
-// in row-major order, so every per-protein list comes out in ascending signal order;
-// the per-signal lists are produced from the row-major N list by a stable counting sort
-// (warp match), i.e. in ascending protein order.  No atomics, no sorting networks.
-// Returns false if the tile does not fit the lists or the packing.
+// scan, phase 1: stream the cell's dense tile once (32*VEC consecutive elements per load
+// instruction, row-major) and push every element with a non-zero Nf, Nb, N or A onto a
+// queue in shared memory (2 words per element), in row-major order.
+// Returns the queue length, or -1 if the tile does not fit the queue / the packing.
 // ---------------------------------------------------------------------------
 template <int VEC>
-__device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, int lane, int &n_act_out) {
-  const int p = a.p, s = a.s, total = p * s;
-  const long long tile = cell * (long long)total;
+__device__ int scan_tile(const KinArgs &a, unsigned *queue, int cap, long long tile, int lane) {
+  const int s = a.s, total = a.p * s;
   const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
   const unsigned lt = (1u << lane) - 1u;
-  unsigned *tmp = (unsigned *)w.nvs;
   constexpr int STEP = 32 * VEC;
   const int drow = STEP / s, dsig = STEP - drow * s;
-
   int q0 = lane * VEC;
   int row = q0 / s, sig0 = q0 - row * s;
-  int sub_tot = 0, prd_tot = 0, nnz_tot = 0, reg_tot = 0;
-  int chk = 0;
-
-  constexpr int U = VEC == 4 ? 1 : (VEC == 2 ? 2 : 4);  // iterations of loads in flight per lane
-  int nf[U][VEC], nb[U][VEC], nn[U][VEC], na[U][VEC];
-  for (int base = 0; base < total; base += U * STEP) {
+  int nq = 0, chk = 0;
+#pragma unroll 1
+  for (int base = 0; base < total; base += STEP) {
+    const bool ok = q0 < total;
+    int nf[VEC], nb[VEC], nn[VEC], na[VEC];
+    load_vec<VEC>(gNf + q0, ok, nf);
+    load_vec<VEC>(gNb + q0, ok, nb);
+    load_vec<VEC>(gN + q0, ok, nn);
+    load_vec<VEC>(gA + q0, ok, na);
+    unsigned mask = 0;
 #pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int q = q0 + u * STEP;
-      const bool ok = q < total;
-      load_vec<VEC>(gNf + q, ok, nf[u]);
-      load_vec<VEC>(gNb + q, ok, nb[u]);
-      load_vec<VEC>(gN + q, ok, nn[u]);
-      load_vec<VEC>(gA + q, ok, na[u]);
-    }
+    for (int e = 0; e < VEC; e++) mask |= ((nf[e] | nb[e] | nn[e] | na[e]) != 0 ? 1u : 0u) << e;
+    if (__ballot_sync(FULL, mask != 0) != 0) {
+      int pos = nq;
 #pragma unroll
-    for (int u = 0; u < U; u++) {
-      if (base + u * STEP < total) {
-        const bool ok = q0 < total;
-        unsigned msub = 0, mprd = 0, mnnz = 0, mreg = 0;
+      for (int e = 0; e < VEC; e++) {
+        const unsigned be = __ballot_sync(FULL, (mask >> e) & 1u);
+        pos += __popc(be & lt);
+        nq += __popc(be);
+      }
 #pragma unroll
-        for (int e = 0; e < VEC; e++) {
-          msub |= (nf[u][e] != 0 ? 1u : 0u) << e;
-          mprd |= (nb[u][e] != 0 ? 1u : 0u) << e;
-          mnnz |= (nn[u][e] != 0 ? 1u : 0u) << e;
-          mreg |= (na[u][e] != 0 ? 1u : 0u) << e;
+      for (int e = 0; e < VEC; e++) {
+        if ((mask >> e) & 1u) {
+          // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
+          chk |= ((nf[e] | nb[e]) & 0xffffff00) | ((nn[e] + 32768) & 0xffff0000) |
+                 ((na[e] + 128) & 0xffffff00);
+          if (pos < cap) {
+            queue[2 * pos] = (unsigned)(sig0 + e) | ((unsigned)row << 8) | ((unsigned)(na[e] & 0xff) << 16);
+            queue[2 * pos + 1] = ((unsigned)nf[e] & 0xffu) | (((unsigned)nb[e] & 0xffu) << 8) |
+                                 ((unsigned)nn[e] << 16);
+          }
+          pos++;
         }
-        const unsigned many = msub | mprd | mnnz | mreg;
-        int psub = sub_tot, pprd = prd_tot, pnnz = nnz_tot, preg = reg_tot;
-        if (__ballot_sync(FULL, many != 0) != 0) {
-          // exclusive prefix of the three list counts in one packed shuffle scan
-          const unsigned pk = __popc(msub) | (__popc(mprd) << 10) | (__popc(mnnz) << 20);
-          unsigned incl = pk;
-#pragma unroll
-          for (int d = 1; d < 32; d <<= 1) {
-            const unsigned y = __shfl_up_sync(FULL, incl, d);
-            if (lane >= d) incl += y;
-          }
-          const unsigned excl = incl - pk;
-          const unsigned tot = __shfl_sync(FULL, incl, 31);
-          psub += (int)(excl & 0x3ffu);
-          pprd += (int)((excl >> 10) & 0x3ffu);
-          pnnz += (int)(excl >> 20);
-          sub_tot += (int)(tot & 0x3ffu);
-          prd_tot += (int)((tot >> 10) & 0x3ffu);
-          nnz_tot += (int)(tot >> 20);
-          const unsigned breg = __ballot_sync(FULL, mreg != 0);
-          if (breg) {  // regulatory entries are rare: only then a second scan
-            unsigned ri = __popc(mreg);
-            const unsigned rown = ri;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-              const unsigned y = __shfl_up_sync(FULL, ri, d);
-              if (lane >= d) ri += y;
-            }
-            preg += (int)(ri - rown);
-            reg_tot += (int)__shfl_sync(FULL, ri, 31);
-          }
-          if (ok && sig0 == 0) {
-            w.rowA[row] = (unsigned)min(psub, 0xffff) | ((unsigned)min(pprd, 0xffff) << 16);
-            w.rowB[row] = (unsigned)preg;
-          }
-          if (many) {
-#pragma unroll
-            for (int e = 0; e < VEC; e++) {
-              const int sg = sig0 + e;
-              // range of the packing: exponents < 2^24 and >= 0, |N| < 2^15, |A| < 2^7
-              chk |= ((nf[u][e] | nb[u][e]) & 0xff000000) | ((nn[u][e] + 32768) & 0xffff0000) |
-                     ((na[u][e] + 128) & 0xffffff00);
-              if ((msub >> e) & 1u) {
-                if (psub < a.e_sub) w.sub[psub] = (unsigned)sg | ((unsigned)nf[u][e] << 8);
-                psub++;
-              }
-              if ((mprd >> e) & 1u) {
-                if (pprd < a.e_sub) w.prd[pprd] = (unsigned)sg | ((unsigned)nb[u][e] << 8);
-                pprd++;
-              }
-              if ((mnnz >> e) & 1u) {
-                if (pnnz < a.e_nnz)
-                  tmp[pnnz] = (unsigned)sg | ((unsigned)row << 8) | ((unsigned)nn[u][e] << 16);
-                pnnz++;
-              }
-              if ((mreg >> e) & 1u) {
-                if (preg < a.e_reg)
-                  w.reg[preg] = (unsigned)sg | ((unsigned)(na[u][e] & 0xff) << 8) | ((unsigned)row << 16);
-                preg++;
-              }
-            }
-          }
-        } else if (ok && sig0 == 0) {
-          w.rowA[row] = (unsigned)min(psub, 0xffff) | ((unsigned)min(pprd, 0xffff) << 16);
-          w.rowB[row] = (unsigned)preg;
-        }
-        q0 += STEP;
-        row += drow;
-        sig0 += dsig;
-        if (sig0 >= s) { sig0 -= s; row++; }
       }
     }
+    q0 += STEP;
+    row += drow;
+    sig0 += dsig;
+    if (sig0 >= s) { sig0 -= s; row++; }
   }
-  if (lane == 0) {
-    w.rowA[p] = (unsigned)min(sub_tot, 0xffff) | ((unsigned)min(prd_tot, 0xffff) << 16);
-    w.rowB[p] = (unsigned)reg_tot;
+  if (__any_sync(FULL, chk != 0) || nq > cap) return -1;
+  return nq;
+}
+
+// ---------------------------------------------------------------------------
+// scan, phase 2: one lane per queued element: distribute it to the per-protein lists
+// (ent, reg) and the unsorted N list, then sort the N list by signal into csc (stable
+// counting sort via warp match, so each signal's entries stay in ascending protein
+// order).  No atomics, no sorting networks.  Returns false if a list overflows.
+// ---------------------------------------------------------------------------
+__device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, int lane, int nq,
+                            int &n_act_out) {
+  const int p = a.p, s = a.s;
+  const unsigned lt = (1u << lane) - 1u;
+  unsigned *queue = (unsigned *)w.nvs();  // nvs and csc are contiguous: 2 * e_nnz words
+  unsigned *tmp = (unsigned *)w.nvs();    // unsorted N list, written over consumed queue words
+  int ent_tot = 0, nnz_tot = 0, reg_tot = 0;
+  int prev_row = -1;
+  __syncwarp();
+#pragma unroll 1
+  for (int base = 0; base < nq; base += 32) {
+    const int k = base + lane;
+    const bool v = k < nq;
+    const unsigned w0 = v ? queue[2 * k] : 0u, w1 = v ? queue[2 * k + 1] : 0u;
+    __syncwarp();  // the whole chunk is in registers before tmp overwrites queue words
+    const unsigned sig = w0 & 0xffu;
+    const int row = v ? (int)((w0 >> 8) & 0xffu) : p;  // padding lanes close the trailing rows
+    const int av = (int)(int8_t)((w0 >> 16) & 0xffu);
+    const unsigned nf = w1 & 0xffu, nb = (w1 >> 8) & 0xffu;
+    const int n = (int)w1 >> 16;
+    const unsigned bs = __ballot_sync(FULL, nf != 0), bp = __ballot_sync(FULL, nb != 0);
+    const unsigned bn = __ballot_sync(FULL, n != 0), br = __ballot_sync(FULL, av != 0);
+    // entries of one element: substrate side first, then product side
+    int pe = ent_tot + __popc(bs & lt) + __popc(bp & lt);
+    const int pr = reg_tot + __popc(br & lt);
+    const int pn = nnz_tot + __popc(bn & lt);
+    // row pointers: the first queued element of a row also closes the empty rows before it
+    int before = __shfl_up_sync(FULL, row, 1);
+    if (lane == 0) before = prev_row;
+    if (row != before) {
+      const unsigned ptr = (unsigned)min(pe, 0xffff) | ((unsigned)min(pr, 0xffff) << 16);
+      for (int r = before + 1; r <= row; r++) w.rowptr()[r] = ptr;
+    }
+    prev_row = __shfl_sync(FULL, row, 31);
+    if (nf) {
+      if (pe < a.e_ent) w.ent()[pe] = sig | (nf << 8);
+      pe++;
+    }
+    if (nb && pe < a.e_ent) w.ent()[pe] = sig | (nb << 8) | 0x80000000u;
+    if (n != 0 && pn < a.e_nnz) tmp[pn] = sig | ((unsigned)row << 8) | ((unsigned)n << 16);
+    if (av != 0 && pr < a.e_reg) w.reg()[pr] = sig | ((unsigned)(av & 0xff) << 8) | ((unsigned)row << 16);
+    ent_tot += __popc(bs) + __popc(bp);
+    nnz_tot += __popc(bn);
+    reg_tot += __popc(br);
   }
-  if (__any_sync(FULL, chk != 0) || sub_tot > a.e_sub || prd_tot > a.e_sub || nnz_tot > a.e_nnz ||
-      reg_tot > a.e_reg) {
-    n_act_out = 0;
-    return false;
+  if (lane == 0) {  // rows after the last element when the last chunk had no padding lane
+    const unsigned ptr = (unsigned)min(ent_tot, 0xffff) | ((unsigned)min(reg_tot, 0xffff) << 16);
+    for (int r = prev_row + 1; r <= p; r++) w.rowptr()[r] = ptr;
   }
+  if (ent_tot > a.e_ent || nnz_tot > a.e_nnz || reg_tot > a.e_reg) return false;
   __syncwarp();
 
   // proteins with substrate/product entries, in ascending order
   int n_act = 0;
+#pragma unroll 1
   for (int j0 = 0; j0 < p; j0 += 32) {
     const int j = j0 + lane;
-    const bool has = j < p && w.rowA[j + 1] != w.rowA[j];
+    const bool has = j < p && (w.rowptr()[j + 1] & 0xffffu) != (w.rowptr()[j] & 0xffffu);
     const unsigned b = __ballot_sync(FULL, has);
-    if (has) w.act[n_act + __popc(b & lt)] = (unsigned)j;
+    if (has) w.act()[n_act + __popc(b & lt)] = (unsigned)j;
     n_act += __popc(b);
   }
   n_act_out = n_act;
 
   // stable counting sort of the N list by signal -> csc
-  unsigned *cursor = (unsigned *)w.Fsig;
+  unsigned *cursor = (unsigned *)w.Fsig();
   for (int i = lane; i < s; i += 32) cursor[i] = 0;
   __syncwarp();
+#pragma unroll 1
   for (int base = 0; base < nnz_tot; base += 32) {
     const int e = base + lane;
     const bool v = e < nnz_tot;
@@ -302,6 +300,7 @@ __device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, in
     __syncwarp();
   }
   unsigned carry = 0;
+#pragma unroll 1
   for (int i0 = 0; i0 < s; i0 += 32) {
     const int i = i0 + lane;
     const unsigned cnt = i < s ? cursor[i] : 0u;
@@ -312,13 +311,15 @@ __device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, in
       if (lane >= d) incl += y;
     }
     if (i < s) {
-      w.colptr[i] = carry + incl - cnt;
+      w.colptr()[i] = carry + incl - cnt;
       cursor[i] = carry + incl - cnt;
     }
     carry += __shfl_sync(FULL, incl, 31);
   }
-  if (lane == 0) w.colptr[s] = carry;
+  if (lane == 0) w.colptr()[s] = carry;
   __syncwarp();
+  // tmp (in the nvs half) is read chunk by chunk while csc (the other half) is written
+#pragma unroll 1
   for (int base = 0; base < nnz_tot; base += 32) {
     const int e = base + lane;
     const bool v = e < nnz_tot;
@@ -327,7 +328,7 @@ __device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, in
     const unsigned peers = __match_any_sync(FULL, sg);
     if (v) {
       const unsigned pos = cursor[sg] + __popc(peers & lt);
-      w.csc[pos] = ((wd >> 8) & 0xffu) | ((unsigned)((int)wd >> 16) << 8);
+      w.csc()[pos] = ((wd >> 8) & 0xffu) | ((unsigned)((int)wd >> 16) << 8);
     }
     __syncwarp();
     if (v && lane == 31 - __clz(peers)) cursor[sg] += __popc(peers);
@@ -336,37 +337,41 @@ __device__ bool scan_cell(const KinArgs &a, const WarpMem &w, long long cell, in
 
   // per-protein scalars, and the Kmr values of the (few) regulatory entries
   const long long prow = cell * (long long)p;
+  const long long tile = prow * s;
   for (int j = lane; j < p; j += 32) {
-    w.Ke[j] = __ldcs(a.Ke + prow + j);
-    w.Kmf[j] = __ldcs(a.Kmf + prow + j);
-    w.Kmb[j] = __ldcs(a.Kmb + prow + j);
-    w.Vmax[j] = a.adj_vmax ? __ldcs(a.adj_vmax + prow + j) : __ldcs(a.Vmax + prow + j);
+    w.Ke()[j] = __ldcs(a.Ke + prow + j);
+    w.Kmf()[j] = __ldcs(a.Kmf + prow + j);
+    w.Kmb()[j] = __ldcs(a.Kmb + prow + j);
+    w.Vmax()[j] = a.adj_vmax ? __ldcs(a.adj_vmax + prow + j) : __ldcs(a.Vmax + prow + j);
   }
   for (int e = lane; e < reg_tot; e += 32) {
-    const unsigned wd = w.reg[e];
-    w.regk[e] = __ldcs(a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
+    const unsigned wd = w.reg()[e];
+    w.regk()[e] = __ldcs(a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
   }
   __syncwarp();
   return true;
 }
 
-// products over a protein's substrate and product lists (kinetics.py:894-918)
+// products over a protein's substrate and product entries (kinetics.py:894-918), each side in
+// ascending signal order; bit0 / bit1 of `sides` tell which sides have entries at all
 __device__ __forceinline__ void list_products(const WarpMem &w, const float *X, int j, float &xf,
-                                              float &xb, bool &invf, bool &invb) {
-  const unsigned r0 = w.rowA[j], r1 = w.rowA[j + 1];
+                                              float &xb, unsigned &sides) {
+  const unsigned e0 = w.rowptr()[j] & 0xffffu, e1 = w.rowptr()[j + 1] & 0xffffu;
   xf = 1.0f;
   xb = 1.0f;
-  const unsigned f0 = r0 & 0xffffu, f1 = r1 & 0xffffu, b0 = r0 >> 16, b1 = r1 >> 16;
-  for (unsigned e = f0; e < f1; e++) {
-    const unsigned wd = w.sub[e];
-    xf = xf * pow_entry(X[wd & 0xffu], wd >> 8);
+  sides = 0;
+#pragma unroll 1
+  for (unsigned e = e0; e < e1; e++) {
+    const unsigned wd = w.ent()[e];
+    const float v = pow_entry(X[wd & 0xffu], (wd >> 8) & 0x7fffffu);
+    if (wd & 0x80000000u) {
+      xb = xb * v;
+      sides |= 2u;
+    } else {
+      xf = xf * v;
+      sides |= 1u;
+    }
   }
-  for (unsigned e = b0; e < b1; e++) {
-    const unsigned wd = w.prd[e];
-    xb = xb * pow_entry(X[wd & 0xffu], wd >> 8);
-  }
-  invf = f1 > f0;
-  invb = b1 > b0;
   xf = fix_product(xf);
   xb = fix_product(xb);
 }
@@ -378,91 +383,97 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
                            unsigned *sflags) {
   const int p = a.p, s = a.s;
   const float qnan = __int_as_float(0x7fc00000);
+#pragma unroll 1
   for (int q = 0; q < a.n_parts; q++) {
     const float trim = a.trims[q];
     for (int j = lane; j < p; j += 32) {
-      w.V[j] = 0.0f;  // proteins without substrate/product entries have V = 0
-      w.F[j] = 1.0f;
-      w.FminKey[j] = KEY_ONE;
+      w.V()[j] = 0.0f;  // proteins without substrate/product entries have V = 0
+      w.F()[j] = 1.0f;
+      w.FminKey()[j] = KEY_ONE;
     }
     __syncwarp();
     // ---- velocities (kinetics.py:771-806) on the active proteins
     bool poison = false;
+#pragma unroll 1
     for (int t = lane; t < n_act; t += 32) {
-      const int j = (int)w.act[t];
+      const int j = (int)w.act()[t];
       float xf, xb;
-      bool invf, invb;
-      list_products(w, w.X0, j, xf, xb, invf, invb);
-      float kf = xf / w.Kmf[j];
-      if (!invf) kf = 0.0f;
+      unsigned sides;
+      list_products(w, w.X0(), j, xf, xb, sides);
+      float kf = xf / w.Kmf()[j];
+      if (!(sides & 1u)) kf = 0.0f;
       if (isinf(kf)) kf = V_MAX;
-      float kb = xb / w.Kmb[j];
-      if (!invb) kb = 0.0f;
+      float kb = xb / w.Kmb()[j];
+      if (!(sides & 2u)) kb = 0.0f;
       if (isinf(kb)) kb = V_MAX;
       float a_reg = 1.0f;
-      for (unsigned e = w.rowB[j]; e < w.rowB[j + 1]; e++) {
-        const unsigned wd = w.reg[e];
-        a_reg = a_reg * reg_factor(w.X0[wd & 0xffu], (int)(int8_t)((wd >> 8) & 0xff), w.regk[e]);
+      for (unsigned e = w.rowptr()[j] >> 16; e < (w.rowptr()[j + 1] >> 16); e++) {
+        const unsigned wd = w.reg()[e];
+        a_reg = a_reg * reg_factor(w.X0()[wd & 0xffu], (int)(int8_t)((wd >> 8) & 0xff), w.regk()[e]);
       }
-      float vmax = w.Vmax[j];
+      float vmax = w.Vmax()[j];
       if (!a.adj_vmax) vmax = clamp0(vmax * trim);  // kinetics.py:749
       const float v = velocity_from(kf, kb, a_reg, vmax);
-      w.V[j] = v;
+      w.V()[j] = v;
       poison |= isnan(v);
     }
     poison = __any_sync(FULL, poison);  // 0 * NaN of the dense reference reaches every signal
     __syncwarp();
 
     // ---- substrate trimming (kinetics.py:861-879)
+#pragma unroll 1
     for (int i = lane; i < s; i += 32) {
-      const unsigned c0 = w.colptr[i], c1 = w.colptr[i + 1];
+      const unsigned c0 = w.colptr()[i], c1 = w.colptr()[i + 1];
       float d = 0.0f;
       for (unsigned e = c0; e < c1; e++) {
-        const unsigned wd = w.csc[e];
-        const float nv = (float)((int)wd >> 8) * w.V[wd & 0xffu];  // kinetics.py:759
-        w.nvs[e] = nv;
+        const unsigned wd = w.csc()[e];
+        const float nv = (float)((int)wd >> 8) * w.V()[wd & 0xffu];  // kinetics.py:759
+        w.nvs()[e] = nv;
         float neg = -nv;
         neg = neg < 0.0f ? 0.0f : neg;
         d = d + neg;
       }
-      float f = w.X0[i] / d;
+      float f = w.X0()[i] / d;
       if (f > 1.0f) f = 1.0f;
       const unsigned key = fkey(f);
       for (unsigned e = c0; e < c1; e++)  // every protein that removes signal i is limited by F_i
-        if (w.nvs[e] < 0.0f) atomicMin(&w.FminKey[w.csc[e] & 0xffu], key);
+        if (w.nvs()[e] < 0.0f) atomicMin(&w.FminKey()[w.csc()[e] & 0xffu], key);
     }
     __syncwarp();
     // X1 = max(X0 + sum_j NV'_ji, 0)   (kinetics.py:763-764)
+#pragma unroll 1
     for (int i = lane; i < s; i += 32) {
       float acc = 0.0f;
-      for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++) {
-        const float nvp = w.nvs[e] * fkey_decode(w.FminKey[w.csc[e] & 0xffu]);
-        w.nvs[e] = nvp;
+      for (unsigned e = w.colptr()[i]; e < w.colptr()[i + 1]; e++) {
+        const float nvp = w.nvs()[e] * fkey_decode(w.FminKey()[w.csc()[e] & 0xffu]);
+        w.nvs()[e] = nvp;
         acc = acc + nvp;
       }
-      float x = clamp0(w.X0[i] + acc);
+      float x = clamp0(w.X0()[i] + acc);
       if (poison) x = qnan;
-      w.X1[i] = x;
+      w.X1()[i] = x;
     }
     __syncwarp();
 
     // ---- equilibrium trimming (kinetics.py:808-859)
     const int iters = a.eq_iters[q];
+#pragma unroll 1
     for (int k = 0; k < iters; k++) {
       const float inc = eq_increment(k);
       unsigned mine = 0;
+#pragma unroll 1
       for (int t = lane; t < n_act; t += 32) {
-        const int j = (int)w.act[t];
+        const int j = (int)w.act()[t];
         float xf, xb;
-        bool invf, invb;
-        list_products(w, w.X1, j, xf, xb, invf, invb);
-        if (!invf) xf = 0.0f;
-        if (!invb) xb = 0.0f;
-        const float F = w.F[j];
-        const unsigned dec = eq_decide(w.V[j], quotient_from(xb, xf), w.Ke[j], F);
+        unsigned sides;
+        list_products(w, w.X1(), j, xf, xb, sides);
+        if (!(sides & 1u)) xf = 0.0f;
+        if (!(sides & 2u)) xb = 0.0f;
+        const float F = w.F()[j];
+        const unsigned dec = eq_decide(w.V()[j], quotient_from(xb, xf), w.Ke()[j], F);
         if (dec & 3u) {
           mine |= (dec & 4u) ? 3u : 2u;
-          w.F[j] = eq_update(F, dec, inc);
+          w.F()[j] = eq_update(F, dec, inc);
         }
       }
       const unsigned any = __reduce_or_sync(FULL, mine);
@@ -472,21 +483,22 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       }
       if (!any) break;  // no adjustable protein: F, X1 and every later iteration are unchanged
       __syncwarp();
+#pragma unroll 1
       for (int i = lane; i < s; i += 32) {
         float acc = 0.0f;
-        for (unsigned e = w.colptr[i]; e < w.colptr[i + 1]; e++)
-          acc = acc + w.nvs[e] * w.F[w.csc[e] & 0xffu];
-        float x = clamp0(w.X0[i] + acc);
+        for (unsigned e = w.colptr()[i]; e < w.colptr()[i + 1]; e++)
+          acc = acc + w.nvs()[e] * w.F()[w.csc()[e] & 0xffu];
+        float x = clamp0(w.X0()[i] + acc);
         if (poison) x = qnan;
-        w.X1[i] = x;
+        w.X1()[i] = x;
       }
       __syncwarp();
     }
 
     if (a.V_out)
-      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = w.V[j];
+      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = w.V()[j];
     // next part starts from this part's result
-    for (int i = lane; i < s; i += 32) w.X0[i] = w.X1[i];
+    for (int i = lane; i < s; i += 32) w.X0()[i] = w.X1()[i];
     __syncwarp();
   }
 }
@@ -512,7 +524,7 @@ __device__ float dense_product(const float *X, const int *K, int s, bool &involv
   return fix_product(xx);
 }
 
-__device__ void run_dense(const KinArgs &a, float *X0, float *X1, float *Fsig, float *V, float *Fmin,
+__device__ __noinline__ void run_dense(const KinArgs &a, float *X0, float *X1, float *Fsig, float *V, float *Fmin,
                           float *F, long long cell, int lane, unsigned *sflags) {
   const int p = a.p, s = a.s;
   const long long row = cell * (long long)p;
@@ -610,7 +622,8 @@ __device__ void run_dense(const KinArgs &a, float *X0, float *X1, float *Fsig, f
 }
 
 template <int VEC>
-__global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, float *dense_scratch) {
+__global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
+                                                                    float *dense_scratch) {
   extern __shared__ __align__(16) unsigned smem[];
   __shared__ unsigned sflags[MS_N_FLAGS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -645,8 +658,9 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(KinArgs a, f
     int n_act = 0;
     WarpMem w;
     if (a.sparse_enabled) {
-      w = carve(wbase, p, s, a.e_sub, a.e_nnz, a.e_reg);
-      sparse = scan_cell<VEC>(a, w, cell, lane, n_act);
+      w = carve(wbase, p, s, a.e_ent, a.e_nnz, a.e_reg);
+      const int nq = scan_tile<VEC>(a, (unsigned *)w.nvs(), a.e_nnz, cell * (long long)p * s, lane);
+      sparse = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
     }
     if (sparse) {
       run_sparse(a, w, cell, lane, n_act, sflags);
@@ -779,7 +793,7 @@ __global__ void fill_kernel(float *x, long long n, float v) {
 // host side
 // ---------------------------------------------------------------------------
 struct LaunchPlan {
-  int e_sub, e_nnz, e_reg, words_per_warp, sparse_enabled, grid, warps_per_cta;
+  int e_ent, e_nnz, e_reg, words_per_warp, sparse_enabled, grid, warps_per_cta;
   size_t smem_bytes;
 };
 
@@ -812,19 +826,20 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   LaunchPlan pl = {};
   pl.sparse_enabled = sparse_possible(p, s) ? 1 : 0;
   const int full = (int)(p * s);
-  int e_sub = (int)((5 * p + 1) / 2), e_nnz = (int)((7 * p + 1) / 2), e_reg = (int)p;
-  if (e_sub < 32) e_sub = 32;
-  if (e_nnz < 32) e_nnz = 32;
+  // e_nnz also bounds the element queue (all non-zero positions of the tile)
+  int e_ent = (int)(5 * p), e_nnz = (int)(4 * p), e_reg = (int)p;
+  if (e_ent < 64) e_ent = 64;
+  if (e_nnz < 64) e_nnz = 64;
   if (e_reg < 32) e_reg = 32;
-  pl.e_sub = round32(e_sub < full ? e_sub : full);
+  pl.e_ent = round32(e_ent < 2 * full ? e_ent : 2 * full);
   pl.e_nnz = round32(e_nnz < full ? e_nnz : full);
   pl.e_reg = round32(e_reg < full ? e_reg : full);
   pl.warps_per_cta = WARPS_PER_CTA;
-  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_sub, pl.e_nnz, pl.e_reg);
+  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg);
   pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
   if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
     pl.sparse_enabled = 0;
-    pl.e_sub = pl.e_nnz = pl.e_reg = 0;
+    pl.e_ent = pl.e_nnz = pl.e_reg = 0;
     pl.words_per_warp = 3 * round32((int)s);
     pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
   }
@@ -837,9 +852,10 @@ static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
   pl = {};
   if (!sparse_possible(p, s)) return false;
   pl.sparse_enabled = 1;
-  pl.e_sub = pl.e_nnz = pl.e_reg = round32((int)(p * s));
-  if (pl.e_sub > 0xffff) return false;  // 16-bit list offsets
-  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_sub, pl.e_nnz, pl.e_reg);
+  pl.e_nnz = pl.e_reg = round32((int)(p * s));
+  pl.e_ent = 2 * pl.e_nnz;
+  if (pl.e_ent > 0xffff) return false;  // 16-bit list offsets
+  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg);
   const size_t per_warp = (size_t)pl.words_per_warp * 4;
   if (per_warp > SMEM_PER_CTA_MAX) return false;
   int w = (int)((SMEM_PER_SM / 2) / per_warp);
@@ -871,7 +887,7 @@ extern "C" size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s) {
 template <typename K>
 static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
   MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
-  a.e_sub = pl.e_sub; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
+  a.e_ent = pl.e_ent; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
   a.sparse_enabled = pl.sparse_enabled;
   kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);
   MS_CUDA_CHECK(cudaGetLastError());

@@ -118,23 +118,19 @@ __device__ __forceinline__ float fkey_decode(unsigned k) {
 }
 constexpr unsigned KEY_ONE = 0xbf800000u;  // fkey(1.0f)
 
-// exponents >= 4 are rare: keep their loop out of the hot instruction stream
-__device__ __noinline__ float pow_tail(float r, float b, unsigned n) {
-  while (n) {
-    b = b * b;
-    if (n & 1u) r = r * b;
-    n >>= 1;
-  }
-  return r;
-}
-
 // x^k for a list entry, k >= 1; same multiplication order as powi()
 __device__ __forceinline__ float pow_entry(float x, unsigned k) {
   float r = (k & 1u) ? x : 1.0f;
   if (k > 1u) {
-    const float b = x * x;
+    float b = x * x;
     if (k & 2u) r = r * b;
-    if (k > 3u) r = pow_tail(r, b, k >> 2);
+    unsigned n = k >> 2;
+#pragma unroll 1
+    while (n) {  // exponents >= 4 are rare
+      b = b * b;
+      if (n & 1u) r = r * b;
+      n >>= 1;
+    }
   }
   return r;
 }
@@ -407,6 +403,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       if (!(sides & 2u)) kb = 0.0f;
       if (isinf(kb)) kb = V_MAX;
       float a_reg = 1.0f;
+#pragma unroll 1
       for (unsigned e = w.rowptr()[j] >> 16; e < (w.rowptr()[j + 1] >> 16); e++) {
         const unsigned wd = w.reg()[e];
         a_reg = a_reg * reg_factor(w.X0()[wd & 0xffu], (int)(int8_t)((wd >> 8) & 0xff), w.regk()[e]);
@@ -425,6 +422,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     for (int i = lane; i < s; i += 32) {
       const unsigned c0 = w.colptr()[i], c1 = w.colptr()[i + 1];
       float d = 0.0f;
+#pragma unroll 1
       for (unsigned e = c0; e < c1; e++) {
         const unsigned wd = w.csc()[e];
         const float nv = (float)((int)wd >> 8) * w.V()[wd & 0xffu];  // kinetics.py:759
@@ -436,6 +434,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       float f = w.X0()[i] / d;
       if (f > 1.0f) f = 1.0f;
       const unsigned key = fkey(f);
+#pragma unroll 1
       for (unsigned e = c0; e < c1; e++)  // every protein that removes signal i is limited by F_i
         if (w.nvs()[e] < 0.0f) atomicMin(&w.FminKey()[w.csc()[e] & 0xffu], key);
     }
@@ -444,6 +443,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
 #pragma unroll 1
     for (int i = lane; i < s; i += 32) {
       float acc = 0.0f;
+#pragma unroll 1
       for (unsigned e = w.colptr()[i]; e < w.colptr()[i + 1]; e++) {
         const float nvp = w.nvs()[e] * fkey_decode(w.FminKey()[w.csc()[e] & 0xffu]);
         w.nvs()[e] = nvp;
@@ -470,7 +470,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
         if (!(sides & 1u)) xf = 0.0f;
         if (!(sides & 2u)) xb = 0.0f;
         const float F = w.F()[j];
-        const unsigned dec = eq_decide(w.V()[j], quotient_from(xb, xf), w.Ke()[j], F);
+        const unsigned dec = eq_decide_fast(w.V()[j], quotient_fixed(xb, xf), w.Ke()[j], F);
         if (dec & 3u) {
           mine |= (dec & 4u) ? 3u : 2u;
           w.F()[j] = eq_update(F, dec, inc);
@@ -486,7 +486,9 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
 #pragma unroll 1
       for (int i = lane; i < s; i += 32) {
         float acc = 0.0f;
-        for (unsigned e = w.colptr()[i]; e < w.colptr()[i + 1]; e++)
+        const unsigned c1 = w.colptr()[i + 1];
+#pragma unroll 1
+        for (unsigned e = w.colptr()[i]; e < c1; e++)
           acc = acc + w.nvs()[e] * w.F()[w.csc()[e] & 0xffu];
         float x = clamp0(w.X0()[i] + acc);
         if (poison) x = qnan;

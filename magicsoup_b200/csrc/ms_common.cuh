@@ -58,6 +58,19 @@ __device__ __forceinline__ float quotient_from(float xb, float xf) {
   return q;
 }
 
+// Same value as quotient_from() for products that went through fix_product (finite,
+// >= 0, never NaN), but without dividing by or into zero: x/0 = inf -> MAX, 0/0 = NaN -> 1,
+// 0/x = 0 -> EPS.  Saturated quotients are the common case and would
+// otherwise take the slow path of the IEEE division.
+__device__ __forceinline__ float quotient_fixed(float xb, float xf) {
+  if (xf == 0.0f) return xb == 0.0f ? 1.0f : V_MAX;
+  if (xb == 0.0f) return V_EPS;
+  float q = xb / xf;
+  if (q < V_EPS) q = V_EPS;
+  if (q > V_MAX) q = V_MAX;
+  return q;
+}
+
 // kinetics.py:786-806 from kf, kb (already masked / inf-fixed), a_reg, vmax
 __device__ __forceinline__ float velocity_from(float kf, float kb, float a_reg, float vmax) {
   float a_cat = (kf - kb) / ((1.0f + kf) + kb);
@@ -85,6 +98,34 @@ __device__ __forceinline__ unsigned eq_decide(float v, float q, float ke, float 
   bool lo = fwd ? (r < LOWER) : (r > UPPER);
   if (fwd && F == 1.0f) lo = false;
   bool hi = fwd ? (r > UPPER) : (r < LOWER);
+  if (!fwd && F == 0.0f) hi = false;
+  return (hi ? 1u : 0u) | (lo ? 2u : 0u) | (imp ? 4u : 0u);
+}
+
+// Same decisions as eq_decide() for q in [EPS, MAX] (a clamped quotient).  The value of
+// r = q / ke only matters relative to 1/1.5 and 1.5: for a positive normal ke,
+// q > 4 ke implies fl(q/ke) >= 4 > 1.5 and q < ke/4 implies fl(q/ke) <= 1/4 < 1/1.5 (the
+// scalings by 4 are exact), so the division is only needed near the equilibrium.
+__device__ __forceinline__ unsigned eq_decide_fast(float v, float q, float ke, float F) {
+  const bool imp = fabsf(v) > IMPACT;
+  const bool fwd = v > 0.0f;
+  bool below, above;
+  if (ke >= 1e-37f && ke <= 1e37f) {
+    above = q > 4.0f * ke;
+    below = q < 0.25f * ke;
+    if (!above && !below) {
+      const float r = q / ke;
+      below = r < LOWER;
+      above = r > UPPER;
+    }
+  } else {
+    const float r = q / ke;
+    below = r < LOWER;
+    above = r > UPPER;
+  }
+  bool lo = fwd ? below : above;
+  if (fwd && F == 1.0f) lo = false;
+  bool hi = fwd ? above : below;
   if (!fwd && F == 0.0f) hi = false;
   return (hi ? 1u : 0u) | (lo ? 2u : 0u) | (imp ? 4u : 0u);
 }

@@ -238,14 +238,14 @@ typedef struct {
  */
 static int eq_adjust(const params_t *P, const real *NV_dense, const real *V,
                      const real *Fmin, const real *X0, real *X1, real *F, int8_t *dir,
-                     int max_iters, int nt) {
+                     int max_iters, int nt, int forced, uint32_t *flag_imp, uint32_t *flag_any) {
   const i64 c = P->c, p = P->p, s = P->s;
   (void)nt;
   for (i64 r = 0; r < c * p; r++) F[r] = (real)1; /* :829 */
   int done = 0;
   for (int it = 0; it < max_iters && it < 4; it++) {
-    int any = 0;
-#pragma omp parallel for num_threads(nt) reduction(| : any) schedule(static)
+    int any = 0, anyflag = 0;
+#pragma omp parallel for num_threads(nt) reduction(| : any, anyflag) schedule(static)
     for (i64 ci = 0; ci < c; ci++) {
       for (i64 j = 0; j < p; j++) {
         i64 r = ci * p + j;
@@ -260,9 +260,14 @@ static int eq_adjust(const params_t *P, const real *NV_dense, const real *V,
         if (!is_fwd && F[r] == (real)0) hi = 0;        /* :843 */
         dir[r] = (int8_t)((hi ? 1 : 0) | (lo ? 2 : 0));
         if ((lo || hi) && has_impact) any = 1;
+        if (lo || hi) anyflag = 1;
       }
     }
-    if (!any) break; /* :846-847 */
+    if (flag_imp && any) flag_imp[it] = 1;
+    if (flag_any && anyflag) flag_any[it] = 1;
+    /* :846-847; `forced` mirrors the CUDA entry points, which apply a given number of
+       iterations and report the flags instead of deciding themselves */
+    if (!any && !forced) break;
     done++;
     real inc = (real)INCS[it];
 #pragma omp parallel for num_threads(nt) schedule(static)
@@ -303,7 +308,7 @@ int ms_oracle_equilibrium_adjusted_x(const real *X0, const real *X1_in, const re
   int8_t *dir = (int8_t *)malloc((size_t)(c * p + 1));
   if (!F || !dir) return -1;
   memcpy(X1, X1_in, sizeof(real) * (size_t)(c * s));
-  int done = eq_adjust(&P, NV, V, 0, X0, X1, F, dir, 4, n_threads_or_default(n_threads));
+  int done = eq_adjust(&P, NV, V, 0, X0, X1, F, dir, 4, n_threads_or_default(n_threads), 0, 0, 0);
   if (n_done) *n_done = done;
   free(F);
   free(dir);
@@ -322,7 +327,8 @@ int ms_oracle_equilibrium_adjusted_x(const real *X0, const real *X1_in, const re
  */
 static void integrate_part(const params_t *P, const real *adj_vmax, const real *X0,
                            real *X1, int max_eq_iters, int *eq_done, real *V, real *Fmin,
-                           real *F, int8_t *dir, int nt) {
+                           real *F, int8_t *dir, int nt, int forced, uint32_t *flag_imp,
+                           uint32_t *flag_any) {
   const i64 c = P->c, p = P->p, s = P->s;
 #pragma omp parallel num_threads(nt)
   {
@@ -348,7 +354,7 @@ static void integrate_part(const params_t *P, const real *adj_vmax, const real *
     }
     free(NV);
   }
-  int done = eq_adjust(P, 0, V, Fmin, X0, X1, F, dir, max_eq_iters, nt);
+  int done = eq_adjust(P, 0, V, Fmin, X0, X1, F, dir, max_eq_iters, nt, forced, flag_imp, flag_any);
   if (eq_done) *eq_done = done;
 }
 
@@ -367,7 +373,7 @@ int ms_oracle_integrate_part(const i32 *N, const i32 *Nf, const i32 *Nb, const i
   int8_t *dir = (int8_t *)malloc(cp);
   if (!V || !dir) return -1;
   integrate_part(&P, adj_vmax, X0, X1, max_eq_iters, eq_done, V, V + cp, V + 2 * cp, dir,
-                 n_threads_or_default(n_threads));
+                 n_threads_or_default(n_threads), 0, 0, 0);
   if (V_out) memcpy(V_out, V, sizeof(real) * (size_t)(c * p));
   free(V);
   free(dir);
@@ -378,11 +384,11 @@ int ms_oracle_integrate_part(const i32 *N, const i32 *Nf, const i32 *Nb, const i
  * kinetics.py:725-751 integrate_signals: three parts with trim 0.7, 0.2, 0.1.
  * eq_done (optional, int[3]) receives the number of F updates per part.
  */
-int ms_oracle_integrate_signals(const i32 *N, const i32 *Nf, const i32 *Nb, const i32 *A,
-                                const real *Kmr, const real *Ke, const real *Kmf,
-                                const real *Kmb, const real *Vmax, i64 c, i64 p, i64 s,
-                                const real *X_in, real *X_out, int *eq_done,
-                                int n_threads) {
+static int integrate_signals_impl(const i32 *N, const i32 *Nf, const i32 *Nb, const i32 *A,
+                                  const real *Kmr, const real *Ke, const real *Kmf,
+                                  const real *Kmb, const real *Vmax, i64 c, i64 p, i64 s,
+                                  const real *X_in, real *X_out, int *eq_done, int n_threads,
+                                  const int *eq_iters, uint32_t *flags) {
   params_t P = {N, Nf, Nb, A, Kmr, Ke, Kmf, Kmb, c, p, s};
   static const double TRIMS[3] = {0.7, 0.2, 0.1};
   size_t cp = (size_t)(c * p + 1), cs = (size_t)(c * s + 1);
@@ -400,7 +406,9 @@ int ms_oracle_integrate_signals(const i32 *N, const i32 *Nf, const i32 *Nb, cons
       if (v < (real)0) v = (real)0;
       adj[r] = v;
     }
-    integrate_part(&P, adj, Xa, Xb, 4, eq_done ? eq_done + q : 0, V, Fmin, F, dir, nt);
+    integrate_part(&P, adj, Xa, Xb, eq_iters ? eq_iters[q] : 4, eq_done ? eq_done + q : 0, V,
+                   Fmin, F, dir, nt, eq_iters != 0, flags ? flags + 4 * q : 0,
+                   flags ? flags + 12 + 4 * q : 0);
     real *t = Xa;
     Xa = Xb;
     Xb = t;
@@ -409,6 +417,33 @@ int ms_oracle_integrate_signals(const i32 *N, const i32 *Nf, const i32 *Nb, cons
   free(V);
   free(dir);
   return 0;
+}
+
+int ms_oracle_integrate_signals(const i32 *N, const i32 *Nf, const i32 *Nb, const i32 *A,
+                                const real *Kmr, const real *Ke, const real *Kmf,
+                                const real *Kmb, const real *Vmax, i64 c, i64 p, i64 s,
+                                const real *X_in, real *X_out, int *eq_done,
+                                int n_threads) {
+  return integrate_signals_impl(N, Nf, Nb, A, Kmr, Ke, Kmf, Kmb, Vmax, c, p, s, X_in, X_out,
+                                eq_done, n_threads, 0, 0);
+}
+
+/*
+ * CPU mirror of the CONTRACT of the CUDA entry point ms_integrate_signals
+ * (include/magicsoup_b200.h): apply eq_iters[q] adjustment iterations in part q without
+ * deciding the global early exit, and report flags[q*4+k] (some cell had an adjustable
+ * protein with |V| > 0.1) and flags[12+q*4+k] (some cell had any adjustable protein).
+ * Lets the multi-rank host protocol (flags all-reduced over ranks) be tested on CPU.
+ */
+int ms_oracle_integrate_signals_iters(const i32 *N, const i32 *Nf, const i32 *Nb,
+                                      const i32 *A, const real *Kmr, const real *Ke,
+                                      const real *Kmf, const real *Kmb, const real *Vmax,
+                                      i64 c, i64 p, i64 s, const real *X_in, real *X_out,
+                                      const int *eq_iters, uint32_t *flags, int n_threads) {
+  memset(flags, 0, 24 * sizeof(uint32_t));
+  if (c == 0) return 0;
+  return integrate_signals_impl(N, Nf, Nb, A, Kmr, Ke, Kmf, Kmb, Vmax, c, p, s, X_in, X_out, 0,
+                                n_threads, eq_iters, flags);
 }
 
 /* ------------------------------------------------------------------ */
@@ -457,48 +492,76 @@ static void fixsum_add(real x, i64 *hi, i64 *lo) {
 }
 
 /*
- * 3x3 circular stencil, weights [[a,a,a],[a,b,a],[a,a,a]] (world.py:966-972),
- * then += (sum_before - sum_after) / (H*W), then clamp(0).  In place on
- * molecule_map (m,H,W); a, b are float32 arrays of length m.
+ * 3x3 circular stencil of a ROW SLAB (m,H,W) with weights [[a,a,a],[a,b,a],[a,a,a]]
+ * (world.py:966-972) into out (m,H,W).  The rows above row 0 / below row H-1 come from
+ * halo_top / halo_bot (m,W) (NULL: wrap around inside the slab = the whole map).
+ * sums (4 per plane) receive the exact fixed-point plane sums {hi,lo} before and after.
  * Spec order: top=(nw+n)+ne ; mid=w+e ; bot=(sw+s)+se ; nb=(top+mid)+bot ;
  * out = b*c + a*nb (two roundings for the products, one for the sum).
  */
-int ms_oracle_diffuse(real *molecule_map, const real *a, const real *b, i64 m, i64 H,
-                      i64 W, int n_threads) {
-  real *out = (real *)malloc(sizeof(real) * (size_t)(H * W));
-  if (!out) return -1;
-  (void)n_threads;
+int ms_oracle_diffuse_stencil(const real *map, const real *halo_top, const real *halo_bot,
+                              const real *a, const real *b, i64 m, i64 H, i64 W, real *out,
+                              i64 *sums) {
   for (i64 k = 0; k < m; k++) {
-    real *in = molecule_map + k * H * W;
+    const real *in = map + k * H * W;
+    real *o_ = out + k * H * W;
     i64 hi0 = 0, lo0 = 0, hi1 = 0, lo1 = 0;
     for (i64 x = 0; x < H; x++) {
-      i64 xm = (x + H - 1) % H, xp = (x + 1) % H;
+      const real *rm = x > 0 ? in + (x - 1) * W : (halo_top ? halo_top + k * W : in + (H - 1) * W);
+      const real *r0 = in + x * W;
+      const real *rp = x < H - 1 ? in + (x + 1) * W : (halo_bot ? halo_bot + k * W : in);
       for (i64 y = 0; y < W; y++) {
         i64 ym = (y + W - 1) % W, yp = (y + 1) % W;
-        real top = (in[xm * W + ym] + in[xm * W + y]) + in[xm * W + yp];
-        real mid = in[x * W + ym] + in[x * W + yp];
-        real bot = (in[xp * W + ym] + in[xp * W + y]) + in[xp * W + yp];
+        real top = (rm[ym] + rm[y]) + rm[yp];
+        real mid = r0[ym] + r0[yp];
+        real bot = (rp[ym] + rp[y]) + rp[yp];
         real nb = (top + mid) + bot;
-        real c0 = in[x * W + y];
+        real c0 = r0[y];
         real o = b[k] * c0 + a[k] * nb;
-        out[x * W + y] = o;
+        o_[x * W + y] = o;
         fixsum_add(c0, &hi0, &lo0);
         fixsum_add(o, &hi1, &lo1);
       }
     }
-    /* world.py:640-648: total_before / total_after are float32 scalars (torch.sum),
-       their difference and the division by n_pxls are float32 too.  The exact sum
-       rounded once to `real` stands in for torch.sum's float32 tree. */
-    real s0 = (real)((double)hi0 + (double)lo0 * 2.3283064365386963e-10);
-    real s1 = (real)((double)hi1 + (double)lo1 * 2.3283064365386963e-10);
-    real corr = (s0 - s1) / (real)(H * W);
+    sums[4 * k] = hi0;
+    sums[4 * k + 1] = lo0;
+    sums[4 * k + 2] = hi1;
+    sums[4 * k + 3] = lo1;
+  }
+  return 0;
+}
+
+/*
+ * world.py:640-649: total_before / total_after are float32 scalars (torch.sum), their
+ * difference and the division by n_pxls are float32 too.  The exact sum rounded once to
+ * `real` stands in for torch.sum's float32 tree.  map = clamp(out + corr, 0).
+ */
+int ms_oracle_diffuse_correct(const real *out, real *map, const i64 *sums, i64 m, i64 H, i64 W,
+                              i64 n_pxls_total) {
+  for (i64 k = 0; k < m; k++) {
+    real s0 = (real)((double)sums[4 * k] + (double)sums[4 * k + 1] * 2.3283064365386963e-10);
+    real s1 = (real)((double)sums[4 * k + 2] + (double)sums[4 * k + 3] * 2.3283064365386963e-10);
+    real corr = (s0 - s1) / (real)n_pxls_total;
     for (i64 t = 0; t < H * W; t++) {
-      real v = out[t] + corr;
+      real v = out[k * H * W + t] + corr;
       if (v < (real)0) v = (real)0;
-      in[t] = v;
+      map[k * H * W + t] = v;
     }
   }
+  return 0;
+}
+
+/* world.py:638-649 on a whole map, in place */
+int ms_oracle_diffuse(real *molecule_map, const real *a, const real *b, i64 m, i64 H,
+                      i64 W, int n_threads) {
+  (void)n_threads;
+  real *out = (real *)malloc(sizeof(real) * (size_t)(m * H * W + 1));
+  i64 *sums = (i64 *)malloc(sizeof(i64) * (size_t)(4 * m + 1));
+  if (!out || !sums) return -1;
+  ms_oracle_diffuse_stencil(molecule_map, 0, 0, a, b, m, H, W, out, sums);
+  ms_oracle_diffuse_correct(out, molecule_map, sums, m, H, W, H * W);
   free(out);
+  free(sums);
   return 0;
 }
 

@@ -152,6 +152,48 @@ def integrate_signals(P: Params, X, n_threads=0, return_eq_done=False):
     return (out, list(done)) if return_eq_done else out
 
 
+def integrate_signals_iters(P: Params, X, eq_iters, n_threads=0):
+    """
+    CPU mirror of the contract of the CUDA entry point ms_integrate_signals: applies
+    eq_iters[q] adjustment iterations per part and returns (X_out, flags[24]).
+    """
+    X = _r(X, P.dtype)
+    out = np.empty_like(X)
+    flags = np.zeros(24, dtype=np.uint32)
+    eq = (C.c_int * 3)(*[int(v) for v in eq_iters])
+    rc = _lib(P.dtype).ms_oracle_integrate_signals_iters(
+        *P._args(), _p(P.Vmax), _i64(P.c), _i64(P.p), _i64(P.s), _p(X), _p(out), eq, _p(flags),
+        C.c_int(n_threads))
+    assert rc == 0
+    return out, flags
+
+
+def diffuse_stencil(map_slab, halo_top, halo_bottom, a, b, dtype=np.float32):
+    """slab stencil -> (out (m,H,W), sums int64[4*m]); a, b float32 weight vectors"""
+    mm = _r(map_slab, dtype)
+    m, H, W = mm.shape
+    top = None if halo_top is None else _r(halo_top, dtype)
+    bot = None if halo_bottom is None else _r(halo_bottom, dtype)
+    out = np.empty_like(mm)
+    sums = np.zeros(4 * m, dtype=np.int64)
+    rc = _lib(dtype).ms_oracle_diffuse_stencil(_p(mm), _p(top), _p(bot), _p(_r(a, dtype)), _p(_r(b, dtype)),
+                                               _i64(m), _i64(H), _i64(W), _p(out), _p(sums))
+    assert rc == 0
+    return out, sums
+
+
+def diffuse_correct(out, sums, n_pxls_total, dtype=np.float32):
+    """second pass of the slab diffusion -> new map slab"""
+    o = _r(out, dtype)
+    m, H, W = o.shape
+    res = np.empty_like(o)
+    sums = np.ascontiguousarray(sums, dtype=np.int64)
+    rc = _lib(dtype).ms_oracle_diffuse_correct(_p(o), _p(res), _p(sums), _i64(m), _i64(H), _i64(W),
+                                               _i64(n_pxls_total))
+    assert rc == 0
+    return res
+
+
 def enzymatic_activity(P: Params, positions, cell_molecules, molecule_map, n_threads=0):
     """world.py:610-625; returns new (cell_molecules, molecule_map), inputs untouched"""
     pos = _i(positions)

@@ -51,61 +51,122 @@ struct KinArgs {
   int *defer_list;        // device list of deferred cell indices (capacity c)
 };
 
-// per-warp shared memory carve-up (32-bit words).  Only the base pointer and a few word
-// offsets are kept in registers; the arrays are addressed as base + offset.
-struct WarpMem {
-  unsigned *b;
-  int s32, p32, o_ent, o_nvs, o_csc, o_reg, o_regk;
-  // s32 each (Fsig doubles as the counting-sort cursor in the scan)
-  __device__ __forceinline__ float *X0() const { return (float *)b; }
-  __device__ __forceinline__ float *X1() const { return (float *)(b + s32); }
-  __device__ __forceinline__ float *Fsig() const { return (float *)(b + 2 * s32); }
-  __device__ __forceinline__ unsigned *colptr() const { return b + 3 * s32; }  // s32 + 4
-  // p32 each
-  __device__ __forceinline__ float *V() const { return (float *)(b + 4 * s32 + 4); }
-  __device__ __forceinline__ float *F() const { return (float *)(b + 4 * s32 + 4 + p32); }
-  // order-preserving key of F_min (atomicMin target)
-  __device__ __forceinline__ unsigned *FminKey() const { return b + 4 * s32 + 4 + 2 * p32; }
-  __device__ __forceinline__ float *Ke() const { return (float *)(b + 4 * s32 + 4 + 3 * p32); }
-  __device__ __forceinline__ float *Kmf() const { return (float *)(b + 4 * s32 + 4 + 4 * p32); }
-  __device__ __forceinline__ float *Kmb() const { return (float *)(b + 4 * s32 + 4 + 5 * p32); }
-  __device__ __forceinline__ float *Vmax() const { return (float *)(b + 4 * s32 + 4 + 6 * p32); }
-  // proteins that have substrate or product entries
-  __device__ __forceinline__ unsigned *act() const { return b + 4 * s32 + 4 + 7 * p32; }
-  // p32 + 4: ent offset | reg offset << 16
-  __device__ __forceinline__ unsigned *rowptr() const { return b + 4 * s32 + 4 + 8 * p32; }
-  // e_ent: signal | exponent << 8 | (1 << 31 if product side), per protein, ascending signal
-  __device__ __forceinline__ unsigned *ent() const { return b + o_ent; }
-  // e_nnz: rate per csc entry (nvs + csc hold the element queue during the scan)
-  __device__ __forceinline__ float *nvs() const { return (float *)(b + o_nvs); }
-  // e_nnz: protein | N << 8, per signal, ascending protein
-  __device__ __forceinline__ unsigned *csc() const { return b + o_csc; }
-  // e_reg: signal | (A & 0xff) << 8 | protein << 16 ; Kmr of that entry
-  __device__ __forceinline__ unsigned *reg() const { return b + o_reg; }
-  __device__ __forceinline__ float *regk() const { return (float *)(b + o_regk); }
-};
-
+// ---------------------------------------------------------------------------
+// Per-warp shared memory region (32-bit words).  The arrays that the hot loops index with
+// a value taken from a packed list entry (signal -> X0/X1, protein -> V, F, ...) start at
+// addresses aligned to their power-of-two stride, so that `base | (entry & 0x3fc)` is the
+// element's address (one LOP3, no shift/add).  The hot loops address shared memory with
+// explicit 32-bit shared-window addresses.
+//
+//   X0 [S2] X1 [S2] Fsig/cursor [S2] colptr [S2+32] pad
+//   V F FminKey Ke Kmf Kmb Vmax act [P2 each]  rowptr [P2+32]
+//   ent [e_ent]  csc [e_nnz] nvs [e_nnz]  reg [e_reg] regk [e_reg]
+//
+// ent : signal*4 | exponent << 10 | (1 << 31 if product side); per protein, ascending signal
+// csc : protein*4 | N << 10; per signal, ascending protein; nvs: the rate of that entry
+// act : protein*4 | (has substrates) << 10 | (has products) << 11
+// rowptr : ent offset | reg offset << 16;  reg: signal | (A & 0xff) << 8 | protein << 16
+// During the scan csc+nvs hold the queue of non-zero tile elements (2 words each) and
+// then the unsorted N list.
+// ---------------------------------------------------------------------------
 __host__ __device__ inline int round32(int x) { return (x + 31) & ~31; }
-
-__host__ __device__ inline int warp_words(int p, int s, int e_ent, int e_nnz, int e_reg) {
-  const int s32 = round32(s), p32 = round32(p);
-  return 3 * s32 + (s32 + 4) + 8 * p32 + (p32 + 4) + e_ent + 2 * e_nnz + 2 * e_reg;
+__host__ __device__ inline int pow2_at_least_32(int x) {
+  int r = 32;
+  while (r < x) r <<= 1;
+  return r;
 }
 
-__device__ __forceinline__ WarpMem carve(unsigned *w, int p, int s, int e_ent, int e_nnz, int e_reg) {
+struct Layout {
+  int S2, P2, oP, oEnt, oCsc, oNvs, oReg, oRegk, words;
+};
+
+__host__ __device__ inline Layout make_layout(int p, int s, int e_ent, int e_nnz, int e_reg) {
+  Layout L;
+  L.S2 = pow2_at_least_32(s);
+  L.P2 = pow2_at_least_32(p);
+  L.oP = ((4 * L.S2 + 32 + L.P2 - 1) / L.P2) * L.P2;
+  L.oEnt = L.oP + 9 * L.P2 + 32;
+  L.oCsc = L.oEnt + e_ent;
+  L.oNvs = L.oCsc + e_nnz;
+  L.oReg = L.oNvs + e_nnz;
+  L.oRegk = L.oReg + e_reg;
+  const int align = L.S2 > L.P2 ? L.S2 : L.P2;
+  L.words = ((L.oRegk + e_reg + align - 1) / align) * align;
+  return L;
+}
+
+struct WarpMem {
+  unsigned *b;    // generic pointer to the region
+  unsigned sb;    // the same location as a 32-bit shared-window byte address
+  int S2, P2, oP, oEnt, oCsc, oNvs, oReg, oRegk;
+  // generic views (scan / list building)
+  __device__ __forceinline__ float *X0() const { return (float *)b; }
+  __device__ __forceinline__ unsigned *cursor() const { return b + 2 * S2; }
+  __device__ __forceinline__ unsigned *colptr() const { return b + 3 * S2; }
+  __device__ __forceinline__ unsigned *FminKey() const { return b + oP + 2 * P2; }
+  __device__ __forceinline__ float *Ke() const { return (float *)(b + oP + 3 * P2); }
+  __device__ __forceinline__ float *Kmf() const { return (float *)(b + oP + 4 * P2); }
+  __device__ __forceinline__ float *Kmb() const { return (float *)(b + oP + 5 * P2); }
+  __device__ __forceinline__ float *Vmax() const { return (float *)(b + oP + 6 * P2); }
+  __device__ __forceinline__ unsigned *act() const { return b + oP + 7 * P2; }
+  __device__ __forceinline__ unsigned *rowptr() const { return b + oP + 8 * P2; }
+  __device__ __forceinline__ unsigned *ent() const { return b + oEnt; }
+  __device__ __forceinline__ unsigned *csc() const { return b + oCsc; }
+  __device__ __forceinline__ unsigned *nvs() const { return b + oNvs; }
+  __device__ __forceinline__ unsigned *reg() const { return b + oReg; }
+  __device__ __forceinline__ float *regk() const { return (float *)(b + oRegk); }
+  // shared-window byte addresses (hot loops)
+  __device__ __forceinline__ unsigned aX0() const { return sb; }
+  __device__ __forceinline__ unsigned aX1() const { return sb + 4 * S2; }
+  __device__ __forceinline__ unsigned aCol() const { return sb + 12 * S2; }
+  __device__ __forceinline__ unsigned aV() const { return sb + 4 * oP; }
+  __device__ __forceinline__ unsigned aF() const { return sb + 4 * (oP + P2); }
+  __device__ __forceinline__ unsigned aFk() const { return sb + 4 * (oP + 2 * P2); }
+  __device__ __forceinline__ unsigned aKe() const { return sb + 4 * (oP + 3 * P2); }
+  __device__ __forceinline__ unsigned aKmf() const { return sb + 4 * (oP + 4 * P2); }
+  __device__ __forceinline__ unsigned aKmb() const { return sb + 4 * (oP + 5 * P2); }
+  __device__ __forceinline__ unsigned aVmax() const { return sb + 4 * (oP + 6 * P2); }
+  __device__ __forceinline__ unsigned aAct() const { return sb + 4 * (oP + 7 * P2); }
+  __device__ __forceinline__ unsigned aRow() const { return sb + 4 * (oP + 8 * P2); }
+  __device__ __forceinline__ unsigned aEnt() const { return sb + 4 * oEnt; }
+  __device__ __forceinline__ unsigned aCsc() const { return sb + 4 * oCsc; }
+  __device__ __forceinline__ unsigned aNvs() const { return sb + 4 * oNvs; }
+  __device__ __forceinline__ unsigned aReg() const { return sb + 4 * oReg; }
+  __device__ __forceinline__ unsigned aRegk() const { return sb + 4 * oRegk; }
+};
+
+__device__ __forceinline__ WarpMem carve(unsigned *w, unsigned shared_addr, int p, int s, int e_ent,
+                                         int e_nnz, int e_reg) {
+  const Layout L = make_layout(p, s, e_ent, e_nnz, e_reg);
   WarpMem m;
-  m.b = w;
-  m.s32 = round32(s);
-  m.p32 = round32(p);
-  m.o_ent = 4 * m.s32 + 4 + 9 * m.p32 + 4;
-  m.o_nvs = m.o_ent + e_ent;
-  m.o_csc = m.o_nvs + e_nnz;
-  m.o_reg = m.o_csc + e_nnz;
-  m.o_regk = m.o_reg + e_reg;
+  m.b = w; m.sb = shared_addr;
+  m.S2 = L.S2; m.P2 = L.P2; m.oP = L.oP; m.oEnt = L.oEnt; m.oCsc = L.oCsc; m.oNvs = L.oNvs;
+  m.oReg = L.oReg; m.oRegk = L.oRegk;
   return m;
 }
 
-// order-preserving unsigned key of a float; NaN maps to 0 so that it wins atomicMin
+// explicit shared-memory accesses by 32-bit shared-window address
+__device__ __forceinline__ unsigned lds_u(unsigned addr) {
+  unsigned v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_f(unsigned addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u(unsigned addr, unsigned v) {
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_f(unsigned addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void atom_min_shared(unsigned addr, unsigned v) {
+  asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// order-preserving unsigned key of a float; NaN maps to 0 so that it wins the atomic min
 // (torch.min propagates NaN, kinetics.py:877)
 __device__ __forceinline__ unsigned fkey(float f) {
   if (isnan(f)) return 0u;
@@ -117,23 +178,6 @@ __device__ __forceinline__ float fkey_decode(unsigned k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 constexpr unsigned KEY_ONE = 0xbf800000u;  // fkey(1.0f)
-
-// x^k for a list entry, k >= 1; same multiplication order as powi()
-__device__ __forceinline__ float pow_entry(float x, unsigned k) {
-  float r = (k & 1u) ? x : 1.0f;
-  if (k > 1u) {
-    float b = x * x;
-    if (k & 2u) r = r * b;
-    unsigned n = k >> 2;
-#pragma unroll 1
-    while (n) {  // exponents >= 4 are rare
-      b = b * b;
-      if (n & 1u) r = r * b;
-      n >>= 1;
-    }
-  }
-  return r;
-}
 
 template <int VEC>
 __device__ __forceinline__ void load_vec(const int *ptr, bool ok, int (&v)[VEC]) {
@@ -216,16 +260,18 @@ __device__ int scan_tile(const KinArgs &a, unsigned *queue, int cap, long long t
 // scan, phase 2: one lane per queued element: distribute it to the per-protein lists
 // (ent, reg) and the unsorted N list, then sort the N list by signal into csc (stable
 // counting sort via warp match, so each signal's entries stay in ascending protein
-// order).  No atomics, no sorting networks.  Returns false if a list overflows.
+// order).  Returns false if a list overflows.
 // ---------------------------------------------------------------------------
 __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, int lane, int nq,
                             int &n_act_out) {
   const int p = a.p, s = a.s;
   const unsigned lt = (1u << lane) - 1u;
-  unsigned *queue = (unsigned *)w.nvs();  // nvs and csc are contiguous: 2 * e_nnz words
-  unsigned *tmp = (unsigned *)w.nvs();    // unsorted N list, written over consumed queue words
+  unsigned *queue = w.csc();  // csc and nvs are contiguous: 2 * e_nnz words
+  unsigned *tmp = w.csc();    // unsorted N list, written over consumed queue words
+  unsigned *sides = w.FminKey();  // per protein: bit 10 = has substrates, bit 11 = has products
   int ent_tot = 0, nnz_tot = 0, reg_tot = 0;
   int prev_row = -1;
+  for (int j = lane; j < p; j += 32) sides[j] = 0;
   __syncwarp();
 #pragma unroll 1
   for (int base = 0; base < nq; base += 32) {
@@ -252,11 +298,12 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
       for (int r = before + 1; r <= row; r++) w.rowptr()[r] = ptr;
     }
     prev_row = __shfl_sync(FULL, row, 31);
+    if (nf | nb) atomicOr(&sides[row], (nf ? 0x400u : 0u) | (nb ? 0x800u : 0u));
     if (nf) {
-      if (pe < a.e_ent) w.ent()[pe] = sig | (nf << 8);
+      if (pe < a.e_ent) w.ent()[pe] = (sig << 2) | (nf << 10);
       pe++;
     }
-    if (nb && pe < a.e_ent) w.ent()[pe] = sig | (nb << 8) | 0x80000000u;
+    if (nb && pe < a.e_ent) w.ent()[pe] = (sig << 2) | (nb << 10) | 0x80000000u;
     if (n != 0 && pn < a.e_nnz) tmp[pn] = sig | ((unsigned)row << 8) | ((unsigned)n << 16);
     if (av != 0 && pr < a.e_reg) w.reg()[pr] = sig | ((unsigned)(av & 0xff) << 8) | ((unsigned)row << 16);
     ent_tot += __popc(bs) + __popc(bp);
@@ -275,15 +322,15 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
 #pragma unroll 1
   for (int j0 = 0; j0 < p; j0 += 32) {
     const int j = j0 + lane;
-    const bool has = j < p && (w.rowptr()[j + 1] & 0xffffu) != (w.rowptr()[j] & 0xffffu);
-    const unsigned b = __ballot_sync(FULL, has);
-    if (has) w.act()[n_act + __popc(b & lt)] = (unsigned)j;
+    const unsigned sd = j < p ? sides[j] : 0u;
+    const unsigned b = __ballot_sync(FULL, sd != 0);
+    if (sd) w.act()[n_act + __popc(b & lt)] = ((unsigned)j << 2) | sd;
     n_act += __popc(b);
   }
   n_act_out = n_act;
 
   // stable counting sort of the N list by signal -> csc
-  unsigned *cursor = (unsigned *)w.Fsig();
+  unsigned *cursor = w.cursor();
   for (int i = lane; i < s; i += 32) cursor[i] = 0;
   __syncwarp();
 #pragma unroll 1
@@ -314,7 +361,8 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   }
   if (lane == 0) w.colptr()[s] = carry;
   __syncwarp();
-  // tmp (in the nvs half) is read chunk by chunk while csc (the other half) is written
+  // The sorted list goes to the nvs half first (tmp occupies the csc half), then moves.
+  unsigned *sorted = w.nvs();
 #pragma unroll 1
   for (int base = 0; base < nnz_tot; base += 32) {
     const int e = base + lane;
@@ -324,12 +372,13 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
     const unsigned peers = __match_any_sync(FULL, sg);
     if (v) {
       const unsigned pos = cursor[sg] + __popc(peers & lt);
-      w.csc()[pos] = ((wd >> 8) & 0xffu) | ((unsigned)((int)wd >> 16) << 8);
+      sorted[pos] = (((wd >> 8) & 0xffu) << 2) | ((unsigned)((int)wd >> 16) << 10);
     }
     __syncwarp();
     if (v && lane == 31 - __clz(peers)) cursor[sg] += __popc(peers);
     __syncwarp();
   }
+  for (int e = lane; e < nnz_tot; e += 32) w.csc()[e] = sorted[e];
 
   // per-protein scalars, and the Kmr values of the (few) regulatory entries
   const long long prow = cell * (long long)p;
@@ -348,25 +397,30 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   return true;
 }
 
-// products over a protein's substrate and product entries (kinetics.py:894-918), each side in
-// ascending signal order; bit0 / bit1 of `sides` tell which sides have entries at all
-__device__ __forceinline__ void list_products(const WarpMem &w, const float *X, int j, float &xf,
-                                              float &xb, unsigned &sides) {
-  const unsigned e0 = w.rowptr()[j] & 0xffffu, e1 = w.rowptr()[j + 1] & 0xffffu;
+// products over a protein's substrate and product entries (kinetics.py:894-918), each side
+// in ascending signal order.  xaddr: shared address of X0 or X1 (aligned to its stride).
+__device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsigned pend, float &xf,
+                                              float &xb) {
   xf = 1.0f;
   xb = 1.0f;
-  sides = 0;
 #pragma unroll 1
-  for (unsigned e = e0; e < e1; e++) {
-    const unsigned wd = w.ent()[e];
-    const float v = pow_entry(X[wd & 0xffu], (wd >> 8) & 0x7fffffu);
-    if (wd & 0x80000000u) {
-      xb = xb * v;
-      sides |= 2u;
-    } else {
-      xf = xf * v;
-      sides |= 1u;
+  for (; pe < pend; pe += 4) {
+    const unsigned wd = lds_u(pe);
+    const float x = lds_f(xaddr | (wd & 0x3fcu));
+    float r = (wd & 0x400u) ? x : 1.0f;  // same multiplication order as powi()
+    if (wd & 0x7ffff800u) {              // exponent >= 2
+      float b = x * x;
+      if (wd & 0x800u) r = r * b;
+      unsigned n = (wd >> 12) & 0x7ffffu;
+#pragma unroll 1
+      while (n) {
+        b = b * b;
+        if (n & 1u) r = r * b;
+        n >>= 1;
+      }
     }
+    if ((int)wd < 0) xb = xb * r;
+    else xf = xf * r;
   }
   xf = fix_product(xf);
   xb = fix_product(xb);
@@ -379,39 +433,44 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
                            unsigned *sflags) {
   const int p = a.p, s = a.s;
   const float qnan = __int_as_float(0x7fc00000);
+  const unsigned aX0 = w.aX0(), aX1 = w.aX1(), aV = w.aV(), aF = w.aF(), aFk = w.aFk();
+  const unsigned aRow = w.aRow(), aEnt = w.aEnt(), aCsc = w.aCsc();
+  const unsigned dNvs = 4u * (unsigned)(w.oNvs - w.oCsc);  // nvs[e] lives dNvs bytes after csc[e]
 #pragma unroll 1
   for (int q = 0; q < a.n_parts; q++) {
     const float trim = a.trims[q];
     for (int j = lane; j < p; j += 32) {
-      w.V()[j] = 0.0f;  // proteins without substrate/product entries have V = 0
-      w.F()[j] = 1.0f;
-      w.FminKey()[j] = KEY_ONE;
+      sts_f(aV + 4 * j, 0.0f);  // proteins without substrate/product entries have V = 0
+      sts_f(aF + 4 * j, 1.0f);
+      sts_u(aFk + 4 * j, KEY_ONE);
     }
     __syncwarp();
     // ---- velocities (kinetics.py:771-806) on the active proteins
     bool poison = false;
 #pragma unroll 1
     for (int t = lane; t < n_act; t += 32) {
-      const int j = (int)w.act()[t];
+      const unsigned aw = lds_u(w.aAct() + 4 * t);
+      const unsigned j4 = aw & 0x3fcu;
+      const unsigned r0 = lds_u(aRow | j4), r1 = lds_u((aRow | j4) + 4);
       float xf, xb;
-      unsigned sides;
-      list_products(w, w.X0(), j, xf, xb, sides);
-      float kf = xf / w.Kmf()[j];
-      if (!(sides & 1u)) kf = 0.0f;
+      list_products(aX0, aEnt + 4 * (r0 & 0xffffu), aEnt + 4 * (r1 & 0xffffu), xf, xb);
+      float kf = xf / lds_f(w.aKmf() | j4);
+      if (!(aw & 0x400u)) kf = 0.0f;
       if (isinf(kf)) kf = V_MAX;
-      float kb = xb / w.Kmb()[j];
-      if (!(sides & 2u)) kb = 0.0f;
+      float kb = xb / lds_f(w.aKmb() | j4);
+      if (!(aw & 0x800u)) kb = 0.0f;
       if (isinf(kb)) kb = V_MAX;
       float a_reg = 1.0f;
 #pragma unroll 1
-      for (unsigned e = w.rowptr()[j] >> 16; e < (w.rowptr()[j + 1] >> 16); e++) {
-        const unsigned wd = w.reg()[e];
-        a_reg = a_reg * reg_factor(w.X0()[wd & 0xffu], (int)(int8_t)((wd >> 8) & 0xff), w.regk()[e]);
+      for (unsigned e = r0 >> 16; e < (r1 >> 16); e++) {
+        const unsigned wd = lds_u(w.aReg() + 4 * e);
+        a_reg = a_reg * reg_factor(lds_f(aX0 + 4 * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
+                                   lds_f(w.aRegk() + 4 * e));
       }
-      float vmax = w.Vmax()[j];
+      float vmax = lds_f(w.aVmax() | j4);
       if (!a.adj_vmax) vmax = clamp0(vmax * trim);  // kinetics.py:749
       const float v = velocity_from(kf, kb, a_reg, vmax);
-      w.V()[j] = v;
+      sts_f(aV | j4, v);
       poison |= isnan(v);
     }
     poison = __any_sync(FULL, poison);  // 0 * NaN of the dense reference reaches every signal
@@ -420,38 +479,39 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     // ---- substrate trimming (kinetics.py:861-879)
 #pragma unroll 1
     for (int i = lane; i < s; i += 32) {
-      const unsigned c0 = w.colptr()[i], c1 = w.colptr()[i + 1];
+      const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
       float d = 0.0f;
 #pragma unroll 1
-      for (unsigned e = c0; e < c1; e++) {
-        const unsigned wd = w.csc()[e];
-        const float nv = (float)((int)wd >> 8) * w.V()[wd & 0xffu];  // kinetics.py:759
-        w.nvs()[e] = nv;
+      for (unsigned pc = c0; pc < c1; pc += 4) {
+        const unsigned wd = lds_u(pc);
+        const float nv = (float)((int)wd >> 10) * lds_f(aV | (wd & 0x3fcu));  // kinetics.py:759
+        sts_f(pc + dNvs, nv);
         float neg = -nv;
         neg = neg < 0.0f ? 0.0f : neg;
         d = d + neg;
       }
-      float f = w.X0()[i] / d;
+      float f = lds_f(aX0 + 4 * i) / d;
       if (f > 1.0f) f = 1.0f;
       const unsigned key = fkey(f);
 #pragma unroll 1
-      for (unsigned e = c0; e < c1; e++)  // every protein that removes signal i is limited by F_i
-        if (w.nvs()[e] < 0.0f) atomicMin(&w.FminKey()[w.csc()[e] & 0xffu], key);
+      for (unsigned pc = c0; pc < c1; pc += 4)  // every protein that removes signal i is limited by F_i
+        if (lds_f(pc + dNvs) < 0.0f) atom_min_shared(aFk | (lds_u(pc) & 0x3fcu), key);
     }
     __syncwarp();
     // X1 = max(X0 + sum_j NV'_ji, 0)   (kinetics.py:763-764)
 #pragma unroll 1
     for (int i = lane; i < s; i += 32) {
+      const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
       float acc = 0.0f;
 #pragma unroll 1
-      for (unsigned e = w.colptr()[i]; e < w.colptr()[i + 1]; e++) {
-        const float nvp = w.nvs()[e] * fkey_decode(w.FminKey()[w.csc()[e] & 0xffu]);
-        w.nvs()[e] = nvp;
+      for (unsigned pc = c0; pc < c1; pc += 4) {
+        const float nvp = lds_f(pc + dNvs) * fkey_decode(lds_u(aFk | (lds_u(pc) & 0x3fcu)));
+        sts_f(pc + dNvs, nvp);
         acc = acc + nvp;
       }
-      float x = clamp0(w.X0()[i] + acc);
+      float x = clamp0(lds_f(aX0 + 4 * i) + acc);
       if (poison) x = qnan;
-      w.X1()[i] = x;
+      sts_f(aX1 + 4 * i, x);
     }
     __syncwarp();
 
@@ -463,17 +523,18 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       unsigned mine = 0;
 #pragma unroll 1
       for (int t = lane; t < n_act; t += 32) {
-        const int j = (int)w.act()[t];
+        const unsigned aw = lds_u(w.aAct() + 4 * t);
+        const unsigned j4 = aw & 0x3fcu;
+        const unsigned r0 = lds_u(aRow | j4), r1 = lds_u((aRow | j4) + 4);
         float xf, xb;
-        unsigned sides;
-        list_products(w, w.X1(), j, xf, xb, sides);
-        if (!(sides & 1u)) xf = 0.0f;
-        if (!(sides & 2u)) xb = 0.0f;
-        const float F = w.F()[j];
-        const unsigned dec = eq_decide_fast(w.V()[j], quotient_fixed(xb, xf), w.Ke()[j], F);
+        list_products(aX1, aEnt + 4 * (r0 & 0xffffu), aEnt + 4 * (r1 & 0xffffu), xf, xb);
+        if (!(aw & 0x400u)) xf = 0.0f;
+        if (!(aw & 0x800u)) xb = 0.0f;
+        const float F = lds_f(aF | j4);
+        const unsigned dec = eq_decide_fast(lds_f(aV | j4), quotient_fixed(xb, xf), lds_f(w.aKe() | j4), F);
         if (dec & 3u) {
           mine |= (dec & 4u) ? 3u : 2u;
-          w.F()[j] = eq_update(F, dec, inc);
+          sts_f(aF | j4, eq_update(F, dec, inc));
         }
       }
       const unsigned any = __reduce_or_sync(FULL, mine);
@@ -485,22 +546,22 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       __syncwarp();
 #pragma unroll 1
       for (int i = lane; i < s; i += 32) {
+        const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
         float acc = 0.0f;
-        const unsigned c1 = w.colptr()[i + 1];
 #pragma unroll 1
-        for (unsigned e = w.colptr()[i]; e < c1; e++)
-          acc = acc + w.nvs()[e] * w.F()[w.csc()[e] & 0xffu];
-        float x = clamp0(w.X0()[i] + acc);
+        for (unsigned pc = c0; pc < c1; pc += 4)
+          acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
+        float x = clamp0(lds_f(aX0 + 4 * i) + acc);
         if (poison) x = qnan;
-        w.X1()[i] = x;
+        sts_f(aX1 + 4 * i, x);
       }
       __syncwarp();
     }
 
     if (a.V_out)
-      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = w.V()[j];
+      for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = lds_f(aV + 4 * j);
     // next part starts from this part's result
-    for (int i = lane; i < s; i += 32) w.X0()[i] = w.X1()[i];
+    for (int i = lane; i < s; i += 32) sts_f(aX0 + 4 * i, lds_f(aX1 + 4 * i));
     __syncwarp();
   }
 }
@@ -632,8 +693,12 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(const __grid
   const int warps_per_cta = blockDim.x >> 5;
   if (threadIdx.x < MS_N_FLAGS) sflags[threadIdx.x] = 0;
   __syncthreads();
-  unsigned *wbase = smem + (size_t)warp * a.words_per_warp;
-  const int p = a.p, s = a.s, s32 = round32(s);
+  // warp regions start at a 1 KB aligned shared address (see the layout comment)
+  const unsigned raw = (unsigned)__cvta_generic_to_shared(smem);
+  const unsigned aligned = (raw + 1023u) & ~1023u;
+  unsigned *wbase = smem + ((aligned - raw) >> 2) + (size_t)warp * a.words_per_warp;
+  const unsigned wshared = aligned + (unsigned)warp * (unsigned)a.words_per_warp * 4u;
+  const int p = a.p, s = a.s, s32 = pow2_at_least_32(s);
   const long long gw = (long long)blockIdx.x * warps_per_cta + warp;
   const long long nw = (long long)gridDim.x * warps_per_cta;
   float *dscr = dense_scratch + gw * (size_t)(3 * round32(p));
@@ -660,8 +725,8 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(const __grid
     int n_act = 0;
     WarpMem w;
     if (a.sparse_enabled) {
-      w = carve(wbase, p, s, a.e_ent, a.e_nnz, a.e_reg);
-      const int nq = scan_tile<VEC>(a, (unsigned *)w.nvs(), a.e_nnz, cell * (long long)p * s, lane);
+      w = carve(wbase, wshared, p, s, a.e_ent, a.e_nnz, a.e_reg);
+      const int nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
       sparse = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
     }
     if (sparse) {
@@ -813,6 +878,7 @@ static int sm_count() {
 
 constexpr size_t SMEM_PER_SM = 222 * 1024;   // usable per SM (227 KB max per CTA on sm_100a)
 constexpr size_t SMEM_PER_CTA_MAX = 200 * 1024;
+constexpr size_t SMEM_ALIGN_SLACK = 1024;  // the kernel aligns its warp regions to 1 KB
 
 static bool sparse_possible(int64_t p, int64_t s) { return p >= 1 && p <= 256 && s >= 1 && s <= MAX_S_SPARSE; }
 
@@ -829,7 +895,7 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   pl.sparse_enabled = sparse_possible(p, s) ? 1 : 0;
   const int full = (int)(p * s);
   // e_nnz also bounds the element queue (all non-zero positions of the tile)
-  int e_ent = (int)(5 * p), e_nnz = (int)(4 * p), e_reg = (int)p;
+  int e_ent = (int)(5 * p), e_nnz = (int)((7 * p + 1) / 2), e_reg = (int)p;
   if (e_ent < 64) e_ent = 64;
   if (e_nnz < 64) e_nnz = 64;
   if (e_reg < 32) e_reg = 32;
@@ -837,13 +903,13 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   pl.e_nnz = round32(e_nnz < full ? e_nnz : full);
   pl.e_reg = round32(e_reg < full ? e_reg : full);
   pl.warps_per_cta = WARPS_PER_CTA;
-  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg);
-  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
+  pl.words_per_warp = make_layout((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg).words;
+  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + SMEM_ALIGN_SLACK;
   if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
     pl.sparse_enabled = 0;
     pl.e_ent = pl.e_nnz = pl.e_reg = 0;
-    pl.words_per_warp = 3 * round32((int)s);
-    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta;
+    pl.words_per_warp = 4 * pow2_at_least_32((int)s);
+    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + SMEM_ALIGN_SLACK;
   }
   finish_plan(pl);
   return pl;
@@ -857,14 +923,14 @@ static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
   pl.e_nnz = pl.e_reg = round32((int)(p * s));
   pl.e_ent = 2 * pl.e_nnz;
   if (pl.e_ent > 0xffff) return false;  // 16-bit list offsets
-  pl.words_per_warp = warp_words((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg);
+  pl.words_per_warp = make_layout((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg).words;
   const size_t per_warp = (size_t)pl.words_per_warp * 4;
-  if (per_warp > SMEM_PER_CTA_MAX) return false;
+  if (per_warp + SMEM_ALIGN_SLACK > SMEM_PER_CTA_MAX) return false;
   int w = (int)((SMEM_PER_SM / 2) / per_warp);
   if (w < 1) w = 1;
   if (w > WARPS_PER_CTA) w = WARPS_PER_CTA;
   pl.warps_per_cta = w;
-  pl.smem_bytes = per_warp * w;
+  pl.smem_bytes = per_warp * w + SMEM_ALIGN_SLACK;
   finish_plan(pl);
   return true;
 }

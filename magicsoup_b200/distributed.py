@@ -1,0 +1,220 @@
+"""
+Multi-GPU world: one process per GPU (`torch.distributed`, NCCL over NVLink on the B200
+box, gloo in the CPU tests).  The reference is single-device; this is the
+sharding north_star asks for:
+
+  * the molecule map (m, H, W) is split into `world_size` row slabs of H / world_size rows;
+  * every cell lives on the rank that owns its pixel's slab, together with its slice of the
+    nine kinetics parameter tensors, so the gather/scatter of `enzymatic_activity`
+    (world.py:619-625) and the permeation (world.py:651-665) stay local;
+  * `diffuse_molecules` exchanges ONE edge row per neighbour (m*W floats each way, circular:
+    the slab above rank 0 is the last rank's) and all-reduces the 4*m exact integer plane sums
+    of the mass correction (world.py:640-648); because those sums are integers the result is
+    bit-identical to the single-device result on the whole map;
+  * `enzymatic_activity` all-reduces (max) the 24 early-exit flags so that every rank takes the
+    same decision about the reference's GLOBAL early exit (kinetics.py:846-847).
+
+Cell indices are local to the rank; the global index of local cell i is
+`global_cell_offset() + i` (ranks in order).  `kill_cells`, `add_cells_from_params` and
+`divide_cells_at` act on the local partition and keep all per-cell tensors and the parameter
+slices consistent; `migrate_cells` moves cells (with their parameters) to the rank that owns
+their new pixel, e.g. after a division or move across a slab boundary.
+"""
+from __future__ import annotations
+
+from typing import Any
+
+import torch
+import torch.distributed as dist
+
+from magicsoup_b200.kinetics import _ALL_PARAMS
+from magicsoup_b200.world import World
+
+
+class SlabWorld(World):
+    """`World` of one row slab; constructor takes the GLOBAL map size (rows, cols)"""
+
+    def __init__(
+        self,
+        chemistry: Any,
+        global_map_size: int | tuple[int, int],
+        group: dist.ProcessGroup | None = None,
+        abs_temp: float = 310.0,
+        mol_map_init: str = "randn",
+        device: str = "cpu",
+    ):
+        if not dist.is_initialized():
+            raise RuntimeError("SlabWorld needs an initialised torch.distributed process group")
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world_size = dist.get_world_size(group)
+        H, W = (global_map_size, global_map_size) if isinstance(global_map_size, int) else global_map_size
+        if H % self.world_size != 0:
+            raise ValueError(f"{H} map rows do not split evenly over {self.world_size} ranks")
+        self.global_map_size = (H, W)
+        self.slab_rows = H // self.world_size
+        self.row0 = self.rank * self.slab_rows  # first global row of this slab
+        super().__init__(chemistry=chemistry, map_size=(self.slab_rows, W), abs_temp=abs_temp,
+                         mol_map_init=mol_map_init, device=device)
+
+    def __getstate__(self):
+        state = super().__getstate__()
+        state["group"] = None
+        return state
+
+    # ------------------------------------------------------------------ global bookkeeping
+    def global_n_cells(self) -> list[int]:
+        """number of cells on every rank"""
+        counts = torch.zeros(self.world_size, dtype=torch.int64, device=self._comm_device())
+        counts[self.rank] = self.n_cells
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=self.group)
+        return [int(x) for x in counts.tolist()]
+
+    def global_cell_offset(self) -> int:
+        """global index of this rank's local cell 0 (ranks in order)"""
+        return sum(self.global_n_cells()[: self.rank])
+
+    def global_positions(self) -> torch.Tensor:
+        """(c,2) pixel coordinates on the whole map"""
+        pos = self.cell_positions.clone()
+        pos[:, 0] += self.row0
+        return pos
+
+    def owner_of_rows(self, rows: torch.Tensor) -> torch.Tensor:
+        return torch.div(rows, self.slab_rows, rounding_mode="floor")
+
+    def _comm_device(self) -> torch.device:
+        backend = dist.get_backend(self.group)
+        if backend == "nccl":
+            return self._cuda()
+        return torch.device("cpu")
+
+    # ------------------------------------------------------------------ exchange steps
+    def _all_ranks_empty(self) -> bool:
+        return sum(self.global_n_cells()) == 0
+
+    def _reduce_flags(self, flags: list[int]) -> list[int]:
+        if self.world_size == 1:
+            return flags
+        t = torch.tensor(flags, dtype=torch.int32, device=self._comm_device())
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return t.tolist()
+
+    def _reduce_sums(self, sums: torch.Tensor) -> torch.Tensor:
+        if self.world_size > 1:
+            if sums.device != self._comm_device():
+                moved = sums.to(self._comm_device())
+                dist.all_reduce(moved, op=dist.ReduceOp.SUM, group=self.group)
+                sums.copy_(moved)
+            else:
+                dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=self.group)
+        return sums
+
+    def _n_pixels_total(self, H: int, W: int) -> int:
+        return self.global_map_size[0] * self.global_map_size[1]
+
+    def _exchange_halos(self, mm: torch.Tensor):
+        """
+        One edge row per neighbour: my first row becomes the BOTTOM halo of the rank above,
+        my last row the TOP halo of the rank below (circular).  Returns (top, bottom) halos
+        of shape (m, W) on mm's device.
+        """
+        if self.world_size == 1:
+            return None, None
+        comm = self._comm_device()
+        first = mm[:, 0, :].contiguous().to(comm)
+        last = mm[:, -1, :].contiguous().to(comm)
+        top = torch.empty_like(first)
+        bottom = torch.empty_like(first)
+        prev = (self.rank - 1) % self.world_size
+        nxt = (self.rank + 1) % self.world_size
+        if self.group is not None:
+            prev, nxt = dist.get_global_rank(self.group, prev), dist.get_global_rank(self.group, nxt)
+        ops = [
+            dist.P2POp(dist.isend, last, nxt, group=self.group),
+            dist.P2POp(dist.irecv, top, prev, group=self.group),
+            dist.P2POp(dist.isend, first, prev, group=self.group),
+            dist.P2POp(dist.irecv, bottom, nxt, group=self.group),
+        ]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        return top.to(mm.device), bottom.to(mm.device)
+
+    # ------------------------------------------------------------------ moving cells between ranks
+    def export_cells(self, cell_idxs: list[int]) -> dict[str, torch.Tensor]:
+        """per-cell state + parameter slices of the given local cells, positions global"""
+        idx = torch.as_tensor(cell_idxs, dtype=torch.long, device=self.cell_positions.device)
+        out = {
+            "positions": self.global_positions()[idx],
+            "molecules": self.cell_molecules[idx],
+            "lifetimes": self.cell_lifetimes[idx],
+            "divisions": self.cell_divisions[idx],
+        }
+        kidx = idx.to(self.kinetics.N.device)
+        for k in _ALL_PARAMS:
+            out[k] = getattr(self.kinetics, k)[kidx]
+        return out
+
+    def import_cells(self, payload: dict[str, torch.Tensor]) -> list[int]:
+        """append cells exported by another rank; their pixels must lie in this slab"""
+        n = int(payload["positions"].shape[0])
+        if n == 0:
+            return []
+        pos = payload["positions"].clone()
+        pos[:, 0] -= self.row0
+        if bool(((pos[:, 0] < 0) | (pos[:, 0] >= self.slab_rows)).any()):
+            raise ValueError("imported cells do not live in this rank's slab")
+        new = self.add_cells_from_params(pos, cell_molecules=payload["molecules"],
+                                         **{k: payload[k] for k in _ALL_PARAMS})
+        self.cell_lifetimes[new] = payload["lifetimes"].to(self.cell_lifetimes.device)
+        self.cell_divisions[new] = payload["divisions"].to(self.cell_divisions.device)
+        return new
+
+    def migrate_cells(self) -> int:
+        """
+        Move every local cell whose (local) row left the slab -- after the caller changed
+        `cell_positions`, e.g. a division or move across the slab boundary -- to the rank
+        that owns its pixel.  Collective: every rank must call it.  Returns the number of
+        cells received.  Local indices are compacted exactly like `kill_cells` does.
+        """
+        H = self.global_map_size[0]
+        gpos = self.global_positions()
+        gpos[:, 0] = gpos[:, 0] % H
+        owner = self.owner_of_rows(gpos[:, 0].long())
+        leaving = torch.nonzero(owner != self.rank).flatten().tolist()
+        payloads: list[dict[str, torch.Tensor] | None] = [None] * self.world_size
+        for dst in range(self.world_size):
+            idxs = [i for i in leaving if int(owner[i]) == dst]
+            if idxs:
+                pl = self.export_cells(idxs)
+                pl["positions"][:, 0] = pl["positions"][:, 0] % H
+                payloads[dst] = {k: v.cpu() for k, v in pl.items()}
+        if leaving:  # remove without spilling molecules onto the map: the cells live on
+            xs = self.cell_positions[leaving, 0].long().clamp(0, self.slab_rows - 1)
+            self._drop_cells(leaving)
+            del xs
+        inbox: list[Any] = [None] * self.world_size
+        dist.all_to_all_object = getattr(dist, "all_to_all_object", None)
+        gathered: list[Any] = [None] * self.world_size
+        dist.all_gather_object(gathered, payloads, group=self.group)
+        received = 0
+        for src in range(self.world_size):
+            pl = gathered[src][self.rank]
+            if pl is not None:
+                received += len(self.import_cells(pl))
+        del inbox
+        return received
+
+    def _drop_cells(self, cell_idxs: list[int]):
+        """kill_cells' compaction (world.py:527-540) without the spill and cell_map update"""
+        keep = torch.ones(self.cell_lifetimes.size(0), dtype=torch.bool, device=self.cell_lifetimes.device)
+        keep[cell_idxs] = False
+        self.cell_lifetimes = self.cell_lifetimes[keep]
+        self.cell_positions = self.cell_positions[keep]
+        self.cell_divisions = self.cell_divisions[keep]
+        self.cell_molecules = self.cell_molecules[keep]
+        self.kinetics.remove_cell_params(keep=keep.to(self.kinetics.N.device))
+        for idx in sorted(cell_idxs, reverse=True):
+            self.cell_genomes.pop(idx)
+            self.cell_labels.pop(idx)
+        self.n_cells -= len(cell_idxs)

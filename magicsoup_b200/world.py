@@ -30,7 +30,7 @@ from typing import Any
 import torch
 
 from magicsoup_b200 import _native as nat
-from magicsoup_b200.kinetics import Kinetics, _settle_early_exit, _ALL_PARAMS
+from magicsoup_b200.kinetics import Kinetics, _settle_early_exit, _ALL_PARAMS, _STAGE_METHODS
 
 
 @dataclass(frozen=True)
@@ -88,7 +88,7 @@ class World:
     ):
         self.device = device
         self.batch_size = batch_size
-        self.map_size = map_size
+        self.map_size = map_size  # the reference's maps are square; a (rows, cols) pair is accepted too
         self.abs_temp = abs_temp
         self.chemistry = chemistry
         self.start_codons = start_codons
@@ -106,12 +106,13 @@ class World:
         self.n_cells = 0
         self.cell_genomes: list[str] = []
         self.cell_labels: list[str] = []
-        self.cell_map = torch.zeros(map_size, map_size, dtype=torch.bool, device=device)
+        n_rows, n_cols = (map_size, map_size) if isinstance(map_size, int) else map_size
+        self.cell_map = torch.zeros(n_rows, n_cols, dtype=torch.bool, device=device)
         self.cell_positions = torch.zeros(0, 2, dtype=torch.int32, device=device)
         self.cell_lifetimes = torch.zeros(0, dtype=torch.int32, device=device)
         self.cell_divisions = torch.zeros(0, dtype=torch.int32, device=device)
         self.cell_molecules = torch.zeros(0, self.n_molecules, dtype=torch.float32, device=device)
-        self.molecule_map = self._get_molecule_map(n=self.n_molecules, size=map_size, init=mol_map_init)
+        self.molecule_map = self._get_molecule_map(n=self.n_molecules, size=(n_rows, n_cols), init=mol_map_init)
         self._scratch: dict[str, torch.Tensor] = {}
         # when set to a list, (start, end) CUDA event pairs around each kinetics kernel
         # launch are appended to it (used by bench.py for the roofline of that kernel)
@@ -159,66 +160,116 @@ class World:
         return mm, cm, pos
 
     # ------------------------------------------------------------------ step methods
-    def enzymatic_activity(self):
-        """world.py:610-625"""
-        if self.n_cells == 0:
-            return
-        dev = self._cuda()
+    # The step methods are written against a few hooks so that the multi-GPU SlabWorld
+    # (magicsoup_b200/distributed.py) only adds the exchange steps: _reduce_flags,
+    # _exchange_halos, _reduce_sums, _n_pixels_total.
+    def _reduce_flags(self, flags: list[int]) -> list[int]:
+        return flags
+
+    def _exchange_halos(self, mm: torch.Tensor):
+        return None, None  # one device holds the whole map: rows wrap around inside it
+
+    def _reduce_sums(self, sums: torch.Tensor) -> torch.Tensor:
+        return sums
+
+    def _n_pixels_total(self, H: int, W: int) -> int:
+        return H * W
+
+    def _launch_activity(self, dev, pos, cm, mm, X, eq) -> list[int]:
+        """ms_enzymatic_activity with eq iterations -> the 24 early-exit flags"""
         kin = self.kinetics
-        mm, cm, pos = self._state_on_device(dev)
         m = self.n_molecules
         _, H, W = mm.shape
         c, s = self.n_cells, 2 * m
-        if any(kin._overrides(k) for k in ("integrate_signals",)) or any(
-                kin._overrides(k) for k in ("_integrate_signals_part", "_get_velocities", "_multiply_signals",
-                                            "_get_quotient", "_get_negative_adjusted_nv",
-                                            "_get_equilibrium_adjusted_x")):
-            xs, ys = pos[:, 0].long(), pos[:, 1].long()
-            X = kin.integrate_signals(X=torch.cat([cm, mm[:, xs, ys].T], dim=1))
-        else:
-            st, keep, p = kin._params(dev, c, s)
-            scratch, nbytes = kin._kin_scratch(dev, c, p, s)
-            flags = kin._flags(dev)
-            X = torch.empty(c, s, dtype=torch.float32, device=dev)
-            eq = [4, 4, 4]
-            while True:
-                if self._kernel_events is not None:
-                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-                    ev[0].record(torch.cuda.current_stream(dev))
-                nat.check(nat.lib().ms_enzymatic_activity(
-                    st, nat.ptr(pos), nat.ptr(cm), nat.ptr(mm), m, H, W, nat.ptr(X), nat.eq_array(eq),
-                    nat.ptr(flags), nat.ptr(scratch), nbytes, nat.stream_ptr(dev)))
-                if self._kernel_events is not None:
-                    ev[1].record(torch.cuda.current_stream(dev))
-                    self._kernel_events.append(ev)
-                if not _settle_early_exit(kin._read_flags(flags), eq, 3):
-                    break
-        new_cm = torch.empty(c, m, dtype=torch.float32, device=dev)
-        nat.check(nat.lib().ms_scatter_signals(nat.ptr(X), nat.ptr(pos), c, m, H, W, nat.ptr(new_cm), nat.ptr(mm),
-                                               nat.stream_ptr(dev)))
-        self.cell_molecules = new_cm
+        st, keep, p = kin._params(dev, c, s)
+        scratch, nbytes = kin._kin_scratch(dev, c, p, s)
+        flags = kin._flags(dev)
+        if self._kernel_events is not None:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record(torch.cuda.current_stream(dev))
+        nat.check(nat.lib().ms_enzymatic_activity(
+            st, nat.ptr(pos), nat.ptr(cm), nat.ptr(mm), m, H, W, nat.ptr(X), nat.eq_array(eq),
+            nat.ptr(flags), nat.ptr(scratch), nbytes, nat.stream_ptr(dev)))
+        if self._kernel_events is not None:
+            ev[1].record(torch.cuda.current_stream(dev))
+            self._kernel_events.append(ev)
+        return kin._read_flags(flags)
 
-    @torch.no_grad()
-    def diffuse_molecules(self):
-        """world.py:627-665"""
-        dev = self._cuda()
-        mm, cm, pos = self._state_on_device(dev)
+    def _launch_scatter(self, dev, X, pos, mm) -> torch.Tensor:
+        m = self.n_molecules
+        _, H, W = mm.shape
+        new_cm = torch.empty(self.n_cells, m, dtype=torch.float32, device=dev)
+        nat.check(nat.lib().ms_scatter_signals(nat.ptr(X), nat.ptr(pos), self.n_cells, m, H, W, nat.ptr(new_cm),
+                                               nat.ptr(mm), nat.stream_ptr(dev)))
+        return new_cm
+
+    def _launch_stencil(self, dev, mm, top, bottom) -> tuple[torch.Tensor, torch.Tensor]:
+        """ms_diffuse_stencil -> (stencil output in scratch, int64 plane sums (4*m))"""
         m, H, W = mm.shape
-        if m == 0:
-            return
         a = self._const_f32("diff_a", [w[0] for w in self._diffusion], dev)
         b = self._const_f32("diff_b", [w[1] for w in self._diffusion], dev)
-        nbytes = int(nat.lib().ms_diffuse_scratch_bytes(m, H, W))
-        scratch = self._buffer("diffuse", nbytes, dev)
-        nat.check(nat.lib().ms_diffuse_molecules(nat.ptr(mm), nat.ptr(a), nat.ptr(b), m, H, W, nat.ptr(scratch),
-                                                 nbytes, nat.stream_ptr(dev)))
-        if self.n_cells == 0:
-            return
+        out = self._buffer("diffuse", m * H * W * 4, dev)
+        sums = self._buffer("diffuse_sums", 4 * m * 8, dev)[: 4 * m * 8].view(torch.int64)
+        nat.check(nat.lib().ms_diffuse_stencil(nat.ptr(mm), nat.ptr(top), nat.ptr(bottom), nat.ptr(a), nat.ptr(b),
+                                               m, H, W, nat.ptr(out), nat.ptr(sums), nat.stream_ptr(dev)))
+        return out, sums
+
+    def _launch_correct(self, dev, out, mm, sums, n_total: int):
+        m, H, W = mm.shape
+        nat.check(nat.lib().ms_diffuse_correct(nat.ptr(out), nat.ptr(mm), nat.ptr(sums), m, H, W, n_total,
+                                               nat.stream_ptr(dev)))
+
+    def _launch_permeate(self, dev, cm, mm, pos) -> torch.Tensor:
+        m, H, W = mm.shape
         perm = self._const_f32("perm", list(self._permeation), dev)
         new_cm = torch.empty_like(cm)
         nat.check(nat.lib().ms_permeate(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pos), nat.ptr(perm),
                                         self.n_cells, m, H, W, nat.stream_ptr(dev)))
-        self.cell_molecules = new_cm
+        return new_cm
+
+    def _device_for_step(self) -> torch.device:
+        return self._cuda()
+
+    def enzymatic_activity(self):
+        """world.py:610-625"""
+        if self._all_ranks_empty():
+            return
+        dev = self._device_for_step()
+        kin = self.kinetics
+        mm, cm, pos = self._state_on_device(dev)
+        m = self.n_molecules
+        c, s = self.n_cells, 2 * m
+        if kin._overrides("integrate_signals") or any(kin._overrides(k) for k in _STAGE_METHODS):
+            xs, ys = pos[:, 0].long(), pos[:, 1].long()
+            X = kin.integrate_signals(X=torch.cat([cm, mm[:, xs, ys].T], dim=1))
+        else:
+            X = torch.empty(c, s, dtype=torch.float32, device=dev)
+            eq = [4, 4, 4]
+            while True:
+                flags = self._launch_activity(dev, pos, cm, mm, X, eq) if c > 0 else [0] * nat.N_FLAGS
+                if not _settle_early_exit(self._reduce_flags(flags), eq, 3):
+                    break
+        if c > 0:
+            self.cell_molecules = self._launch_scatter(dev, X, pos, mm)
+
+    def _all_ranks_empty(self) -> bool:
+        return self.n_cells == 0
+
+    @torch.no_grad()
+    def diffuse_molecules(self):
+        """world.py:627-665"""
+        dev = self._device_for_step()
+        mm, cm, pos = self._state_on_device(dev)
+        m, H, W = mm.shape
+        if m == 0:
+            return
+        top, bottom = self._exchange_halos(mm)
+        out, sums = self._launch_stencil(dev, mm, top, bottom)
+        sums = self._reduce_sums(sums)
+        self._launch_correct(dev, out, mm, sums, self._n_pixels_total(H, W))
+        if self.n_cells == 0:
+            return
+        self.cell_molecules = self._launch_permeate(dev, cm, mm, pos)
 
     def degrade_molecules(self):
         """world.py:667-678 (per-molecule scalar decay; plain tensor ops, not a kernel of this package)"""
@@ -320,12 +371,13 @@ class World:
         return list(zip(parent_idxs, child_idxs))
 
     # ------------------------------------------------------------------ helpers
-    def _get_molecule_map(self, n: int, size: int, init: str) -> torch.Tensor:
+    def _get_molecule_map(self, n: int, size, init: str) -> torch.Tensor:
         """world.py:922-933"""
+        rows, cols = (size, size) if isinstance(size, int) else size
         if init == "zeros":
-            return torch.zeros(n, size, size, device=self.device, dtype=torch.float32)
+            return torch.zeros(n, rows, cols, device=self.device, dtype=torch.float32)
         if init == "randn":
-            return (torch.randn(n, size, size, dtype=torch.float32, device=self.device) + 10.0).abs()
+            return (torch.randn(n, rows, cols, dtype=torch.float32, device=self.device) + 10.0).abs()
         raise ValueError(f"Didnt recognize mol_map_init={init}. Should be one of: 'zeros', 'randn'.")
 
     def _expand_c(self, t: torch.Tensor, n: int) -> torch.Tensor:

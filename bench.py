@@ -121,7 +121,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def build_world(args, device, seed):
+def build_world(args, device, seed, world_size=1):
     import torch
     import magicsoup_b200 as ms
     from magicsoup_b200.synthetic import make_population
@@ -129,7 +129,15 @@ def build_world(args, device, seed):
     pop = make_population(args.cells, args.proteins, args.molecules, args.map, seed=seed, device=device)
     mols = [ms.Molecule(f"b{i}", 10e3, diffusivity=pop.diffusivities[i], permeability=pop.permeabilities[i])
             for i in range(pop.m)]
-    world = ms.World(chemistry=ms.Chemistry(molecules=mols, reactions=[]), map_size=args.map, device=str(device))
+    chem = ms.Chemistry(molecules=mols, reactions=[])
+    if world_size > 1:
+        # every rank owns one (map x map) row slab of a (world_size*map x map) torus and the
+        # cells on it: halo rows, plane sums and early-exit flags go over NCCL every step
+        from magicsoup_b200.distributed import SlabWorld
+
+        world = SlabWorld(chemistry=chem, global_map_size=(args.map * world_size, args.map), device=str(device))
+    else:
+        world = ms.World(chemistry=chem, map_size=args.map, device=str(device))
     # install the population without the (c,p,s)-sized copies the append path would make
     world.molecule_map = pop.molecule_map
     world.cell_positions = pop.cell_positions
@@ -235,7 +243,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    world, pop = build_world(args, device, seed=rank)
+    world, pop = build_world(args, device, seed=rank, world_size=world_size)
     c, p, m = pop.c, pop.p, pop.m
     s = 2 * m
     torch.cuda.synchronize()

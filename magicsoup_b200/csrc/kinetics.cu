@@ -41,6 +41,7 @@ struct KinArgs {
   float *V_out;           // optional (c,p), n_parts == 1 only
   int e_ent, e_nnz, e_reg;  // list capacities (entries)
   int words_per_warp;     // shared memory words per warp
+  int smem_align;         // alignment of the warp regions in bytes (power of two)
   int sparse_enabled;     // 0 forces the dense path (p > 256 or s > 128)
   // Two tiers.  Tier 1 (small lists, 32 warps/SM) defers cells whose tile does not fit to
   // defer_list; tier 2 (lists sized for a full tile, few warps/SM) integrates exactly those
@@ -407,10 +408,12 @@ __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsig
   for (; pe < pend; pe += 4) {
     const unsigned wd = lds_u(pe);
     const float x = lds_f(xaddr | (wd & 0x3fcu));
-    float r = (wd & 0x400u) ? x : 1.0f;  // same multiplication order as powi()
-    if (wd & 0x7ffff800u) {              // exponent >= 2
-      float b = x * x;
-      if (wd & 0x800u) r = r * b;
+    // same multiplication order as powi(); exponents 1..3 (99.8 %) without a branch
+    float r = (wd & 0x400u) ? x : 1.0f;
+    float b = x * x;
+    const float rb = r * b;
+    r = (wd & 0x800u) ? rb : r;
+    if (wd & 0x7ffff000u) {  // exponent >= 4
       unsigned n = (wd >> 12) & 0x7ffffu;
 #pragma unroll 1
       while (n) {
@@ -693,9 +696,9 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(const __grid
   const int warps_per_cta = blockDim.x >> 5;
   if (threadIdx.x < MS_N_FLAGS) sflags[threadIdx.x] = 0;
   __syncthreads();
-  // warp regions start at a 1 KB aligned shared address (see the layout comment)
+  // warp regions start at an address aligned to the largest array stride (layout comment)
   const unsigned raw = (unsigned)__cvta_generic_to_shared(smem);
-  const unsigned aligned = (raw + 1023u) & ~1023u;
+  const unsigned aligned = (raw + (unsigned)a.smem_align - 1u) & ~((unsigned)a.smem_align - 1u);
   unsigned *wbase = smem + ((aligned - raw) >> 2) + (size_t)warp * a.words_per_warp;
   const unsigned wshared = aligned + (unsigned)warp * (unsigned)a.words_per_warp * 4u;
   const int p = a.p, s = a.s, s32 = pow2_at_least_32(s);
@@ -860,7 +863,7 @@ __global__ void fill_kernel(float *x, long long n, float v) {
 // host side
 // ---------------------------------------------------------------------------
 struct LaunchPlan {
-  int e_ent, e_nnz, e_reg, words_per_warp, sparse_enabled, grid, warps_per_cta;
+  int e_ent, e_nnz, e_reg, words_per_warp, sparse_enabled, grid, warps_per_cta, align;
   size_t smem_bytes;
 };
 
@@ -878,12 +881,17 @@ static int sm_count() {
 
 constexpr size_t SMEM_PER_SM = 222 * 1024;   // usable per SM (227 KB max per CTA on sm_100a)
 constexpr size_t SMEM_PER_CTA_MAX = 200 * 1024;
-constexpr size_t SMEM_ALIGN_SLACK = 1024;  // the kernel aligns its warp regions to 1 KB
+constexpr size_t SMEM_PER_SM_HW = 227 * 1024;  // sm_100a: 228 KB per SM, 1 KB reserved per CTA
 
 static bool sparse_possible(int64_t p, int64_t s) { return p >= 1 && p <= 256 && s >= 1 && s <= MAX_S_SPARSE; }
 
+static int align_bytes(int64_t p, int64_t s) {
+  const int S2 = pow2_at_least_32((int)s), P2 = pow2_at_least_32((int)p);
+  return 4 * (S2 > P2 ? S2 : P2);
+}
+
 static void finish_plan(LaunchPlan &pl) {
-  size_t per_sm = SMEM_PER_SM / (pl.smem_bytes + 1024);
+  size_t per_sm = (SMEM_PER_SM_HW + 1024) / (pl.smem_bytes + 1024);
   if (per_sm > 4) per_sm = 4;
   if (per_sm < 1) per_sm = 1;
   pl.grid = sm_count() * (int)per_sm;
@@ -903,13 +911,14 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   pl.e_nnz = round32(e_nnz < full ? e_nnz : full);
   pl.e_reg = round32(e_reg < full ? e_reg : full);
   pl.warps_per_cta = WARPS_PER_CTA;
+  pl.align = align_bytes(p, s);
   pl.words_per_warp = make_layout((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg).words;
-  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + SMEM_ALIGN_SLACK;
+  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + pl.align;
   if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
     pl.sparse_enabled = 0;
     pl.e_ent = pl.e_nnz = pl.e_reg = 0;
     pl.words_per_warp = 4 * pow2_at_least_32((int)s);
-    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + SMEM_ALIGN_SLACK;
+    pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + pl.align;
   }
   finish_plan(pl);
   return pl;
@@ -923,14 +932,15 @@ static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
   pl.e_nnz = pl.e_reg = round32((int)(p * s));
   pl.e_ent = 2 * pl.e_nnz;
   if (pl.e_ent > 0xffff) return false;  // 16-bit list offsets
+  pl.align = align_bytes(p, s);
   pl.words_per_warp = make_layout((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg).words;
   const size_t per_warp = (size_t)pl.words_per_warp * 4;
-  if (per_warp + SMEM_ALIGN_SLACK > SMEM_PER_CTA_MAX) return false;
+  if (per_warp + pl.align > SMEM_PER_CTA_MAX) return false;
   int w = (int)((SMEM_PER_SM / 2) / per_warp);
   if (w < 1) w = 1;
   if (w > WARPS_PER_CTA) w = WARPS_PER_CTA;
   pl.warps_per_cta = w;
-  pl.smem_bytes = per_warp * w + SMEM_ALIGN_SLACK;
+  pl.smem_bytes = per_warp * w + pl.align;
   finish_plan(pl);
   return true;
 }
@@ -956,6 +966,7 @@ template <typename K>
 static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
   MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
   a.e_ent = pl.e_ent; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
+  a.smem_align = pl.align;
   a.sparse_enabled = pl.sparse_enabled;
   kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);
   MS_CUDA_CHECK(cudaGetLastError());

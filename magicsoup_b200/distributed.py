@@ -175,34 +175,30 @@ class SlabWorld(World):
         Move every local cell whose (local) row left the slab -- after the caller changed
         `cell_positions`, e.g. a division or move across the slab boundary -- to the rank
         that owns its pixel.  Collective: every rank must call it.  Returns the number of
-        cells received.  Local indices are compacted exactly like `kill_cells` does.
+        cells received.  Local indices are compacted exactly like `kill_cells` does
+        (world.py:527-540); received cells are appended.
         """
         H = self.global_map_size[0]
         gpos = self.global_positions()
-        gpos[:, 0] = gpos[:, 0] % H
+        gpos[:, 0] = gpos[:, 0] % H  # the map is a torus
         owner = self.owner_of_rows(gpos[:, 0].long())
         leaving = torch.nonzero(owner != self.rank).flatten().tolist()
-        payloads: list[dict[str, torch.Tensor] | None] = [None] * self.world_size
+        outgoing: list[dict[str, torch.Tensor] | None] = [None] * self.world_size
         for dst in range(self.world_size):
             idxs = [i for i in leaving if int(owner[i]) == dst]
             if idxs:
-                pl = self.export_cells(idxs)
-                pl["positions"][:, 0] = pl["positions"][:, 0] % H
-                payloads[dst] = {k: v.cpu() for k, v in pl.items()}
-        if leaving:  # remove without spilling molecules onto the map: the cells live on
-            xs = self.cell_positions[leaving, 0].long().clamp(0, self.slab_rows - 1)
+                payload = self.export_cells(idxs)
+                payload["positions"][:, 0] = payload["positions"][:, 0] % H
+                outgoing[dst] = {k: v.cpu() for k, v in payload.items()}
+        if leaving:
             self._drop_cells(leaving)
-            del xs
-        inbox: list[Any] = [None] * self.world_size
-        dist.all_to_all_object = getattr(dist, "all_to_all_object", None)
         gathered: list[Any] = [None] * self.world_size
-        dist.all_gather_object(gathered, payloads, group=self.group)
+        dist.all_gather_object(gathered, outgoing, group=self.group)
         received = 0
         for src in range(self.world_size):
-            pl = gathered[src][self.rank]
-            if pl is not None:
-                received += len(self.import_cells(pl))
-        del inbox
+            payload = gathered[src][self.rank]
+            if payload is not None:
+                received += len(self.import_cells(payload))
         return received
 
     def _drop_cells(self, cell_idxs: list[int]):

@@ -1,0 +1,39 @@
+"""
+Multi-GPU parity (needs >= 2 CUDA devices; skipped on a single-GPU box): N ranks over NCCL,
+each owning a row slab and its cells, must reproduce the single-domain CPU oracle bit for
+bit (tests/dist_worker.py).  Run by hand with
+    gpurun --gpus 2 -- 'python -m pytest tests/test_gpu_distributed.py -m gpu -q'
+"""
+import os
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("shape", [(300, 16, 24), (20000, 128, 128)], ids=["generic-stencil", "tiled-stencil"])
+def test_nccl_slab_world_matches_oracle(shape):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    nproc = min(n, 4)
+    cells, rows, cols = shape
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           str(ROOT / "tests" / "dist_worker.py"), "--backend", "nccl", "--cells", str(cells),
+           "--rows-per-rank", str(rows), "--cols", str(cols)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=dict(os.environ))
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "dist_worker ok" in res.stdout

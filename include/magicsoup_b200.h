@@ -181,6 +181,29 @@ int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, i
                        int64_t W, int64_t n_pxls_total, void *stream);
 
 /*
+ * ms_diffuse_molecules without scratch from the caller -- no counterpart in the reference.
+ * For hosts that cannot allocate device memory around the call (all memory already handed to
+ * their own pool, or a step loop that must avoid the device-wide synchronisation that
+ * cudaMalloc / cudaFree imply): the stencil output and the plane sums live in a fixed
+ * `static __device__` array inside the library, so the call allocates nothing and needs no
+ * scratch argument.  Same arithmetic and results as ms_diffuse_molecules.
+ *   - Limit: m * H * W <= ms_diffuse_static_max_floats() (4 Mi floats = 16 MiB, e.g. 16 planes
+ *     of 512 x 512) and m <= 256.  Larger maps are rejected with MS_ERR_TOO_LARGE and
+ *     ms_diffuse_static_last_error() says which limit was hit; nothing is launched.
+ *   - Every GPU that loads the library carries the 16 MiB array until the process exits.
+ *   - All calls on one GPU share that array; calls that overlap on the device (e.g. from two
+ *     streams) race on it.  Its contents survive between calls and are never assumed zero:
+ *     each call clears the sums it accumulates into and rewrites the output before reading it.
+ *   - The first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current); make that first call before any
+ *     stream capture begins.
+ */
+int ms_diffuse_molecules_static(float *molecule_map, const float *a, const float *b, int64_t m,
+                                int64_t H, int64_t W, void *stream);
+int64_t ms_diffuse_static_max_floats(void);
+const char *ms_diffuse_static_last_error(void);
+
+/*
  * World.diffuse_molecules(), permeation half                   world.py:651-665
  * perm[k] from World._get_permeate (world.py:935-946).  cell_molecules_out may
  * alias cell_molecules_in; molecule_map is updated at the cells' pixels.

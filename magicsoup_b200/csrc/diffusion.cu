@@ -227,6 +227,9 @@ __global__ void scatter_kernel(const float *X, const int *pos, long long c, int 
 
 using namespace ms;
 
+#include <stdio.h>
+static thread_local char g_static_too_large_msg[320] = "";
+
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 extern "C" size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W) {
@@ -327,3 +330,82 @@ extern "C" int ms_scatter_signals(const float *X, const int32_t *cell_positions,
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Diffusion without any caller-provided or allocated scratch.
+//
+// Who needs this: hosts that embed the library but may not allocate device memory when they
+// call it -- for example an application that hands all device memory to its own pool at
+// start-up and forbids cudaMalloc afterwards, or a step loop that must not hit the implicit
+// device synchronisation of cudaMalloc/cudaFree.  ms_diffuse_molecules makes such a caller
+// carve ms_diffuse_scratch_bytes() out of its own memory; this variant needs nothing: the
+// stencil output and the plane sums live in a fixed array inside the library image.
+//
+// The price: the array has a fixed size (MS_STATIC_DIFFUSE_MAX_FLOATS floats = 16 MiB, plus
+// MS_STATIC_DIFFUSE_MAX_PLANES plane sums) that every GPU which loads the library holds
+// until the process exits, and ALL calls on one GPU share it: two calls that overlap on the
+// device (different streams) race on it.  The array keeps whatever the previous call left;
+// the stencil output is fully rewritten before it is read, and the plane sums are cleared by
+// every call before use.
+// ---------------------------------------------------------------------------
+#include <mutex>
+
+#define MS_STATIC_DIFFUSE_MAX_FLOATS (4ll * 1024 * 1024)
+#define MS_STATIC_DIFFUSE_MAX_PLANES 256
+
+static __device__ __align__(256) float g_static_diffuse_out[MS_STATIC_DIFFUSE_MAX_FLOATS];
+static __device__ __align__(256) unsigned long long g_static_diffuse_sums[4 * MS_STATIC_DIFFUSE_MAX_PLANES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+struct StaticScratch {
+  float *out = nullptr;
+  unsigned long long *sums = nullptr;
+};
+StaticScratch g_static_scratch[kMaxDevices];
+std::mutex g_static_scratch_mutex;
+}  // namespace
+
+// The names above are host-side stand-ins in host code, not device addresses: the device
+// address of the copy that lives on the CURRENT device is looked up once per device.
+static int static_scratch_for_current_device(StaticScratch &res) {
+  int dev = -1;
+  MS_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return MS_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch[dev].out == nullptr) {
+    void *out = nullptr, *sums = nullptr;
+    MS_CUDA_CHECK(cudaGetSymbolAddress(&out, g_static_diffuse_out));
+    MS_CUDA_CHECK(cudaGetSymbolAddress(&sums, g_static_diffuse_sums));
+    g_static_scratch[dev].out = (float *)out;
+    g_static_scratch[dev].sums = (unsigned long long *)sums;
+  }
+  res = g_static_scratch[dev];
+  return MS_OK;
+}
+
+extern "C" int64_t ms_diffuse_static_max_floats(void) { return MS_STATIC_DIFFUSE_MAX_FLOATS; }
+
+extern "C" int ms_diffuse_molecules_static(float *molecule_map, const float *a, const float *b,
+                                           int64_t m, int64_t H, int64_t W, void *stream) {
+  if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!molecule_map || !a || !b) return MS_ERR_INVALID_ARGUMENT;
+  if (m > MS_STATIC_DIFFUSE_MAX_PLANES || m * H * W > MS_STATIC_DIFFUSE_MAX_FLOATS) {
+    snprintf(g_static_too_large_msg, sizeof(g_static_too_large_msg),
+             "ms_diffuse_molecules_static: map of %lld x %lld x %lld floats exceeds the built-in scratch of "
+             "%lld floats / %d planes; use ms_diffuse_molecules with caller scratch",
+             (long long)m, (long long)H, (long long)W, (long long)MS_STATIC_DIFFUSE_MAX_FLOATS,
+             MS_STATIC_DIFFUSE_MAX_PLANES);
+    return MS_ERR_TOO_LARGE;
+  }
+  StaticScratch sc;
+  int rc = static_scratch_for_current_device(sc);
+  if (rc != MS_OK) return rc;
+  // stencil_launch clears the plane sums (cudaMemsetAsync) before accumulating into them
+  rc = stencil_launch(molecule_map, nullptr, nullptr, a, b, m, H, W, sc.out, sc.sums, (cudaStream_t)stream);
+  if (rc != MS_OK) return rc;
+  return correct_launch(sc.out, molecule_map, m, H, W, (long long)H * W, sc.sums, (cudaStream_t)stream);
+}
+
+extern "C" const char *ms_diffuse_static_last_error(void) { return g_static_too_large_msg; }

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     lib = nat.lib()
     for name in declared:
         assert hasattr(lib, name), name
-    assert declared <= set(nat.exported_symbols()) | {"ms_diffuse_molecules_static"}
+    assert declared <= set(nat.exported_symbols())
     assert lib.ms_version() >= 100
     assert lib.ms_error_string(-3).decode().startswith("scratch")
     assert lib.ms_kinetics_scratch_bytes(1000, 64, 32) > 4000

@@ -524,6 +524,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     for (int k = 0; k < iters; k++) {
       const float inc = eq_increment(k);
       unsigned mine = 0;
+      bool changed = false;
 #pragma unroll 1
       for (int t = lane; t < n_act; t += 32) {
         const unsigned aw = lds_u(w.aAct() + 4 * t);
@@ -537,15 +538,24 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
         const unsigned dec = eq_decide_fast(lds_f(aV | j4), quotient_fixed(xb, xf), lds_f(w.aKe() | j4), F);
         if (dec & 3u) {
           mine |= (dec & 4u) ? 3u : 2u;
-          sts_f(aF | j4, eq_update(F, dec, inc));
+          const float Fn = eq_update(F, dec, inc);
+          changed |= (Fn != F);
+          sts_f(aF | j4, Fn);
         }
       }
       const unsigned any = __reduce_or_sync(FULL, mine);
+      // If no F moved (adjustable proteins can sit clamped at 0 or 1), X1 would be recomputed
+      // bit-identically and every later iteration of this part repeats this one exactly: same
+      // decisions, same flags, no change.  Report the flags for those iterations and stop.
+      const bool moved = __any_sync(FULL, changed);
       if (lane == 0 && any) {
-        if (any & 1u) sflags[q * 4 + k] = 1u;
-        sflags[12 + q * 4 + k] = 1u;
+        const int k_end = moved ? k + 1 : iters;
+        for (int kk = k; kk < k_end; kk++) {
+          if (any & 1u) sflags[q * 4 + kk] = 1u;
+          sflags[12 + q * 4 + kk] = 1u;
+        }
       }
-      if (!any) break;  // no adjustable protein: F, X1 and every later iteration are unchanged
+      if (!moved) break;
       __syncwarp();
 #pragma unroll 1
       for (int i = lane; i < s; i += 32) {

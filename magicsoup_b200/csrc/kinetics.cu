@@ -12,12 +12,15 @@
 // on those lists out of shared memory.  Cells whose tiles do not fit the lists or the
 // 8-bit packing take a dense path straight from global memory with identical
 // arithmetic.  See DESIGN.md for the layout, the spec order and the roofline.
+#include <stdlib.h>
+
 #include "ms_common.cuh"
 
 namespace ms {
 
 constexpr int WARPS_PER_CTA = 8;
 constexpr int THREADS = WARPS_PER_CTA * 32;
+constexpr int MAX_THREADS = 1024;
 constexpr int MAX_S_SPARSE = 256;  // 8-bit signal / protein indices in the packed lists
 constexpr unsigned FULL = 0xffffffffu;
 
@@ -166,6 +169,12 @@ __device__ __forceinline__ void sts_f(unsigned addr, float v) {
 __device__ __forceinline__ void atom_min_shared(unsigned addr, unsigned v) {
   asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
+
+// asynchronous 4-byte global -> shared copies (LDGSTS): no registers, latency overlaps the scan
+__device__ __forceinline__ void cp_async4(unsigned saddr, const void *gptr) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // order-preserving unsigned key of a float; NaN maps to 0 so that it wins the atomic min
 // (torch.min propagates NaN, kinetics.py:877)
@@ -317,6 +326,13 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   }
   if (ent_tot > a.e_ent || nnz_tot > a.e_nnz || reg_tot > a.e_reg) return false;
   __syncwarp();
+  {  // Kmr of the (few) regulatory entries: asynchronous gather, overlapped with the sort below
+    const long long tile = cell * (long long)p * s;
+    for (int e = lane; e < reg_tot; e += 32) {
+      const unsigned wd = w.reg()[e];
+      cp_async4(w.aRegk() + 4 * e, a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
+    }
+  }
 
   // proteins with substrate/product entries, in ascending order
   int n_act = 0;
@@ -381,19 +397,7 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   }
   for (int e = lane; e < nnz_tot; e += 32) w.csc()[e] = sorted[e];
 
-  // per-protein scalars, and the Kmr values of the (few) regulatory entries
-  const long long prow = cell * (long long)p;
-  const long long tile = prow * s;
-  for (int j = lane; j < p; j += 32) {
-    w.Ke()[j] = __ldcs(a.Ke + prow + j);
-    w.Kmf()[j] = __ldcs(a.Kmf + prow + j);
-    w.Kmb()[j] = __ldcs(a.Kmb + prow + j);
-    w.Vmax()[j] = a.adj_vmax ? __ldcs(a.adj_vmax + prow + j) : __ldcs(a.Vmax + prow + j);
-  }
-  for (int e = lane; e < reg_tot; e += 32) {
-    const unsigned wd = w.reg()[e];
-    w.regk()[e] = __ldcs(a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
-  }
+  cp_async_wait_all();  // per-protein scalars (issued before the scan) and the Kmr gather
   __syncwarp();
   return true;
 }
@@ -404,7 +408,7 @@ __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsig
                                               float &xb) {
   xf = 1.0f;
   xb = 1.0f;
-#pragma unroll 1
+#pragma unroll 2
   for (; pe < pend; pe += 4) {
     const unsigned wd = lds_u(pe);
     const float x = lds_f(xaddr | (wd & 0x3fcu));
@@ -484,7 +488,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     for (int i = lane; i < s; i += 32) {
       const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
       float d = 0.0f;
-#pragma unroll 1
+#pragma unroll 2
       for (unsigned pc = c0; pc < c1; pc += 4) {
         const unsigned wd = lds_u(pc);
         const float nv = (float)((int)wd >> 10) * lds_f(aV | (wd & 0x3fcu));  // kinetics.py:759
@@ -496,7 +500,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       float f = lds_f(aX0 + 4 * i) / d;
       if (f > 1.0f) f = 1.0f;
       const unsigned key = fkey(f);
-#pragma unroll 1
+#pragma unroll 2
       for (unsigned pc = c0; pc < c1; pc += 4)  // every protein that removes signal i is limited by F_i
         if (lds_f(pc + dNvs) < 0.0f) atom_min_shared(aFk | (lds_u(pc) & 0x3fcu), key);
     }
@@ -506,7 +510,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     for (int i = lane; i < s; i += 32) {
       const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
       float acc = 0.0f;
-#pragma unroll 1
+#pragma unroll 2
       for (unsigned pc = c0; pc < c1; pc += 4) {
         const float nvp = lds_f(pc + dNvs) * fkey_decode(lds_u(aFk | (lds_u(pc) & 0x3fcu)));
         sts_f(pc + dNvs, nvp);
@@ -561,7 +565,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
       for (int i = lane; i < s; i += 32) {
         const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
         float acc = 0.0f;
-#pragma unroll 1
+#pragma unroll 2
         for (unsigned pc = c0; pc < c1; pc += 4)
           acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
         float x = clamp0(lds_f(aX0 + 4 * i) + acc);
@@ -698,7 +702,7 @@ __device__ __noinline__ void run_dense(const KinArgs &a, float *X0, float *X1, f
 }
 
 template <int VEC>
-__global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
+__global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
                                                                     float *dense_scratch) {
   extern __shared__ __align__(16) unsigned smem[];
   __shared__ unsigned sflags[MS_N_FLAGS];
@@ -716,31 +720,63 @@ __global__ void __launch_bounds__(THREADS, 4) kinetics_fused_kernel(const __grid
   const long long nw = (long long)gridDim.x * warps_per_cta;
   float *dscr = dense_scratch + gw * (size_t)(3 * round32(p));
   const long long n_items = a.tier == 2 ? (long long)*a.defer_count : a.c;
+  WarpMem w;
+  if (a.sparse_enabled) w = carve(wbase, wshared, p, s, a.e_ent, a.e_nnz, a.e_reg);
+  float *X0 = (float *)wbase, *X1 = X0 + s32, *Fsig = X1 + s32;
 
-  for (long long item = gw; item < n_items; item += nw) {
-    const long long cell = a.tier == 2 ? (long long)a.defer_list[item] : item;
-    float *X0 = (float *)wbase, *X1 = X0 + s32, *Fsig = X1 + s32;
-    // gather X0 (world.py:619-621) or read it
-    for (int i = lane; i < s; i += 32) {
-      float x;
-      if (a.X_in) {
-        x = a.X_in[cell * s + i];
-      } else if (i < a.m) {
-        x = a.cell_mols[cell * a.m + i];
-      } else {
-        const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
-        x = a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
+  // X0 of a cell: gathered (world.py:619-621) or read; lane i holds signals i, i+32 (s <= 64),
+  // so that the next cell's values can be fetched while the current cell is integrated
+  auto cell_of = [&](long long item) -> long long {
+    return a.tier == 2 ? (long long)a.defer_list[item] : item;
+  };
+  auto load_x = [&](long long cell, int i) -> float {
+    if (a.X_in) return a.X_in[cell * s + i];
+    if (i < a.m) return a.cell_mols[cell * a.m + i];
+    const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
+    return a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
+  };
+  const bool prefetch = s <= 64;
+  float xa = 0.0f, xb = 0.0f;
+  if (prefetch && gw < n_items) {
+    const long long c0 = cell_of(gw);
+    if (lane < s) xa = load_x(c0, lane);
+    if (lane + 32 < s) xb = load_x(c0, lane + 32);
+  }
+
+  const long long first_of_cta = (long long)blockIdx.x * warps_per_cta;
+  const long long n_rounds = first_of_cta < n_items ? (n_items - first_of_cta + nw - 1) / nw : 0;
+  for (long long round = 0; round < n_rounds; round++) {
+    const long long item = gw + round * nw;
+    if (item >= n_items) continue;
+    const long long cell = cell_of(item);
+    if (prefetch) {
+      if (lane < s) X0[lane] = xa;
+      if (lane + 32 < s) X0[lane + 32] = xb;
+    } else {
+      for (int i = lane; i < s; i += 32) X0[i] = load_x(cell, i);
+    }
+    if (a.sparse_enabled) {  // per-protein scalars: asynchronous copies that land during the scan
+      const long long prow = cell * (long long)p;
+      const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
+      for (int j = lane; j < p; j += 32) {
+        cp_async4(w.aKe() + 4 * j, a.Ke + prow + j);
+        cp_async4(w.aKmf() + 4 * j, a.Kmf + prow + j);
+        cp_async4(w.aKmb() + 4 * j, a.Kmb + prow + j);
+        cp_async4(w.aVmax() + 4 * j, gv + prow + j);
       }
-      X0[i] = x;
     }
     __syncwarp();
     bool sparse = false;
     int n_act = 0;
-    WarpMem w;
     if (a.sparse_enabled) {
-      w = carve(wbase, wshared, p, s, a.e_ent, a.e_nnz, a.e_reg);
       const int nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
       sparse = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
+      if (!sparse) cp_async_wait_all();
+    }
+    if (prefetch && item + nw < n_items) {  // next cell's signals: in flight during this cell's parts
+      const long long cn = cell_of(item + nw);
+      if (lane < s) xa = load_x(cn, lane);
+      if (lane + 32 < s) xb = load_x(cn, lane + 32);
     }
     if (sparse) {
       run_sparse(a, w, cell, lane, n_act, sflags);
@@ -904,6 +940,15 @@ static void finish_plan(LaunchPlan &pl) {
   size_t per_sm = (SMEM_PER_SM_HW + 1024) / (pl.smem_bytes + 1024);
   if (per_sm > 4) per_sm = 4;
   if (per_sm < 1) per_sm = 1;
+  // tuning knob: fewer resident CTAs per SM (the shared memory request is padded accordingly)
+  if (const char *env = getenv("MS_KIN_MAX_CTAS_PER_SM")) {
+    const size_t want = (size_t)atoi(env);
+    if (want >= 1 && want < per_sm) {
+      per_sm = want;
+      const size_t pad = (SMEM_PER_SM_HW + 1024) / (per_sm + 1) + 1024;  // too big for per_sm + 1 CTAs
+      if (pl.smem_bytes < pad && pad <= SMEM_PER_SM_HW) pl.smem_bytes = pad;
+    }
+  }
   pl.grid = sm_count() * (int)per_sm;
 }
 

@@ -19,8 +19,7 @@
 namespace ms {
 
 constexpr int WARPS_PER_CTA = 8;
-constexpr int THREADS = WARPS_PER_CTA * 32;
-constexpr int MAX_THREADS = 1024;
+constexpr int MAX_THREADS = 1024;  // launch bound; CTAs are launched with 8 warps (tier 1)
 constexpr int MAX_S_SPARSE = 256;  // 8-bit signal / protein indices in the packed lists
 constexpr unsigned FULL = 0xffffffffu;
 

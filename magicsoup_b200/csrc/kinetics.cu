@@ -52,6 +52,7 @@ struct KinArgs {
   int defer_enabled;      // tier 1: a tier-2 launch follows
   int *defer_count;       // device counter (zeroed before tier 1)
   int *defer_list;        // device list of deferred cell indices (capacity c)
+  int *work_counter;      // device counter handing out cells to warps (zeroed before the launch)
 };
 
 // ---------------------------------------------------------------------------
@@ -716,7 +717,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
   const unsigned wshared = aligned + (unsigned)warp * (unsigned)a.words_per_warp * 4u;
   const int p = a.p, s = a.s, s32 = pow2_at_least_32(s);
   const long long gw = (long long)blockIdx.x * warps_per_cta + warp;
-  const long long nw = (long long)gridDim.x * warps_per_cta;
   float *dscr = dense_scratch + gw * (size_t)(3 * round32(p));
   const long long n_items = a.tier == 2 ? (long long)*a.defer_count : a.c;
   WarpMem w;
@@ -734,19 +734,25 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
     const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
     return a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
   };
+  // Cells are handed out dynamically (one atomic per cell): with a static stride the slowest of
+  // the 4736 warps finishes several per cent after the average one.  A warp always holds its
+  // current item and the next one, so that the next cell's X0 can be fetched early.
+  auto grab = [&]() -> long long {
+    int v = 0;
+    if (lane == 0) v = atomicAdd(a.work_counter, 1);
+    return (long long)__shfl_sync(FULL, v, 0);
+  };
   const bool prefetch = s <= 64;
   float xa = 0.0f, xb = 0.0f;
-  if (prefetch && gw < n_items) {
-    const long long c0 = cell_of(gw);
+  long long item = grab();
+  if (prefetch && item < n_items) {
+    const long long c0 = cell_of(item);
     if (lane < s) xa = load_x(c0, lane);
     if (lane + 32 < s) xb = load_x(c0, lane + 32);
   }
 
-  const long long first_of_cta = (long long)blockIdx.x * warps_per_cta;
-  const long long n_rounds = first_of_cta < n_items ? (n_items - first_of_cta + nw - 1) / nw : 0;
-  for (long long round = 0; round < n_rounds; round++) {
-    const long long item = gw + round * nw;
-    if (item >= n_items) continue;
+  while (item < n_items) {
+    const long long next_item = grab();
     const long long cell = cell_of(item);
     if (prefetch) {
       if (lane < s) X0[lane] = xa;
@@ -772,8 +778,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
       sparse = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
       if (!sparse) cp_async_wait_all();
     }
-    if (prefetch && item + nw < n_items) {  // next cell's signals: in flight during this cell's parts
-      const long long cn = cell_of(item + nw);
+    if (prefetch && next_item < n_items) {  // next cell's signals: in flight during this cell's parts
+      const long long cn = cell_of(next_item);
       if (lane < s) xa = load_x(cn, lane);
       if (lane + 32 < s) xb = load_x(cn, lane + 32);
     }
@@ -781,6 +787,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
       run_sparse(a, w, cell, lane, n_act, sflags);
     } else if (a.tier == 1 && a.defer_enabled) {
       if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
+      item = next_item;
       continue;  // integrated by the tier-2 launch
     } else {
       __syncwarp();
@@ -788,6 +795,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
     }
     for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
     __syncwarp();
+    item = next_item;
   }
   __syncthreads();
   if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
@@ -1054,6 +1062,7 @@ static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, 
   if (!scratch || scratch_bytes < ms_kinetics_scratch_bytes(P->c, P->p, P->s)) return MS_ERR_SCRATCH_TOO_SMALL;
   float *dense = (float *)scratch;
   a.defer_count = (int *)((char *)scratch + dense_scratch_bytes(P->p));
+  a.work_counter = a.defer_count + 1;  // [0] deferred count, [1] tier-1 work, [2] tier-2 work
   a.defer_list = a.defer_count + 64;
 
   LaunchPlan p1 = plan_tier1(P->p, P->s), p2;
@@ -1062,11 +1071,12 @@ static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, 
   if (p1.grid > ctas_needed) p1.grid = (int)ctas_needed;
   a.tier = 1;
   a.defer_enabled = two_tiers ? 1 : 0;
-  if (two_tiers) MS_CUDA_CHECK(cudaMemsetAsync(a.defer_count, 0, sizeof(int), st));
+  MS_CUDA_CHECK(cudaMemsetAsync(a.defer_count, 0, 4 * sizeof(int), st));
   int rc = launch_plan(p1, a, dense, st);
   if (rc != MS_OK || !two_tiers) return rc;
   a.tier = 2;
   a.defer_enabled = 0;
+  a.work_counter = a.defer_count + 2;
   const int64_t ctas2 = ceil_div(P->c, p2.warps_per_cta);
   if (p2.grid > ctas2) p2.grid = (int)ctas2;
   return launch_plan(p2, a, dense, st);

@@ -53,6 +53,7 @@ struct KinArgs {
   int *defer_count;       // device counter (zeroed before tier 1)
   int *defer_list;        // device list of deferred cell indices (capacity c)
   int *work_counter;      // device counter handing out cells to warps (zeroed before the launch)
+  int batch_enabled;      // tier 1, p, s <= 64, 8 warps per CTA: the CTA integrates 8 cells together
 };
 
 // ---------------------------------------------------------------------------
@@ -584,6 +585,205 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
 }
 
 // ---------------------------------------------------------------------------
+// batch path: the 8 warps of a CTA integrate their 8 cells TOGETHER.  In the warp-per-cell
+// path a sweep costs as many loop iterations as the longest list among 32 proteins (signals),
+// three times the average.  Here the proteins (and the signals) of all 8 cells are pooled and
+// sorted by list length, so the 32 lanes of a warp walk lists of equal length.  Every item is
+// computed exactly as in run_sparse (same loops, same order), so results are bit-identical;
+// only the order in which independent items are visited changes.
+// ---------------------------------------------------------------------------
+constexpr int BATCH = 8;            // cells per CTA = warps per CTA
+constexpr int BATCH_MAX_PS = 64;    // p and s limit of the batch path (item tables below)
+constexpr unsigned CS_POISON = 1u, CS_IMP = 2u, CS_ANY = 4u, CS_MOVED = 8u;
+
+struct BatchShared {
+  unsigned short pitem[BATCH * BATCH_MAX_PS];  // slot << 12 | act word (protein*4 | side flags)
+  unsigned short citem[BATCH * BATCH_MAX_PS];  // slot << 8 | signal
+  unsigned hist_p[17], hist_c[33];             // bucket counters / cursors (longest lists first)
+  unsigned n_pitems, n_citems;
+  unsigned cell_state[BATCH];                  // CS_* bits of the current pass
+  unsigned cell_live[BATCH];                   // 1 while the cell still iterates in this part
+  unsigned n_live;
+  long long next_base;
+};
+
+__device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_bytes, BatchShared &bs,
+                          const long long *cells /* per slot, -1 = absent */, unsigned *sflags) {
+  const int tid = threadIdx.x, lane = tid & 31, slot_own = tid >> 5;
+  const int p = a.p, s = a.s;
+  const float qnan = __int_as_float(0x7fc00000);
+  const unsigned dNvs = 4u * (unsigned)(w0.oNvs - w0.oCsc);
+  const bool own = cells[slot_own] >= 0;
+  const unsigned sb_own = w0.sb + (unsigned)slot_own * region_bytes;
+  const unsigned oX1 = w0.aX1() - w0.sb, oV = w0.aV() - w0.sb, oF = w0.aF() - w0.sb, oFk = w0.aFk() - w0.sb;
+  const unsigned oRow = w0.aRow() - w0.sb, oEnt = w0.aEnt() - w0.sb, oCsc = w0.aCsc() - w0.sb;
+  const unsigned oCol = w0.aCol() - w0.sb, oKe = w0.aKe() - w0.sb, oKmf = w0.aKmf() - w0.sb;
+  const unsigned oKmb = w0.aKmb() - w0.sb, oVmax = w0.aVmax() - w0.sb, oReg = w0.aReg() - w0.sb;
+  const unsigned oRegk = w0.aRegk() - w0.sb;
+  const int n_p = (int)bs.n_pitems, n_c = (int)bs.n_citems;
+
+#pragma unroll 1
+  for (int q = 0; q < a.n_parts; q++) {
+    const float trim = a.trims[q];
+    const int iters = a.eq_iters[q];
+    if (own) {
+      for (int j = lane; j < p; j += 32) {
+        sts_f(sb_own + oV + 4 * j, 0.0f);
+        sts_f(sb_own + oF + 4 * j, 1.0f);
+        sts_u(sb_own + oFk + 4 * j, KEY_ONE);
+      }
+    }
+    if (tid < BATCH) {
+      bs.cell_state[tid] = 0;
+      bs.cell_live[tid] = (cells[tid] >= 0 && iters > 0) ? 1u : 0u;
+    }
+    __syncthreads();
+    // ---- velocities (kinetics.py:771-806)
+#pragma unroll 1
+    for (int it = tid; it < n_p; it += BATCH * 32) {
+      const unsigned item = bs.pitem[it];
+      const unsigned sb = w0.sb + (item >> 12) * region_bytes;
+      const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
+      const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
+      float xf, xb;
+      list_products(sb, sb + oEnt + 4 * (r0 & 0xffffu), sb + oEnt + 4 * (r1 & 0xffffu), xf, xb);
+      float kf = xf / lds_f((sb + oKmf) | j4);
+      if (!(aw & 0x400u)) kf = 0.0f;
+      if (isinf(kf)) kf = V_MAX;
+      float kb = xb / lds_f((sb + oKmb) | j4);
+      if (!(aw & 0x800u)) kb = 0.0f;
+      if (isinf(kb)) kb = V_MAX;
+      float a_reg = 1.0f;
+#pragma unroll 1
+      for (unsigned e = r0 >> 16; e < (r1 >> 16); e++) {
+        const unsigned wd = lds_u(sb + oReg + 4 * e);
+        a_reg = a_reg * reg_factor(lds_f(sb + 4 * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
+                                   lds_f(sb + oRegk + 4 * e));
+      }
+      float vmax = lds_f((sb + oVmax) | j4);
+      if (!a.adj_vmax) vmax = clamp0(vmax * trim);
+      const float v = velocity_from(kf, kb, a_reg, vmax);
+      sts_f((sb + oV) | j4, v);
+      if (isnan(v)) atomicOr(&bs.cell_state[item >> 12], CS_POISON);
+    }
+    __syncthreads();
+    // ---- substrate trimming (kinetics.py:861-879)
+#pragma unroll 1
+    for (int it = tid; it < n_c; it += BATCH * 32) {
+      const unsigned item = bs.citem[it];
+      const unsigned sb = w0.sb + (item >> 8) * region_bytes;
+      const unsigned i = item & 0xffu;
+      const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
+      const unsigned aV = sb + oV, aFk = sb + oFk;
+      float d = 0.0f;
+#pragma unroll 2
+      for (unsigned pc = c0; pc < c1; pc += 4) {
+        const unsigned wd = lds_u(pc);
+        const float nv = (float)((int)wd >> 10) * lds_f(aV | (wd & 0x3fcu));
+        sts_f(pc + dNvs, nv);
+        float neg = -nv;
+        neg = neg < 0.0f ? 0.0f : neg;
+        d = d + neg;
+      }
+      float f = lds_f(sb + 4 * i) / d;
+      if (f > 1.0f) f = 1.0f;
+      const unsigned key = fkey(f);
+#pragma unroll 2
+      for (unsigned pc = c0; pc < c1; pc += 4)
+        if (lds_f(pc + dNvs) < 0.0f) atom_min_shared(aFk | (lds_u(pc) & 0x3fcu), key);
+    }
+    __syncthreads();
+    // X1 = max(X0 + sum_j NV'_ji, 0)
+#pragma unroll 1
+    for (int it = tid; it < n_c; it += BATCH * 32) {
+      const unsigned item = bs.citem[it];
+      const unsigned slot = item >> 8, sb = w0.sb + slot * region_bytes, i = item & 0xffu;
+      const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
+      const unsigned aFk = sb + oFk;
+      float acc = 0.0f;
+#pragma unroll 2
+      for (unsigned pc = c0; pc < c1; pc += 4) {
+        const float nvp = lds_f(pc + dNvs) * fkey_decode(lds_u(aFk | (lds_u(pc) & 0x3fcu)));
+        sts_f(pc + dNvs, nvp);
+        acc = acc + nvp;
+      }
+      float x = clamp0(lds_f(sb + 4 * i) + acc);
+      if (bs.cell_state[slot] & CS_POISON) x = qnan;
+      sts_f(sb + oX1 + 4 * i, x);
+    }
+    __syncthreads();
+
+    // ---- equilibrium trimming (kinetics.py:808-859)
+#pragma unroll 1
+    for (int k = 0; k < iters; k++) {
+      const float inc = eq_increment(k);
+#pragma unroll 1
+      for (int it = tid; it < n_p; it += BATCH * 32) {
+        const unsigned item = bs.pitem[it];
+        const unsigned slot = item >> 12;
+        if (!bs.cell_live[slot]) continue;
+        const unsigned sb = w0.sb + slot * region_bytes;
+        const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
+        const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
+        float xf, xb;
+        list_products(sb + oX1, sb + oEnt + 4 * (r0 & 0xffffu), sb + oEnt + 4 * (r1 & 0xffffu), xf, xb);
+        if (!(aw & 0x400u)) xf = 0.0f;
+        if (!(aw & 0x800u)) xb = 0.0f;
+        const float F = lds_f((sb + oF) | j4);
+        const unsigned dec = eq_decide_fast(lds_f((sb + oV) | j4), quotient_fixed(xb, xf), lds_f((sb + oKe) | j4), F);
+        if (dec & 3u) {
+          const float Fn = eq_update(F, dec, inc);
+          sts_f((sb + oF) | j4, Fn);
+          atomicOr(&bs.cell_state[slot], ((dec & 4u) ? (CS_IMP | CS_ANY) : CS_ANY) | (Fn != F ? CS_MOVED : 0u));
+        }
+      }
+      __syncthreads();
+      if (tid < BATCH && bs.cell_live[tid]) {
+        const unsigned st = bs.cell_state[tid];
+        const bool moved = (st & CS_MOVED) != 0;
+        if (st & CS_ANY) {  // see run_sparse: an unmoved cell repeats this iteration exactly
+          const int k_end = moved ? k + 1 : iters;
+          for (int kk = k; kk < k_end; kk++) {
+            if (st & CS_IMP) sflags[q * 4 + kk] = 1u;
+            sflags[12 + q * 4 + kk] = 1u;
+          }
+        }
+        bs.cell_state[tid] = st & CS_POISON;
+        if (!moved) bs.cell_live[tid] = 0;
+      }
+      __syncthreads();
+      unsigned live = 0;
+#pragma unroll
+      for (int c = 0; c < BATCH; c++) live |= bs.cell_live[c];
+      if (!live) break;
+#pragma unroll 1
+      for (int it = tid; it < n_c; it += BATCH * 32) {
+        const unsigned item = bs.citem[it];
+        const unsigned slot = item >> 8;
+        if (!bs.cell_live[slot]) continue;
+        const unsigned sb = w0.sb + slot * region_bytes, i = item & 0xffu;
+        const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
+        const unsigned aF = sb + oF;
+        float acc = 0.0f;
+#pragma unroll 2
+        for (unsigned pc = c0; pc < c1; pc += 4) acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
+        float x = clamp0(lds_f(sb + 4 * i) + acc);
+        if (bs.cell_state[slot] & CS_POISON) x = qnan;
+        sts_f(sb + oX1 + 4 * i, x);
+      }
+      __syncthreads();
+    }
+
+    if (own) {
+      if (a.V_out)
+        for (int j = lane; j < p; j += 32) a.V_out[cells[slot_own] * (long long)p + j] = lds_f(sb_own + oV + 4 * j);
+      for (int i = lane; i < s; i += 32) sts_f(sb_own + 4 * i, lds_f(sb_own + oX1 + 4 * i));
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
 // dense path: same arithmetic straight from global memory (any p, s, any int32)
 // F, V, Fmin live in `scr` (global, 3*p floats per warp) when p is too large for
 // the shared arrays; X0/X1/Fsig always fit (s32 words are reserved per warp).
@@ -734,6 +934,113 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
     const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
     return a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
   };
+  if (a.batch_enabled) {
+    // ---- batch mode: 8 cells per CTA at a time, scanned per warp, integrated together
+    __shared__ BatchShared bs;
+    __shared__ long long batch_cells[BATCH];
+    const int tid = threadIdx.x;
+    const unsigned lt = (1u << lane) - 1u;
+    (void)lt;
+    if (tid == 0) bs.next_base = (long long)atomicAdd(a.work_counter, BATCH);
+    __syncthreads();
+    long long base = bs.next_base;
+    float xa = 0.0f, xb = 0.0f;
+    if (base + warp < n_items) {
+      if (lane < s) xa = load_x(base + warp, lane);
+      if (lane + 32 < s) xb = load_x(base + warp, lane + 32);
+    }
+    const unsigned region_bytes = (unsigned)a.words_per_warp * 4u;
+    const WarpMem w0 = carve(smem + ((aligned - raw) >> 2), aligned, p, s, a.e_ent, a.e_nnz, a.e_reg);
+    while (base < n_items) {
+      __syncthreads();  // the previous batch is finished, `base` has been read by everyone
+      if (tid == 0) bs.next_base = (long long)atomicAdd(a.work_counter, BATCH);
+      if (tid < 17) bs.hist_p[tid] = 0;
+      if (tid < 33) bs.hist_c[tid] = 0;
+      const long long cell = base + warp;
+      const bool present = cell < n_items;
+      int n_act = 0;
+      bool ok = false;
+      if (present) {
+        if (lane < s) X0[lane] = xa;
+        if (lane + 32 < s) X0[lane + 32] = xb;
+        const long long prow = cell * (long long)p;
+        const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
+        for (int j = lane; j < p; j += 32) {
+          cp_async4(w.aKe() + 4 * j, a.Ke + prow + j);
+          cp_async4(w.aKmf() + 4 * j, a.Kmf + prow + j);
+          cp_async4(w.aKmb() + 4 * j, a.Kmb + prow + j);
+          cp_async4(w.aVmax() + 4 * j, gv + prow + j);
+        }
+        __syncwarp();
+        const int nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
+        ok = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
+        if (!ok) {
+          cp_async_wait_all();
+          if (a.defer_enabled) {
+            if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
+          } else {
+            __syncwarp();
+            run_dense(a, X0, X1, Fsig, dscr, dscr + round32(p), dscr + 2 * round32(p), cell, lane, sflags);
+            for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
+          }
+        }
+      }
+      if (lane == 0) batch_cells[warp] = ok ? cell : -1;
+      __syncthreads();  // histograms are zero, next_base is visible
+      const long long next_base = bs.next_base;
+      if (next_base + warp < n_items) {  // next cell's signals: in flight during this batch
+        if (lane < s) xa = load_x(next_base + warp, lane);
+        if (lane + 32 < s) xb = load_x(next_base + warp, lane + 32);
+      }
+      // pool the proteins and signals of the 8 cells, longest lists first (counting sort)
+      unsigned aw_mine[2] = {0, 0}, len_p[2] = {0, 0}, len_c[2] = {0, 0};
+      if (ok) {
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+          const int t = lane + 32 * r;
+          if (t < n_act) {
+            aw_mine[r] = w.act()[t];
+            const unsigned j = (aw_mine[r] & 0x3fcu) >> 2;
+            len_p[r] = min((w.rowptr()[j + 1] & 0xffffu) - (w.rowptr()[j] & 0xffffu), 16u);
+            atomicAdd(&bs.hist_p[16 - len_p[r]], 1u);
+          }
+          if (t < s) {
+            len_c[r] = min(w.colptr()[t + 1] - w.colptr()[t], 32u);
+            atomicAdd(&bs.hist_c[32 - len_c[r]], 1u);
+          }
+        }
+      }
+      __syncthreads();
+      if (tid == 0) {
+        unsigned run = 0;
+        for (int b = 0; b < 17; b++) { const unsigned c_ = bs.hist_p[b]; bs.hist_p[b] = run; run += c_; }
+        bs.n_pitems = run;
+        run = 0;
+        for (int b = 0; b < 33; b++) { const unsigned c_ = bs.hist_c[b]; bs.hist_c[b] = run; run += c_; }
+        bs.n_citems = run;
+      }
+      __syncthreads();
+      if (ok) {
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+          const int t = lane + 32 * r;
+          if (t < n_act)
+            bs.pitem[atomicAdd(&bs.hist_p[16 - len_p[r]], 1u)] = (unsigned short)(((unsigned)warp << 12) | (aw_mine[r] & 0xfffu));
+          if (t < s)
+            bs.citem[atomicAdd(&bs.hist_c[32 - len_c[r]], 1u)] = (unsigned short)(((unsigned)warp << 8) | (unsigned)t);
+        }
+      }
+      __syncthreads();
+      run_batch(a, w0, region_bytes, bs, batch_cells, sflags);
+      if (ok)
+        for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
+      base = next_base;
+    }
+    __syncthreads();
+    if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
+    return;
+  }
+
   // Cells are handed out dynamically (one atomic per cell): with a static stride the slowest of
   // the 4736 warps finishes several per cent after the average one.  A warp always holds its
   // current item and the next one, so that the next cell's X0 can be fetched early.
@@ -965,7 +1272,7 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   pl.sparse_enabled = sparse_possible(p, s) ? 1 : 0;
   const int full = (int)(p * s);
   // e_nnz also bounds the element queue (all non-zero positions of the tile)
-  int e_ent = (int)(5 * p), e_nnz = (int)((7 * p + 1) / 2), e_reg = (int)p;
+  int e_ent = (int)((9 * p + 1) / 2), e_nnz = (int)((7 * p + 1) / 2), e_reg = (int)p;
   if (e_ent < 64) e_ent = 64;
   if (e_nnz < 64) e_nnz = 64;
   if (e_reg < 32) e_reg = 32;
@@ -1029,6 +1336,8 @@ static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cu
   MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
   a.e_ent = pl.e_ent; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
   a.smem_align = pl.align;
+  a.batch_enabled = (a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS && a.s <= BATCH_MAX_PS &&
+                     pl.warps_per_cta == BATCH && !getenv("MS_KIN_NO_BATCH")) ? 1 : 0;
   a.sparse_enabled = pl.sparse_enabled;
   kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);
   MS_CUDA_CHECK(cudaGetLastError());

@@ -215,7 +215,7 @@ __device__ __forceinline__ void load_vec(const int *ptr, bool ok, int (&v)[VEC])
 // Returns the queue length, or -1 if the tile does not fit the queue / the packing.
 // ---------------------------------------------------------------------------
 template <int VEC>
-__device__ int scan_tile(const KinArgs &a, unsigned *queue, int cap, long long tile, int lane) {
+__device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap, long long tile, int lane) {
   const int s = a.s, total = a.p * s;
   const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
   const unsigned lt = (1u << lane) - 1u;

@@ -14,6 +14,8 @@ Fixtures
                            pushed through the reference stage by stage and end to
                            end, incl. the reference's own summation-order noise
                            floor (same inputs, proteins permuted).
+  ref_drift_1000.npz       population statistics of a 1000-step reference trajectory (and of
+                           the reference with permuted proteins) every 100 steps.
   ref_world.npz            World.diffuse_molecules / enzymatic_activity on small
                            maps incl. the 5x5 known-answer map of
                            tests/fast/test_world.py:8-51.
@@ -192,6 +194,37 @@ def synthetic_fixture(ms, tag, c, p, m, map_size, seed, n_steps):
           f"last={d['noise_floor_last']:.4f}")
 
 
+def drift_fixture(ms, c=96, p=20, m=6, n_steps=1000, seed=21):
+    """
+    north_star: "drift over 1000 steps".  Population statistics of the reference's own
+    trajectory (and of the same run with its proteins permuted = the reference's own drift)
+    every 100 steps; parameters and X0 are regenerated from the seed by the test.
+    """
+    pop = make_population(c, p, m, 16, seed=seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    perm = torch.randperm(p, generator=g)
+    out = {"shape": np.array([c, p, m, 16, seed, n_steps])}
+    for tag, pr in (("ref", None), ("perm", perm)):
+        kin = _ref_kinetics(ms, pop, pr)
+        X = pop.X0().clone()
+        means, zeros, q99, tot = [], [], [], []
+        for step in range(1, n_steps + 1):
+            X = kin.integrate_signals(X=X)
+            if step % 100 == 0:
+                x = _np(X)
+                means.append(x.mean(0))
+                zeros.append((x == 0).mean())
+                q99.append(np.quantile(x, 0.99, axis=0))
+                tot.append(x.sum(dtype=np.float64))
+        out[f"{tag}_mean"] = np.stack(means)
+        out[f"{tag}_zero_frac"] = np.array(zeros)
+        out[f"{tag}_q99"] = np.stack(q99)
+        out[f"{tag}_total"] = np.array(tot)
+        out[f"{tag}_final"] = _np(X)
+    np.savez_compressed(OUT / "ref_drift_1000.npz", **out)
+    print("drift fixture: total mass ref", out["ref_total"][-1], "perm", out["perm_total"][-1])
+
+
 def world_fixture(ms):
     d: dict[str, np.ndarray] = {}
     # (1) the 5x5 known-answer map of tests/fast/test_world.py:8-51
@@ -260,6 +293,7 @@ def main():
     synthetic_fixture(ms, "c1", c=100, p=22, m=4, map_size=16, seed=11, n_steps=20)
     synthetic_fixture(ms, "wl", c=256, p=35, m=14, map_size=32, seed=12, n_steps=20)
     synthetic_fixture(ms, "two", c=2, p=6, m=3, map_size=4, seed=13, n_steps=30)
+    drift_fixture(ms)
     world_fixture(ms)
 
 

@@ -343,3 +343,27 @@ def test_large_population_invariants(ms):
     assert bits_equal(out[idx], ora), describe_mismatch(out[idx], ora)
     # idempotent launch: same inputs, same bits
     assert torch.equal(out, kin.integrate_signals(X=X))
+
+
+def test_drift_over_1000_steps_gpu(ms):
+    # 1000 steps on the device: bit-identical to the oracle every 100 steps, and within the
+    # reference's own drift bounds (tests/test_oracle_golden.py::check_drift)
+    from tests.test_oracle_golden import drift_population, check_drift
+
+    z, pop, n_steps = drift_population()
+    kin = install(_kinetics(ms, pop.s), pop)
+    P = oracle_params(pop)
+    X = pop.X0().cuda()
+    Xo = pop.X0().numpy()
+    stats = {"mean": [], "q99": [], "total": [], "zero_frac": []}
+    for step in range(1, n_steps + 1):
+        X = kin.integrate_signals(X=X)
+        Xo = O.integrate_signals(P, Xo)
+        if step % 100 == 0:
+            x = X.cpu().numpy()
+            assert bits_equal(x, Xo), f"step {step}: " + describe_mismatch(x, Xo)
+            stats["mean"].append(x.mean(0))
+            stats["q99"].append(np.quantile(x, 0.99, axis=0))
+            stats["total"].append(x.sum(dtype=np.float64))
+            stats["zero_frac"].append((x == 0).mean())
+    check_drift(z, {k: np.array(v) for k, v in stats.items()})

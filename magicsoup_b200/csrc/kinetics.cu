@@ -190,6 +190,15 @@ __device__ __forceinline__ float fkey_decode(unsigned k) {
 }
 constexpr unsigned KEY_ONE = 0xbf800000u;  // fkey(1.0f)
 
+#ifndef MS_TUNE_SCAN_PIPE
+#define MS_TUNE_SCAN_PIPE 0
+#endif
+
+template <int VEC>
+struct TileVec {  // VEC consecutive elements of the four integer tiles
+  int nf[VEC], nb[VEC], nn[VEC], na[VEC];
+};
+
 template <int VEC>
 __device__ __forceinline__ void load_vec(const int *ptr, bool ok, int (&v)[VEC]) {
   if (!ok) {
@@ -208,10 +217,53 @@ __device__ __forceinline__ void load_vec(const int *ptr, bool ok, int (&v)[VEC])
   }
 }
 
+template <int VEC>
+__device__ __forceinline__ int pick(const int (&v)[VEC], int e) {
+  if constexpr (VEC == 4) {
+    const int lo = (e & 1) ? v[1] : v[0], hi = (e & 1) ? v[3] : v[2];
+    return (e & 2) ? hi : lo;
+  } else if constexpr (VEC == 2) {
+    return (e & 1) ? v[1] : v[0];
+  } else {
+    return v[0];
+  }
+}
+
+// Pushes the non-zero elements of one 32*VEC-element step (lane-major, i.e. row-major order).
+template <int VEC>
+__device__ __forceinline__ void push_step(const TileVec<VEC> &t, unsigned *queue, int cap, int row, int sig0,
+                                          unsigned lt, int &nq, int &chk) {
+  unsigned mask = 0;
+#pragma unroll
+  for (int e = 0; e < VEC; e++) mask |= ((t.nf[e] | t.nb[e] | t.nn[e] | t.na[e]) != 0 ? 1u : 0u) << e;
+  if (__ballot_sync(FULL, mask != 0) == 0) return;
+  int pos = nq;
+#pragma unroll
+  for (int e = 0; e < VEC; e++) {
+    const unsigned be = __ballot_sync(FULL, (mask >> e) & 1u);
+    pos += __popc(be & lt);
+    nq += __popc(be);
+  }
+#pragma unroll 1
+  while (mask) {  // most lanes hold no element, the others one or (rarely) more
+    const int e = __ffs(mask) - 1;
+    mask &= mask - 1u;
+    const int nf = pick<VEC>(t.nf, e), nb = pick<VEC>(t.nb, e), nn = pick<VEC>(t.nn, e), na = pick<VEC>(t.na, e);
+    // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
+    chk |= ((nf | nb) & 0xffffff00) | ((nn + 32768) & 0xffff0000) | ((na + 128) & 0xffffff00);
+    if (pos < cap)
+      *reinterpret_cast<uint2 *>(queue + 2 * pos) =
+          make_uint2((unsigned)(sig0 + e) | ((unsigned)row << 8) | ((unsigned)(na & 0xff) << 16),
+                     ((unsigned)nf & 0xffu) | (((unsigned)nb & 0xffu) << 8) | ((unsigned)nn << 16));
+    pos++;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // scan, phase 1: stream the cell's dense tile once (32*VEC consecutive elements per load
 // instruction, row-major) and push every element with a non-zero Nf, Nb, N or A onto a
-// queue in shared memory (2 words per element), in row-major order.
+// queue in shared memory (2 words per element, 8-byte aligned), in row-major order.  The
+// loads of a step are issued before the previous step is pushed (two register sets).
 // Returns the queue length, or -1 if the tile does not fit the queue / the packing.
 // ---------------------------------------------------------------------------
 template <int VEC>
@@ -224,45 +276,40 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
   int q0 = lane * VEC;
   int row = q0 / s, sig0 = q0 - row * s;
   int nq = 0, chk = 0;
-#pragma unroll 1
-  for (int base = 0; base < total; base += STEP) {
-    const bool ok = q0 < total;
-    int nf[VEC], nb[VEC], nn[VEC], na[VEC];
-    load_vec<VEC>(gNf + q0, ok, nf);
-    load_vec<VEC>(gNb + q0, ok, nb);
-    load_vec<VEC>(gN + q0, ok, nn);
-    load_vec<VEC>(gA + q0, ok, na);
-    unsigned mask = 0;
-#pragma unroll
-    for (int e = 0; e < VEC; e++) mask |= ((nf[e] | nb[e] | nn[e] | na[e]) != 0 ? 1u : 0u) << e;
-    if (__ballot_sync(FULL, mask != 0) != 0) {
-      int pos = nq;
-#pragma unroll
-      for (int e = 0; e < VEC; e++) {
-        const unsigned be = __ballot_sync(FULL, (mask >> e) & 1u);
-        pos += __popc(be & lt);
-        nq += __popc(be);
-      }
-#pragma unroll
-      for (int e = 0; e < VEC; e++) {
-        if ((mask >> e) & 1u) {
-          // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
-          chk |= ((nf[e] | nb[e]) & 0xffffff00) | ((nn[e] + 32768) & 0xffff0000) |
-                 ((na[e] + 128) & 0xffffff00);
-          if (pos < cap) {
-            queue[2 * pos] = (unsigned)(sig0 + e) | ((unsigned)row << 8) | ((unsigned)(na[e] & 0xff) << 16);
-            queue[2 * pos + 1] = ((unsigned)nf[e] & 0xffu) | (((unsigned)nb[e] & 0xffu) << 8) |
-                                 ((unsigned)nn[e] << 16);
-          }
-          pos++;
-        }
-      }
-    }
+  auto fetch = [&](TileVec<VEC> &t, int q) {
+    const bool ok = q < total;
+    load_vec<VEC>(gNf + q, ok, t.nf);
+    load_vec<VEC>(gNb + q, ok, t.nb);
+    load_vec<VEC>(gN + q, ok, t.nn);
+    load_vec<VEC>(gA + q, ok, t.na);
+  };
+  auto advance = [&]() {
     q0 += STEP;
     row += drow;
     sig0 += dsig;
     if (sig0 >= s) { sig0 -= s; row++; }
+  };
+#if MS_TUNE_SCAN_PIPE
+  TileVec<VEC> t0, t1;
+  fetch(t0, q0);
+#pragma unroll 1
+  for (int base = 0; base < total; base += 2 * STEP) {
+    fetch(t1, q0 + STEP);
+    push_step<VEC>(t0, queue, cap, row, sig0, lt, nq, chk);
+    advance();
+    fetch(t0, q0 + STEP);
+    push_step<VEC>(t1, queue, cap, row, sig0, lt, nq, chk);
+    advance();
   }
+#else
+#pragma unroll 1
+  for (int base = 0; base < total; base += STEP) {
+    TileVec<VEC> t0;
+    fetch(t0, q0);
+    push_step<VEC>(t0, queue, cap, row, sig0, lt, nq, chk);
+    advance();
+  }
+#endif
   if (__any_sync(FULL, chk != 0) || nq > cap) return -1;
   return nq;
 }
@@ -403,33 +450,84 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   return true;
 }
 
+// tuning switches (defaults are the measured best; -D overrides are for the A/B builds of
+// profiles/ab_variants.py)
+#ifndef MS_TUNE_UNROLL_C
+#define MS_TUNE_UNROLL_C 2
+#endif
+#ifndef MS_TUNE_UNROLL_P
+#define MS_TUNE_UNROLL_P 2
+#endif
+#ifndef MS_TUNE_PIPE_P
+#define MS_TUNE_PIPE_P 1
+#endif
+#ifndef MS_TUNE_BOOK_WARP
+#define MS_TUNE_BOOK_WARP 7
+#endif
+#ifndef MS_TUNE_SNAKE
+#define MS_TUNE_SNAKE 1
+#endif
+constexpr int UNROLL_C = MS_TUNE_UNROLL_C, UNROLL_P = MS_TUNE_UNROLL_P;
+constexpr bool SNAKE = MS_TUNE_SNAKE != 0;
+
+// One list entry's factor x^n: same multiplication order as powi(); exponents 1..3 (99.8 %)
+// without a branch.  An all-zero word is a neutral entry (factor 1 on the substrate side).
+__device__ __forceinline__ float entry_factor(unsigned wd, float x) {
+  float r = (wd & 0x400u) ? x : 1.0f;
+  float b = x * x;
+  const float rb = r * b;
+  r = (wd & 0x800u) ? rb : r;
+  unsigned n = wd & 0x7ffff000u;  // exponent >> 2, still in place
+  if (n) {                        // exponent >= 4
+#pragma unroll 1
+    do {
+      b = b * b;
+      if (n & 0x1000u) r = r * b;
+      n = (n >> 1) & 0x7ffff000u;
+    } while (n);
+  }
+  return r;
+}
+
 // products over a protein's substrate and product entries (kinetics.py:894-918), each side
 // in ascending signal order.  xaddr: shared address of X0 or X1 (aligned to its stride).
 __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsigned pend, float &xf,
                                               float &xb) {
   xf = 1.0f;
   xb = 1.0f;
-#pragma unroll 2
+#if MS_TUNE_PIPE_P
+  // W entries per trip; the next trip's entry words are fetched before this trip's signal
+  // values, so that one shared-memory latency (not two) separates consecutive trips.  A list
+  // whose length is not a multiple of W ends with neutral entries (x * 1.0f is exact).
+  constexpr int W = MS_TUNE_PIPE_P == 1 ? 2 : MS_TUNE_PIPE_P;
+  unsigned wd[W];
+#pragma unroll
+  for (int e = 0; e < W; e++) wd[e] = pe + 4 * e < pend ? lds_u(pe + 4 * e) : 0u;
+#pragma unroll 1
+  for (; pe < pend; pe += 4 * W) {
+    unsigned nx[W];
+    float x[W];
+#pragma unroll
+    for (int e = 0; e < W; e++) nx[e] = pe + 4 * (W + e) < pend ? lds_u(pe + 4 * (W + e)) : 0u;
+#pragma unroll
+    for (int e = 0; e < W; e++) x[e] = lds_f(xaddr | (wd[e] & 0x3fcu));
+#pragma unroll
+    for (int e = 0; e < W; e++) {
+      const float r = entry_factor(wd[e], x[e]);
+      if ((int)wd[e] < 0) xb = xb * r;
+      else xf = xf * r;
+      wd[e] = nx[e];
+    }
+  }
+#else
+#pragma unroll UNROLL_P
   for (; pe < pend; pe += 4) {
     const unsigned wd = lds_u(pe);
-    const float x = lds_f(xaddr | (wd & 0x3fcu));
-    // same multiplication order as powi(); exponents 1..3 (99.8 %) without a branch
-    float r = (wd & 0x400u) ? x : 1.0f;
-    float b = x * x;
-    const float rb = r * b;
-    r = (wd & 0x800u) ? rb : r;
-    if (wd & 0x7ffff000u) {  // exponent >= 4
-      unsigned n = (wd >> 12) & 0x7ffffu;
-#pragma unroll 1
-      while (n) {
-        b = b * b;
-        if (n & 1u) r = r * b;
-        n >>= 1;
-      }
-    }
+    const float r = entry_factor(wd, lds_f(xaddr | (wd & 0x3fcu)));
     if ((int)wd < 0) xb = xb * r;
     else xf = xf * r;
   }
+#endif
   xf = fix_product(xf);
   xb = fix_product(xb);
 }
@@ -596,19 +694,54 @@ constexpr int BATCH = 8;            // cells per CTA = warps per CTA
 constexpr int BATCH_MAX_PS = 64;    // p and s limit of the batch path (item tables below)
 constexpr unsigned CS_POISON = 1u, CS_IMP = 2u, CS_ANY = 4u, CS_MOVED = 8u;
 
+constexpr int ITEMS_PER_WARP = BATCH_MAX_PS;  // 8 * 64 pooled items over 8 warps
+
+// The sorted item sequence is dealt to the warps in chunks of 32, and each warp's chunks are stored
+// contiguously: sorted position -> index in pitem / citem.  A sweep lasts as long as its slowest
+// warp (the sweeps are separated by CTA barriers), and that is the warp with chunk 0, the longest
+// lists.  The chunks after the first eight are therefore dealt backwards (chunk 8 to warp 7, ...),
+// and the per-iteration flag bookkeeping is done by lanes of warp 7, which has the shortest lists.
+__device__ __forceinline__ unsigned item_index(unsigned pos) {
+  const unsigned chunk = pos >> 5;
+  const unsigned owner = SNAKE ? (chunk < BATCH ? chunk : 2 * BATCH - 1 - chunk) : (chunk & (BATCH - 1));
+  return owner * ITEMS_PER_WARP + (chunk / BATCH) * 32 + (pos & 31u);
+}
+// number of the n sorted items that land in `warp`'s list
+__device__ __forceinline__ int items_of_warp(int n, int warp) {
+  const int a = n - 32 * warp, b = n - 32 * (SNAKE ? 2 * BATCH - 1 - warp : BATCH + warp);
+  return min(max(a, 0), 32) + min(max(b, 0), 32);
+}
+
 struct BatchShared {
-  unsigned short pitem[BATCH * BATCH_MAX_PS];  // slot << 12 | act word (protein*4 | side flags)
-  unsigned short citem[BATCH * BATCH_MAX_PS];  // slot << 8 | signal
-  unsigned hist_p[17], hist_c[33];             // bucket counters / cursors (longest lists first)
-  unsigned n_pitems, n_citems;
-  unsigned cell_state[BATCH];                  // CS_* bits of the current pass
-  unsigned cell_live[BATCH];                   // 1 while the cell still iterates in this part
-  unsigned n_live;
+  unsigned short pitem[BATCH * ITEMS_PER_WARP];  // slot << 12 | act word (protein*4 | side flags)
+  unsigned short citem[BATCH * ITEMS_PER_WARP];  // slot << 8 | signal
+  unsigned cnt_p[17], cnt_c[33];                 // items per list-length bucket (longest lists first)
+  unsigned cur_p[17], cur_c[33];                 // placement cursors inside the buckets
+  unsigned cell_state[2][BATCH];                 // CS_IMP/ANY/MOVED of equilibrium iteration k in [k & 1]
+  unsigned cell_poison[BATCH];                   // a velocity of the cell is NaN in this part
   long long next_base;
 };
 
+// Regulatory factors of one cell from its X0 (kinetics.py:789-799), one lane per entry, into the
+// cell's act array (free once the items are pooled); the velocity sweep multiplies them up in
+// list order.  They depend on X0 only, so every warp does this for its own cell outside the
+// sweeps, where the 1-3 entries of a regulated protein would otherwise prolong its lane.
+__device__ __forceinline__ void regulation_pass(unsigned sb, unsigned oRow, unsigned oReg, unsigned oRegk,
+                                                unsigned oAct, int p, int lane) {
+  const unsigned n_reg = lds_u(sb + oRow + 4u * (unsigned)p) >> 16;
+  for (unsigned e = lane; e < n_reg; e += 32) {
+    const unsigned wd = lds_u(sb + oReg + 4 * e);
+    sts_f(sb + oAct + 4 * e, reg_factor(lds_f(sb + 4 * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
+                                        lds_f(sb + oRegk + 4 * e)));
+  }
+}
+
+// On entry (and again at the end of every part) V = 0, F = 1, FminKey = 1 in every present cell's
+// region, its regulatory factors are in place, cell_state and cell_poison are zero, and a CTA
+// barrier has been passed.
 __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_bytes, BatchShared &bs,
-                          const long long *cells /* per slot, -1 = absent */, unsigned *sflags) {
+                          const long long *cells /* per slot, -1 = absent */, int n_pitems, int n_citems,
+                          unsigned *sflags) {
   const int tid = threadIdx.x, lane = tid & 31, slot_own = tid >> 5;
   const int p = a.p, s = a.s;
   const float qnan = __int_as_float(0x7fc00000);
@@ -619,29 +752,21 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
   const unsigned oRow = w0.aRow() - w0.sb, oEnt = w0.aEnt() - w0.sb, oCsc = w0.aCsc() - w0.sb;
   const unsigned oCol = w0.aCol() - w0.sb, oKe = w0.aKe() - w0.sb, oKmf = w0.aKmf() - w0.sb;
   const unsigned oKmb = w0.aKmb() - w0.sb, oVmax = w0.aVmax() - w0.sb, oReg = w0.aReg() - w0.sb;
-  const unsigned oRegk = w0.aRegk() - w0.sb;
-  const int n_p = (int)bs.n_pitems, n_c = (int)bs.n_citems;
+  const unsigned oRegk = w0.aRegk() - w0.sb, oAct = w0.aAct() - w0.sb;
+  // this warp's share of the pooled items
+  const unsigned short *pmine = bs.pitem + slot_own * ITEMS_PER_WARP;
+  const unsigned short *cmine = bs.citem + slot_own * ITEMS_PER_WARP;
+  const int n_p = items_of_warp(n_pitems, slot_own), n_c = items_of_warp(n_citems, slot_own);
+  if (a.n_parts <= 0) __syncthreads();  // callers rely on a barrier at the end
 
 #pragma unroll 1
   for (int q = 0; q < a.n_parts; q++) {
     const float trim = a.trims[q];
     const int iters = a.eq_iters[q];
-    if (own) {
-      for (int j = lane; j < p; j += 32) {
-        sts_f(sb_own + oV + 4 * j, 0.0f);
-        sts_f(sb_own + oF + 4 * j, 1.0f);
-        sts_u(sb_own + oFk + 4 * j, KEY_ONE);
-      }
-    }
-    if (tid < BATCH) {
-      bs.cell_state[tid] = 0;
-      bs.cell_live[tid] = (cells[tid] >= 0 && iters > 0) ? 1u : 0u;
-    }
-    __syncthreads();
     // ---- velocities (kinetics.py:771-806)
 #pragma unroll 1
-    for (int it = tid; it < n_p; it += BATCH * 32) {
-      const unsigned item = bs.pitem[it];
+    for (int it = lane; it < n_p; it += 32) {
+      const unsigned item = pmine[it];
       const unsigned sb = w0.sb + (item >> 12) * region_bytes;
       const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
       const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
@@ -655,28 +780,24 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       if (isinf(kb)) kb = V_MAX;
       float a_reg = 1.0f;
 #pragma unroll 1
-      for (unsigned e = r0 >> 16; e < (r1 >> 16); e++) {
-        const unsigned wd = lds_u(sb + oReg + 4 * e);
-        a_reg = a_reg * reg_factor(lds_f(sb + 4 * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
-                                   lds_f(sb + oRegk + 4 * e));
-      }
+      for (unsigned e = r0 >> 16; e < (r1 >> 16); e++) a_reg = a_reg * lds_f(sb + oAct + 4 * e);
       float vmax = lds_f((sb + oVmax) | j4);
       if (!a.adj_vmax) vmax = clamp0(vmax * trim);
       const float v = velocity_from(kf, kb, a_reg, vmax);
       sts_f((sb + oV) | j4, v);
-      if (isnan(v)) atomicOr(&bs.cell_state[item >> 12], CS_POISON);
+      if (isnan(v)) bs.cell_poison[item >> 12] = 1u;
     }
     __syncthreads();
     // ---- substrate trimming (kinetics.py:861-879)
 #pragma unroll 1
-    for (int it = tid; it < n_c; it += BATCH * 32) {
-      const unsigned item = bs.citem[it];
+    for (int it = lane; it < n_c; it += 32) {
+      const unsigned item = cmine[it];
       const unsigned sb = w0.sb + (item >> 8) * region_bytes;
       const unsigned i = item & 0xffu;
       const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
       const unsigned aV = sb + oV, aFk = sb + oFk;
       float d = 0.0f;
-#pragma unroll 2
+#pragma unroll UNROLL_C
       for (unsigned pc = c0; pc < c1; pc += 4) {
         const unsigned wd = lds_u(pc);
         const float nv = (float)((int)wd >> 10) * lds_f(aV | (wd & 0x3fcu));
@@ -688,40 +809,44 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       float f = lds_f(sb + 4 * i) / d;
       if (f > 1.0f) f = 1.0f;
       const unsigned key = fkey(f);
-#pragma unroll 2
+#pragma unroll UNROLL_C
       for (unsigned pc = c0; pc < c1; pc += 4)
         if (lds_f(pc + dNvs) < 0.0f) atom_min_shared(aFk | (lds_u(pc) & 0x3fcu), key);
     }
     __syncthreads();
     // X1 = max(X0 + sum_j NV'_ji, 0)
 #pragma unroll 1
-    for (int it = tid; it < n_c; it += BATCH * 32) {
-      const unsigned item = bs.citem[it];
+    for (int it = lane; it < n_c; it += 32) {
+      const unsigned item = cmine[it];
       const unsigned slot = item >> 8, sb = w0.sb + slot * region_bytes, i = item & 0xffu;
       const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
       const unsigned aFk = sb + oFk;
       float acc = 0.0f;
-#pragma unroll 2
+#pragma unroll UNROLL_C
       for (unsigned pc = c0; pc < c1; pc += 4) {
         const float nvp = lds_f(pc + dNvs) * fkey_decode(lds_u(aFk | (lds_u(pc) & 0x3fcu)));
         sts_f(pc + dNvs, nvp);
         acc = acc + nvp;
       }
       float x = clamp0(lds_f(sb + 4 * i) + acc);
-      if (bs.cell_state[slot] & CS_POISON) x = qnan;
+      if (bs.cell_poison[slot]) x = qnan;
       sts_f(sb + oX1 + 4 * i, x);
     }
     __syncthreads();
 
     // ---- equilibrium trimming (kinetics.py:808-859)
+    // A cell iterates as long as one of its F moved in the previous iteration (see run_sparse);
+    // CS_MOVED of iteration k - 1 is therefore the cell's "still iterating" flag of iteration k.
 #pragma unroll 1
     for (int k = 0; k < iters; k++) {
       const float inc = eq_increment(k);
+      unsigned *st_cur = bs.cell_state[k & 1], *st_prv = bs.cell_state[(k & 1) ^ 1];
+      int moved_mine = 0;
 #pragma unroll 1
-      for (int it = tid; it < n_p; it += BATCH * 32) {
-        const unsigned item = bs.pitem[it];
+      for (int it = lane; it < n_p; it += 32) {
+        const unsigned item = pmine[it];
         const unsigned slot = item >> 12;
-        if (!bs.cell_live[slot]) continue;
+        if (k > 0 && !(st_prv[slot] & CS_MOVED)) continue;
         const unsigned sb = w0.sb + slot * region_bytes;
         const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
         const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
@@ -734,50 +859,59 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         if (dec & 3u) {
           const float Fn = eq_update(F, dec, inc);
           sts_f((sb + oF) | j4, Fn);
-          atomicOr(&bs.cell_state[slot], ((dec & 4u) ? (CS_IMP | CS_ANY) : CS_ANY) | (Fn != F ? CS_MOVED : 0u));
+          atomicOr(&st_cur[slot], ((dec & 4u) ? (CS_IMP | CS_ANY) : CS_ANY) | (Fn != F ? CS_MOVED : 0u));
+          moved_mine |= (Fn != F) ? 1 : 0;
         }
       }
-      __syncthreads();
-      if (tid < BATCH && bs.cell_live[tid]) {
-        const unsigned st = bs.cell_state[tid];
-        const bool moved = (st & CS_MOVED) != 0;
+      const int any_moved = __syncthreads_or(moved_mine);
+      if (slot_own == MS_TUNE_BOOK_WARP && lane < BATCH) {  // flags of this iteration; runs beside the X1 sweep
+        const int tid = lane;
+        const unsigned st = st_cur[tid];
         if (st & CS_ANY) {  // see run_sparse: an unmoved cell repeats this iteration exactly
-          const int k_end = moved ? k + 1 : iters;
+          const int k_end = (st & CS_MOVED) ? k + 1 : iters;
           for (int kk = k; kk < k_end; kk++) {
             if (st & CS_IMP) sflags[q * 4 + kk] = 1u;
             sflags[12 + q * 4 + kk] = 1u;
           }
         }
-        bs.cell_state[tid] = st & CS_POISON;
-        if (!moved) bs.cell_live[tid] = 0;
+        st_prv[tid] = 0;  // becomes iteration k + 1's state; its readers finished before the barrier
       }
-      __syncthreads();
-      unsigned live = 0;
-#pragma unroll
-      for (int c = 0; c < BATCH; c++) live |= bs.cell_live[c];
-      if (!live) break;
+      if (!any_moved) break;
 #pragma unroll 1
-      for (int it = tid; it < n_c; it += BATCH * 32) {
-        const unsigned item = bs.citem[it];
+      for (int it = lane; it < n_c; it += 32) {
+        const unsigned item = cmine[it];
         const unsigned slot = item >> 8;
-        if (!bs.cell_live[slot]) continue;
+        if (!(st_cur[slot] & CS_MOVED)) continue;
         const unsigned sb = w0.sb + slot * region_bytes, i = item & 0xffu;
         const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
         const unsigned aF = sb + oF;
         float acc = 0.0f;
-#pragma unroll 2
+#pragma unroll UNROLL_C
         for (unsigned pc = c0; pc < c1; pc += 4) acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
         float x = clamp0(lds_f(sb + 4 * i) + acc);
-        if (bs.cell_state[slot] & CS_POISON) x = qnan;
+        if (bs.cell_poison[slot]) x = qnan;
         sts_f(sb + oX1 + 4 * i, x);
       }
       __syncthreads();
     }
 
+    // this part's result is the next part's start; arrays and flags back to their entry state
     if (own) {
       if (a.V_out)
         for (int j = lane; j < p; j += 32) a.V_out[cells[slot_own] * (long long)p + j] = lds_f(sb_own + oV + 4 * j);
       for (int i = lane; i < s; i += 32) sts_f(sb_own + 4 * i, lds_f(sb_own + oX1 + 4 * i));
+      __syncwarp();
+      if (q + 1 < a.n_parts) regulation_pass(sb_own, oRow, oReg, oRegk, oAct, p, lane);
+      for (int j = lane; j < p; j += 32) {
+        sts_f(sb_own + oV + 4 * j, 0.0f);  // proteins without substrate/product entries have V = 0
+        sts_f(sb_own + oF + 4 * j, 1.0f);
+        sts_u(sb_own + oFk + 4 * j, KEY_ONE);
+      }
+    }
+    if (tid < BATCH) {
+      bs.cell_state[0][tid] = 0;
+      bs.cell_state[1][tid] = 0;
+      bs.cell_poison[tid] = 0;
     }
     __syncthreads();
   }
@@ -939,8 +1073,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
     __shared__ BatchShared bs;
     __shared__ long long batch_cells[BATCH];
     const int tid = threadIdx.x;
-    const unsigned lt = (1u << lane) - 1u;
-    (void)lt;
     if (tid == 0) bs.next_base = (long long)atomicAdd(a.work_counter, BATCH);
     __syncthreads();
     long long base = bs.next_base;
@@ -949,13 +1081,16 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
       if (lane < s) xa = load_x(base + warp, lane);
       if (lane + 32 < s) xb = load_x(base + warp, lane + 32);
     }
+    __syncthreads();  // everyone has read next_base
     const unsigned region_bytes = (unsigned)a.words_per_warp * 4u;
     const WarpMem w0 = carve(smem + ((aligned - raw) >> 2), aligned, p, s, a.e_ent, a.e_nnz, a.e_reg);
     while (base < n_items) {
-      __syncthreads();  // the previous batch is finished, `base` has been read by everyone
+      // The previous batch ended with a CTA barrier (end of run_batch), and everything written
+      // here was last read before it.
       if (tid == 0) bs.next_base = (long long)atomicAdd(a.work_counter, BATCH);
-      if (tid < 17) bs.hist_p[tid] = 0;
-      if (tid < 33) bs.hist_c[tid] = 0;
+      if (tid < 17) bs.cnt_p[tid] = bs.cur_p[tid] = 0;
+      if (tid < 33) bs.cnt_c[tid] = bs.cur_c[tid] = 0;
+      if (tid < BATCH) bs.cell_state[0][tid] = bs.cell_state[1][tid] = bs.cell_poison[tid] = 0;
       const long long cell = base + warp;
       const bool present = cell < n_items;
       int n_act = 0;
@@ -983,17 +1118,19 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
             run_dense(a, X0, X1, Fsig, dscr, dscr + round32(p), dscr + 2 * round32(p), cell, lane, sflags);
             for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
           }
+        } else {
+          for (int j = lane; j < p; j += 32) {  // run_batch's entry state
+            sts_f(w.aV() + 4 * j, 0.0f);
+            sts_f(w.aF() + 4 * j, 1.0f);
+            sts_u(w.aFk() + 4 * j, KEY_ONE);
+          }
         }
       }
       if (lane == 0) batch_cells[warp] = ok ? cell : -1;
-      __syncthreads();  // histograms are zero, next_base is visible
-      const long long next_base = bs.next_base;
-      if (next_base + warp < n_items) {  // next cell's signals: in flight during this batch
-        if (lane < s) xa = load_x(next_base + warp, lane);
-        if (lane + 32 < s) xb = load_x(next_base + warp, lane + 32);
-      }
-      // pool the proteins and signals of the 8 cells, longest lists first (counting sort)
-      unsigned aw_mine[2] = {0, 0}, len_p[2] = {0, 0}, len_c[2] = {0, 0};
+      // pool the proteins and signals of the 8 cells, longest lists first (counting sort);
+      // lane t holds protein act[t], act[t + 32] and signals t, t + 32
+      unsigned aw_mine[2] = {0, 0}, bkt_p[2] = {0, 0}, bkt_c[2] = {0, 0};
+      bool has_p[2] = {false, false}, has_c[2] = {false, false};
       if (ok) {
 #pragma unroll
         for (int r = 0; r < 2; r++) {
@@ -1001,37 +1138,59 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
           if (t < n_act) {
             aw_mine[r] = w.act()[t];
             const unsigned j = (aw_mine[r] & 0x3fcu) >> 2;
-            len_p[r] = min((w.rowptr()[j + 1] & 0xffffu) - (w.rowptr()[j] & 0xffffu), 16u);
-            atomicAdd(&bs.hist_p[16 - len_p[r]], 1u);
+            bkt_p[r] = 16u - min((w.rowptr()[j + 1] & 0xffffu) - (w.rowptr()[j] & 0xffffu), 16u);
+            has_p[r] = true;
           }
           if (t < s) {
-            len_c[r] = min(w.colptr()[t + 1] - w.colptr()[t], 32u);
-            atomicAdd(&bs.hist_c[32 - len_c[r]], 1u);
+            bkt_c[r] = 32u - min(w.colptr()[t + 1] - w.colptr()[t], 32u);
+            has_c[r] = true;
           }
         }
       }
-      __syncthreads();
-      if (tid == 0) {
-        unsigned run = 0;
-        for (int b = 0; b < 17; b++) { const unsigned c_ = bs.hist_p[b]; bs.hist_p[b] = run; run += c_; }
-        bs.n_pitems = run;
-        run = 0;
-        for (int b = 0; b < 33; b++) { const unsigned c_ = bs.hist_c[b]; bs.hist_c[b] = run; run += c_; }
-        bs.n_citems = run;
+      if (ok) {  // act has been read: it now receives the regulatory factors of the first part
+        __syncwarp();
+        regulation_pass(w.sb, w.aRow() - w.sb, w.aReg() - w.sb, w.aRegk() - w.sb, w.aAct() - w.sb, p, lane);
+      }
+      __syncthreads();  // counters are zero, next_base is visible
+      const long long next_base = bs.next_base;
+      if (next_base + warp < n_items) {  // next cell's signals: in flight during this batch
+        if (lane < s) xa = load_x(next_base + warp, lane);
+        if (lane + 32 < s) xb = load_x(next_base + warp, lane + 32);
+      }
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        if (has_p[r]) atomicAdd(&bs.cnt_p[bkt_p[r]], 1u);
+        if (has_c[r]) atomicAdd(&bs.cnt_c[bkt_c[r]], 1u);
       }
       __syncthreads();
-      if (ok) {
+      // every warp scans the two histograms for itself: lane b holds the first position of bucket b
+      unsigned cp_ = lane < 17 ? bs.cnt_p[lane] : 0u, cc_ = bs.cnt_c[lane];
+      unsigned ip = cp_, ic = cc_;
 #pragma unroll
-        for (int r = 0; r < 2; r++) {
-          const int t = lane + 32 * r;
-          if (t < n_act)
-            bs.pitem[atomicAdd(&bs.hist_p[16 - len_p[r]], 1u)] = (unsigned short)(((unsigned)warp << 12) | (aw_mine[r] & 0xfffu));
-          if (t < s)
-            bs.citem[atomicAdd(&bs.hist_c[32 - len_c[r]], 1u)] = (unsigned short)(((unsigned)warp << 8) | (unsigned)t);
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned yp = __shfl_up_sync(FULL, ip, d), yc = __shfl_up_sync(FULL, ic, d);
+        if (lane >= d) {
+          ip += yp;
+          ic += yc;
         }
       }
+      const int n_pitems = (int)__shfl_sync(FULL, ip, 31);
+      const unsigned first32 = __shfl_sync(FULL, ic, 31);  // bucket 32 (empty lists) starts here
+      const int n_citems = (int)(first32 + bs.cnt_c[32]);
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        const unsigned off_p = __shfl_sync(FULL, ip - cp_, (int)bkt_p[r]);
+        unsigned off_c = __shfl_sync(FULL, ic - cc_, (int)(bkt_c[r] & 31u));
+        if (bkt_c[r] == 32u) off_c = first32;
+        if (has_p[r])
+          bs.pitem[item_index(off_p + atomicAdd(&bs.cur_p[bkt_p[r]], 1u))] =
+              (unsigned short)(((unsigned)warp << 12) | (aw_mine[r] & 0xfffu));
+        if (has_c[r])
+          bs.citem[item_index(off_c + atomicAdd(&bs.cur_c[bkt_c[r]], 1u))] =
+              (unsigned short)(((unsigned)warp << 8) | (unsigned)(lane + 32 * r));
+      }
       __syncthreads();
-      run_batch(a, w0, region_bytes, bs, batch_cells, sflags);
+      run_batch(a, w0, region_bytes, bs, batch_cells, n_pitems, n_citems, sflags);
       if (ok)
         for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
       base = next_base;

@@ -140,7 +140,8 @@ __device__ __forceinline__ float eq_update(float F, unsigned dec, float inc) {
 }
 
 __device__ __forceinline__ float eq_increment(int k) {
-  return k == 0 ? 0.5f : (k == 1 ? 0.25f : (k == 2 ? 0.125f : 0.0625f));
+  // 0.5, 0.25, 0.125, 0.0625, 0.0625, ... (kinetics.py:846: 0.5 ** (k + 1), at most 4 iterations)
+  return __int_as_float((126 - (k < 3 ? k : 3)) << 23);
 }
 
 // streaming 32-bit loads that do not pollute L1 (every parameter is read once)

@@ -53,6 +53,7 @@ struct KinArgs {
   int *defer_count;       // device counter (zeroed before tier 1)
   int *defer_list;        // device list of deferred cell indices (capacity c)
   int *work_counter;      // device counter handing out cells to warps (zeroed before the launch)
+  int scan_staged;        // batch mode: steps of the tile scan staged ahead in shared memory (0, 1 or 2)
   int batch_enabled;      // tier 1, p, s <= 64, 8 warps per CTA: the CTA integrates 8 cells together
 };
 
@@ -229,13 +230,19 @@ __device__ __forceinline__ int pick(const int (&v)[VEC], int e) {
   }
 }
 
-// Pushes the non-zero elements of one 32*VEC-element step (lane-major, i.e. row-major order).
+// bit e: element e of the lane's VEC elements has a non-zero Nf, Nb, N or A
 template <int VEC>
-__device__ __forceinline__ void push_step(const TileVec<VEC> &t, unsigned *queue, int cap, int row, int sig0,
-                                          unsigned lt, int &nq, int &chk) {
+__device__ __forceinline__ unsigned elem_mask(const TileVec<VEC> &t) {
   unsigned mask = 0;
 #pragma unroll
   for (int e = 0; e < VEC; e++) mask |= ((t.nf[e] | t.nb[e] | t.nn[e] | t.na[e]) != 0 ? 1u : 0u) << e;
+  return mask;
+}
+
+// Pushes the non-zero elements of one 32*VEC-element step (lane-major, i.e. row-major order).
+template <int VEC>
+__device__ __forceinline__ void push_step(const TileVec<VEC> &t, unsigned mask, unsigned *queue, int cap, int row,
+                                          int sig0, unsigned lt, int &nq, int &chk) {
   if (__ballot_sync(FULL, mask != 0) == 0) return;
   int pos = nq;
 #pragma unroll
@@ -295,10 +302,10 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
 #pragma unroll 1
   for (int base = 0; base < total; base += 2 * STEP) {
     fetch(t1, q0 + STEP);
-    push_step<VEC>(t0, queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
     advance();
     fetch(t0, q0 + STEP);
-    push_step<VEC>(t1, queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC>(t1, elem_mask<VEC>(t1), queue, cap, row, sig0, lt, nq, chk);
     advance();
   }
 #else
@@ -306,10 +313,88 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
   for (int base = 0; base < total; base += STEP) {
     TileVec<VEC> t0;
     fetch(t0, q0);
-    push_step<VEC>(t0, queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
     advance();
   }
 #endif
+  if (__any_sync(FULL, chk != 0) || nq > cap) return -1;
+  return nq;
+}
+
+// The same scan with the tile staged through shared memory (VEC = 4): the 4 x 512 bytes of the
+// next one or two steps are in flight (cp.async, no registers) while a step is pushed.  The
+// staging slots are arrays of the warp's region that are not in use before build_lists:
+//   set 0: ent (2 slots), reg + regk, X1 + cursor + colptr
+//   set 1: V + F + FminKey, act + rowptr, Ke + Kmf, Kmb + Vmax        (depth 2 only, p > 32)
+// (launch_one checks the sizes).  Each lane reads back the 16 bytes it copied itself, so no warp
+// synchronisation is needed.
+__device__ __forceinline__ void cp_async16(unsigned saddr, const void *gptr, unsigned dep) {
+  // dep: a value the copy must wait for (keeps the refill behind the reads of the slot)
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(gptr), "r"(dep) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void lds_vec4(unsigned addr, int (&v)[4]) {
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(addr));
+}
+
+__device__ __noinline__ int scan_tile_staged(const KinArgs &a, unsigned aEnt, unsigned aReg, unsigned aX1,
+                                             unsigned aV, unsigned aAct, unsigned aKe, unsigned aKmb, int depth,
+                                             unsigned *queue, int cap, long long tile, int lane) {
+  constexpr int VEC = 4, STEP = 32 * VEC;
+  const int s = a.s, total = a.p * s;
+  const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
+  const unsigned lt = (1u << lane) - 1u, lo = 16u * (unsigned)lane;
+  // slots of the step being read (c*) and of the other set (o*); equal when depth is 1
+  unsigned cNf = aEnt + lo, cNb = cNf + 512u, cN = aReg + lo, cA = aX1 + lo;
+  unsigned oNf = cNf, oNb = cNb, oN = cN, oA = cA;
+  if (depth == 2) {
+    oNf = aV + lo;
+    oNb = aAct + lo;
+    oN = aKe + lo;
+    oA = aKmb + lo;
+  }
+  const int drow = STEP / s, dsig = STEP - drow * s;
+  int q0 = lane * VEC;
+  int row = q0 / s, sig0 = q0 - row * s;
+  int nq = 0, chk = 0;
+  auto issue = [&](int q, unsigned sNf, unsigned sNb, unsigned sN, unsigned sA, unsigned dep) {
+    if (q < total) {  // one commit group per step, empty past the end
+      cp_async16(sNf, gNf + q, dep);
+      cp_async16(sNb, gNb + q, dep);
+      cp_async16(sN, gN + q, dep);
+      cp_async16(sA, gA + q, dep);
+    }
+    cp_async_commit();
+  };
+  issue(q0, cNf, cNb, cN, cA, 0u);
+  if (depth == 2) issue(q0 + STEP, oNf, oNb, oN, oA, 0u);
+#pragma unroll 1
+  for (int base = 0; base < total; base += STEP) {
+    if (depth == 2) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+    TileVec<VEC> t;
+    if (q0 < total) {
+      lds_vec4(cNf, t.nf);
+      lds_vec4(cNb, t.nb);
+      lds_vec4(cN, t.nn);
+      lds_vec4(cA, t.na);
+    } else {
+#pragma unroll
+      for (int e = 0; e < VEC; e++) t.nf[e] = t.nb[e] = t.nn[e] = t.na[e] = 0;
+    }
+    const unsigned mask = elem_mask<VEC>(t);
+    issue(q0 + depth * STEP, cNf, cNb, cN, cA, mask);  // refill the slots just read
+    push_step<VEC>(t, mask, queue, cap, row, sig0, lt, nq, chk);
+    unsigned x;
+    x = cNf; cNf = oNf; oNf = x;
+    x = cNb; cNb = oNb; oNb = x;
+    x = cN; cN = oN; oN = x;
+    x = cA; cA = oA; oA = x;
+    q0 += STEP;
+    row += drow;
+    sig0 += dsig;
+    if (sig0 >= s) { sig0 -= s; row++; }
+  }
   if (__any_sync(FULL, chk != 0) || nq > cap) return -1;
   return nq;
 }
@@ -320,6 +405,7 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
 // counting sort via warp match, so each signal's entries stay in ascending protein
 // order).  Returns false if a list overflows.
 // ---------------------------------------------------------------------------
+template <bool WAIT_ASYNC>
 __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, int lane, int nq,
                             int &n_act_out) {
   const int p = a.p, s = a.s;
@@ -445,7 +531,8 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   }
   for (int e = lane; e < nnz_tot; e += 32) w.csc()[e] = sorted[e];
 
-  cp_async_wait_all();  // per-protein scalars (issued before the scan) and the Kmr gather
+  // per-protein scalars and the Kmr gather: awaited here, or by the caller before their first use
+  if (WAIT_ASYNC) cp_async_wait_all();
   __syncwarp();
   return true;
 }
@@ -1100,15 +1187,27 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
         if (lane + 32 < s) X0[lane + 32] = xb;
         const long long prow = cell * (long long)p;
         const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
-        for (int j = lane; j < p; j += 32) {
-          cp_async4(w.aKe() + 4 * j, a.Ke + prow + j);
-          cp_async4(w.aKmf() + 4 * j, a.Kmf + prow + j);
-          cp_async4(w.aKmb() + 4 * j, a.Kmb + prow + j);
-          cp_async4(w.aVmax() + 4 * j, gv + prow + j);
+        auto fetch_scalars = [&]() {  // per-protein scalars: asynchronous copies, awaited in build_lists
+          for (int j = lane; j < p; j += 32) {
+            cp_async4(w.aKe() + 4 * j, a.Ke + prow + j);
+            cp_async4(w.aKmf() + 4 * j, a.Kmf + prow + j);
+            cp_async4(w.aKmb() + 4 * j, a.Kmb + prow + j);
+            cp_async4(w.aVmax() + 4 * j, gv + prow + j);
+          }
+        };
+        int nq;
+        if (VEC == 4 && a.scan_staged) {
+          if (a.scan_staged == 1) fetch_scalars();
+          __syncwarp();
+          nq = scan_tile_staged(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(), a.scan_staged,
+                                w.csc(), a.e_nnz, cell * (long long)p * s, lane);
+          if (a.scan_staged == 2) fetch_scalars();  // their arrays were staging slots until now
+        } else {
+          fetch_scalars();
+          __syncwarp();
+          nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
         }
-        __syncwarp();
-        const int nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
-        ok = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
+        ok = nq >= 0 && build_lists<false>(a, w, cell, lane, nq, n_act);
         if (!ok) {
           cp_async_wait_all();
           if (a.defer_enabled) {
@@ -1147,10 +1246,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
           }
         }
       }
-      if (ok) {  // act has been read: it now receives the regulatory factors of the first part
-        __syncwarp();
-        regulation_pass(w.sb, w.aRow() - w.sb, w.aReg() - w.sb, w.aRegk() - w.sb, w.aAct() - w.sb, p, lane);
-      }
       __syncthreads();  // counters are zero, next_base is visible
       const long long next_base = bs.next_base;
       if (next_base + warp < n_items) {  // next cell's signals: in flight during this batch
@@ -1188,6 +1283,13 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
         if (has_c[r])
           bs.citem[item_index(off_c + atomicAdd(&bs.cur_c[bkt_c[r]], 1u))] =
               (unsigned short)(((unsigned)warp << 8) | (unsigned)(lane + 32 * r));
+      }
+      if (ok) {
+        // The asynchronous copies of build_lists (scalars, Kmr) had the pooling above to land.  act
+        // has been read: it now receives the regulatory factors of the first part.
+        cp_async_wait_all();
+        __syncwarp();
+        regulation_pass(w.sb, w.aRow() - w.sb, w.aReg() - w.sb, w.aRegk() - w.sb, w.aAct() - w.sb, p, lane);
       }
       __syncthreads();
       run_batch(a, w0, region_bytes, bs, batch_cells, n_pitems, n_citems, sflags);
@@ -1241,7 +1343,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
     int n_act = 0;
     if (a.sparse_enabled) {
       const int nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
-      sparse = nq >= 0 && build_lists(a, w, cell, lane, nq, n_act);
+      sparse = nq >= 0 && build_lists<true>(a, w, cell, lane, nq, n_act);
       if (!sparse) cp_async_wait_all();
     }
     if (prefetch && next_item < n_items) {  // next cell's signals: in flight during this cell's parts
@@ -1497,6 +1599,13 @@ static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cu
   a.smem_align = pl.align;
   a.batch_enabled = (a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS && a.s <= BATCH_MAX_PS &&
                      pl.warps_per_cta == BATCH && !getenv("MS_KIN_NO_BATCH")) ? 1 : 0;
+  {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
+    const Layout L = make_layout(a.p, a.s, pl.e_ent, pl.e_nnz, pl.e_reg);
+    a.scan_staged = (a.batch_enabled && pl.e_ent >= 256 && 2 * pl.e_reg >= 128 && 3 * L.S2 + 32 >= 128 &&
+                     !getenv("MS_KIN_NO_STAGED_SCAN")) ? 1 : 0;
+    // second slot set (two steps in flight): 3*P2, 2*P2 + 32, 2*P2, 2*P2 words of 128
+    if (a.scan_staged && L.P2 >= 64 && !getenv("MS_KIN_STAGED_DEPTH1")) a.scan_staged = 2;
+  }
   a.sparse_enabled = pl.sparse_enabled;
   kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);
   MS_CUDA_CHECK(cudaGetLastError());

@@ -66,14 +66,14 @@ struct KinArgs {
 //
 //   X0 [S2] X1 [S2] Fsig/cursor [S2] colptr [S2+32] pad
 //   V F FminKey Ke Kmf Kmb Vmax act [P2 each]  rowptr [P2+32]
-//   ent [e_ent]  csc [e_nnz] nvs [e_nnz]  reg [e_reg] regk [e_reg]
+//   ent [e_ent]  nvs [e_nnz] csc [e_nnz]  reg [e_reg] regk [e_reg]
 //
 // ent : signal*4 | exponent << 10 | (1 << 31 if product side); per protein, ascending signal
 // csc : protein*4 | N << 10; per signal, ascending protein; nvs: the rate of that entry
 // act : protein*4 | (has substrates) << 10 | (has products) << 11
 // rowptr : ent offset | reg offset << 16;  reg: signal | (A & 0xff) << 8 | protein << 16
-// During the scan csc+nvs hold the queue of non-zero tile elements (2 words each) and
-// then the unsorted N list.
+// During the scan nvs+csc hold the queue of non-zero tile elements (2 words each) and
+// then (nvs) the unsorted N list, which is sorted into csc.
 // ---------------------------------------------------------------------------
 __host__ __device__ inline int round32(int x) { return (x + 31) & ~31; }
 __host__ __device__ inline int pow2_at_least_32(int x) {
@@ -92,9 +92,9 @@ __host__ __device__ inline Layout make_layout(int p, int s, int e_ent, int e_nnz
   L.P2 = pow2_at_least_32(p);
   L.oP = ((4 * L.S2 + 32 + L.P2 - 1) / L.P2) * L.P2;
   L.oEnt = L.oP + 9 * L.P2 + 32;
-  L.oCsc = L.oEnt + e_ent;
-  L.oNvs = L.oCsc + e_nnz;
-  L.oReg = L.oNvs + e_nnz;
+  L.oNvs = L.oEnt + e_ent;
+  L.oCsc = L.oNvs + e_nnz;
+  L.oReg = L.oCsc + e_nnz;
   L.oRegk = L.oReg + e_reg;
   const int align = L.S2 > L.P2 ? L.S2 : L.P2;
   L.words = ((L.oRegk + e_reg + align - 1) / align) * align;
@@ -119,6 +119,7 @@ struct WarpMem {
   __device__ __forceinline__ unsigned *ent() const { return b + oEnt; }
   __device__ __forceinline__ unsigned *csc() const { return b + oCsc; }
   __device__ __forceinline__ unsigned *nvs() const { return b + oNvs; }
+  __device__ __forceinline__ unsigned *queue() const { return b + oNvs; }  // nvs + csc: 2 * e_nnz words
   __device__ __forceinline__ unsigned *reg() const { return b + oReg; }
   __device__ __forceinline__ float *regk() const { return (float *)(b + oRegk); }
   // shared-window byte addresses (hot loops)
@@ -410,21 +411,22 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
                             int &n_act_out) {
   const int p = a.p, s = a.s;
   const unsigned lt = (1u << lane) - 1u;
-  unsigned *queue = w.csc();  // csc and nvs are contiguous: 2 * e_nnz words
-  unsigned *tmp = w.csc();    // unsorted N list, written over consumed queue words
-  unsigned *sides = w.FminKey();  // per protein: bit 10 = has substrates, bit 11 = has products
+  unsigned *queue = w.queue();
+  unsigned *tmp = w.queue();       // unsorted N list, written over consumed queue words
+  unsigned *rowcnt = w.FminKey();  // per protein: substrate entries | product entries << 10 | reg entries << 20
   int ent_tot = 0, nnz_tot = 0, reg_tot = 0;
-  int prev_row = -1;
-  for (int j = lane; j < p; j += 32) sides[j] = 0;
+  unsigned *cursor = w.cursor();   // per signal: N entries, later the write position of the sort
+  for (int j = lane; j < p; j += 32) rowcnt[j] = 0;
+  for (int i = lane; i < s; i += 32) cursor[i] = 0;
   __syncwarp();
 #pragma unroll 1
   for (int base = 0; base < nq; base += 32) {
     const int k = base + lane;
     const bool v = k < nq;
-    const unsigned w0 = v ? queue[2 * k] : 0u, w1 = v ? queue[2 * k + 1] : 0u;
+    const uint2 qw = v ? *reinterpret_cast<const uint2 *>(queue + 2 * k) : make_uint2(0u, 0u);
+    const unsigned w0 = qw.x, w1 = qw.y;
     __syncwarp();  // the whole chunk is in registers before tmp overwrites queue words
-    const unsigned sig = w0 & 0xffu;
-    const int row = v ? (int)((w0 >> 8) & 0xffu) : p;  // padding lanes close the trailing rows
+    const unsigned sig = w0 & 0xffu, row = (w0 >> 8) & 0xffu;
     const int av = (int)(int8_t)((w0 >> 16) & 0xffu);
     const unsigned nf = w1 & 0xffu, nb = (w1 >> 8) & 0xffu;
     const int n = (int)w1 >> 16;
@@ -434,29 +436,21 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
     int pe = ent_tot + __popc(bs & lt) + __popc(bp & lt);
     const int pr = reg_tot + __popc(br & lt);
     const int pn = nnz_tot + __popc(bn & lt);
-    // row pointers: the first queued element of a row also closes the empty rows before it
-    int before = __shfl_up_sync(FULL, row, 1);
-    if (lane == 0) before = prev_row;
-    if (row != before) {
-      const unsigned ptr = (unsigned)min(pe, 0xffff) | ((unsigned)min(pr, 0xffff) << 16);
-      for (int r = before + 1; r <= row; r++) w.rowptr()[r] = ptr;
-    }
-    prev_row = __shfl_sync(FULL, row, 31);
-    if (nf | nb) atomicOr(&sides[row], (nf ? 0x400u : 0u) | (nb ? 0x800u : 0u));
+    const unsigned inc = (nf ? 1u : 0u) | (nb ? 1u << 10 : 0u) | (av ? 1u << 20 : 0u);
+    if (inc) atomicAdd(&rowcnt[row], inc);
     if (nf) {
       if (pe < a.e_ent) w.ent()[pe] = (sig << 2) | (nf << 10);
       pe++;
     }
     if (nb && pe < a.e_ent) w.ent()[pe] = (sig << 2) | (nb << 10) | 0x80000000u;
-    if (n != 0 && pn < a.e_nnz) tmp[pn] = sig | ((unsigned)row << 8) | ((unsigned)n << 16);
-    if (av != 0 && pr < a.e_reg) w.reg()[pr] = sig | ((unsigned)(av & 0xff) << 8) | ((unsigned)row << 16);
+    if (n != 0) {
+      atomicAdd(&cursor[sig], 1u);
+      if (pn < a.e_nnz) tmp[pn] = sig | (row << 8) | ((unsigned)n << 16);
+    }
+    if (av != 0 && pr < a.e_reg) w.reg()[pr] = sig | ((unsigned)(av & 0xff) << 8) | (row << 16);
     ent_tot += __popc(bs) + __popc(bp);
     nnz_tot += __popc(bn);
     reg_tot += __popc(br);
-  }
-  if (lane == 0) {  // rows after the last element when the last chunk had no padding lane
-    const unsigned ptr = (unsigned)min(ent_tot, 0xffff) | ((unsigned)min(reg_tot, 0xffff) << 16);
-    for (int r = prev_row + 1; r <= p; r++) w.rowptr()[r] = ptr;
   }
   if (ent_tot > a.e_ent || nnz_tot > a.e_nnz || reg_tot > a.e_reg) return false;
   __syncwarp();
@@ -468,31 +462,33 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
     }
   }
 
-  // proteins with substrate/product entries, in ascending order
+  // row pointers (the lists are in row order, so a row starts where the counts of the rows before
+  // it end) and the proteins with substrate/product entries, in ascending order
   int n_act = 0;
+  unsigned row_carry = 0;  // ent entries | reg entries << 16 before this chunk of rows
 #pragma unroll 1
   for (int j0 = 0; j0 < p; j0 += 32) {
     const int j = j0 + lane;
-    const unsigned sd = j < p ? sides[j] : 0u;
+    const unsigned cw = j < p ? rowcnt[j] : 0u;
+    const unsigned cf = cw & 0x3ffu, cb = (cw >> 10) & 0x3ffu;
+    const unsigned cnt = (cf + cb) | ((cw >> 20) << 16);
+    unsigned incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned y = __shfl_up_sync(FULL, incl, d);
+      if (lane >= d) incl += y;
+    }
+    if (j < p) w.rowptr()[j] = row_carry + incl - cnt;
+    row_carry += __shfl_sync(FULL, incl, 31);
+    const unsigned sd = (cf ? 0x400u : 0u) | (cb ? 0x800u : 0u);
     const unsigned b = __ballot_sync(FULL, sd != 0);
     if (sd) w.act()[n_act + __popc(b & lt)] = ((unsigned)j << 2) | sd;
     n_act += __popc(b);
   }
+  if (lane == 0) w.rowptr()[p] = row_carry;
   n_act_out = n_act;
 
-  // stable counting sort of the N list by signal -> csc
-  unsigned *cursor = w.cursor();
-  for (int i = lane; i < s; i += 32) cursor[i] = 0;
-  __syncwarp();
-#pragma unroll 1
-  for (int base = 0; base < nnz_tot; base += 32) {
-    const int e = base + lane;
-    const bool v = e < nnz_tot;
-    const unsigned sg = v ? (tmp[e] & 0xffu) : (0x100u + lane);
-    const unsigned peers = __match_any_sync(FULL, sg);
-    if (v && lane == 31 - __clz(peers)) cursor[sg] += __popc(peers);
-    __syncwarp();
-  }
+  // stable counting sort of the N list by signal -> csc (cursor holds the counts)
   unsigned carry = 0;
 #pragma unroll 1
   for (int i0 = 0; i0 < s; i0 += 32) {
@@ -512,8 +508,7 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   }
   if (lane == 0) w.colptr()[s] = carry;
   __syncwarp();
-  // The sorted list goes to the nvs half first (tmp occupies the csc half), then moves.
-  unsigned *sorted = w.nvs();
+  unsigned *sorted = w.csc();  // the unsorted list (tmp) is in the nvs half
 #pragma unroll 1
   for (int base = 0; base < nnz_tot; base += 32) {
     const int e = base + lane;
@@ -529,7 +524,6 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
     if (v && lane == 31 - __clz(peers)) cursor[sg] += __popc(peers);
     __syncwarp();
   }
-  for (int e = lane; e < nnz_tot; e += 32) w.csc()[e] = sorted[e];
 
   // per-protein scalars and the Kmr gather: awaited here, or by the caller before their first use
   if (WAIT_ASYNC) cp_async_wait_all();
@@ -628,7 +622,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
   const float qnan = __int_as_float(0x7fc00000);
   const unsigned aX0 = w.aX0(), aX1 = w.aX1(), aV = w.aV(), aF = w.aF(), aFk = w.aFk();
   const unsigned aRow = w.aRow(), aEnt = w.aEnt(), aCsc = w.aCsc();
-  const unsigned dNvs = 4u * (unsigned)(w.oNvs - w.oCsc);  // nvs[e] lives dNvs bytes after csc[e]
+  const unsigned dNvs = 4u * (unsigned)(w.oNvs - w.oCsc);  // nvs[e] is at csc[e] + dNvs (mod 2^32)
 #pragma unroll 1
   for (int q = 0; q < a.n_parts; q++) {
     const float trim = a.trims[q];
@@ -1200,12 +1194,12 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
           if (a.scan_staged == 1) fetch_scalars();
           __syncwarp();
           nq = scan_tile_staged(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(), a.scan_staged,
-                                w.csc(), a.e_nnz, cell * (long long)p * s, lane);
+                                w.queue(), a.e_nnz, cell * (long long)p * s, lane);
           if (a.scan_staged == 2) fetch_scalars();  // their arrays were staging slots until now
         } else {
           fetch_scalars();
           __syncwarp();
-          nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
+          nq = scan_tile<VEC>(a, w.queue(), a.e_nnz, cell * (long long)p * s, lane);
         }
         ok = nq >= 0 && build_lists<false>(a, w, cell, lane, nq, n_act);
         if (!ok) {
@@ -1342,7 +1336,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
     bool sparse = false;
     int n_act = 0;
     if (a.sparse_enabled) {
-      const int nq = scan_tile<VEC>(a, w.csc(), a.e_nnz, cell * (long long)p * s, lane);
+      const int nq = scan_tile<VEC>(a, w.queue(), a.e_nnz, cell * (long long)p * s, lane);
       sparse = nq >= 0 && build_lists<true>(a, w, cell, lane, nq, n_act);
       if (!sparse) cp_async_wait_all();
     }

@@ -338,9 +338,11 @@ __device__ __forceinline__ void lds_vec4(unsigned addr, int (&v)[4]) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(addr));
 }
 
+template <int DEPTH>
 __device__ __noinline__ int scan_tile_staged(const KinArgs &a, unsigned aEnt, unsigned aReg, unsigned aX1,
-                                             unsigned aV, unsigned aAct, unsigned aKe, unsigned aKmb, int depth,
+                                             unsigned aV, unsigned aAct, unsigned aKe, unsigned aKmb,
                                              unsigned *queue, int cap, long long tile, int lane) {
+  constexpr int depth = DEPTH;
   constexpr int VEC = 4, STEP = 32 * VEC;
   const int s = a.s, total = a.p * s;
   const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
@@ -373,17 +375,12 @@ __device__ __noinline__ int scan_tile_staged(const KinArgs &a, unsigned aEnt, un
   for (int base = 0; base < total; base += STEP) {
     if (depth == 2) asm volatile("cp.async.wait_group 1;" ::: "memory");
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
-    TileVec<VEC> t;
-    if (q0 < total) {
-      lds_vec4(cNf, t.nf);
-      lds_vec4(cNb, t.nb);
-      lds_vec4(cN, t.nn);
-      lds_vec4(cA, t.na);
-    } else {
-#pragma unroll
-      for (int e = 0; e < VEC; e++) t.nf[e] = t.nb[e] = t.nn[e] = t.na[e] = 0;
-    }
-    const unsigned mask = elem_mask<VEC>(t);
+    TileVec<VEC> t;  // past the end of the tile the slots hold stale words: masked out
+    lds_vec4(cNf, t.nf);
+    lds_vec4(cNb, t.nb);
+    lds_vec4(cN, t.nn);
+    lds_vec4(cA, t.na);
+    const unsigned mask = q0 < total ? elem_mask<VEC>(t) : 0u;
     issue(q0 + depth * STEP, cNf, cNb, cN, cA, mask);  // refill the slots just read
     push_step<VEC>(t, mask, queue, cap, row, sig0, lt, nq, chk);
     unsigned x;
@@ -1193,8 +1190,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
         if (VEC == 4 && a.scan_staged) {
           if (a.scan_staged == 1) fetch_scalars();
           __syncwarp();
-          nq = scan_tile_staged(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(), a.scan_staged,
-                                w.queue(), a.e_nnz, cell * (long long)p * s, lane);
+          nq = a.scan_staged == 2
+                   ? scan_tile_staged<2>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
+                                         w.queue(), a.e_nnz, cell * (long long)p * s, lane)
+                   : scan_tile_staged<1>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
+                                         w.queue(), a.e_nnz, cell * (long long)p * s, lane);
           if (a.scan_staged == 2) fetch_scalars();  // their arrays were staging slots until now
         } else {
           fetch_scalars();

@@ -1124,7 +1124,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
   __syncthreads();
   // warp regions start at an address aligned to the largest array stride (layout comment)
   const unsigned raw = (unsigned)__cvta_generic_to_shared(smem);
-  const unsigned aligned = (raw + (unsigned)a.smem_align - 1u) & ~((unsigned)a.smem_align - 1u);
+  unsigned aligned = (raw + (unsigned)a.smem_align - 1u) & ~((unsigned)a.smem_align - 1u);
+  // Opaque copy: without it the compiler recomputes this address (a dozen uniform instructions)
+  // at every use inside the loops instead of keeping it.
+  asm volatile("mov.b32 %0, %0;" : "+r"(aligned));
   unsigned *wbase = smem + ((aligned - raw) >> 2) + (size_t)warp * a.words_per_warp;
   const unsigned wshared = aligned + (unsigned)warp * (unsigned)a.words_per_warp * 4u;
   const int p = a.p, s = a.s, s32 = pow2_at_least_32(s);

@@ -43,6 +43,7 @@ struct KinArgs {
   float *V_out;           // optional (c,p), n_parts == 1 only
   int e_ent, e_nnz, e_reg;  // list capacities (entries)
   int words_per_warp;     // shared memory words per warp
+  unsigned region_bytes;  // the same in bytes
   int smem_align;         // alignment of the warp regions in bytes (power of two)
   int sparse_enabled;     // 0 forces the dense path (p > 256 or s > 128)
   // Two tiers.  Tier 1 (small lists, 32 warps/SM) defers cells whose tile does not fit to
@@ -1163,7 +1164,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
       if (lane + 32 < s) xb = load_x(base + warp, lane + 32);
     }
     __syncthreads();  // everyone has read next_base
-    const unsigned region_bytes = (unsigned)a.words_per_warp * 4u;
+    const unsigned region_bytes = a.region_bytes;
     const WarpMem w0 = carve(smem + ((aligned - raw) >> 2), aligned, p, s, a.e_ent, a.e_nnz, a.e_reg);
     while (base < n_items) {
       // The previous batch ended with a CTA barrier (end of run_batch), and everything written
@@ -1593,6 +1594,7 @@ template <typename K>
 static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
   MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
   a.e_ent = pl.e_ent; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
+  a.region_bytes = (unsigned)pl.words_per_warp * 4u;
   a.smem_align = pl.align;
   a.batch_enabled = (a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS && a.s <= BATCH_MAX_PS &&
                      pl.warps_per_cta == BATCH && !getenv("MS_KIN_NO_BATCH")) ? 1 : 0;

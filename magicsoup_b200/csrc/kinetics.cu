@@ -821,7 +821,9 @@ __device__ __forceinline__ void regulation_pass(unsigned sb, unsigned oRow, unsi
 __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_bytes, BatchShared &bs,
                           const long long *cells /* per slot, -1 = absent */, int n_pitems, int n_citems,
                           unsigned *sflags) {
-  const int tid = threadIdx.x, lane = tid & 31, slot_own = tid >> 5;
+  int tid = threadIdx.x;
+  asm volatile("mov.b32 %0, %0;" : "+r"(tid));  // opaque: kept, not re-read from the special register in the loops
+  const int lane = tid & 31, slot_own = tid >> 5;
   const int p = a.p, s = a.s;
   const float qnan = __int_as_float(0x7fc00000);
   const unsigned dNvs = 4u * (unsigned)(w0.oNvs - w0.oCsc);

@@ -579,6 +579,7 @@ __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsig
   // values, so that one shared-memory latency (not two) separates consecutive trips.  A list
   // whose length is not a multiple of W ends with neutral entries (x * 1.0f is exact).
   constexpr int W = MS_TUNE_PIPE_P == 1 ? 2 : MS_TUNE_PIPE_P;
+  asm volatile("" : "+r"(xaddr));  // opaque: held in a register instead of being recomputed every trip
   unsigned wd[W];
 #pragma unroll
   for (int e = 0; e < W; e++) wd[e] = pe + 4 * e < pend ? lds_u(pe + 4 * e) : 0u;

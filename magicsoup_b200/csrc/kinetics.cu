@@ -880,10 +880,10 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       const unsigned aV = sb + oV, aFk = sb + oFk;
       float d = 0.0f;
 #pragma unroll UNROLL_C
-      for (unsigned pc = c0; pc < c1; pc += 4) {
+      for (unsigned pc = c0, pn = c0 + dNvs; pc < c1; pc += 4, pn += 4) {
         const unsigned wd = lds_u(pc);
         const float nv = (float)((int)wd >> 10) * lds_f(aV | (wd & 0x3fcu));
-        sts_f(pc + dNvs, nv);
+        sts_f(pn, nv);
         float neg = -nv;
         neg = neg < 0.0f ? 0.0f : neg;
         d = d + neg;
@@ -892,8 +892,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       if (f > 1.0f) f = 1.0f;
       const unsigned key = fkey(f);
 #pragma unroll UNROLL_C
-      for (unsigned pc = c0; pc < c1; pc += 4)
-        if (lds_f(pc + dNvs) < 0.0f) atom_min_shared(aFk | (lds_u(pc) & 0x3fcu), key);
+      for (unsigned pc = c0, pn = c0 + dNvs; pc < c1; pc += 4, pn += 4)
+        if (lds_f(pn) < 0.0f) atom_min_shared(aFk | (lds_u(pc) & 0x3fcu), key);
     }
     __syncthreads();
     // X1 = max(X0 + sum_j NV'_ji, 0)
@@ -905,9 +905,9 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       const unsigned aFk = sb + oFk;
       float acc = 0.0f;
 #pragma unroll UNROLL_C
-      for (unsigned pc = c0; pc < c1; pc += 4) {
-        const float nvp = lds_f(pc + dNvs) * fkey_decode(lds_u(aFk | (lds_u(pc) & 0x3fcu)));
-        sts_f(pc + dNvs, nvp);
+      for (unsigned pc = c0, pn = c0 + dNvs; pc < c1; pc += 4, pn += 4) {
+        const float nvp = lds_f(pn) * fkey_decode(lds_u(aFk | (lds_u(pc) & 0x3fcu)));
+        sts_f(pn, nvp);
         acc = acc + nvp;
       }
       float x = clamp0(lds_f(sb + 4 * i) + acc);
@@ -969,7 +969,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         const unsigned aF = sb + oF;
         float acc = 0.0f;
 #pragma unroll UNROLL_C
-        for (unsigned pc = c0; pc < c1; pc += 4) acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
+        for (unsigned pc = c0, pn = c0 + dNvs; pc < c1; pc += 4, pn += 4)
+          acc = acc + lds_f(pn) * lds_f(aF | (lds_u(pc) & 0x3fcu));
         float x = clamp0(lds_f(sb + 4 * i) + acc);
         if (bs.cell_poison[slot]) x = qnan;
         sts_f(sb + oX1 + 4 * i, x);

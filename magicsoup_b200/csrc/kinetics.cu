@@ -242,8 +242,15 @@ __device__ __forceinline__ unsigned elem_mask(const TileVec<VEC> &t) {
 }
 
 // Pushes the non-zero elements of one 32*VEC-element step (lane-major, i.e. row-major order).
-template <int VEC>
-__device__ __forceinline__ void push_step(const TileVec<VEC> &t, unsigned mask, unsigned *queue, int cap, int row,
+__device__ __forceinline__ void queue_store(unsigned *queue, int pos, unsigned w0, unsigned w1) {
+  *reinterpret_cast<uint2 *>(queue + 2 * pos) = make_uint2(w0, w1);
+}
+__device__ __forceinline__ void queue_store(unsigned queue_saddr, int pos, unsigned w0, unsigned w1) {
+  asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(queue_saddr + 8u * (unsigned)pos), "r"(w0), "r"(w1) : "memory");
+}
+
+template <int VEC, typename Q>
+__device__ __forceinline__ void push_step(const TileVec<VEC> &t, unsigned mask, Q queue, int cap, int row,
                                           int sig0, unsigned lt, int &nq, int &chk) {
   if (__ballot_sync(FULL, mask != 0) == 0) return;
   int pos = nq;
@@ -261,9 +268,8 @@ __device__ __forceinline__ void push_step(const TileVec<VEC> &t, unsigned mask, 
     // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
     chk |= ((nf | nb) & 0xffffff00) | ((nn + 32768) & 0xffff0000) | ((na + 128) & 0xffffff00);
     if (pos < cap)
-      *reinterpret_cast<uint2 *>(queue + 2 * pos) =
-          make_uint2((unsigned)(sig0 + e) | ((unsigned)row << 8) | ((unsigned)(na & 0xff) << 16),
-                     ((unsigned)nf & 0xffu) | (((unsigned)nb & 0xffu) << 8) | ((unsigned)nn << 16));
+      queue_store(queue, pos, (unsigned)(sig0 + e) | ((unsigned)row << 8) | ((unsigned)(na & 0xff) << 16),
+                  ((unsigned)nf & 0xffu) | (((unsigned)nb & 0xffu) << 8) | ((unsigned)nn << 16));
     pos++;
   }
 }
@@ -304,10 +310,10 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
 #pragma unroll 1
   for (int base = 0; base < total; base += 2 * STEP) {
     fetch(t1, q0 + STEP);
-    push_step<VEC>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC, unsigned *>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
     advance();
     fetch(t0, q0 + STEP);
-    push_step<VEC>(t1, elem_mask<VEC>(t1), queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC, unsigned *>(t1, elem_mask<VEC>(t1), queue, cap, row, sig0, lt, nq, chk);
     advance();
   }
 #else
@@ -315,7 +321,7 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
   for (int base = 0; base < total; base += STEP) {
     TileVec<VEC> t0;
     fetch(t0, q0);
-    push_step<VEC>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC, unsigned *>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
     advance();
   }
 #endif
@@ -342,7 +348,7 @@ __device__ __forceinline__ void lds_vec4(unsigned addr, int (&v)[4]) {
 template <int DEPTH>
 __device__ __noinline__ int scan_tile_staged(const KinArgs &a, unsigned aEnt, unsigned aReg, unsigned aX1,
                                              unsigned aV, unsigned aAct, unsigned aKe, unsigned aKmb,
-                                             unsigned *queue, int cap, long long tile, int lane) {
+                                             unsigned queue, int cap, long long tile, int lane) {
   constexpr int depth = DEPTH;
   constexpr int VEC = 4, STEP = 32 * VEC;
   const int s = a.s, total = a.p * s;
@@ -383,7 +389,7 @@ __device__ __noinline__ int scan_tile_staged(const KinArgs &a, unsigned aEnt, un
     lds_vec4(cA, t.na);
     const unsigned mask = q0 < total ? elem_mask<VEC>(t) : 0u;
     issue(q0 + depth * STEP, cNf, cNb, cN, cA, mask);  // refill the slots just read
-    push_step<VEC>(t, mask, queue, cap, row, sig0, lt, nq, chk);
+    push_step<VEC, unsigned>(t, mask, queue, cap, row, sig0, lt, nq, chk);
     unsigned x;
     x = cNf; cNf = oNf; oNf = x;
     x = cNb; cNb = oNb; oNb = x;
@@ -1200,9 +1206,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
           __syncwarp();
           nq = a.scan_staged == 2
                    ? scan_tile_staged<2>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
-                                         w.queue(), a.e_nnz, cell * (long long)p * s, lane)
+                                         w.aNvs(), a.e_nnz, cell * (long long)p * s, lane)
                    : scan_tile_staged<1>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
-                                         w.queue(), a.e_nnz, cell * (long long)p * s, lane);
+                                         w.aNvs(), a.e_nnz, cell * (long long)p * s, lane);
           if (a.scan_staged == 2) fetch_scalars();  // their arrays were staging slots until now
         } else {
           fetch_scalars();

@@ -170,6 +170,14 @@ __device__ __forceinline__ void sts_u(unsigned addr, unsigned v) {
 __device__ __forceinline__ void sts_f(unsigned addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
+__device__ __forceinline__ unsigned lds_u16(unsigned addr) {
+  unsigned v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void red_or_shared(unsigned addr, unsigned v) {
+  asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ void atom_min_shared(unsigned addr, unsigned v) {
   asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
@@ -842,8 +850,13 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
   const unsigned oKmb = w0.aKmb() - w0.sb, oVmax = w0.aVmax() - w0.sb, oReg = w0.aReg() - w0.sb;
   const unsigned oRegk = w0.aRegk() - w0.sb, oAct = w0.aAct() - w0.sb;
   // this warp's share of the pooled items
-  const unsigned short *pmine = bs.pitem + slot_own * ITEMS_PER_WARP;
-  const unsigned short *cmine = bs.citem + slot_own * ITEMS_PER_WARP;
+  // (32-bit shared-window addresses, opaque so that they are held, not rebuilt from the CTA's
+  // shared-window base at every access; aState: cell_state[2][8] followed by cell_poison[8])
+  unsigned aPmine = (unsigned)__cvta_generic_to_shared(bs.pitem + slot_own * ITEMS_PER_WARP);
+  unsigned aCmine = (unsigned)__cvta_generic_to_shared(bs.citem + slot_own * ITEMS_PER_WARP);
+  unsigned aState = (unsigned)__cvta_generic_to_shared(&bs.cell_state[0][0]);
+  asm volatile("" : "+r"(aPmine), "+r"(aCmine), "+r"(aState));
+  const unsigned aPoison = aState + 8u * BATCH;
   const int n_p = items_of_warp(n_pitems, slot_own), n_c = items_of_warp(n_citems, slot_own);
   if (a.n_parts <= 0) __syncthreads();  // callers rely on a barrier at the end
 
@@ -854,7 +867,7 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
     // ---- velocities (kinetics.py:771-806)
 #pragma unroll 1
     for (int it = lane; it < n_p; it += 32) {
-      const unsigned item = pmine[it];
+      const unsigned item = lds_u16(aPmine + 2 * it);
       const unsigned sb = w0.sb + (item >> 12) * region_bytes;
       const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
       const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
@@ -873,13 +886,13 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       if (!a.adj_vmax) vmax = clamp0(vmax * trim);
       const float v = velocity_from(kf, kb, a_reg, vmax);
       sts_f((sb + oV) | j4, v);
-      if (isnan(v)) bs.cell_poison[item >> 12] = 1u;
+      if (isnan(v)) sts_u(aPoison + 4 * (item >> 12), 1u);
     }
     __syncthreads();
     // ---- substrate trimming (kinetics.py:861-879)
 #pragma unroll 1
     for (int it = lane; it < n_c; it += 32) {
-      const unsigned item = cmine[it];
+      const unsigned item = lds_u16(aCmine + 2 * it);
       const unsigned sb = w0.sb + (item >> 8) * region_bytes;
       const unsigned i = item & 0xffu;
       const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
@@ -905,7 +918,7 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
     // X1 = max(X0 + sum_j NV'_ji, 0)
 #pragma unroll 1
     for (int it = lane; it < n_c; it += 32) {
-      const unsigned item = cmine[it];
+      const unsigned item = lds_u16(aCmine + 2 * it);
       const unsigned slot = item >> 8, sb = w0.sb + slot * region_bytes, i = item & 0xffu;
       const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
       const unsigned aFk = sb + oFk;
@@ -917,7 +930,7 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         acc = acc + nvp;
       }
       float x = clamp0(lds_f(sb + 4 * i) + acc);
-      if (bs.cell_poison[slot]) x = qnan;
+      if (lds_u(aPoison + 4 * slot)) x = qnan;
       sts_f(sb + oX1 + 4 * i, x);
     }
     __syncthreads();
@@ -929,12 +942,13 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
     for (int k = 0; k < iters; k++) {
       const float inc = eq_increment(k);
       unsigned *st_cur = bs.cell_state[k & 1], *st_prv = bs.cell_state[(k & 1) ^ 1];
+      const unsigned a_cur = aState + 4u * BATCH * (unsigned)(k & 1), a_prv = aState + 4u * BATCH * (unsigned)((k & 1) ^ 1);
       int moved_mine = 0;
 #pragma unroll 1
       for (int it = lane; it < n_p; it += 32) {
-        const unsigned item = pmine[it];
+        const unsigned item = lds_u16(aPmine + 2 * it);
         const unsigned slot = item >> 12;
-        if (k > 0 && !(st_prv[slot] & CS_MOVED)) continue;
+        if (k > 0 && !(lds_u(a_prv + 4 * slot) & CS_MOVED)) continue;
         const unsigned sb = w0.sb + slot * region_bytes;
         const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
         const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
@@ -947,7 +961,7 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         if (dec & 3u) {
           const float Fn = eq_update(F, dec, inc);
           sts_f((sb + oF) | j4, Fn);
-          atomicOr(&st_cur[slot], ((dec & 4u) ? (CS_IMP | CS_ANY) : CS_ANY) | (Fn != F ? CS_MOVED : 0u));
+          red_or_shared(a_cur + 4 * slot, ((dec & 4u) ? (CS_IMP | CS_ANY) : CS_ANY) | (Fn != F ? CS_MOVED : 0u));
           moved_mine |= (Fn != F) ? 1 : 0;
         }
       }
@@ -967,9 +981,9 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       if (!any_moved) break;
 #pragma unroll 1
       for (int it = lane; it < n_c; it += 32) {
-        const unsigned item = cmine[it];
+        const unsigned item = lds_u16(aCmine + 2 * it);
         const unsigned slot = item >> 8;
-        if (!(st_cur[slot] & CS_MOVED)) continue;
+        if (!(lds_u(a_cur + 4 * slot) & CS_MOVED)) continue;
         const unsigned sb = w0.sb + slot * region_bytes, i = item & 0xffu;
         const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
         const unsigned aF = sb + oF;
@@ -978,7 +992,7 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         for (unsigned pc = c0, pn = c0 + dNvs; pc < c1; pc += 4, pn += 4)
           acc = acc + lds_f(pn) * lds_f(aF | (lds_u(pc) & 0x3fcu));
         float x = clamp0(lds_f(sb + 4 * i) + acc);
-        if (bs.cell_poison[slot]) x = qnan;
+        if (lds_u(aPoison + 4 * slot)) x = qnan;
         sts_f(sb + oX1 + 4 * i, x);
       }
       __syncthreads();

@@ -868,7 +868,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
 #pragma unroll 1
     for (int it = lane; it < n_p; it += 32) {
       const unsigned item = lds_u16(aPmine + 2 * it);
-      const unsigned sb = w0.sb + (item >> 12) * region_bytes;
+      unsigned sb = w0.sb + (item >> 12) * region_bytes;
+      asm volatile("" : "+r"(sb));  // held, not recomputed at each use
       const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
       const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
       float xf, xb;
@@ -893,7 +894,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
 #pragma unroll 1
     for (int it = lane; it < n_c; it += 32) {
       const unsigned item = lds_u16(aCmine + 2 * it);
-      const unsigned sb = w0.sb + (item >> 8) * region_bytes;
+      unsigned sb = w0.sb + (item >> 8) * region_bytes;
+      asm volatile("" : "+r"(sb));  // held, not recomputed at each use
       const unsigned i = item & 0xffu;
       const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
       const unsigned aV = sb + oV, aFk = sb + oFk;
@@ -919,7 +921,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
 #pragma unroll 1
     for (int it = lane; it < n_c; it += 32) {
       const unsigned item = lds_u16(aCmine + 2 * it);
-      const unsigned slot = item >> 8, sb = w0.sb + slot * region_bytes, i = item & 0xffu;
+      unsigned slot = item >> 8, sb = w0.sb + slot * region_bytes, i = item & 0xffu;
+      asm volatile("" : "+r"(sb));  // held, not recomputed at each use
       const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
       const unsigned aFk = sb + oFk;
       float acc = 0.0f;
@@ -949,7 +952,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         const unsigned item = lds_u16(aPmine + 2 * it);
         const unsigned slot = item >> 12;
         if (k > 0 && !(lds_u(a_prv + 4 * slot) & CS_MOVED)) continue;
-        const unsigned sb = w0.sb + slot * region_bytes;
+        unsigned sb = w0.sb + slot * region_bytes;
+        asm volatile("" : "+r"(sb));  // held, not recomputed at each use
         const unsigned aw = item & 0xfffu, j4 = aw & 0x3fcu;
         const unsigned r0 = lds_u((sb + oRow) | j4), r1 = lds_u(((sb + oRow) | j4) + 4);
         float xf, xb;
@@ -984,7 +988,8 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         const unsigned item = lds_u16(aCmine + 2 * it);
         const unsigned slot = item >> 8;
         if (!(lds_u(a_cur + 4 * slot) & CS_MOVED)) continue;
-        const unsigned sb = w0.sb + slot * region_bytes, i = item & 0xffu;
+        unsigned sb = w0.sb + slot * region_bytes, i = item & 0xffu;
+        asm volatile("" : "+r"(sb));  // held, not recomputed at each use
         const unsigned c0 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i), c1 = sb + oCsc + 4 * lds_u(sb + oCol + 4 * i + 4);
         const unsigned aF = sb + oF;
         float acc = 0.0f;

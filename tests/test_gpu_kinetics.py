@@ -191,6 +191,33 @@ def test_integrate_signals_bit_exact(ms, shape):
         X, Xn = out.cpu(), ora
 
 
+_PATH_SWITCHES = [
+    {},                                  # default: batch mode, staged scan (two steps ahead where p > 32)
+    {"MS_KIN_STAGED_DEPTH1": "1"},       # staged scan, one step ahead
+    {"MS_KIN_NO_STAGED_SCAN": "1"},      # register scan
+    {"MS_KIN_NO_BATCH": "1"},            # warp-per-cell path (run_sparse)
+]
+
+
+@pytest.mark.parametrize("shape", [_SHAPES[0], _SHAPES[1], _SHAPES[4]],
+                         ids=[f"c{c}p{p}s{2*m}" for c, p, m, _, _ in [_SHAPES[0], _SHAPES[1], _SHAPES[4]]])
+def test_kernel_paths_agree_bit_for_bit(ms, shape, monkeypatch):
+    """every scan / integration path of the fused kernel gives the oracle's bits (switches are
+    read at launch time, csrc/kinetics.cu launch_one)"""
+    c, p, m, size, seed = shape
+    pop = make_population(c, p, m, size, seed=seed)
+    kin = install(_kinetics(ms, 2 * m), pop)
+    X = pop.X0()
+    ora = O.integrate_signals(oracle_params(pop), X.numpy())
+    for env in _PATH_SWITCHES:
+        for k in ("MS_KIN_STAGED_DEPTH1", "MS_KIN_NO_STAGED_SCAN", "MS_KIN_NO_BATCH"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        out = kin.integrate_signals(X=X.cuda())
+        assert bits_equal(out, ora), f"{env}: " + describe_mismatch(out, ora)
+
+
 @pytest.mark.parametrize("shape", _SHAPES[:6], ids=[f"c{c}p{p}s{2*m}" for c, p, m, _, _ in _SHAPES[:6]])
 def test_stages_bit_exact(ms, shape):
     c, p, m, size, seed = shape

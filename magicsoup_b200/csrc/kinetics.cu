@@ -201,10 +201,6 @@ __device__ __forceinline__ float fkey_decode(unsigned k) {
 }
 constexpr unsigned KEY_ONE = 0xbf800000u;  // fkey(1.0f)
 
-#ifndef MS_TUNE_SCAN_PIPE
-#define MS_TUNE_SCAN_PIPE 0
-#endif
-
 template <int VEC>
 struct TileVec {  // VEC consecutive elements of the four integer tiles
   int nf[VEC], nb[VEC], nn[VEC], na[VEC];
@@ -312,19 +308,6 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
     sig0 += dsig;
     if (sig0 >= s) { sig0 -= s; row++; }
   };
-#if MS_TUNE_SCAN_PIPE
-  TileVec<VEC> t0, t1;
-  fetch(t0, q0);
-#pragma unroll 1
-  for (int base = 0; base < total; base += 2 * STEP) {
-    fetch(t1, q0 + STEP);
-    push_step<VEC, unsigned *>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
-    advance();
-    fetch(t0, q0 + STEP);
-    push_step<VEC, unsigned *>(t1, elem_mask<VEC>(t1), queue, cap, row, sig0, lt, nq, chk);
-    advance();
-  }
-#else
 #pragma unroll 1
   for (int base = 0; base < total; base += STEP) {
     TileVec<VEC> t0;
@@ -332,7 +315,6 @@ __device__ __noinline__ int scan_tile(const KinArgs &a, unsigned *queue, int cap
     push_step<VEC, unsigned *>(t0, elem_mask<VEC>(t0), queue, cap, row, sig0, lt, nq, chk);
     advance();
   }
-#endif
   if (__any_sync(FULL, chk != 0) || nq > cap) return -1;
   return nq;
 }
@@ -548,20 +530,10 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
 #ifndef MS_TUNE_UNROLL_C
 #define MS_TUNE_UNROLL_C 2
 #endif
-#ifndef MS_TUNE_UNROLL_P
-#define MS_TUNE_UNROLL_P 2
-#endif
-#ifndef MS_TUNE_PIPE_P
-#define MS_TUNE_PIPE_P 1
-#endif
 #ifndef MS_TUNE_BOOK_WARP
 #define MS_TUNE_BOOK_WARP 7
 #endif
-#ifndef MS_TUNE_SNAKE
-#define MS_TUNE_SNAKE 1
-#endif
-constexpr int UNROLL_C = MS_TUNE_UNROLL_C, UNROLL_P = MS_TUNE_UNROLL_P;
-constexpr bool SNAKE = MS_TUNE_SNAKE != 0;
+constexpr int UNROLL_C = MS_TUNE_UNROLL_C;
 
 // One list entry's factor x^n: same multiplication order as powi(); exponents 1..3 (99.8 %)
 // without a branch.  An all-zero word is a neutral entry (factor 1 on the substrate side).
@@ -588,11 +560,10 @@ __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsig
                                               float &xb) {
   xf = 1.0f;
   xb = 1.0f;
-#if MS_TUNE_PIPE_P
   // W entries per trip; the next trip's entry words are fetched before this trip's signal
   // values, so that one shared-memory latency (not two) separates consecutive trips.  A list
   // whose length is not a multiple of W ends with neutral entries (x * 1.0f is exact).
-  constexpr int W = MS_TUNE_PIPE_P == 1 ? 2 : MS_TUNE_PIPE_P;
+  constexpr int W = 2;  // 4 was measured slower: short lists pay for the padding
   asm volatile("" : "+r"(xaddr));  // opaque: held in a register instead of being recomputed every trip
   unsigned wd[W];
 #pragma unroll
@@ -613,15 +584,6 @@ __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsig
       wd[e] = nx[e];
     }
   }
-#else
-#pragma unroll UNROLL_P
-  for (; pe < pend; pe += 4) {
-    const unsigned wd = lds_u(pe);
-    const float r = entry_factor(wd, lds_f(xaddr | (wd & 0x3fcu)));
-    if ((int)wd < 0) xb = xb * r;
-    else xf = xf * r;
-  }
-#endif
   xf = fix_product(xf);
   xb = fix_product(xb);
 }
@@ -786,7 +748,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
 // ---------------------------------------------------------------------------
 constexpr int BATCH = 8;            // cells per CTA = warps per CTA
 constexpr int BATCH_MAX_PS = 64;    // p and s limit of the batch path (item tables below)
-constexpr unsigned CS_POISON = 1u, CS_IMP = 2u, CS_ANY = 4u, CS_MOVED = 8u;
+constexpr unsigned CS_IMP = 2u, CS_ANY = 4u, CS_MOVED = 8u;
 
 constexpr int ITEMS_PER_WARP = BATCH_MAX_PS;  // 8 * 64 pooled items over 8 warps
 
@@ -797,12 +759,12 @@ constexpr int ITEMS_PER_WARP = BATCH_MAX_PS;  // 8 * 64 pooled items over 8 warp
 // and the per-iteration flag bookkeeping is done by lanes of warp 7, which has the shortest lists.
 __device__ __forceinline__ unsigned item_index(unsigned pos) {
   const unsigned chunk = pos >> 5;
-  const unsigned owner = SNAKE ? (chunk < BATCH ? chunk : 2 * BATCH - 1 - chunk) : (chunk & (BATCH - 1));
+  const unsigned owner = chunk < BATCH ? chunk : 2 * BATCH - 1 - chunk;
   return owner * ITEMS_PER_WARP + (chunk / BATCH) * 32 + (pos & 31u);
 }
 // number of the n sorted items that land in `warp`'s list
 __device__ __forceinline__ int items_of_warp(int n, int warp) {
-  const int a = n - 32 * warp, b = n - 32 * (SNAKE ? 2 * BATCH - 1 - warp : BATCH + warp);
+  const int a = n - 32 * warp, b = n - 32 * (2 * BATCH - 1 - warp);
   return min(max(a, 0), 32) + min(max(b, 0), 32);
 }
 

@@ -91,12 +91,19 @@ class SlabWorld(World):
 
     # ------------------------------------------------------------------ exchange steps
     def _all_ranks_empty(self) -> bool:
-        return sum(self.global_n_cells()) == 0
+        # A rank without cells still takes part in the flag reduction of the other ranks' cells
+        # (asking all ranks for their counts would cost one more collective and sync per step).
+        return False
 
-    def _reduce_flags(self, flags: list[int]) -> list[int]:
+    def _reduce_flags(self, flags) -> list[int]:
+        """MAX over ranks; flags from the kernel are reduced where they are (one read-back)"""
         if self.world_size == 1:
-            return flags
-        t = torch.tensor(flags, dtype=torch.int32, device=self._comm_device())
+            return super()._reduce_flags(flags)
+        comm = self._comm_device()
+        if isinstance(flags, torch.Tensor) and flags.device == comm:
+            t = flags
+        else:
+            t = torch.as_tensor(flags, dtype=torch.int32).to(comm)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         return t.tolist()
 

@@ -163,8 +163,9 @@ class World:
     # The step methods are written against a few hooks so that the multi-GPU SlabWorld
     # (magicsoup_b200/distributed.py) only adds the exchange steps: _reduce_flags,
     # _exchange_halos, _reduce_sums, _n_pixels_total.
-    def _reduce_flags(self, flags: list[int]) -> list[int]:
-        return flags
+    def _reduce_flags(self, flags) -> list[int]:
+        """the 24 early-exit flags as host integers (a device tensor is read back here: one sync)"""
+        return flags.tolist() if isinstance(flags, torch.Tensor) else flags
 
     def _exchange_halos(self, mm: torch.Tensor):
         return None, None  # one device holds the whole map: rows wrap around inside it
@@ -175,8 +176,8 @@ class World:
     def _n_pixels_total(self, H: int, W: int) -> int:
         return H * W
 
-    def _launch_activity(self, dev, pos, cm, mm, X, eq) -> list[int]:
-        """ms_enzymatic_activity with eq iterations -> the 24 early-exit flags"""
+    def _launch_activity(self, dev, pos, cm, mm, X, eq):
+        """ms_enzymatic_activity with eq iterations -> the 24 early-exit flags (int32, on the device)"""
         kin = self.kinetics
         m = self.n_molecules
         _, H, W = mm.shape
@@ -193,7 +194,7 @@ class World:
         if self._kernel_events is not None:
             ev[1].record(torch.cuda.current_stream(dev))
             self._kernel_events.append(ev)
-        return kin._read_flags(flags)
+        return flags[: nat.N_FLAGS * 4].view(torch.int32)
 
     def _launch_scatter(self, dev, X, pos, mm) -> torch.Tensor:
         m = self.n_molecules

@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-cells", type=int, default=65536)
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--energies", default="modest", choices=["modest", "survey"],
+                    help="molecule energies of the synthetic chemistry: U(10,50) kJ (default) or SURVEY §8(d)'s U(10,500) kJ")
     return ap.parse_args()
 
 
@@ -121,12 +123,17 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def energy_range(args):
+    return (10e3, 500e3) if args.energies == "survey" else (10e3, 50e3)
+
+
 def build_world(args, device, seed, world_size=1):
     import torch
     import magicsoup_b200 as ms
     from magicsoup_b200.synthetic import make_population
 
-    pop = make_population(args.cells, args.proteins, args.molecules, args.map, seed=seed, device=device)
+    pop = make_population(args.cells, args.proteins, args.molecules, args.map, seed=seed, device=device,
+                          energy_range=energy_range(args))
     mols = [ms.Molecule(f"b{i}", 10e3, diffusivity=pop.diffusivities[i], permeability=pop.permeabilities[i])
             for i in range(pop.m)]
     chem = ms.Chemistry(molecules=mols, reactions=[])
@@ -185,7 +192,8 @@ def run_reference(args):
     if rank != 0:
         return
     n = min(args.cells, args.cpu_sample_cells // 4)  # ~2 s of CPU work per step
-    pop = make_population(n, args.proteins, args.molecules, args.map, seed=0, device="cpu")
+    pop = make_population(n, args.proteins, args.molecules, args.map, seed=0, device="cpu",
+                          energy_range=energy_range(args))
     par = [t.numpy() for t in pop.params()]
     X0 = pop.X0().numpy()
     vals = []

@@ -95,6 +95,12 @@ int ms_integrate_signals_part(const ms_kinetics_params *params, const float *adj
 
 size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s);
 
+/* The fused kernel's diagnostic switches (environment variables MS_KIN_NO_BATCH,
+ * MS_KIN_NO_STAGED_SCAN, MS_KIN_STAGED_DEPTH1, MS_KIN_MAX_CTAS_PER_SM) are read
+ * once, at the first launch of the process.  This re-reads them (no counterpart in the
+ * reference; used by the tests that run every kernel path). */
+void ms_kinetics_reload_switches(void);
+
 /* Kinetics._multiply_signals(X, N) -> (xx (c,p), involved (c,p) as uint8)  kinetics.py:894-918 */
 int ms_multiply_signals(const float *X, const int32_t *K, int64_t c, int64_t p, int64_t s,
                         float *xx, uint8_t *involved, void *stream);
@@ -156,6 +162,10 @@ int ms_scatter_signals(const float *X, const int32_t *cell_positions, int64_t c,
  * (centre) from World._get_diffuse (world.py:948-972), then the mass correction
  * += (sum_before - sum_after) / (H*W) and clamp(0).  In place on molecule_map.
  * scratch: ms_diffuse_scratch_bytes(m,H,W) bytes (stencil output + plane sums).
+ * Value range: the plane sums are exact 2^-32 fixed point, which holds finite |x| < 2^31; a NaN,
+ * Inf or larger value in a plane is left out of / saturates its sums (the reference's float32
+ * torch.sum would turn the whole plane NaN instead).  Pointers need only float alignment; the
+ * float4 paths are taken when the buffers are 16-byte aligned.
  */
 int ms_diffuse_molecules(float *molecule_map, const float *a, const float *b, int64_t m, int64_t H,
                          int64_t W, void *scratch, size_t scratch_bytes, void *stream);
@@ -201,6 +211,8 @@ int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, i
 int ms_diffuse_molecules_static(float *molecule_map, const float *a, const float *b, int64_t m,
                                 int64_t H, int64_t W, void *stream);
 int64_t ms_diffuse_static_max_floats(void);
+/* Text of the last MS_ERR_TOO_LARGE refusal of ms_diffuse_molecules_static on the CALLING THREAD
+ * (the buffer is thread-local), "" after a call that was not refused. */
 const char *ms_diffuse_static_last_error(void);
 
 /*

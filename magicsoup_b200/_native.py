@@ -34,6 +34,7 @@ _SIGNATURES = {
     "ms_integrate_signals": (C.c_int, [_PP, _vp, _vp, C.POINTER(_i32), _vp, _vp, _sz, _vp]),
     "ms_integrate_signals_part": (C.c_int, [_PP, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     "ms_kinetics_scratch_bytes": (_sz, [_i64, _i64, _i64]),
+    "ms_kinetics_reload_switches": (None, []),
     "ms_multiply_signals": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "ms_get_quotient": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "ms_get_velocities": (C.c_int, [_PP, _vp, _vp, _vp, _vp]),

@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
 __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restrict__ out,
                                                            float *__restrict__ map, long long n_pxls,
                                                            long long n_pxls_total,
-                                                           const unsigned long long *sums) {
+                                                           const unsigned long long *sums, int vec) {
   const int k = blockIdx.z;
   const long long *sk = reinterpret_cast<const long long *>(sums) + 4 * k;
   const float s0 = (float)((double)sk[0] + (double)sk[1] * 2.3283064365386963e-10);
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restri
   const float *src = out + (size_t)k * n_pxls;
   float *dst = map + (size_t)k * n_pxls;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  if ((n_pxls & 3) == 0) {
+  if (vec) {  // n_pxls % 4 == 0 and both planes 16-byte aligned (correct_launch)
     const float4 *s4 = reinterpret_cast<const float4 *>(src);
     float4 *d4 = reinterpret_cast<float4 *>(dst);
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < (n_pxls >> 2); t += stride) {
@@ -232,17 +232,33 @@ static thread_local char g_static_too_large_msg[320] = "";
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// m * H * W without wrapping: false if the product does not fit `limit`
+static bool volume_fits(int64_t m, int64_t H, int64_t W, int64_t limit, int64_t *volume) {
+  if (m < 0 || H <= 0 || W <= 0 || H > limit / W) return false;
+  const int64_t plane = H * W;
+  if (m > 0 && plane > limit / m) return false;
+  *volume = m * plane;
+  return true;
+}
+
 extern "C" size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W) {
   if (m <= 0 || H <= 0 || W <= 0) return 256;
-  return align256((size_t)m * H * W * sizeof(float)) + align256((size_t)m * 4 * sizeof(long long));
+  int64_t vol = 0;
+  if (!volume_fits(m, H, W, (int64_t)1 << 58, &vol)) return SIZE_MAX;  // no buffer is ever large enough
+  return align256((size_t)vol * sizeof(float)) + align256((size_t)m * 4 * sizeof(long long));
 }
+
+static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 static int stencil_launch(const float *map, const float *halo_top, const float *halo_bot,
                           const float *a, const float *b, int64_t m, int64_t H, int64_t W, float *tmp,
                           unsigned long long *sums, cudaStream_t st) {
   MS_CUDA_CHECK(cudaMemsetAsync(sums, 0, (size_t)m * 4 * sizeof(long long), st));
   const long long n = (long long)H * W;
-  if (W % TW == 0 && H % TH == 0) {
+  // the tiled kernel moves float4: rows must start 16-byte aligned in every buffer it touches
+  const bool vec_ok = aligned16(map) && aligned16(tmp) && (!halo_top || aligned16(halo_top)) &&
+                      (!halo_bot || aligned16(halo_bot));
+  if (W % TW == 0 && H % TH == 0 && vec_ok) {
     dim3 grid((unsigned)(W / TW), (unsigned)(H / TH), (unsigned)m);
     stencil_tiled_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums);
   } else {
@@ -258,10 +274,11 @@ static int stencil_launch(const float *map, const float *halo_top, const float *
 static int correct_launch(const float *tmp, float *map, int64_t m, int64_t H, int64_t W,
                           long long n_pxls_total, const unsigned long long *sums, cudaStream_t st) {
   const long long n = (long long)H * W;
-  long long work = (n & 3) == 0 ? n / 4 : n;
+  const bool vec = (n & 3) == 0 && aligned16(tmp) && aligned16(map);
+  long long work = vec ? n / 4 : n;
   unsigned blocks = (unsigned)((work + DTHREADS - 1) / DTHREADS);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, map, n, n_pxls_total, sums);
+  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, map, n, n_pxls_total, sums, vec ? 1 : 0);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -391,7 +408,9 @@ extern "C" int ms_diffuse_molecules_static(float *molecule_map, const float *a, 
   if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
   if (m == 0) return MS_OK;
   if (!molecule_map || !a || !b) return MS_ERR_INVALID_ARGUMENT;
-  if (m > MS_STATIC_DIFFUSE_MAX_PLANES || m * H * W > MS_STATIC_DIFFUSE_MAX_FLOATS) {
+  g_static_too_large_msg[0] = 0;
+  int64_t vol = 0;  // compared by division: the product of three int64 can wrap below the limit
+  if (m > MS_STATIC_DIFFUSE_MAX_PLANES || !volume_fits(m, H, W, MS_STATIC_DIFFUSE_MAX_FLOATS, &vol)) {
     snprintf(g_static_too_large_msg, sizeof(g_static_too_large_msg),
              "ms_diffuse_molecules_static: map of %lld x %lld x %lld floats exceeds the built-in scratch of "
              "%lld floats / %d planes; use ms_diffuse_molecules with caller scratch",

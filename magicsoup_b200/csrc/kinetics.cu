@@ -19,7 +19,10 @@
 namespace ms {
 
 constexpr int WARPS_PER_CTA = 8;
-constexpr int MAX_THREADS = 1024;  // launch bound; CTAs are launched with 8 warps (tier 1)
+constexpr int MAX_THREADS = 32 * WARPS_PER_CTA;  // every launch uses at most 8 warps per CTA
+#ifndef MS_TUNE_MIN_CTAS
+#define MS_TUNE_MIN_CTAS 4
+#endif
 constexpr int MAX_S_SPARSE = 256;  // 8-bit signal / protein indices in the packed lists
 constexpr unsigned FULL = 0xffffffffu;
 
@@ -589,6 +592,68 @@ __device__ __forceinline__ void list_products(unsigned xaddr, unsigned pe, unsig
 }
 
 // ---------------------------------------------------------------------------
+// equilibrium trimming (kinetics.py:808-859) of ONE cell by one warp, on the cell's lists:
+// per iteration the quotients and decisions of the active proteins, then X1 of every signal.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void eq_iterations(const WarpMem &w, int s, int lane, int n_act, int q, int iters,
+                                              bool poison, unsigned *sflags) {
+  const float qnan = __int_as_float(0x7fc00000);
+  const unsigned aX0 = w.aX0(), aX1 = w.aX1(), aV = w.aV(), aF = w.aF();
+  const unsigned aRow = w.aRow(), aEnt = w.aEnt(), aCsc = w.aCsc();
+  const unsigned dNvs = 4u * (unsigned)(w.oNvs - w.oCsc);  // nvs[e] is at csc[e] + dNvs (mod 2^32)
+#pragma unroll 1
+  for (int k = 0; k < iters; k++) {
+    const float inc = eq_increment(k);
+    unsigned mine = 0;
+    bool changed = false;
+#pragma unroll 1
+    for (int t = lane; t < n_act; t += 32) {
+      const unsigned aw = lds_u(w.aAct() + 4 * t);
+      const unsigned j4 = aw & 0x3fcu;
+      const unsigned r0 = lds_u(aRow | j4), r1 = lds_u((aRow | j4) + 4);
+      float xf, xb;
+      list_products(aX1, aEnt + 4 * (r0 & 0xffffu), aEnt + 4 * (r1 & 0xffffu), xf, xb);
+      if (!(aw & 0x400u)) xf = 0.0f;
+      if (!(aw & 0x800u)) xb = 0.0f;
+      const float F = lds_f(aF | j4);
+      const unsigned dec = eq_decide_fast(lds_f(aV | j4), quotient_fixed(xb, xf), lds_f(w.aKe() | j4), F);
+      if (dec & 3u) {
+        mine |= (dec & 4u) ? 3u : 2u;
+        const float Fn = eq_update(F, dec, inc);
+        changed |= (Fn != F);
+        sts_f(aF | j4, Fn);
+      }
+    }
+    const unsigned any = __reduce_or_sync(FULL, mine);
+    // If no F moved (adjustable proteins can sit clamped at 0 or 1), X1 would be recomputed
+    // bit-identically and every later iteration of this part repeats this one exactly: same
+    // decisions, same flags, no change.  Report the flags for those iterations and stop.
+    const bool moved = __any_sync(FULL, changed);
+    if (lane == 0 && any) {
+      const int k_end = moved ? k + 1 : iters;
+      for (int kk = k; kk < k_end; kk++) {
+        if (any & 1u) sflags[q * 4 + kk] = 1u;
+        sflags[12 + q * 4 + kk] = 1u;
+      }
+    }
+    if (!moved) break;
+    __syncwarp();
+#pragma unroll 1
+    for (int i = lane; i < s; i += 32) {
+      const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
+      float acc = 0.0f;
+#pragma unroll 2
+      for (unsigned pc = c0; pc < c1; pc += 4)
+        acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
+      float x = clamp0(lds_f(aX0 + 4 * i) + acc);
+      if (poison) x = qnan;
+      sts_f(aX1 + 4 * i, x);
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
 // sparse path: all parts of one cell on the shared-memory lists
 // ---------------------------------------------------------------------------
 __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, int lane, int n_act,
@@ -678,57 +743,7 @@ __device__ void run_sparse(const KinArgs &a, const WarpMem &w, long long cell, i
     __syncwarp();
 
     // ---- equilibrium trimming (kinetics.py:808-859)
-    const int iters = a.eq_iters[q];
-#pragma unroll 1
-    for (int k = 0; k < iters; k++) {
-      const float inc = eq_increment(k);
-      unsigned mine = 0;
-      bool changed = false;
-#pragma unroll 1
-      for (int t = lane; t < n_act; t += 32) {
-        const unsigned aw = lds_u(w.aAct() + 4 * t);
-        const unsigned j4 = aw & 0x3fcu;
-        const unsigned r0 = lds_u(aRow | j4), r1 = lds_u((aRow | j4) + 4);
-        float xf, xb;
-        list_products(aX1, aEnt + 4 * (r0 & 0xffffu), aEnt + 4 * (r1 & 0xffffu), xf, xb);
-        if (!(aw & 0x400u)) xf = 0.0f;
-        if (!(aw & 0x800u)) xb = 0.0f;
-        const float F = lds_f(aF | j4);
-        const unsigned dec = eq_decide_fast(lds_f(aV | j4), quotient_fixed(xb, xf), lds_f(w.aKe() | j4), F);
-        if (dec & 3u) {
-          mine |= (dec & 4u) ? 3u : 2u;
-          const float Fn = eq_update(F, dec, inc);
-          changed |= (Fn != F);
-          sts_f(aF | j4, Fn);
-        }
-      }
-      const unsigned any = __reduce_or_sync(FULL, mine);
-      // If no F moved (adjustable proteins can sit clamped at 0 or 1), X1 would be recomputed
-      // bit-identically and every later iteration of this part repeats this one exactly: same
-      // decisions, same flags, no change.  Report the flags for those iterations and stop.
-      const bool moved = __any_sync(FULL, changed);
-      if (lane == 0 && any) {
-        const int k_end = moved ? k + 1 : iters;
-        for (int kk = k; kk < k_end; kk++) {
-          if (any & 1u) sflags[q * 4 + kk] = 1u;
-          sflags[12 + q * 4 + kk] = 1u;
-        }
-      }
-      if (!moved) break;
-      __syncwarp();
-#pragma unroll 1
-      for (int i = lane; i < s; i += 32) {
-        const unsigned c0 = aCsc + 4 * lds_u(w.aCol() + 4 * i), c1 = aCsc + 4 * lds_u(w.aCol() + 4 * i + 4);
-        float acc = 0.0f;
-#pragma unroll 2
-        for (unsigned pc = c0; pc < c1; pc += 4)
-          acc = acc + lds_f(pc + dNvs) * lds_f(aF | (lds_u(pc) & 0x3fcu));
-        float x = clamp0(lds_f(aX0 + 4 * i) + acc);
-        if (poison) x = qnan;
-        sts_f(aX1 + 4 * i, x);
-      }
-      __syncwarp();
-    }
+    eq_iterations(w, s, lane, n_act, q, a.eq_iters[q], poison, sflags);
 
     if (a.V_out)
       for (int j = lane; j < p; j += 32) a.V_out[cell * (long long)p + j] = lds_f(aV + 4 * j);
@@ -779,15 +794,15 @@ struct BatchShared {
 };
 
 // Regulatory factors of one cell from its X0 (kinetics.py:789-799), one lane per entry, into the
-// cell's act array (free once the items are pooled); the velocity sweep multiplies them up in
-// list order.  They depend on X0 only, so every warp does this for its own cell outside the
+// cell's X1 + cursor words (2*S2 >= e_reg; X1 is only written after the velocity sweep, the cursor
+// only while the lists are built); the velocity sweep multiplies them up in list order.  They depend on X0 only, so every warp does this for its own cell outside the
 // sweeps, where the 1-3 entries of a regulated protein would otherwise prolong its lane.
 __device__ __forceinline__ void regulation_pass(unsigned sb, unsigned oRow, unsigned oReg, unsigned oRegk,
-                                                unsigned oAct, int p, int lane) {
+                                                unsigned oFac, int p, int lane) {
   const unsigned n_reg = lds_u(sb + oRow + 4u * (unsigned)p) >> 16;
   for (unsigned e = lane; e < n_reg; e += 32) {
     const unsigned wd = lds_u(sb + oReg + 4 * e);
-    sts_f(sb + oAct + 4 * e, reg_factor(lds_f(sb + 4 * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
+    sts_f(sb + oFac + 4 * e, reg_factor(lds_f(sb + 4 * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
                                         lds_f(sb + oRegk + 4 * e)));
   }
 }
@@ -844,7 +859,7 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
       if (isinf(kb)) kb = V_MAX;
       float a_reg = 1.0f;
 #pragma unroll 1
-      for (unsigned e = r0 >> 16; e < (r1 >> 16); e++) a_reg = a_reg * lds_f(sb + oAct + 4 * e);
+      for (unsigned e = r0 >> 16; e < (r1 >> 16); e++) a_reg = a_reg * lds_f(sb + oX1 + 4 * e);
       float vmax = lds_f((sb + oVmax) | j4);
       if (!a.adj_vmax) vmax = clamp0(vmax * trim);
       const float v = velocity_from(kf, kb, a_reg, vmax);
@@ -971,17 +986,20 @@ __device__ void run_batch(const KinArgs &a, const WarpMem &w0, unsigned region_b
         for (int j = lane; j < p; j += 32) a.V_out[cells[slot_own] * (long long)p + j] = lds_f(sb_own + oV + 4 * j);
       for (int i = lane; i < s; i += 32) sts_f(sb_own + 4 * i, lds_f(sb_own + oX1 + 4 * i));
       __syncwarp();
-      if (q + 1 < a.n_parts) regulation_pass(sb_own, oRow, oReg, oRegk, oAct, p, lane);
+      if (q + 1 < a.n_parts) regulation_pass(sb_own, oRow, oReg, oRegk, oX1, p, lane);
       for (int j = lane; j < p; j += 32) {
         sts_f(sb_own + oV + 4 * j, 0.0f);  // proteins without substrate/product entries have V = 0
         sts_f(sb_own + oF + 4 * j, 1.0f);
         sts_u(sb_own + oFk + 4 * j, KEY_ONE);
       }
     }
-    if (tid < BATCH) {
-      bs.cell_state[0][tid] = 0;
-      bs.cell_state[1][tid] = 0;
-      bs.cell_poison[tid] = 0;
+    // Reset by the lanes that read the states for the flags above: on the early `break` no barrier
+    // separates that read from this write, program order does.  (cell_poison was last read in an
+    // X1 sweep, before the loop's last barrier.)
+    if (slot_own == MS_TUNE_BOOK_WARP && lane < BATCH) {
+      bs.cell_state[0][lane] = 0;
+      bs.cell_state[1][lane] = 0;
+      bs.cell_poison[lane] = 0;
     }
     __syncthreads();
   }
@@ -1106,7 +1124,7 @@ __device__ __noinline__ void run_dense(const KinArgs &a, float *X0, float *X1, f
 }
 
 template <int VEC>
-__global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
+__global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
                                                                     float *dense_scratch) {
   extern __shared__ __align__(16) unsigned smem[];
   __shared__ unsigned sflags[MS_N_FLAGS];
@@ -1274,11 +1292,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) kinetics_fused_kernel(const __
               (unsigned short)(((unsigned)warp << 8) | (unsigned)(lane + 32 * r));
       }
       if (ok) {
-        // The asynchronous copies of build_lists (scalars, Kmr) had the pooling above to land.  act
-        // has been read: it now receives the regulatory factors of the first part.
+        // The asynchronous copies of build_lists (scalars, Kmr) had the pooling above to land.
         cp_async_wait_all();
         __syncwarp();
-        regulation_pass(w.sb, w.aRow() - w.sb, w.aReg() - w.sb, w.aRegk() - w.sb, w.aAct() - w.sb, p, lane);
+        regulation_pass(w.sb, w.aRow() - w.sb, w.aReg() - w.sb, w.aRegk() - w.sb, w.aX1() - w.sb, p, lane);
       }
       __syncthreads();
       run_batch(a, w0, region_bytes, bs, batch_cells, n_pitems, n_citems, sflags);
@@ -1477,18 +1494,38 @@ struct LaunchPlan {
   size_t smem_bytes;
 };
 
-static int g_sm_count = 0;
-
+// multiprocessor count of the current device (cached per device ordinal)
 static int sm_count() {
-  if (g_sm_count == 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 148;
-    g_sm_count = n > 0 ? n : 148;
-  }
-  return g_sm_count;
+  static int cached[64] = {0};
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev >= 0 && dev < 64 && cached[dev] > 0) return cached[dev];
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+  if (dev >= 0 && dev < 64) cached[dev] = n;
+  return n;
 }
 
+// Diagnostic switches, read from the environment ONCE, at the first launch of the
+// process; ms_kinetics_reload_switches() re-reads them (tests flip them between launches).
+struct Switches {
+  bool no_batch, no_staged_scan, staged_depth1;
+  int max_ctas_per_sm;  // 0 = no limit
+};
+static Switches read_switches() {
+  Switches sw;
+  sw.no_batch = getenv("MS_KIN_NO_BATCH") != nullptr;
+  sw.no_staged_scan = getenv("MS_KIN_NO_STAGED_SCAN") != nullptr;
+  sw.staged_depth1 = getenv("MS_KIN_STAGED_DEPTH1") != nullptr;
+  const char *env = getenv("MS_KIN_MAX_CTAS_PER_SM");
+  sw.max_ctas_per_sm = env ? atoi(env) : 0;
+  return sw;
+}
+static Switches &switches() {
+  static Switches sw = read_switches();
+  return sw;
+}
+
+constexpr int MAX_GRID = 256 * 4;  // launches are clamped to this many CTAs (>= 4 per SM on any B200 part)
 constexpr size_t SMEM_PER_SM = 222 * 1024;   // usable per SM (227 KB max per CTA on sm_100a)
 constexpr size_t SMEM_PER_CTA_MAX = 200 * 1024;
 constexpr size_t SMEM_PER_SM_HW = 227 * 1024;  // sm_100a: 228 KB per SM, 1 KB reserved per CTA
@@ -1505,15 +1542,13 @@ static void finish_plan(LaunchPlan &pl) {
   if (per_sm > 4) per_sm = 4;
   if (per_sm < 1) per_sm = 1;
   // tuning knob: fewer resident CTAs per SM (the shared memory request is padded accordingly)
-  if (const char *env = getenv("MS_KIN_MAX_CTAS_PER_SM")) {
-    const size_t want = (size_t)atoi(env);
-    if (want >= 1 && want < per_sm) {
-      per_sm = want;
-      const size_t pad = (SMEM_PER_SM_HW + 1024) / (per_sm + 1) + 1024;  // too big for per_sm + 1 CTAs
-      if (pl.smem_bytes < pad && pad <= SMEM_PER_SM_HW) pl.smem_bytes = pad;
-    }
+  if (switches().max_ctas_per_sm >= 1 && (size_t)switches().max_ctas_per_sm < per_sm) {
+    per_sm = (size_t)switches().max_ctas_per_sm;
+    const size_t pad = (SMEM_PER_SM_HW + 1024) / (per_sm + 1) + 1024;  // too big for per_sm + 1 CTAs
+    if (pl.smem_bytes < pad && pad <= SMEM_PER_SM_HW) pl.smem_bytes = pad;
   }
   pl.grid = sm_count() * (int)per_sm;
+  if (pl.grid > MAX_GRID) pl.grid = MAX_GRID;  // dense_scratch_bytes() is sized for this
 }
 
 // tier 1: lists for a typical proteome (2-6 non-zeros per protein row)
@@ -1568,12 +1603,14 @@ static size_t align256k(size_t x) { return (x + 255) & ~(size_t)255; }
 
 // scratch layout: [dense arrays: max_warps x 3 x round32(p) floats][defer counter][defer list: c ints]
 static size_t dense_scratch_bytes(int64_t p) {
-  return align256k((size_t)148 * 8 * WARPS_PER_CTA * 3 * (size_t)round32((int)p) * sizeof(float));
+  return align256k((size_t)MAX_GRID * WARPS_PER_CTA * 3 * (size_t)round32((int)p) * sizeof(float));
 }
 
 }  // namespace ms
 
 using namespace ms;
+
+extern "C" void ms_kinetics_reload_switches(void) { switches() = read_switches(); }
 
 extern "C" size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s) {
   (void)s;
@@ -1588,13 +1625,13 @@ static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cu
   a.region_bytes = (unsigned)pl.words_per_warp * 4u;
   a.smem_align = pl.align;
   a.batch_enabled = (a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS && a.s <= BATCH_MAX_PS &&
-                     pl.warps_per_cta == BATCH && !getenv("MS_KIN_NO_BATCH")) ? 1 : 0;
+                     pl.warps_per_cta == BATCH && !switches().no_batch) ? 1 : 0;
   {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
     const Layout L = make_layout(a.p, a.s, pl.e_ent, pl.e_nnz, pl.e_reg);
     a.scan_staged = (a.batch_enabled && pl.e_ent >= 256 && 2 * pl.e_reg >= 128 && 3 * L.S2 + 32 >= 128 &&
-                     !getenv("MS_KIN_NO_STAGED_SCAN")) ? 1 : 0;
+                     !switches().no_staged_scan) ? 1 : 0;
     // second slot set (two steps in flight): 3*P2, 2*P2 + 32, 2*P2, 2*P2 words of 128
-    if (a.scan_staged && L.P2 >= 64 && !getenv("MS_KIN_STAGED_DEPTH1")) a.scan_staged = 2;
+    if (a.scan_staged && L.P2 >= 64 && !switches().staged_depth1) a.scan_staged = 2;
   }
   a.sparse_enabled = pl.sparse_enabled;
   kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a, dense);

@@ -13,7 +13,8 @@ Fixtures
   ref_synthetic_<tag>.npz  seeded synthetic populations (magicsoup_b200.synthetic)
                            pushed through the reference stage by stage and end to
                            end, incl. the reference's own summation-order noise
-                           floor (same inputs, proteins permuted).
+                           floor (same inputs, proteins permuted).  Tags c1, wl, two
+                           (small) and c4, c4e, c3, s82 (the benchmarked tile shapes).
   ref_drift_1000.npz       population statistics of a 1000-step reference trajectory (and of
                            the reference with permuted proteins) every 100 steps.
   ref_world.npz            World.diffuse_molecules / enzymatic_activity on small
@@ -145,8 +146,8 @@ def _mismatch(a: np.ndarray, b: np.ndarray, tol=1e-4) -> float:
     return float((rel > tol).mean())
 
 
-def synthetic_fixture(ms, tag, c, p, m, map_size, seed, n_steps):
-    pop = make_population(c, p, m, map_size, seed=seed)
+def synthetic_fixture(ms, tag, c, p, m, map_size, seed, n_steps, energy_range=(10e3, 50e3)):
+    pop = make_population(c, p, m, map_size, seed=seed, energy_range=energy_range)
     kin = _ref_kinetics(ms, pop)
     X0 = pop.X0()
     d: dict[str, np.ndarray] = {k: _np(getattr(pop, k)) for k in PARAMS}
@@ -192,6 +193,19 @@ def synthetic_fixture(ms, tag, c, p, m, map_size, seed, n_steps):
     np.savez_compressed(OUT / f"ref_synthetic_{tag}.npz", **d)
     print(f"synthetic {tag}: c={c} p={p} s={2*m} noise floor step1={d['noise_floor_step1']:.4f} "
           f"last={d['noise_floor_last']:.4f}")
+
+
+def bench_shape_fixtures(ms):
+    """
+    The shapes BASELINE.json's configs are benchmarked on (round 2): C4's tile (p=64, s=32) with
+    the bench's default energies and with SURVEY.md 8(d)'s U(10,500) kJ, C3 (a saturated map,
+    p=35, s=40) and the co2_fixing chemistry's size (s=82).  `python make_golden.py bench` writes
+    only these.
+    """
+    synthetic_fixture(ms, "c4", c=1024, p=64, m=16, map_size=64, seed=31, n_steps=10)
+    synthetic_fixture(ms, "c4e", c=512, p=64, m=16, map_size=64, seed=32, n_steps=10, energy_range=(10e3, 500e3))
+    synthetic_fixture(ms, "c3", c=1024, p=35, m=20, map_size=32, seed=33, n_steps=10)  # 32 x 32 map, every pixel occupied
+    synthetic_fixture(ms, "s82", c=256, p=40, m=41, map_size=16, seed=34, n_steps=10)  # 16 x 16 map, every pixel occupied
 
 
 def drift_fixture(ms, c=96, p=20, m=6, n_steps=1000, seed=21):
@@ -287,12 +301,16 @@ def world_fixture(ms):
 def main():
     ms = ref_loader.load()
     torch.manual_seed(0)
+    if sys.argv[1:] == ["bench"]:
+        bench_shape_fixtures(ms)
+        return
     store = record_reference_tests(ms)
     np.savez_compressed(OUT / "ref_tests_kinetics.npz", **store)
     print("ref_tests_kinetics.npz:", len(store), "arrays")
     synthetic_fixture(ms, "c1", c=100, p=22, m=4, map_size=16, seed=11, n_steps=20)
     synthetic_fixture(ms, "wl", c=256, p=35, m=14, map_size=32, seed=12, n_steps=20)
     synthetic_fixture(ms, "two", c=2, p=6, m=3, map_size=4, seed=13, n_steps=30)
+    bench_shape_fixtures(ms)
     drift_fixture(ms)
     world_fixture(ms)
 

@@ -76,3 +76,19 @@ def rel_err(a: np.ndarray, b: np.ndarray, floor: float = 1e-6) -> np.ndarray:
 
 def mismatch_fraction(a, b, tol=1e-4) -> float:
     return float((rel_err(a, b) > tol).mean())
+
+
+SYNTHETIC_TAGS = ("c1", "wl", "two", "c4", "c4e", "c3", "s82")
+
+
+def velocity_bound(ref_v: np.ndarray, adj_vmax: np.ndarray) -> np.ndarray:
+    """
+    SURVEY.md 8(c) P1 for V, stated so that it holds at every tile shape: relative 2e-5 of |V|
+    plus 2.5e-7 of the protein's trimmed Vmax (4 float32 ulps of Vmax').  V = a_cat * Vmax' *
+    a_reg with a_cat = (kf - kb) / (1 + kf + kb) in (-1, 1): near equilibrium kf - kb cancels,
+    so the error of V is absolute in units of Vmax', not relative to |V|.  Measured on the
+    fixtures of this directory: max 0.9e-7 * Vmax' (oracle f32 vs reference), 0.65e-7 * Vmax' for
+    the reference itself against float64.  (Round 1 used 2e-5 * max(|V|, 1e-3), which 9 of 65,536
+    elements of the p=64, s=32 fixture exceed with |V| < 1e-6 beside Vmax' ~ 1.)
+    """
+    return 2e-5 * np.abs(ref_v) + 2.5e-7 * np.abs(adj_vmax)

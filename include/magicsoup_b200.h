@@ -101,6 +101,41 @@ size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s);
  * reference; used by the tests that run every kernel path). */
 void ms_kinetics_reload_switches(void);
 
+/*
+ * Parameter rows and the list cache -- no counterpart in the reference, which re-reads the dense
+ * tensors with every aten op (kinetics.py:753-918) and re-allocates them on every cell-count
+ * change (kinetics.py:667-703).
+ *   row_map (optional): row_map[i] is the row of the nine parameter tensors (and of `records`)
+ *     that holds logical cell i, so that a store can remove and append cells without moving
+ *     42 KB per cell; X, cell_positions and cell_molecules stay indexed by the logical cell.
+ *     params->c is the logical cell count; the tensors must have a row for every mapped value.
+ *   records (optional): one record of rec_words = ms_kinetics_cache_record_words(p, s) uint32 per
+ *     parameter ROW, 16-byte aligned, holding the sparse lists the kernel builds from that row's
+ *     dense tile.  A row whose record is valid skips the scan of its 20*p*s bytes; results are
+ *     bit-identical either way.  Word 0 of a record is its status: zero-fill a record
+ *     (ms_kinetics_cache_invalidate, or any memset) whenever ANY of the row's parameters change.
+ *     Only shapes with p, s <= 64 have records (ms_kinetics_cache_record_words returns 0 otherwise).
+ */
+typedef struct ms_kinetics_cache {
+  uint32_t *records;
+  int64_t rec_words;
+  const int32_t *row_map;
+} ms_kinetics_cache;
+
+int64_t ms_kinetics_cache_record_words(int64_t p, int64_t s);
+/* rows: n_rows parameter rows whose records become stale (NULL = rows 0 .. n_rows-1) */
+int ms_kinetics_cache_invalidate(uint32_t *records, int64_t rec_words, const int32_t *rows,
+                                 int64_t n_rows, void *stream);
+/* ms_integrate_signals / ms_enzymatic_activity (below) with a row map and/or a list cache */
+int ms_integrate_signals_cached(const ms_kinetics_params *params, const ms_kinetics_cache *cache,
+                                const float *X_in, float *X_out, const int32_t *eq_iters_host,
+                                uint32_t *flags, void *scratch, size_t scratch_bytes, void *stream);
+int ms_enzymatic_activity_cached(const ms_kinetics_params *params, const ms_kinetics_cache *cache,
+                                 const int32_t *cell_positions, const float *cell_molecules,
+                                 const float *molecule_map, int64_t m, int64_t H, int64_t W, float *X_out,
+                                 const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
+                                 size_t scratch_bytes, void *stream);
+
 /* Kinetics._multiply_signals(X, N) -> (xx (c,p), involved (c,p) as uint8)  kinetics.py:894-918 */
 int ms_multiply_signals(const float *X, const int32_t *K, int64_t c, int64_t p, int64_t s,
                         float *xx, uint8_t *involved, void *stream);

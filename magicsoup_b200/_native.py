@@ -25,7 +25,14 @@ class KineticsParams(C.Structure):
         ("c", _i64), ("p", _i64), ("s", _i64)]
 
 
+class KineticsCache(C.Structure):
+    """struct ms_kinetics_cache"""
+
+    _fields_ = [("records", _vp), ("rec_words", _i64), ("row_map", _vp)]
+
+
 _PP = C.POINTER(KineticsParams)
+_PC = C.POINTER(KineticsCache)
 _SIGNATURES = {
     "ms_version": (C.c_int, []),
     "ms_error_string": (C.c_char_p, [C.c_int]),
@@ -35,6 +42,11 @@ _SIGNATURES = {
     "ms_integrate_signals_part": (C.c_int, [_PP, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
     "ms_kinetics_scratch_bytes": (_sz, [_i64, _i64, _i64]),
     "ms_kinetics_reload_switches": (None, []),
+    "ms_kinetics_cache_record_words": (_i64, [_i64, _i64]),
+    "ms_kinetics_cache_invalidate": (C.c_int, [_vp, _i64, _vp, _i64, _vp]),
+    "ms_integrate_signals_cached": (C.c_int, [_PP, _PC, _vp, _vp, C.POINTER(_i32), _vp, _vp, _sz, _vp]),
+    "ms_enzymatic_activity_cached": (C.c_int, [_PP, _PC, _vp, _vp, _vp, _i64, _i64, _i64, _vp, C.POINTER(_i32), _vp,
+                                               _vp, _sz, _vp]),
     "ms_multiply_signals": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "ms_get_quotient": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "ms_get_velocities": (C.c_int, [_PP, _vp, _vp, _vp, _vp]),

@@ -59,7 +59,24 @@ struct KinArgs {
   int *work_counter;      // device counter handing out cells to warps (zeroed before the launch)
   int scan_staged;        // batch mode: steps of the tile scan staged ahead in shared memory (0, 1 or 2)
   int batch_enabled;      // tier 1, p, s <= 64, 8 warps per CTA: the CTA integrates 8 cells together
+  // Parameter rows and the list cache (ms_*_cached entry points).  row_map[cell] is the row of the
+  // nine parameter tensors (and of the cache) that holds logical cell `cell`; X, positions and cell
+  // molecules are always indexed by the logical cell.  cache: one record per parameter row with the
+  // lists build_lists produced for it (batch mode only); rec_seg: the three region segments a record
+  // holds, {word offset, words} each.
+  const int *row_map;
+  unsigned *cache;
+  int rec_words;
+  int rec_seg[6];
 };
+
+// list-cache record: word 0 = n_act | status << 16, words 1..3 unused, then the three segments
+constexpr unsigned REC_STALE = 0, REC_VALID = 1, REC_OVERFLOW = 2;
+constexpr int REC_HEADER_WORDS = 4;
+
+__device__ __forceinline__ long long param_row(const KinArgs &a, long long cell) {
+  return a.row_map ? (long long)a.row_map[cell] : cell;
+}
 
 // ---------------------------------------------------------------------------
 // Per-warp shared memory region (32-bit words).  The arrays that the hot loops index with
@@ -404,7 +421,7 @@ __device__ __noinline__ int scan_tile_staged(const KinArgs &a, unsigned aEnt, un
 // order).  Returns false if a list overflows.
 // ---------------------------------------------------------------------------
 template <bool WAIT_ASYNC>
-__device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, int lane, int nq,
+__device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long prm_row, int lane, int nq,
                             int &n_act_out) {
   const int p = a.p, s = a.s;
   const unsigned lt = (1u << lane) - 1u;
@@ -452,7 +469,7 @@ __device__ bool build_lists(const KinArgs &a, const WarpMem &w, long long cell, 
   if (ent_tot > a.e_ent || nnz_tot > a.e_nnz || reg_tot > a.e_reg) return false;
   __syncwarp();
   {  // Kmr of the (few) regulatory entries: asynchronous gather, overlapped with the sort below
-    const long long tile = cell * (long long)p * s;
+    const long long tile = prm_row * (long long)p * s;
     for (int e = lane; e < reg_tot; e += 32) {
       const unsigned wd = w.reg()[e];
       cp_async4(w.aRegk() + 4 * e, a.Kmr + tile + (long long)(wd >> 16) * s + (wd & 0xffu));
@@ -1029,7 +1046,8 @@ __device__ float dense_product(const float *X, const int *K, int s, bool &involv
 __device__ __noinline__ void run_dense(const KinArgs &a, float *X0, float *X1, float *Fsig, float *V, float *Fmin,
                           float *F, long long cell, int lane, unsigned *sflags) {
   const int p = a.p, s = a.s;
-  const long long row = cell * (long long)p;
+  // adj_vmax / V_out (logical cell index) are never combined with a row map (launch_fused)
+  const long long row = param_row(a, cell) * (long long)p;
   const long long tile = row * s;
   const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
   const float *gKmr = a.Kmr + tile;
@@ -1189,7 +1207,8 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
       if (present) {
         if (lane < s) X0[lane] = xa;
         if (lane + 32 < s) X0[lane + 32] = xb;
-        const long long prow = cell * (long long)p;
+        const long long prm = param_row(a, cell);
+        const long long prow = prm * (long long)p;
         const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
         auto fetch_scalars = [&]() {  // per-protein scalars: asynchronous copies, awaited in build_lists
           for (int j = lane; j < p; j += 32) {
@@ -1199,22 +1218,57 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
             cp_async4(w.aVmax() + 4 * j, gv + prow + j);
           }
         };
-        int nq;
-        if (VEC == 4 && a.scan_staged) {
-          if (a.scan_staged == 1) fetch_scalars();
+        // list cache: a valid record replaces the scan of the dense tile (the record holds exactly
+        // what build_lists left in the region for these parameters, so the results are identical)
+        unsigned *rec = a.cache ? a.cache + prm * (long long)a.rec_words : nullptr;
+        const unsigned hdr = rec ? __ldg(rec) : 0u;
+        const unsigned status = hdr >> 16;
+        if (status == REC_VALID) {
+          const uint4 *src = reinterpret_cast<const uint4 *>(rec + REC_HEADER_WORDS);
+#pragma unroll
+          for (int g = 0; g < 3; g++) {
+            const unsigned dst = w.sb + 4u * (unsigned)a.rec_seg[2 * g];
+            const int n16 = a.rec_seg[2 * g + 1] >> 2;
+            for (int e = lane; e < n16; e += 32) cp_async16(dst + 16u * (unsigned)e, src + e, 0u);
+            src += n16;
+          }
+          cp_async_wait_all();  // the pooling below reads act, rowptr and colptr
           __syncwarp();
-          nq = a.scan_staged == 2
-                   ? scan_tile_staged<2>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
-                                         w.aNvs(), a.e_nnz, cell * (long long)p * s, lane)
-                   : scan_tile_staged<1>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
-                                         w.aNvs(), a.e_nnz, cell * (long long)p * s, lane);
-          if (a.scan_staged == 2) fetch_scalars();  // their arrays were staging slots until now
-        } else {
-          fetch_scalars();
-          __syncwarp();
-          nq = scan_tile<VEC>(a, w.queue(), a.e_nnz, cell * (long long)p * s, lane);
+          n_act = (int)(hdr & 0xffffu);
+          ok = true;
+        } else if (status != REC_OVERFLOW) {
+          int nq;
+          if (VEC == 4 && a.scan_staged) {
+            if (a.scan_staged == 1) fetch_scalars();
+            __syncwarp();
+            nq = a.scan_staged == 2
+                     ? scan_tile_staged<2>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
+                                           w.aNvs(), a.e_nnz, prow * s, lane)
+                     : scan_tile_staged<1>(a, w.aEnt(), w.aReg(), w.aX1(), w.aV(), w.aAct(), w.aKe(), w.aKmb(),
+                                           w.aNvs(), a.e_nnz, prow * s, lane);
+            if (a.scan_staged == 2) fetch_scalars();  // their arrays were staging slots until now
+          } else {
+            fetch_scalars();
+            __syncwarp();
+            nq = scan_tile<VEC>(a, w.queue(), a.e_nnz, prow * s, lane);
+          }
+          ok = nq >= 0 && build_lists<false>(a, w, prm, lane, nq, n_act);
+          if (rec) {  // keep the lists for the next steps
+            if (ok) {
+              cp_async_wait_all();  // scalars and Kmr have landed
+              __syncwarp();
+              uint4 *dst = reinterpret_cast<uint4 *>(rec + REC_HEADER_WORDS);
+#pragma unroll
+              for (int g = 0; g < 3; g++) {
+                const uint4 *seg = reinterpret_cast<const uint4 *>(w.b + a.rec_seg[2 * g]);
+                const int n16 = a.rec_seg[2 * g + 1] >> 2;
+                for (int e = lane; e < n16; e += 32) dst[e] = seg[e];
+                dst += n16;
+              }
+            }
+            if (lane == 0) rec[0] = (ok ? (REC_VALID << 16) | (unsigned)n_act : REC_OVERFLOW << 16);
+          }
         }
-        ok = nq >= 0 && build_lists<false>(a, w, cell, lane, nq, n_act);
         if (!ok) {
           cp_async_wait_all();
           if (a.defer_enabled) {
@@ -1334,8 +1388,9 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
     } else {
       for (int i = lane; i < s; i += 32) X0[i] = load_x(cell, i);
     }
+    const long long prm = param_row(a, cell);
     if (a.sparse_enabled) {  // per-protein scalars: asynchronous copies that land during the scan
-      const long long prow = cell * (long long)p;
+      const long long prow = prm * (long long)p;
       const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
       for (int j = lane; j < p; j += 32) {
         cp_async4(w.aKe() + 4 * j, a.Ke + prow + j);
@@ -1348,8 +1403,8 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
     bool sparse = false;
     int n_act = 0;
     if (a.sparse_enabled) {
-      const int nq = scan_tile<VEC>(a, w.queue(), a.e_nnz, cell * (long long)p * s, lane);
-      sparse = nq >= 0 && build_lists<true>(a, w, cell, lane, nq, n_act);
+      const int nq = scan_tile<VEC>(a, w.queue(), a.e_nnz, prm * (long long)p * s, lane);
+      sparse = nq >= 0 && build_lists<true>(a, w, prm, lane, nq, n_act);
       if (!sparse) cp_async_wait_all();
     }
     if (prefetch && next_item < n_items) {  // next cell's signals: in flight during this cell's parts
@@ -1654,10 +1709,34 @@ static int launch_plan(const LaunchPlan &pl, KinArgs &a, float *dense, cudaStrea
   return launch_one(kinetics_fused_kernel<1>, pl, a, dense, st);
 }
 
+// words of a list-cache record for tier-1 lists of this shape (0: the shape has no batch mode)
+static int64_t record_words(int64_t p, int64_t s, int *seg) {
+  if (p < 1 || s < 1 || p > BATCH_MAX_PS || s > BATCH_MAX_PS) return 0;
+  const LaunchPlan pl = plan_tier1(p, s);
+  if (!pl.sparse_enabled || pl.warps_per_cta != BATCH) return 0;
+  const Layout L = make_layout((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg);
+  int sg[6] = {3 * L.S2, L.S2 + 32,                          // colptr
+               L.oP + 3 * L.P2, 6 * L.P2 + 32 + pl.e_ent,    // Ke Kmf Kmb Vmax act rowptr ent
+               L.oCsc, pl.e_nnz + 2 * pl.e_reg};             // csc reg regk
+  if (seg)
+    for (int i = 0; i < 6; i++) seg[i] = sg[i];
+  return REC_HEADER_WORDS + sg[1] + sg[3] + sg[5];
+}
+
 static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, size_t scratch_bytes,
-                        cudaStream_t st) {
+                        cudaStream_t st, const ms_kinetics_cache *cache = nullptr) {
   if (!P || P->c < 0 || P->p < 0 || P->s < 0) return MS_ERR_INVALID_ARGUMENT;
   if (P->p > 65535 || P->s > 8192 || P->c > INT32_MAX) return MS_ERR_TOO_LARGE;
+  if (cache) {
+    if ((cache->row_map || cache->records) && (a.adj_vmax || a.V_out)) return MS_ERR_INVALID_ARGUMENT;
+    a.row_map = cache->row_map;
+    if (cache->records) {
+      const int64_t rw = record_words(P->p, P->s, a.rec_seg);
+      if (rw == 0 || cache->rec_words != rw || ((uintptr_t)cache->records & 15)) return MS_ERR_INVALID_ARGUMENT;
+      a.cache = cache->records;
+      a.rec_words = (int)rw;
+    }
+  }
   a.N = P->N; a.Nf = P->Nf; a.Nb = P->Nb; a.A = P->A;
   a.Kmr = P->Kmr; a.Ke = P->Ke; a.Kmf = P->Kmf; a.Kmb = P->Kmb; a.Vmax = P->Vmax;
   a.c = P->c; a.p = (int)P->p; a.s = (int)P->s;
@@ -1709,6 +1788,35 @@ extern "C" int ms_integrate_signals(const ms_kinetics_params *params, const floa
   return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
+extern "C" int64_t ms_kinetics_cache_record_words(int64_t p, int64_t s) { return record_words(p, s, nullptr); }
+
+__global__ void cache_invalidate_kernel(unsigned *records, long long rec_words, const int *rows, long long n) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n) records[(rows ? (long long)rows[r] : r) * rec_words] = 0u;  // REC_STALE
+}
+
+extern "C" int ms_kinetics_cache_invalidate(uint32_t *records, int64_t rec_words, const int32_t *rows,
+                                            int64_t n_rows, void *stream) {
+  if (!records || rec_words < REC_HEADER_WORDS || n_rows < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (n_rows == 0) return MS_OK;
+  cache_invalidate_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(records, rec_words,
+                                                                                              rows, n_rows);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_integrate_signals_cached(const ms_kinetics_params *params, const ms_kinetics_cache *cache,
+                                           const float *X_in, float *X_out, const int32_t *eq_iters_host,
+                                           uint32_t *flags, void *scratch, size_t scratch_bytes, void *stream) {
+  if (!params || !cache || !flags || (params->c > 0 && (!X_in || !X_out)) || X_in == X_out)
+    return MS_ERR_INVALID_ARGUMENT;
+  KinArgs a = {};
+  int rc = fill_eq(a, eq_iters_host);
+  if (rc) return rc;
+  a.X_in = X_in; a.X_out = X_out; a.flags = flags;
+  return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream, cache);
+}
+
 extern "C" int ms_integrate_signals_part(const ms_kinetics_params *params, const float *adj_vmax,
                                          const float *X0, float *X1, int32_t max_eq_iters,
                                          uint32_t *flags, float *V_out, void *scratch,
@@ -1726,11 +1834,11 @@ extern "C" int ms_integrate_signals_part(const ms_kinetics_params *params, const
   return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
-extern "C" int ms_enzymatic_activity(const ms_kinetics_params *params, const int32_t *cell_positions,
-                                     const float *cell_molecules, const float *molecule_map,
-                                     int64_t m, int64_t H, int64_t W, float *X_out,
-                                     const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
-                                     size_t scratch_bytes, void *stream) {
+static int enzymatic_activity_impl(const ms_kinetics_params *params, const ms_kinetics_cache *cache,
+                                   const int32_t *cell_positions, const float *cell_molecules,
+                                   const float *molecule_map, int64_t m, int64_t H, int64_t W, float *X_out,
+                                   const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
+                                   size_t scratch_bytes, void *stream) {
   if (!params || !flags || params->s != 2 * m || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX ||
       (params->c > 0 && (!cell_positions || !cell_molecules || !molecule_map || !X_out)))
     return MS_ERR_INVALID_ARGUMENT;
@@ -1740,7 +1848,26 @@ extern "C" int ms_enzymatic_activity(const ms_kinetics_params *params, const int
   a.X_in = nullptr; a.cell_mols = cell_molecules; a.mol_map = molecule_map; a.pos = cell_positions;
   a.m = (int)m; a.H = (int)H; a.W = (int)W;
   a.X_out = X_out; a.flags = flags;
-  return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream);
+  return launch_fused(params, a, scratch, scratch_bytes, (cudaStream_t)stream, cache);
+}
+
+extern "C" int ms_enzymatic_activity(const ms_kinetics_params *params, const int32_t *cell_positions,
+                                     const float *cell_molecules, const float *molecule_map,
+                                     int64_t m, int64_t H, int64_t W, float *X_out,
+                                     const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
+                                     size_t scratch_bytes, void *stream) {
+  return enzymatic_activity_impl(params, nullptr, cell_positions, cell_molecules, molecule_map, m, H, W, X_out,
+                                 eq_iters_host, flags, scratch, scratch_bytes, stream);
+}
+
+extern "C" int ms_enzymatic_activity_cached(const ms_kinetics_params *params, const ms_kinetics_cache *cache,
+                                            const int32_t *cell_positions, const float *cell_molecules,
+                                            const float *molecule_map, int64_t m, int64_t H, int64_t W,
+                                            float *X_out, const int32_t *eq_iters_host, uint32_t *flags,
+                                            void *scratch, size_t scratch_bytes, void *stream) {
+  if (!cache) return MS_ERR_INVALID_ARGUMENT;
+  return enzymatic_activity_impl(params, cache, cell_positions, cell_molecules, molecule_map, m, H, W, X_out,
+                                 eq_iters_host, flags, scratch, scratch_bytes, stream);
 }
 
 static inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }

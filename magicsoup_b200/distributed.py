@@ -157,9 +157,7 @@ class SlabWorld(World):
             "lifetimes": self.cell_lifetimes[idx],
             "divisions": self.cell_divisions[idx],
         }
-        kidx = idx.to(self.kinetics.N.device)
-        for k in _ALL_PARAMS:
-            out[k] = getattr(self.kinetics, k)[kidx]
+        out.update(self.kinetics.cell_params(idx))
         return out
 
     def import_cells(self, payload: dict[str, torch.Tensor]) -> list[int]:
@@ -216,7 +214,7 @@ class SlabWorld(World):
         self.cell_positions = self.cell_positions[keep]
         self.cell_divisions = self.cell_divisions[keep]
         self.cell_molecules = self.cell_molecules[keep]
-        self.kinetics.remove_cell_params(keep=keep.to(self.kinetics.N.device))
+        self.kinetics.remove_cell_params(keep=keep)
         for idx in sorted(cell_idxs, reverse=True):
             self.cell_genomes.pop(idx)
             self.cell_labels.pop(idx)

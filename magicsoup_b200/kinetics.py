@@ -23,6 +23,7 @@ side genetics and not part of this hot path; populations are installed with
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Any, Sequence
 
 import torch
@@ -80,28 +81,38 @@ class Kinetics:
         self.mol_names = [d.name for d in molecules]
         self.mol_energies = torch.tensor([d.energy for d in molecules] * 2, dtype=torch.float32, device=device)
         n_signals = 2 * len(molecules)
-        self.Ke = self._zeros_f32_tensor(0, 0)
-        self.Kmf = self._zeros_f32_tensor(0, 0)
-        self.Kmb = self._zeros_f32_tensor(0, 0)
-        self.Kmr = self._zeros_f32_tensor(0, 0, n_signals)
-        self.Vmax = self._zeros_f32_tensor(0, 0)
-        self.N = self._zeros_i32_tensor(0, 0, n_signals)
-        self.Nf = self._zeros_i32_tensor(0, 0, n_signals)
-        self.Nb = self._zeros_i32_tensor(0, 0, n_signals)
-        self.A = self._zeros_i32_tensor(0, 0, n_signals)
+        z_i = lambda: self._zeros_i32_tensor(0, 0, n_signals)  # noqa: E731
+        z_f = lambda: self._zeros_f32_tensor(0, 0)  # noqa: E731
+        self._buf: dict[str, torch.Tensor] = {
+            "N": z_i(), "Nf": z_i(), "Nb": z_i(), "A": z_i(), "Kmr": self._zeros_f32_tensor(0, 0, n_signals),
+            "Ke": z_f(), "Kmf": z_f(), "Kmb": z_f(), "Vmax": z_f()}
+        self._len: dict[str, int] = {k: 0 for k in _ALL_PARAMS}
+        self._rows: torch.Tensor | None = None   # int32 row map (logical cell -> buffer row); None = identity
+        self._phys_end = 0                       # buffer rows in use
+        self._cache: torch.Tensor | None = None  # (buffer rows, record words) int32 list-cache records
+        self.list_cache = True                   # keep the kernel's sparse lists between steps (p, s <= 64)
+        self._stamps: dict[str, tuple[int, int]] = {}
+        self._stamp()
         self._scratch: dict[str, torch.Tensor] = {}
 
     # ------------------------------------------------------------------ pickling
     def __getstate__(self):
+        self._materialize()
         state = dict(self.__dict__)
         state["_scratch"] = {}  # device scratch is rebuilt lazily (world.py:747-793 pickles the object)
+        state["_cache"] = None
+        state["_buf"] = {k: self._view(k).clone() for k in _ALL_PARAMS}  # without the spare capacity
         return state
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+        self._stamp()
 
     # ------------------------------------------------------------------ device plumbing
     def _cuda(self) -> torch.device:
         nat.require_cuda()
         dev = torch.device(self.device)
-        if dev.type != "cuda":
+        if dev.type != "cuda" or dev.index is None:
             dev = torch.device("cuda", torch.cuda.current_device())
         return dev
 
@@ -124,20 +135,20 @@ class Kinetics:
 
     def _params(self, dev: torch.device, c: int, s: int, need: Sequence[str] = _ALL_PARAMS):
         """
-        Normalised views of the current attributes + the C struct.  Tensors a call does
+        Normalised dense views of the current attributes + the C struct.  Tensors a call does
         not read may be left at their initial (0,0[,s]) shape, as the reference's tests do.
         """
         p = None
         for k in need:
-            t = getattr(self, k)
+            t = self._view(k)
             if t.dim() >= 2 and t.shape[0] == c:
                 p = int(t.shape[1])
                 break
         if p is None:
-            p = int(getattr(self, need[0]).shape[1])
+            p = int(self._view(need[0]).shape[1])
         keep = {}
         for k in _ALL_PARAMS:
-            t = getattr(self, k)
+            t = self._view(k)
             want = (c, p, s) if k in _CPS_PARAMS else (c, p)
             if k in need:
                 if tuple(t.shape) != want:
@@ -147,6 +158,37 @@ class Kinetics:
                 keep[k] = None
         st = nat.KineticsParams(**{k: nat.ptr(v) for k, v in keep.items()}, c=c, p=p, s=s)
         return st, keep, p
+
+    def _launch_args(self, dev: torch.device, c: int, s: int):
+        """
+        Arguments of the fused three-part launches (integrate_signals, World.enzymatic_activity):
+        (params struct, cache struct or None, tensors to keep alive, p).  With the store in its
+        managed state on `dev` the kernels read the capacity buffers in place through the row
+        map, and the list cache is used; anything else (user-assigned CPU tensors, odd dtypes)
+        goes through _params' normalised copies without a cache.
+        """
+        b = self._buf
+        if not (self._managed() and b["N"].device == dev and self._len["N"] == c and b["N"].shape[2] == s
+                and all(t.is_contiguous() for t in b.values())):
+            st, keep, p = self._params(dev, c, s)
+            return st, None, keep, p
+        p = int(b["N"].shape[1])
+        st = nat.KineticsParams(**{k: nat.ptr(b[k]) for k in _ALL_PARAMS}, c=c, p=p, s=s)
+        rec_words = int(nat.lib().ms_kinetics_cache_record_words(p, s)) if self.list_cache else 0
+        if rec_words == 0:
+            self._cache = None
+        else:
+            rows = int(b["N"].shape[0])
+            if self._cache is None or tuple(self._cache.shape) != (rows, rec_words) or self._cache.device != dev:
+                self._cache = torch.zeros(rows, rec_words, dtype=torch.int32, device=dev)
+                self._stamp()
+            elif self._written_from_outside():
+                self._stale(None)  # someone wrote into an attribute view: every record may be stale
+                self._stamp()
+        if self._cache is None and self._rows is None:
+            return st, None, b, p
+        cs = nat.KineticsCache(records=nat.ptr(self._cache), rec_words=rec_words, row_map=nat.ptr(self._rows))
+        return st, cs, (b, self._cache, self._rows), p
 
     def _kin_scratch(self, dev: torch.device, c: int, p: int, s: int):
         n = int(nat.lib().ms_kinetics_scratch_bytes(c, p, s))
@@ -178,14 +220,20 @@ class Kinetics:
         out = torch.empty_like(Xd)
         if c == 0 or s == 0:
             return out
-        st, keep, p = self._params(dev, c, s)
+        st, cache, keep, p = self._launch_args(dev, c, s)
         scratch, nbytes = self._kin_scratch(dev, c, p, s)
         flags = self._flags(dev)
         eq = [4, 4, 4]
         while True:
-            nat.check(nat.lib().ms_integrate_signals(
-                st, nat.ptr(Xd), nat.ptr(out), nat.eq_array(eq), nat.ptr(flags), nat.ptr(scratch),
-                nbytes, nat.stream_ptr(dev)))
+            if cache is None:
+                rc = nat.lib().ms_integrate_signals(
+                    st, nat.ptr(Xd), nat.ptr(out), nat.eq_array(eq), nat.ptr(flags), nat.ptr(scratch),
+                    nbytes, nat.stream_ptr(dev))
+            else:
+                rc = nat.lib().ms_integrate_signals_cached(
+                    st, C.byref(cache), nat.ptr(Xd), nat.ptr(out), nat.eq_array(eq), nat.ptr(flags),
+                    nat.ptr(scratch), nbytes, nat.stream_ptr(dev))
+            nat.check(rc)
             if not _settle_early_exit(self._read_flags(flags), eq, 3):
                 return out
 
@@ -298,6 +346,118 @@ class Kinetics:
                 return out
 
     # ------------------------------------------------------------------ parameter store
+    # The nine public attributes (kinetics.py:399-409) are views of capacity buffers.  The
+    # reference re-allocates all of them on every change of the cell count (torch.cat in
+    # kinetics.py:688-703, boolean-mask copies in :667-686: 42 KB per cell at p=64, s=32, i.e. two
+    # 44 GB copies per kill or divide call at 1M cells).  Here
+    #   * growth is amortised (capacity grows by half, new rows are zeroed);
+    #   * removing cells only edits an int32 row map (logical cell -> buffer row, increasing); the
+    #     kernels read parameter tiles through it, nothing is moved;
+    #   * reading an attribute compacts the buffers in place first (chunked, no second copy), so
+    #     users and tests always see the reference's dense (c,p[,s]) tensors;
+    #   * assigning an attribute adopts the tensor as the new buffer, as in the reference.
+    # A per-row cache of the kernel's sparse lists rides along (see _launch_args).
+
+    def _managed(self) -> bool:
+        """all nine tensors describe the same cells in same-sized buffers on one device"""
+        b = self._buf
+        n, rows = self._len["N"], b["N"].shape[0]
+        if b["N"].dim() != 3:
+            return False
+        p, s_ = b["N"].shape[1], b["N"].shape[2]
+        dev = b["N"].device
+        for k in _ALL_PARAMS:
+            t = b[k]
+            want = (rows, p, s_) if k in _CPS_PARAMS else (rows, p)
+            dt = torch.int32 if k in _INT_PARAMS else torch.float32
+            if tuple(t.shape) != want or self._len[k] != n or t.device != dev or t.dtype != dt:
+                return False
+        return True
+
+    @property
+    def _n(self) -> int:
+        return self._len["N"]
+
+    def _view(self, k: str) -> torch.Tensor:
+        self._materialize()
+        t = self._buf[k]
+        return t if t.dim() == 0 or t.shape[0] == self._len[k] else t[: self._len[k]]
+
+    def _adopt(self, k: str, value: Any):
+        """`kinetics.N = tensor` (kinetics.py's attributes are plain tensors that users replace)"""
+        self._materialize()
+        if not isinstance(value, torch.Tensor):
+            value = torch.as_tensor(value)
+        self._buf[k] = value
+        self._len[k] = int(value.shape[0]) if value.dim() > 0 else 0
+        self._phys_end = self._len["N"]
+        self._cache = None
+        self._stamp()
+
+    def _stamp(self):
+        self._stamps = {k: (t.data_ptr(), t._version) for k, t in self._buf.items()}
+
+    def _written_from_outside(self) -> bool:
+        return any(self._stamps.get(k) != (t.data_ptr(), t._version) for k, t in self._buf.items())
+
+    def _phys(self, idxs) -> torch.Tensor:
+        """buffer rows of logical cells"""
+        dev = self._buf["N"].device
+        idx = torch.as_tensor(idxs, dtype=torch.long, device=dev)
+        if idx.dtype == torch.bool:
+            idx = torch.nonzero(idx).flatten()
+        return idx if self._rows is None else self._rows[idx].long()
+
+    def _materialize(self):
+        """compact the buffers in place so that row i holds cell i (the row map is increasing)"""
+        if self._rows is None:
+            return
+        rows, n = self._rows.long(), self._len["N"]
+        self._rows = None
+        self._phys_end = n
+        if n == 0:
+            return
+        moved = torch.nonzero(rows != torch.arange(n, device=rows.device)).flatten()
+        if moved.numel() == 0:
+            return
+        start = int(moved[0])
+        bufs = [self._buf[k] for k in _ALL_PARAMS] + ([self._cache] if self._cache is not None else [])
+        row_bytes = max(t[0].numel() * t.element_size() for t in bufs)
+        chunk = max(1, (256 << 20) // max(row_bytes, 1))
+        for a in range(start, n, chunk):
+            r = rows[a:a + chunk]
+            for t in bufs:  # rows[i] >= i: writing rows [a, a+chunk) never destroys an unread row
+                t[a:a + r.numel()] = t[r]
+        self._stamp()
+
+    def _reserve(self, new_rows: int):
+        end = self._phys_end
+        for k in _ALL_PARAMS:
+            old = self._buf[k]
+            new = torch.empty((new_rows,) + tuple(old.shape[1:]), dtype=old.dtype, device=old.device)
+            new[:end] = old[:end]
+            self._buf[k] = new
+            del old
+        if self._cache is not None:
+            new = torch.zeros((new_rows, self._cache.shape[1]), dtype=torch.int32, device=self._cache.device)
+            new[:end] = self._cache[:end]
+            self._cache = new
+
+    def _stale(self, phys: torch.Tensor | None):
+        """the list-cache records of these buffer rows no longer describe their parameters"""
+        if self._cache is not None:
+            if phys is None:
+                self._cache[:, 0] = 0
+            else:
+                self._cache[phys.to(self._cache.device), 0] = 0
+
+    def cell_params(self, cell_idxs) -> dict[str, torch.Tensor]:
+        """the nine parameter slices of the given cells (copies), without compacting the store"""
+        if not self._managed():
+            return {k: self._view(k)[cell_idxs] for k in _ALL_PARAMS}
+        phys = self._phys(cell_idxs)
+        return {k: self._buf[k][phys] for k in _ALL_PARAMS}
+
     def set_cell_params_from_tensors(self, cell_idxs: list[int] | torch.Tensor, **tensors: torch.Tensor):
         """
         Install ready-made parameters for `cell_idxs` (what set_cell_params derives from
@@ -305,14 +465,20 @@ class Kinetics:
         """
         p_new = int(tensors["N"].shape[1])
         self.increase_max_proteins(max_n=p_new)
-        p = int(self.N.shape[1])
+        managed = self._managed()
+        phys = self._phys(cell_idxs) if managed else cell_idxs
         for k in _ALL_PARAMS:
-            src = tensors[k].to(device=self.device, dtype=getattr(self, k).dtype)
+            dst = self._buf[k] if managed else self._view(k)
+            p = int(dst.shape[1])
+            src = tensors[k].to(device=dst.device, dtype=dst.dtype)
             if p_new < p:  # pad like unset proteins
                 pad_shape = list(src.shape)
                 pad_shape[1] = p - p_new
                 src = torch.cat([src, torch.zeros(pad_shape, dtype=src.dtype, device=src.device)], dim=1)
-            getattr(self, k)[cell_idxs] = src
+            dst[phys] = src
+        if managed:
+            self._stale(phys)
+        self._stamp()
 
     def set_cell_params(self, cell_idxs, proteomes):
         raise NotImplementedError(
@@ -321,31 +487,86 @@ class Kinetics:
 
     def unset_cell_params(self, cell_idxs: list[int]):
         """kinetics.py:627-644"""
+        managed = self._managed()
+        phys = self._phys(cell_idxs) if managed else cell_idxs
         for k in _ALL_PARAMS:
-            getattr(self, k)[cell_idxs] = 0
+            (self._buf[k] if managed else self._view(k))[phys] = 0
+        if managed:
+            self._stale(phys)
+        self._stamp()
 
     def copy_cell_params(self, from_idxs: list[int], to_idxs: list[int]):
         """kinetics.py:646-665"""
+        managed = self._managed()
+        src = self._phys(from_idxs) if managed else from_idxs
+        dst = self._phys(to_idxs) if managed else to_idxs
         for k in _ALL_PARAMS:
-            t = getattr(self, k)
-            t[to_idxs] = t[from_idxs]
+            t = self._buf[k] if managed else self._view(k)
+            t[dst] = t[src]
+        if managed and self._cache is not None:
+            self._cache[dst] = self._cache[src]  # same parameters, same lists
+        self._stamp()
 
     def remove_cell_params(self, keep: torch.Tensor):
-        """kinetics.py:667-686: order-preserving compaction of the cell dimension"""
+        """kinetics.py:667-686: order-preserving removal; only the row map is edited"""
+        if not self._managed():
+            for k in _ALL_PARAMS:
+                self._adopt(k, self._view(k)[keep])
+            return
+        dev = self._buf["N"].device
+        keep = torch.as_tensor(keep, dtype=torch.bool, device=dev)
+        n = self._len["N"]
+        rows = self._rows if self._rows is not None else torch.arange(n, dtype=torch.int32, device=dev)
+        self._rows = rows[keep].contiguous()
         for k in _ALL_PARAMS:
-            setattr(self, k, getattr(self, k)[keep])
+            self._len[k] = int(self._rows.numel())
 
     def increase_max_cells(self, by_n: int):
-        """kinetics.py:688-703"""
+        """kinetics.py:688-703: by_n new all-zero cells at the end"""
+        if by_n <= 0:
+            return
+        if not self._managed():
+            for k in _ALL_PARAMS:
+                self._adopt(k, self._expand(self._view(k), dim=0, n=by_n))
+            return
+        n, end, cap = self._len["N"], self._phys_end, int(self._buf["N"].shape[0])
+        if end + by_n > cap:
+            if self._rows is not None and (end - n) >= by_n and 4 * (end - n) >= cap:
+                self._materialize()  # enough freed rows inside: compact instead of growing
+                end = n
+            if end + by_n > cap:
+                self._reserve(max(end + by_n, cap + cap // 2 + 16) if cap > 0 else by_n)
         for k in _ALL_PARAMS:
-            setattr(self, k, self._expand(getattr(self, k), dim=0, n=by_n))
+            self._buf[k][end:end + by_n].zero_()
+            self._len[k] = n + by_n
+        if self._cache is not None:
+            self._cache[end:end + by_n].zero_()
+        if self._rows is not None:
+            new = torch.arange(end, end + by_n, dtype=torch.int32, device=self._rows.device)
+            self._rows = torch.cat([self._rows, new])
+        self._phys_end = end + by_n
+        self._stamp()
 
     def increase_max_proteins(self, max_n: int):
         """kinetics.py:705-723: the protein dimension only ever grows"""
-        n_prots = int(self.N.size(1))
-        if max_n > n_prots:
+        n_prots = int(self._buf["N"].size(1))
+        if max_n <= n_prots:
+            return
+        if not self._managed():
             for k in _ALL_PARAMS:
-                setattr(self, k, self._expand(getattr(self, k), dim=1, n=max_n - n_prots))
+                self._adopt(k, self._expand(self._view(k), dim=1, n=max_n - n_prots))
+            return
+        end = self._phys_end
+        for k in _ALL_PARAMS:
+            old = self._buf[k]
+            shape = list(old.shape)
+            shape[1] = max_n
+            new = torch.zeros(shape, dtype=old.dtype, device=old.device)
+            new[:end, :n_prots] = old[:end]
+            self._buf[k] = new
+            del old
+        self._cache = None  # the record size depends on p
+        self._stamp()
 
     def _expand(self, t: torch.Tensor, dim: int, n: int) -> torch.Tensor:
         shape = list(t.shape)
@@ -357,3 +578,17 @@ class Kinetics:
 
     def _zeros_f32_tensor(self, *args) -> torch.Tensor:
         return torch.zeros(*args, device=self.device, dtype=torch.float32)
+
+
+def _param_property(name: str) -> property:
+    def getter(self) -> torch.Tensor:
+        return self._view(name)
+
+    def setter(self, value):
+        self._adopt(name, value)
+
+    return property(getter, setter, doc=f"Kinetics.{name} (kinetics.py:399-409): dense tensor of the current cells")
+
+
+for _k in _ALL_PARAMS:
+    setattr(Kinetics, _k, _param_property(_k))

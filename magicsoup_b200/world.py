@@ -22,6 +22,7 @@ raise without a CUDA device.
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
 import random
 from dataclasses import dataclass
@@ -128,7 +129,7 @@ class World:
     def _cuda(self) -> torch.device:
         nat.require_cuda()
         dev = torch.device(self.device)
-        if dev.type != "cuda":
+        if dev.type != "cuda" or dev.index is None:
             dev = torch.device("cuda", torch.cuda.current_device())
         return dev
 
@@ -182,15 +183,21 @@ class World:
         m = self.n_molecules
         _, H, W = mm.shape
         c, s = self.n_cells, 2 * m
-        st, keep, p = kin._params(dev, c, s)
+        st, cache, keep, p = kin._launch_args(dev, c, s)
         scratch, nbytes = kin._kin_scratch(dev, c, p, s)
         flags = kin._flags(dev)
         if self._kernel_events is not None:
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record(torch.cuda.current_stream(dev))
-        nat.check(nat.lib().ms_enzymatic_activity(
-            st, nat.ptr(pos), nat.ptr(cm), nat.ptr(mm), m, H, W, nat.ptr(X), nat.eq_array(eq),
-            nat.ptr(flags), nat.ptr(scratch), nbytes, nat.stream_ptr(dev)))
+        if cache is None:
+            rc = nat.lib().ms_enzymatic_activity(
+                st, nat.ptr(pos), nat.ptr(cm), nat.ptr(mm), m, H, W, nat.ptr(X), nat.eq_array(eq),
+                nat.ptr(flags), nat.ptr(scratch), nbytes, nat.stream_ptr(dev))
+        else:
+            rc = nat.lib().ms_enzymatic_activity_cached(
+                st, C.byref(cache), nat.ptr(pos), nat.ptr(cm), nat.ptr(mm), m, H, W, nat.ptr(X),
+                nat.eq_array(eq), nat.ptr(flags), nat.ptr(scratch), nbytes, nat.stream_ptr(dev))
+        nat.check(rc)
         if self._kernel_events is not None:
             ev[1].record(torch.cuda.current_stream(dev))
             self._kernel_events.append(ev)

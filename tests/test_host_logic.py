@@ -139,3 +139,115 @@ def test_synthetic_population_invariants():
     assert len({(int(x), int(y)) for x, y in pop.cell_positions.tolist()}) == 64
     again = make_population(64, 16, 6, 16, seed=9)
     assert torch.equal(pop.N, again.N) and torch.equal(pop.Kmr, again.Kmr)
+
+
+class _NaiveStore:
+    """the reference's way (kinetics.py:627-723): torch.cat growth, boolean-mask removal"""
+
+    def __init__(self, s):
+        self.t = {k: (torch.zeros(0, 0, s, dtype=torch.int32) if k in ("N", "Nf", "Nb", "A") else
+                      torch.zeros(0, 0, s) if k == "Kmr" else torch.zeros(0, 0)) for k in _ALL_PARAMS}
+
+    def grow_c(self, n):
+        for k, t in self.t.items():
+            self.t[k] = torch.cat([t, torch.zeros(n, *t.shape[1:], dtype=t.dtype)], 0)
+
+    def grow_p(self, p):
+        for k, t in self.t.items():
+            if p > t.shape[1]:
+                shape = list(t.shape)
+                shape[1] = p - t.shape[1]
+                self.t[k] = torch.cat([t, torch.zeros(shape, dtype=t.dtype)], 1)
+
+
+def test_parameter_store_matches_reference_semantics_under_random_lifecycle():
+    g = torch.Generator().manual_seed(0)
+    kin, ref = _kin(), _NaiveStore(4)
+    pop = make_population(64, 3, 2, 8, seed=1)
+    src = {k: getattr(pop, k) for k in _ALL_PARAMS}
+    kin.increase_max_proteins(3)
+    ref.grow_p(3)
+    n = 0
+    for step in range(60):
+        op = int(torch.randint(0, 5, (1,), generator=g))
+        if op == 0 or n < 4:  # new cells with parameters
+            k_new = int(torch.randint(1, 6, (1,), generator=g))
+            pick = torch.randint(0, 64, (k_new,), generator=g)
+            kin.increase_max_cells(by_n=k_new)
+            ref.grow_c(k_new)
+            idxs = list(range(n, n + k_new))
+            kin.set_cell_params_from_tensors(idxs, **{k: v[pick] for k, v in src.items()})
+            for k in _ALL_PARAMS:
+                ref.t[k][idxs] = src[k][pick]
+            n += k_new
+        elif op == 1:  # kill
+            keep = torch.rand(n, generator=g) > 0.3
+            kin.remove_cell_params(keep=keep)
+            for k in _ALL_PARAMS:
+                ref.t[k] = ref.t[k][keep]
+            n = int(keep.sum())
+        elif op == 2:  # divide: children appended, parameters copied
+            k_new = int(torch.randint(1, 4, (1,), generator=g))
+            parents = torch.randint(0, n, (k_new,), generator=g).tolist()
+            kin.increase_max_cells(by_n=k_new)
+            ref.grow_c(k_new)
+            kids = list(range(n, n + k_new))
+            kin.copy_cell_params(from_idxs=parents, to_idxs=kids)
+            for k in _ALL_PARAMS:
+                ref.t[k][kids] = ref.t[k][parents]
+            n += k_new
+        elif op == 3:
+            idx = torch.randint(0, n, (2,), generator=g).tolist()
+            kin.unset_cell_params(cell_idxs=idx)
+            for k in _ALL_PARAMS:
+                ref.t[k][idx] = 0
+        else:  # peek without compacting
+            idx = torch.randint(0, n, (3,), generator=g).tolist()
+            got = kin.cell_params(idx)
+            for k in _ALL_PARAMS:
+                assert torch.equal(got[k], ref.t[k][idx])
+        if step % 7 == 0 or step == 59:  # reading an attribute compacts in place
+            for k in _ALL_PARAMS:
+                assert torch.equal(getattr(kin, k), ref.t[k]), (step, k)
+            assert kin._rows is None and kin._phys_end == n
+    assert kin._n == n
+
+
+def test_parameter_store_growth_is_amortised_and_removal_moves_nothing():
+    kin = _kin()
+    pop = make_population(200, 4, 2, 16, seed=2)
+    kin.increase_max_cells(by_n=100)
+    kin.set_cell_params_from_tensors(list(range(100)), **{k: getattr(pop, k)[:100] for k in _ALL_PARAMS})
+    kin.increase_max_cells(by_n=10)  # grows the capacity by half
+    ptr = kin._buf["N"].data_ptr()
+    assert kin._buf["N"].shape[0] >= 150
+    for _ in range(4):
+        kin.increase_max_cells(by_n=10)  # fits the spare rows: no reallocation
+        assert kin._buf["N"].data_ptr() == ptr
+    keep = torch.ones(150, dtype=torch.bool)
+    keep[::3] = False
+    kin.remove_cell_params(keep=keep)
+    assert kin._buf["N"].data_ptr() == ptr and kin._rows is not None and kin._n == 100
+    assert torch.equal(kin._rows.long(), torch.nonzero(keep).flatten())
+    assert kin.N.shape == (100, 4, 4) and kin._rows is None  # attribute access compacted the rows
+    assert torch.equal(kin.N[:66], pop.N[:100][keep[:100]])
+
+
+def test_parameter_store_notices_outside_writes_and_assignment():
+    kin = _kin()
+    pop = make_population(8, 3, 2, 4, seed=3)
+    kin.increase_max_cells(by_n=8)
+    kin.set_cell_params_from_tensors(list(range(8)), **{k: getattr(pop, k) for k in _ALL_PARAMS})
+    assert not kin._written_from_outside()
+    kin.N[2, 1, 0] = 7  # in place through the attribute view, as users do (SURVEY H5)
+    assert kin._written_from_outside() and int(kin._buf["N"][2, 1, 0]) == 7
+    kin._stamp()
+    kin.Vmax = torch.ones(8, 3)  # assignment adopts the tensor
+    assert kin._managed() and not kin._written_from_outside() and float(kin.Vmax.sum()) == 24.0
+    kin.Ke = torch.ones(5, 3)  # inconsistent shapes are allowed, as in the reference
+    assert not kin._managed() and kin.Ke.shape == (5, 3)
+    import pickle
+    kin.Ke = torch.ones(8, 3)
+    kin.remove_cell_params(keep=torch.tensor([True, False] * 4))
+    back = pickle.loads(pickle.dumps(kin))
+    assert back.N.shape == (4, 3, 4) and torch.equal(back.N, kin.N) and back._cache is None

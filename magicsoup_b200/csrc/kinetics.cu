@@ -59,6 +59,7 @@ struct KinArgs {
   int *work_counter;      // device counter handing out cells to warps (zeroed before the launch)
   int scan_staged;        // batch mode: steps of the tile scan staged ahead in shared memory (0, 1 or 2)
   int batch_enabled;      // tier 1, p, s <= 64, 8 warps per CTA: the CTA integrates 8 cells together
+  int lane_enabled;       // tier 1, p, s <= 64: one warp per cell on fixed-format lists (kinetics_lanes.cuh)
   // Parameter rows and the list cache (ms_*_cached entry points).  row_map[cell] is the row of the
   // nine parameter tensors (and of the cache) that holds logical cell `cell`; X, positions and cell
   // molecules are always indexed by the logical cell.  cache: one record per parameter row with the
@@ -71,7 +72,7 @@ struct KinArgs {
 };
 
 // list-cache record: word 0 = n_act | status << 16, words 1..3 unused, then the three segments
-constexpr unsigned REC_STALE = 0, REC_VALID = 1, REC_OVERFLOW = 2;
+constexpr unsigned REC_STALE = 0, REC_VALID = 1, REC_OVERFLOW = 2;  // in bits 24.. of word 0
 constexpr int REC_HEADER_WORDS = 4;
 
 __device__ __forceinline__ long long param_row(const KinArgs &a, long long cell) {
@@ -1141,6 +1142,10 @@ __device__ __noinline__ void run_dense(const KinArgs &a, float *X0, float *X1, f
   }
 }
 
+}  // namespace ms
+#include "kinetics_lanes.cuh"
+namespace ms {
+
 template <int VEC>
 __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
                                                                     float *dense_scratch) {
@@ -1177,6 +1182,84 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
     const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
     return a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
   };
+  if (a.lane_enabled) {
+    // ---- lane path: every warp takes cells from the work counter and integrates them alone
+    const LaneLayout L = make_lane_layout(p, s);
+    unsigned *b = wbase;
+    const unsigned sb = wshared;
+    auto grab = [&]() -> long long {
+      int v = 0;
+      if (lane == 0) v = atomicAdd(a.work_counter, 1);
+      return (long long)__shfl_sync(FULL, v, 0);
+    };
+    float xa = 0.0f, xb = 0.0f;
+    long long cell = grab();
+    if (cell < n_items) {
+      if (lane < s) xa = load_x(cell, lane);
+      if (lane + 32 < s) xb = load_x(cell, lane + 32);
+    }
+    while (cell < n_items) {
+      const long long next_cell = grab();
+      const long long prm = param_row(a, cell);
+      unsigned *rec = a.cache ? a.cache + prm * (long long)a.rec_words : nullptr;
+      const unsigned hdr = rec ? __ldg(rec) : 0u;
+      const unsigned status = hdr >> 24;
+      LaneCounts cnt = {0, 0, 0};
+      bool ok = false;
+      if (status == REC_VALID) {
+        // a valid record holds exactly what build_lane_lists left in the static arrays
+        const uint4 *src = reinterpret_cast<const uint4 *>(rec + REC_HEADER_WORDS);
+        const int n16 = L.static_words >> 2;
+        for (int e = lane; e < n16; e += 32) cp_async16(sb + 16u * (unsigned)e, src + e, 0u);
+        cnt = unpack_counts(hdr);
+        ok = true;
+      } else if (status != REC_OVERFLOW) {
+        const long long tile = prm * (long long)p * s;
+        int nq;
+        if (VEC == 4 && a.scan_staged)
+          nq = scan_tile_staged<2>(a, sb, sb + 1024u, sb + 1536u, sb + 2048u, sb + 2560u, sb + 3072u, sb + 3584u,
+                                   sb + 4u * (unsigned)L.oQueue, L.q_cap, tile, lane);
+        else
+          nq = scan_tile<VEC>(a, b + L.oQueue, L.q_cap, tile, lane);
+        __syncwarp();
+        ok = nq >= 0 && build_lane_lists(a, L, b, sb, prm, lane, nq, cnt);
+        if (rec) {  // keep the lists for the next steps
+          if (ok) {
+            cp_async_wait_all();  // scalars and Kmr have landed
+            __syncwarp();
+            uint4 *dst = reinterpret_cast<uint4 *>(rec + REC_HEADER_WORDS);
+            const uint4 *seg = reinterpret_cast<const uint4 *>(b);
+            const int n16 = L.static_words >> 2;
+            for (int e = lane; e < n16; e += 32) dst[e] = seg[e];
+          }
+          if (lane == 0) rec[0] = ok ? (REC_VALID << 24) | pack_counts(cnt) : REC_OVERFLOW << 24;
+        }
+      }
+      float *X0 = reinterpret_cast<float *>(b + (ok ? L.oX0 : 0));
+      if (lane < s) X0[lane] = xa;
+      if (lane + 32 < s) X0[lane + 32] = xb;
+      if (next_cell < n_items) {  // next cell's signals: in flight during this cell's parts
+        if (lane < s) xa = load_x(next_cell, lane);
+        if (lane + 32 < s) xb = load_x(next_cell, lane + 32);
+      }
+      cp_async_wait_all();
+      __syncwarp();
+      if (ok) {
+        run_lanes(a, L, sb, cell, lane, cnt, sflags);
+        for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
+      } else if (a.defer_enabled) {
+        if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
+      } else {
+        run_dense(a, X0, X0 + s32, X0 + 2 * s32, dscr, dscr + round32(p), dscr + 2 * round32(p), cell, lane, sflags);
+        for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
+      }
+      __syncwarp();
+      cell = next_cell;
+    }
+    __syncthreads();
+    if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
+    return;
+  }
   if (a.batch_enabled) {
     // ---- batch mode: 8 cells per CTA at a time, scanned per warp, integrated together
     __shared__ BatchShared bs;
@@ -1222,7 +1305,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
         // what build_lists left in the region for these parameters, so the results are identical)
         unsigned *rec = a.cache ? a.cache + prm * (long long)a.rec_words : nullptr;
         const unsigned hdr = rec ? __ldg(rec) : 0u;
-        const unsigned status = hdr >> 16;
+        const unsigned status = hdr >> 24;
         if (status == REC_VALID) {
           const uint4 *src = reinterpret_cast<const uint4 *>(rec + REC_HEADER_WORDS);
 #pragma unroll
@@ -1266,7 +1349,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
                 dst += n16;
               }
             }
-            if (lane == 0) rec[0] = (ok ? (REC_VALID << 16) | (unsigned)n_act : REC_OVERFLOW << 16);
+            if (lane == 0) rec[0] = (ok ? (REC_VALID << 24) | (unsigned)n_act : REC_OVERFLOW << 24);
           }
         }
         if (!ok) {
@@ -1563,11 +1646,12 @@ static int sm_count() {
 // Diagnostic switches, read from the environment ONCE, at the first launch of the
 // process; ms_kinetics_reload_switches() re-reads them (tests flip them between launches).
 struct Switches {
-  bool no_batch, no_staged_scan, staged_depth1;
+  bool no_lanes, no_batch, no_staged_scan, staged_depth1;
   int max_ctas_per_sm;  // 0 = no limit
 };
 static Switches read_switches() {
   Switches sw;
+  sw.no_lanes = getenv("MS_KIN_NO_LANES") != nullptr;
   sw.no_batch = getenv("MS_KIN_NO_BATCH") != nullptr;
   sw.no_staged_scan = getenv("MS_KIN_NO_STAGED_SCAN") != nullptr;
   sw.staged_depth1 = getenv("MS_KIN_STAGED_DEPTH1") != nullptr;
@@ -1633,6 +1717,24 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   return pl;
 }
 
+static bool lanes_possible(int64_t p, int64_t s) {
+  return p >= 1 && s >= 1 && p <= LANE_MAX_PS && s <= LANE_MAX_PS && !switches().no_lanes;
+}
+
+// tier 1 of the lane path (kinetics_lanes.cuh): one warp per cell, 8 independent warps per CTA
+static LaunchPlan plan_lanes(int64_t p, int64_t s) {
+  LaunchPlan pl = {};
+  const LaneLayout L = make_lane_layout((int)p, (int)s);
+  pl.sparse_enabled = 1;
+  pl.e_nnz = L.q_cap;
+  pl.warps_per_cta = WARPS_PER_CTA;
+  pl.align = 128;
+  pl.words_per_warp = L.words;
+  pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + pl.align;
+  finish_plan(pl);
+  return pl;
+}
+
 // tier 2: lists that hold a completely dense tile; as many warps per CTA as fit
 static bool plan_tier2(int64_t p, int64_t s, LaunchPlan &pl) {
   pl = {};
@@ -1679,9 +1781,12 @@ static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cu
   a.e_ent = pl.e_ent; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
   a.region_bytes = (unsigned)pl.words_per_warp * 4u;
   a.smem_align = pl.align;
-  a.batch_enabled = (a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS && a.s <= BATCH_MAX_PS &&
-                     pl.warps_per_cta == BATCH && !switches().no_batch) ? 1 : 0;
-  {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
+  a.lane_enabled = (a.tier == 1 && lanes_possible(a.p, a.s)) ? 1 : 0;
+  a.batch_enabled = (!a.lane_enabled && a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS &&
+                     a.s <= BATCH_MAX_PS && pl.warps_per_cta == BATCH && !switches().no_batch) ? 1 : 0;
+  if (a.lane_enabled) {
+    a.scan_staged = switches().no_staged_scan ? 0 : 2;
+  } else {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
     const Layout L = make_layout(a.p, a.s, pl.e_ent, pl.e_nnz, pl.e_reg);
     a.scan_staged = (a.batch_enabled && pl.e_ent >= 256 && 2 * pl.e_reg >= 128 && 3 * L.S2 + 32 >= 128 &&
                      !switches().no_staged_scan) ? 1 : 0;
@@ -1712,6 +1817,7 @@ static int launch_plan(const LaunchPlan &pl, KinArgs &a, float *dense, cudaStrea
 // words of a list-cache record for tier-1 lists of this shape (0: the shape has no batch mode)
 static int64_t record_words(int64_t p, int64_t s, int *seg) {
   if (p < 1 || s < 1 || p > BATCH_MAX_PS || s > BATCH_MAX_PS) return 0;
+  if (lanes_possible(p, s)) return REC_HEADER_WORDS + make_lane_layout((int)p, (int)s).static_words;
   const LaunchPlan pl = plan_tier1(p, s);
   if (!pl.sparse_enabled || pl.warps_per_cta != BATCH) return 0;
   const Layout L = make_layout((int)p, (int)s, pl.e_ent, pl.e_nnz, pl.e_reg);
@@ -1748,7 +1854,7 @@ static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, 
   a.work_counter = a.defer_count + 1;  // [0] deferred count, [1] tier-1 work, [2] tier-2 work
   a.defer_list = a.defer_count + 64;
 
-  LaunchPlan p1 = plan_tier1(P->p, P->s), p2;
+  LaunchPlan p1 = lanes_possible(P->p, P->s) ? plan_lanes(P->p, P->s) : plan_tier1(P->p, P->s), p2;
   const bool two_tiers = p1.sparse_enabled && plan_tier2(P->p, P->s, p2) && p2.e_nnz > p1.e_nnz;
   const int64_t ctas_needed = ceil_div(P->c, p1.warps_per_cta);
   if (p1.grid > ctas_needed) p1.grid = (int)ctas_needed;

@@ -193,10 +193,12 @@ def test_integrate_signals_bit_exact(ms, shape):
 
 
 _PATH_SWITCHES = [
-    {},                                  # default: batch mode, staged scan (two steps ahead where p > 32)
-    {"MS_KIN_STAGED_DEPTH1": "1"},       # staged scan, one step ahead
-    {"MS_KIN_NO_STAGED_SCAN": "1"},      # register scan
-    {"MS_KIN_NO_BATCH": "1"},            # warp-per-cell path (run_sparse)
+    {},                                                        # default: lane path, staged scan
+    {"MS_KIN_NO_STAGED_SCAN": "1"},                            # lane path, register scan
+    {"MS_KIN_NO_LANES": "1"},                                  # batch mode, staged scan two steps ahead
+    {"MS_KIN_NO_LANES": "1", "MS_KIN_STAGED_DEPTH1": "1"},     # batch mode, staged scan one step ahead
+    {"MS_KIN_NO_LANES": "1", "MS_KIN_NO_STAGED_SCAN": "1"},    # batch mode, register scan
+    {"MS_KIN_NO_LANES": "1", "MS_KIN_NO_BATCH": "1"},          # warp-per-cell path on variable-length lists
 ]
 
 
@@ -212,7 +214,7 @@ def test_kernel_paths_agree_bit_for_bit(ms, shape, monkeypatch):
     X = pop.X0()
     ora = O.integrate_signals(oracle_params(pop), X.numpy())
     for env in _PATH_SWITCHES:
-        for k in ("MS_KIN_STAGED_DEPTH1", "MS_KIN_NO_STAGED_SCAN", "MS_KIN_NO_BATCH"):
+        for k in ("MS_KIN_STAGED_DEPTH1", "MS_KIN_NO_STAGED_SCAN", "MS_KIN_NO_BATCH", "MS_KIN_NO_LANES"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)

@@ -44,7 +44,7 @@ def test_cached_lists_give_the_same_bits(shape):
     X = pop.X0().cuda()
     ora = _oracle(kin, X)
     first = kin.integrate_signals(X)   # scans the tiles and stores the lists
-    assert kin._cache is not None and int((kin._cache[: c, 0] >> 16 == 1).sum()) > 0.9 * c
+    assert kin._cache is not None and int((kin._cache[: c, 0] >> 24 == 1).sum()) > 0.9 * c
     second = kin.integrate_signals(X)  # integrates from the stored lists
     assert bits_equal(first, ora), describe_mismatch(first, ora)
     assert bits_equal(second, ora), describe_mismatch(second, ora)
@@ -67,7 +67,7 @@ def test_overflowing_and_unpackable_cells_with_cache():
     for _ in range(3):
         out = kin.integrate_signals(X)
         assert bits_equal(out, ora), describe_mismatch(out, ora)
-    status = (kin._cache[:160, 0] >> 16).cpu()
+    status = (kin._cache[:160, 0] >> 24).cpu()
     assert set(status[pick].tolist()) == {2} and int((status == 1).sum()) == int((~pick).sum()) - 1
 
 

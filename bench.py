@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-cells", type=int, default=65536)
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-list-cache", action="store_true",
+                    help="scan the dense parameter tiles in every step (Kinetics.list_cache = False)")
     ap.add_argument("--energies", default="modest", choices=["modest", "survey"],
                     help="molecule energies of the synthetic chemistry: U(10,50) kJ (default) or SURVEY §8(d)'s U(10,500) kJ")
     return ap.parse_args()
@@ -157,6 +159,7 @@ def build_world(args, device, seed, world_size=1):
     world.cell_labels = [""] * pop.c
     for k in PARAMS:
         setattr(world.kinetics, k, getattr(pop, k))
+    world.kinetics.list_cache = not args.no_list_cache
     return world, pop
 
 

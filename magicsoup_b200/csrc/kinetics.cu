@@ -15,6 +15,7 @@
 #include <stdlib.h>
 
 #include "ms_common.cuh"
+#include "kinetics_layout.cuh"
 
 namespace ms {
 
@@ -60,6 +61,7 @@ struct KinArgs {
   int scan_staged;        // batch mode: steps of the tile scan staged ahead in shared memory (0, 1 or 2)
   int batch_enabled;      // tier 1, p, s <= 64, 8 warps per CTA: the CTA integrates 8 cells together
   int lane_enabled;       // tier 1, p, s <= 64: one warp per cell on fixed-format lists (kinetics_lanes.cuh)
+  LaneLayout lanes;       // its region layout (host-computed: constant-bank operands in the kernel)
   // Parameter rows and the list cache (ms_*_cached entry points).  row_map[cell] is the row of the
   // nine parameter tensors (and of the cache) that holds logical cell `cell`; X, positions and cell
   // molecules are always indexed by the logical cell.  cache: one record per parameter row with the
@@ -97,12 +99,6 @@ __device__ __forceinline__ long long param_row(const KinArgs &a, long long cell)
 // During the scan nvs+csc hold the queue of non-zero tile elements (2 words each) and
 // then (nvs) the unsorted N list, which is sorted into csc.
 // ---------------------------------------------------------------------------
-__host__ __device__ inline int round32(int x) { return (x + 31) & ~31; }
-__host__ __device__ inline int pow2_at_least_32(int x) {
-  int r = 32;
-  while (r < x) r <<= 1;
-  return r;
-}
 
 struct Layout {
   int S2, P2, oP, oEnt, oCsc, oNvs, oReg, oRegk, words;
@@ -1184,7 +1180,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
   };
   if (a.lane_enabled) {
     // ---- lane path: every warp takes cells from the work counter and integrates them alone
-    const LaneLayout L = make_lane_layout(p, s);
+    const LaneLayout &L = a.lanes;
     unsigned *b = wbase;
     const unsigned sb = wshared;
     auto grab = [&]() -> long long {
@@ -1193,6 +1189,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
       return (long long)__shfl_sync(FULL, v, 0);
     };
     float xa = 0.0f, xb = 0.0f;
+    unsigned wflags = 0;  // early-exit flags of this warp's cells (bit = index in the flags buffer)
     long long cell = grab();
     if (cell < n_items) {
       if (lane < s) xa = load_x(cell, lane);
@@ -1245,7 +1242,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
       cp_async_wait_all();
       __syncwarp();
       if (ok) {
-        run_lanes(a, L, sb, cell, lane, cnt, sflags);
+        run_lanes(a, L, sb, cell, lane, cnt, wflags);
         for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
       } else if (a.defer_enabled) {
         if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
@@ -1256,6 +1253,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
       __syncwarp();
       cell = next_cell;
     }
+    if (lane < MS_N_FLAGS && ((wflags >> lane) & 1u)) sflags[lane] = 1u;
     __syncthreads();
     if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
     return;
@@ -1785,6 +1783,7 @@ static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cu
   a.batch_enabled = (!a.lane_enabled && a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS &&
                      a.s <= BATCH_MAX_PS && pl.warps_per_cta == BATCH && !switches().no_batch) ? 1 : 0;
   if (a.lane_enabled) {
+    a.lanes = make_lane_layout(a.p, a.s);
     a.scan_staged = switches().no_staged_scan ? 0 : 2;
   } else {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
     const Layout L = make_layout(a.p, a.s, pl.e_ent, pl.e_nnz, pl.e_reg);

@@ -20,59 +20,6 @@
 
 namespace ms {
 
-struct LaneLayout {
-  int S2, PA, PA2, TS, EX, RG, CH, R;
-  // static arrays (cache record), word offsets in the warp's region
-  int oCol, oKe, oKmf, oKmb, oVmax, oPf, oEnt8, oExt8, oRare, oRegw, oRegk, oCsc, static_words;
-  // working arrays
-  int oX0, oX1, oRegf, oNv, oT, oV, oF, oFk, words;
-  int oQueue, q_cap;  // scan-time element queue (2 words each): the last 2*q_cap words
-};
-
-constexpr int LANE_MAX_PS = 64;   // p and s limit of the lane path
-constexpr int LANE_EXT_MAX = 7;   // extension chunks per protein (<= 32 entries per side)
-constexpr int LANE_REG_MAX = 15;  // regulatory entries per protein
-
-__host__ __device__ inline LaneLayout make_lane_layout(int p, int s) {
-  LaneLayout L;
-  L.S2 = pow2_at_least_32(s);
-  L.PA = round32(p);
-  L.PA2 = L.PA + 32;  // + the dummy protein of the padding entries
-  L.R = 31;
-  L.TS = 3 * L.S2 + 32;
-  L.EX = 16;
-  L.RG = L.PA;
-  L.CH = ((7 * p / 2 + 3) / 4 + s / 2 + 3) & ~3;
-  L.q_cap = round32((7 * p + 1) / 2 < 64 ? 64 : (7 * p + 1) / 2);
-  int o = 0;
-  L.oCol = o; o += L.S2;
-  L.oKe = o; o += L.PA;
-  L.oKmf = o; o += L.PA;
-  L.oKmb = o; o += L.PA;
-  L.oVmax = o; o += L.PA;
-  L.oPf = o; o += L.PA;
-  L.oEnt8 = o; o += 2 * L.PA;
-  L.oExt8 = o; o += 2 * L.EX;
-  L.oRare = o; o += 32;
-  L.oRegw = o; o += L.RG;
-  L.oRegk = o; o += L.RG;
-  L.oCsc = o; o += 2 * L.CH;
-  L.static_words = o;
-  L.oX0 = o; o += L.S2;
-  L.oX1 = o; o += L.S2;
-  L.oRegf = o; o += L.RG;
-  L.oNv = o; o += 4 * L.CH;
-  L.oT = o; o += L.TS;
-  L.oV = o; o += L.PA2;
-  L.oF = o; o += L.PA2;
-  L.oFk = o; o += L.PA2;
-  // the queue and the scan's staging slots (8 x 512 B) share the region while the tile is scanned
-  if (o < 1024 + 2 * L.q_cap) o = 1024 + 2 * L.q_cap;
-  L.words = (o + 31) & ~31;
-  L.oQueue = L.words - 2 * L.q_cap;
-  return L;
-}
-
 // header of a lane-path record / of the warp's current cell
 struct LaneCounts {
   int n_act, n_rare, n_reg;
@@ -348,7 +295,7 @@ __device__ __forceinline__ int csc_n(unsigned h) { return (int)(short)(unsigned 
 // all parts of one cell on the fixed-format lists; one warp, no CTA barrier
 // ---------------------------------------------------------------------------
 __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, long long cell, int lane,
-                          const LaneCounts cnt, unsigned *sflags) {
+                          const LaneCounts cnt, unsigned &wflags) {
   const int s = a.s;
   const float qnan = __int_as_float(0x7fc00000);
   const unsigned aCol = sb + 4u * L.oCol, aKe = sb + 4u * L.oKe, aKmf = sb + 4u * L.oKmf, aKmb = sb + 4u * L.oKmb;
@@ -365,7 +312,7 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
     // table of X0, regulatory factors (kinetics.py:789-799), entry state of the part
     if (q == 0) {  // later parts start from the previous part's X1, whose powers the table already holds
       for (int i = lane; i < s; i += 32) table_store(aT, S2x4, (unsigned)i, lds_f(aX0 + 4u * (unsigned)i));
-      table_rare(aT, S2x4, aRare, aX0, n_rare, lane);
+      if (n_rare) table_rare(aT, S2x4, aRare, aX0, n_rare, lane);
     }
     for (int e = lane; e < n_reg; e += 32) {
       const unsigned wd = lds_u(aRegw + 4u * (unsigned)e);
@@ -470,14 +417,17 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
       table_store(aT, S2x4, (unsigned)i, x);
     }
     __syncwarp();
-    table_rare(aT, S2x4, aRare, aX1, n_rare, lane);
-    if (n_rare) __syncwarp();
+    if (n_rare) {
+      table_rare(aT, S2x4, aRare, aX1, n_rare, lane);
+      __syncwarp();
+    }
 
     // ---- equilibrium trimming (kinetics.py:808-859)
     const int iters = a.eq_iters[q];
+    float inc = 1.0f;
 #pragma unroll 1
     for (int k = 0; k < iters; k++) {
-      const float inc = eq_increment(k);
+      if (k < 4) inc = inc * 0.5f;  // 0.5, 0.25, 0.125, 0.0625 (kinetics.py:846)
       unsigned mine = 0;
       bool changed = false;
 #pragma unroll 1
@@ -500,12 +450,10 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
       const unsigned any = __reduce_or_sync(FULL, mine);
       // If no F moved, every later iteration of this part repeats this one exactly (run_sparse).
       const bool moved = __any_sync(FULL, changed);
-      if (lane == 0 && any) {
+      if (any) {  // flag bits q*4+kk and 12+q*4+kk for kk in [k, k_end), warp-uniform
         const int k_end = moved ? k + 1 : iters;
-        for (int kk = k; kk < k_end; kk++) {
-          if (any & 1u) sflags[q * 4 + kk] = 1u;
-          sflags[12 + q * 4 + kk] = 1u;
-        }
+        const unsigned span = ((1u << k_end) - (1u << k)) << (4 * q);
+        wflags |= (span << 12) | ((any & 1u) ? span : 0u);
       }
       if (!moved) break;
       __syncwarp();
@@ -529,8 +477,10 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
         table_store(aT, S2x4, (unsigned)i, x);
       }
       __syncwarp();
-      table_rare(aT, S2x4, aRare, aX1, n_rare, lane);
-      if (n_rare) __syncwarp();
+      if (n_rare) {
+        table_rare(aT, S2x4, aRare, aX1, n_rare, lane);
+        __syncwarp();
+      }
     }
 
     if (a.V_out) {  // single-part calls: V of every protein, 0 for those without entries

@@ -27,7 +27,8 @@ def function_ranges(src: Path):
     pat = re.compile(r"^(?:template.*\n)?(?:__device__|__global__|static|template|extern).*?(\w+)\s*\(")
     while i < len(lines):
         ln = lines[i]
-        if (ln.startswith("__device__") or ln.startswith("__global__") or ln.startswith("template")) and not ln.rstrip().endswith(";"):
+        if (ln.startswith("__device__") or ln.startswith("__global__") or ln.startswith("template") or
+                ln.startswith("__host__")) and not ln.rstrip().endswith(";"):
             # find the opening brace
             j = i
             while j < len(lines) and "{" not in lines[j]:
@@ -93,13 +94,13 @@ def main():
     total = sum(v[0] for v in per_line.values())
     total_s = sum(v[2] for v in per_line.values())
     print(f"total warp instructions {total}" + (f" = {total / cells:.0f} per cell" if cells else ""))
-    kin = ROOT / "magicsoup_b200" / "csrc" / "kinetics.cu"
-    fr = function_ranges(kin)
+    csrc = ROOT / "magicsoup_b200" / "csrc"
+    fr = {f.name: function_ranges(f) for f in list(csrc.glob("*.cu")) + list(csrc.glob("*.cuh"))}
     by_fn = defaultdict(lambda: [0, 0, 0, 0])
     for (f, ln), v in per_line.items():
         name = f
-        if f == "kinetics.cu":
-            name = next((n for n, a, b in fr if a <= ln <= b), "kinetics.cu:other")
+        if f in fr:
+            name = next((n for n, a, b in fr[f] if a <= ln <= b), f + ":other")
         for i in range(4):
             by_fn[name][i] += v[i]
     print(f"{'function':28s} {'inst%':>6s} {'inst/cell':>9s} {'lanes':>6s} {'samples%':>8s} {'barrier%':>8s}")

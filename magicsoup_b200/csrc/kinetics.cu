@@ -1214,8 +1214,7 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
         const long long tile = prm * (long long)p * s;
         int nq;
         if (VEC == 4 && a.scan_staged)
-          nq = scan_tile_staged<2>(a, sb, sb + 1024u, sb + 1536u, sb + 2048u, sb + 2560u, sb + 3072u, sb + 3584u,
-                                   sb + 4u * (unsigned)L.oQueue, L.q_cap, tile, lane);
+          nq = scan_tile_lanes(a, sb, sb + 4u * (unsigned)L.oQueue, L.q_cap, tile, lane);
         else
           nq = scan_tile<VEC>(a, b + L.oQueue, L.q_cap, tile, lane);
         __syncwarp();

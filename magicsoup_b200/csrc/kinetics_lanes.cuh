@@ -35,6 +35,9 @@ __device__ __forceinline__ LaneCounts unpack_counts(unsigned w) {
   return c;
 }
 
+__device__ __forceinline__ void red_add_shared(unsigned addr, unsigned v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ void sts_u8(unsigned addr, unsigned v) {
   asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
@@ -56,6 +59,117 @@ __device__ __forceinline__ void sts_f4(unsigned addr, float4 v) {
 }
 
 // ---------------------------------------------------------------------------
+// Scan of the lane path: the cell's dense (p,s) tiles of Nf, Nb, N, A are streamed once, 512 bytes
+// per tensor and step, staged through shared memory two steps ahead (cp.async, 16 bytes per lane,
+// two slot sets of 4 x 512 bytes at `stage`), and every element with a non-zero value is pushed onto
+// the queue (2 words per element, row-major order).  Half of the steps of a typical tile are all
+// zero: such a step costs four 128-bit loads, an OR tree and one vote.  The loop is unrolled by the
+// two slot sets, so no slot addresses are swapped.  Returns the queue length or -1 (does not fit).
+// ---------------------------------------------------------------------------
+struct ScanState {
+  int q0, row, sig0, nq, chk;
+};
+
+__device__ __forceinline__ void scan_step(const KinArgs &a, ScanState &st, unsigned slots, const int *gNf,
+                                          const int *gNb, const int *gN, const int *gA, int total, int drow,
+                                          int dsig, unsigned aQueue, int cap, unsigned lt) {
+  int nf[4], nb[4], nn[4], na[4];
+  lds_vec4(slots, nf);
+  lds_vec4(slots + 512u, nb);
+  lds_vec4(slots + 1024u, nn);
+  lds_vec4(slots + 1536u, na);
+  const bool valid = st.q0 < total;  // past the end the slots hold stale words
+  const int o0 = nf[0] | nb[0] | nn[0] | na[0], o1 = nf[1] | nb[1] | nn[1] | na[1];
+  const int o2 = nf[2] | nb[2] | nn[2] | na[2], o3 = nf[3] | nb[3] | nn[3] | na[3];
+  const unsigned any_l = valid ? (unsigned)(o0 | o1 | o2 | o3) : 0u;
+  {  // refill the slots just read with the step after next (ordered behind the reads by `any_l`)
+    const int q = st.q0 + 256;
+    if (q < total) {
+      cp_async16(slots, gNf + q, any_l);
+      cp_async16(slots + 512u, gNb + q, any_l);
+      cp_async16(slots + 1024u, gN + q, any_l);
+      cp_async16(slots + 1536u, gA + q, any_l);
+    }
+    cp_async_commit();
+  }
+  const unsigned b1 = __ballot_sync(FULL, any_l != 0u);
+  if (b1) {
+    const unsigned m = (o0 != 0 ? 1u : 0u) | (o1 != 0 ? 2u : 0u) | (o2 != 0 ? 4u : 0u) | (o3 != 0 ? 8u : 0u);
+    const unsigned mm = valid ? m : 0u;
+    const int cnt = __popc(mm);
+    // exclusive prefix of cnt over the lanes: most lanes hold no element, few hold more than one
+    int pos = st.nq + __popc(b1 & lt), tot = __popc(b1);
+    const unsigned b2 = __ballot_sync(FULL, cnt >= 2);
+    if (b2) {
+      pos += __popc(b2 & lt);
+      tot += __popc(b2);
+      const unsigned b3 = __ballot_sync(FULL, cnt >= 3);
+      if (b3) {
+        const unsigned b4 = __ballot_sync(FULL, cnt >= 4);
+        pos += __popc(b3 & lt) + __popc(b4 & lt);
+        tot += __popc(b3) + __popc(b4);
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      if (mm & (1u << e)) {
+        // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
+        st.chk |= ((nf[e] | nb[e]) & 0xffffff00) | ((nn[e] + 32768) & 0xffff0000) | ((na[e] + 128) & 0xffffff00);
+        if (pos < cap)
+          queue_store(aQueue, pos, (unsigned)(st.sig0 + e) | ((unsigned)st.row << 8) | ((unsigned)(na[e] & 0xff) << 16),
+                      ((unsigned)nf[e] & 0xffu) | (((unsigned)nb[e] & 0xffu) << 8) | ((unsigned)nn[e] << 16));
+        pos++;
+      }
+    }
+    st.nq += tot;
+  }
+  st.q0 += 128;
+  st.row += drow;
+  st.sig0 += dsig;
+  if (st.sig0 >= a.s) { st.sig0 -= a.s; st.row++; }
+}
+
+__device__ __noinline__ int scan_tile_lanes(const KinArgs &a, unsigned stage, unsigned aQueue, int cap, long long tile,
+                                            int lane) {
+  const int s = a.s, total = a.p * s;
+  const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
+  const unsigned lt = (1u << lane) - 1u;
+  const unsigned setA = stage + 16u * (unsigned)lane, setB = setA + 2048u;
+  const int drow = 128 / s, dsig = 128 - drow * s;
+  ScanState st;
+  st.q0 = 4 * lane;
+  st.row = st.q0 / s;
+  st.sig0 = st.q0 - st.row * s;
+  st.nq = 0;
+  st.chk = 0;
+  if (st.q0 < total) {
+    cp_async16(setA, gNf + st.q0, 0u);
+    cp_async16(setA + 512u, gNb + st.q0, 0u);
+    cp_async16(setA + 1024u, gN + st.q0, 0u);
+    cp_async16(setA + 1536u, gA + st.q0, 0u);
+  }
+  cp_async_commit();
+  if (st.q0 + 128 < total) {
+    cp_async16(setB, gNf + st.q0 + 128, 0u);
+    cp_async16(setB + 512u, gNb + st.q0 + 128, 0u);
+    cp_async16(setB + 1024u, gN + st.q0 + 128, 0u);
+    cp_async16(setB + 1536u, gA + st.q0 + 128, 0u);
+  }
+  cp_async_commit();
+#pragma unroll 1
+  for (int base = 0; base < total; base += 256) {
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    scan_step(a, st, setA, gNf, gNb, gN, gA, total, drow, dsig, aQueue, cap, lt);
+    if (base + 128 < total) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      scan_step(a, st, setB, gNf, gNb, gN, gA, total, drow, dsig, aQueue, cap, lt);
+    }
+  }
+  if (__any_sync(FULL, st.chk != 0) || st.nq > cap) return -1;
+  return st.nq;
+}
+
+// ---------------------------------------------------------------------------
 // Builds the fixed-format lists of one cell from the queue of its non-zero tile elements (scan
 // phase 1: row-major order, i.e. ascending protein, then ascending signal).  Every position is a
 // deterministic rank (ballot / match), never the return value of an atomic.  Returns false if the
@@ -65,20 +179,20 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
                                  int lane, int nq, LaneCounts &cnt) {
   const int p = a.p, s = a.s;
   const unsigned lt = (1u << lane) - 1u;
-  const unsigned *queue = b + L.oQueue;
-  // temporaries in working arrays that are idle until the cell is integrated
-  unsigned *rowcnt = b + L.oX0;                   // [PA]  substrate | product << 8 | regulatory << 16 entries of a row
-  unsigned *rowmap = b + L.oX0 + L.PA;            // [PA]  active index of a row (0xff: inactive) | chunk/reg starts
-  unsigned *rowrun = b + L.oX0 + 2 * L.PA;        // [PA]  entries placed so far: substrate | product << 8
-  unsigned *sigcnt = b + L.oX0 + 3 * L.PA;        // [S2]  N entries of a signal, then its first chunk
-  unsigned *sigrun = b + L.oX0 + 3 * L.PA + L.S2; // [S2]  N entries placed so far
+  (void)b;
+  const unsigned aQueue = sb + 4u * (unsigned)L.oQueue;
+  // temporaries in working arrays that are idle until the cell is integrated (shared-window addresses)
+  const unsigned rowcnt = sb + 4u * (unsigned)L.oX0;        // [PA]  substrate | product << 8 | regulatory << 16 entries of a row
+  const unsigned rowmap = rowcnt + 4u * (unsigned)L.PA;     // [PA]  active index of a row (0xff: inactive) | chunk/reg starts
+  const unsigned rowrun = rowmap + 4u * (unsigned)L.PA;     // [PA]  entries placed so far: substrate | product << 8
+  const unsigned sigcnt = rowrun + 4u * (unsigned)L.PA;     // [S2]  N entries of a signal, then its first chunk
+  const unsigned sigrun = sigcnt + 4u * (unsigned)L.S2;     // [S2]  N entries placed so far
   // (3*PA + 2*S2 <= 2*S2 + RG + 4*CH words between oX0 and oT for every shape of the lane path)
-  for (int j = lane; j < L.PA; j += 32) { rowcnt[j] = 0; rowrun[j] = 0; }
-  for (int i = lane; i < L.S2; i += 32) { sigcnt[i] = 0; sigrun[i] = 0; }
-  for (int e = lane; e < 2 * L.PA + 2 * L.EX; e += 32) b[L.oEnt8 + e] = 0;  // ent8 and ext8 are adjacent
+  for (int j = lane; j < 3 * L.PA + 2 * L.S2; j += 32) sts_u(rowcnt + 4u * (unsigned)j, 0u);
+  for (int e = lane; e < 2 * L.PA + 2 * L.EX; e += 32) sts_u(sb + 4u * (unsigned)(L.oEnt8 + e), 0u);  // ent8, ext8
   {
     const unsigned pad = (unsigned)L.PA | ((unsigned)L.PA << 16);  // (dummy protein, N = 0) twice
-    for (int e = lane; e < 2 * L.CH; e += 32) b[L.oCsc + e] = pad;
+    for (int e = lane; e < 2 * L.CH; e += 32) sts_u(sb + 4u * (unsigned)(L.oCsc + e), pad);
   }
   __syncwarp();
   // ---- pass A: counts
@@ -87,14 +201,14 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
   for (int base = 0; base < nq; base += 32) {
     const int k = base + lane;
     const bool v = k < nq;
-    const uint2 qw = v ? *reinterpret_cast<const uint2 *>(queue + 2 * k) : make_uint2(0u, 0u);
+    const uint2 qw = v ? lds_v2(aQueue + 8u * (unsigned)k) : make_uint2(0u, 0u);
     const unsigned sig = qw.x & 0xffu, row = (qw.x >> 8) & 0xffu;
     const int av = (int)(int8_t)((qw.x >> 16) & 0xffu);
     const unsigned nf = qw.y & 0xffu, nb = (qw.y >> 8) & 0xffu;
     const int n = (int)qw.y >> 16;
     const unsigned inc = (nf ? 1u : 0u) | (nb ? 1u << 8 : 0u) | (av ? 1u << 16 : 0u);
-    if (inc) atomicAdd(&rowcnt[row], inc);
-    if (n != 0) atomicAdd(&sigcnt[sig], 1u);
+    if (inc) red_add_shared(rowcnt + 4u * row, inc);
+    if (n != 0) red_add_shared(sigcnt + 4u * sig, 1u);
     bad |= (n < -256 || n > 255) ? 1 : 0;
     n_rare += __popc(__ballot_sync(FULL, nf > 3u)) + __popc(__ballot_sync(FULL, nb > 3u));
   }
@@ -105,7 +219,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
 #pragma unroll 1
   for (int j0 = 0; j0 < L.PA; j0 += 32) {
     const int j = j0 + lane;
-    const unsigned cw = j < p ? rowcnt[j] : 0u;
+    const unsigned cw = j < p ? lds_u(rowcnt + 4u * (unsigned)j) : 0u;
     const unsigned ns = cw & 0xffu, np = (cw >> 8) & 0xffu;
     const bool active = (ns | np) != 0u;
     const unsigned nr = active ? (cw >> 16) & 0xffu : 0u;
@@ -123,10 +237,10 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
     const unsigned excl = incl - own;
     const unsigned t = (unsigned)n_act + __popc(ab & lt);
     const unsigned ext_start = (unsigned)ext_tot + (excl & 0xffffu), reg_start = (unsigned)reg_tot + (excl >> 16);
-    if (j < L.PA) rowmap[j] = active ? (t | (ext_start << 8) | (reg_start << 16)) : 0xffu;
+    if (j < L.PA) sts_u(rowmap + 4u * (unsigned)j, active ? (t | (ext_start << 8) | (reg_start << 16)) : 0xffu);
     if (active && ext_start + n_ext <= (unsigned)L.EX && reg_start + nr <= (unsigned)L.RG)
-      b[L.oPf + t] = (ns ? 1u : 0u) | (np ? 2u : 0u) | (n_ext << 2) | (ext_start << 5) | (nr << 10) |
-                     (reg_start << 14) | ((unsigned)j << 21);
+      sts_u(sb + 4u * ((unsigned)L.oPf + t), (ns ? 1u : 0u) | (np ? 2u : 0u) | (n_ext << 2) | (ext_start << 5) |
+                                                 (nr << 10) | (reg_start << 14) | ((unsigned)j << 21));
     n_act += __popc(ab);
     const unsigned tot = __shfl_sync(FULL, incl, 31);
     ext_tot += (int)(tot & 0xffffu);
@@ -138,7 +252,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
 #pragma unroll 1
   for (int i0 = 0; i0 < L.S2; i0 += 32) {
     const int i = i0 + lane;
-    const unsigned c = i < s ? sigcnt[i] : 0u;
+    const unsigned c = i < s ? lds_u(sigcnt + 4u * (unsigned)i) : 0u;
     const unsigned nch = (c + 3u) / 4u;
     unsigned incl = nch;
 #pragma unroll
@@ -147,8 +261,8 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
       if (lane >= d) incl += y;
     }
     const unsigned start = (unsigned)ch_tot + incl - nch;
-    sigcnt[i] = start;
-    b[L.oCol + i] = start | (nch << 16);
+    sts_u(sigcnt + 4u * (unsigned)i, start);
+    sts_u(sb + 4u * (unsigned)(L.oCol + i), start | (nch << 16));
     ch_tot += (int)__shfl_sync(FULL, incl, 31);
   }
   if (ch_tot > L.CH) return false;
@@ -158,7 +272,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
     const long long prow = prm_row * (long long)p;
     const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
     for (int t = lane; t < n_act; t += 32) {
-      const unsigned j = b[L.oPf + t] >> 21;
+      const unsigned j = lds_u(sb + 4u * (unsigned)(L.oPf + t)) >> 21;
       cp_async4(sb + 4u * (unsigned)(L.oKe + t), a.Ke + prow + j);
       cp_async4(sb + 4u * (unsigned)(L.oKmf + t), a.Kmf + prow + j);
       cp_async4(sb + 4u * (unsigned)(L.oKmb + t), a.Kmb + prow + j);
@@ -172,18 +286,18 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
   for (int base = 0; base < nq; base += 32) {
     const int k = base + lane;
     const bool v = k < nq;
-    const uint2 qw = v ? *reinterpret_cast<const uint2 *>(queue + 2 * k) : make_uint2(0u, 0u);
+    const uint2 qw = v ? lds_v2(aQueue + 8u * (unsigned)k) : make_uint2(0u, 0u);
     const unsigned sig = qw.x & 0xffu, row = (qw.x >> 8) & 0xffu;
     const int av = (int)(int8_t)((qw.x >> 16) & 0xffu);
     const unsigned nf = qw.y & 0xffu, nb = (qw.y >> 8) & 0xffu;
     const int n = (int)qw.y >> 16;
-    const unsigned rm = v ? rowmap[row] : 0xffu;
+    const unsigned rm = v ? lds_u(rowmap + 4u * row) : 0xffu;
     const bool active = (rm & 0xffu) != 0xffu;
     const unsigned t = rm & 0xffu, ext_start = (rm >> 8) & 0xffu;
     // ranks inside the row (the row's elements are consecutive, ascending signal)
     const unsigned peers = __match_any_sync(FULL, v ? row : 0x100u + (unsigned)lane);
     const unsigned bs = __ballot_sync(FULL, nf != 0u), bp = __ballot_sync(FULL, nb != 0u);
-    const unsigned run = v ? rowrun[row] : 0u;
+    const unsigned run = v ? lds_u(rowrun + 4u * row) : 0u;
     const unsigned ks = (run & 0xffu) + __popc(peers & bs & lt), kp = (run >> 8) + __popc(peers & bp & lt);
     // table slots of exponents >= 4, in queue order (substrate side first)
     const unsigned rs = __ballot_sync(FULL, nf > 3u), rp = __ballot_sync(FULL, nb > 3u);
@@ -193,7 +307,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
       unsigned idx = 1u + (nf - 1u) * (unsigned)L.S2 + sig;
       if (nf > 3u) {
         idx = 1u + 3u * (unsigned)L.S2 + r_sub;
-        b[L.oRare + r_sub] = sig | (nf << 8);
+        sts_u(sb + 4u * ((unsigned)L.oRare + r_sub), sig | (nf << 8));
       }
       const unsigned word = ks < 4u ? (unsigned)L.oEnt8 + 2u * t : (unsigned)L.oExt8 + 2u * (ext_start + ks / 4u - 1u);
       sts_u8(sb + 4u * word + (ks & 3u), idx);
@@ -202,7 +316,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
       unsigned idx = 1u + (nb - 1u) * (unsigned)L.S2 + sig;
       if (nb > 3u) {
         idx = 1u + 3u * (unsigned)L.S2 + r_prod;
-        b[L.oRare + r_prod] = sig | (nb << 8);
+        sts_u(sb + 4u * ((unsigned)L.oRare + r_prod), sig | (nb << 8));
       }
       const unsigned word = kp < 4u ? (unsigned)L.oEnt8 + 2u * t : (unsigned)L.oExt8 + 2u * (ext_start + kp / 4u - 1u);
       sts_u8(sb + 4u * (word + 1u) + (kp & 3u), idx);
@@ -212,7 +326,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
     const unsigned br = __ballot_sync(FULL, av != 0 && active);
     if (av != 0 && active) {
       const unsigned pos = (unsigned)reg_run + __popc(br & lt);
-      b[L.oRegw + pos] = sig | ((unsigned)(av & 0xff) << 8);
+      sts_u(sb + 4u * ((unsigned)L.oRegw + pos), sig | ((unsigned)(av & 0xff) << 8));
       cp_async4(sb + 4u * ((unsigned)L.oRegk + pos), a.Kmr + tile + (long long)row * s + sig);
     }
     reg_run += __popc(br);
@@ -222,13 +336,13 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
     const bool has_n = v && n != 0;
     const unsigned speers = __match_any_sync(FULL, has_n ? sig : 0x100u + (unsigned)lane);
     if (has_n) {
-      const unsigned pos = 4u * sigcnt[sig] + sigrun[sig] + __popc(speers & lt);
+      const unsigned pos = 4u * lds_u(sigcnt + 4u * sig) + lds_u(sigrun + 4u * sig) + __popc(speers & lt);
       const unsigned tt = active ? t : (unsigned)L.PA;
       sts_u16r(sb + 4u * (unsigned)L.oCsc + 2u * pos, tt | (((unsigned)n & 0x1ffu) << 7));
     }
     __syncwarp();
-    if (v && lane == 31 - __clz(peers)) rowrun[row] = run + (__popc(peers & bs) | (__popc(peers & bp) << 8));
-    if (has_n && lane == 31 - __clz(speers)) sigrun[sig] += __popc(speers);
+    if (v && lane == 31 - __clz(peers)) sts_u(rowrun + 4u * row, run + (__popc(peers & bs) | (__popc(peers & bp) << 8)));
+    if (has_n && lane == 31 - __clz(speers)) red_add_shared(sigrun + 4u * sig, (unsigned)__popc(speers));
     __syncwarp();
   }
   cnt.n_act = n_act;
@@ -391,6 +505,9 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
       }
     }
     __syncwarp();
+    // the limiting factor of each protein as a float (decoded once per protein, not once per entry)
+    for (int t = lane; t < L.PA2; t += 32) sts_f(aFk + 4u * (unsigned)t, fkey_decode(lds_u(aFk + 4u * (unsigned)t)));
+    __syncwarp();
     // X1 = max(X0 + sum_j NV'_ji, 0)   (kinetics.py:763-764)
 #pragma unroll 1
     for (int i = lane; i < s; i += 32) {
@@ -401,10 +518,10 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
       for (unsigned c = c0; c < c0 + nc; c++) {
         const uint2 w = lds_v2(aCsc + 8u * c);
         float4 nv = lds_f4(aNv + 16u * c);
-        nv.x = nv.x * fkey_decode(lds_u(aFk + ((w.x & 0x7fu) << 2)));
-        nv.y = nv.y * fkey_decode(lds_u(aFk + ((w.x >> 14) & 0x1fcu)));
-        nv.z = nv.z * fkey_decode(lds_u(aFk + ((w.y & 0x7fu) << 2)));
-        nv.w = nv.w * fkey_decode(lds_u(aFk + ((w.y >> 14) & 0x1fcu)));
+        nv.x = nv.x * lds_f(aFk + ((w.x & 0x7fu) << 2));
+        nv.y = nv.y * lds_f(aFk + ((w.x >> 14) & 0x1fcu));
+        nv.z = nv.z * lds_f(aFk + ((w.y & 0x7fu) << 2));
+        nv.w = nv.w * lds_f(aFk + ((w.y >> 14) & 0x1fcu));
         sts_f4(aNv + 16u * c, nv);
         acc = acc + nv.x;
         acc = acc + nv.y;

@@ -60,8 +60,7 @@ struct KinArgs {
   int *work_counter;      // device counter handing out cells to warps (zeroed before the launch)
   int scan_staged;        // batch mode: steps of the tile scan staged ahead in shared memory (0, 1 or 2)
   int batch_enabled;      // tier 1, p, s <= 64, 8 warps per CTA: the CTA integrates 8 cells together
-  int lane_enabled;       // tier 1, p, s <= 64: one warp per cell on fixed-format lists (kinetics_lanes.cuh)
-  LaneLayout lanes;       // its region layout (host-computed: constant-bank operands in the kernel)
+  LaneLayout lanes;       // region layout of the lane kernel (host-computed: constant-bank operands)
   // Parameter rows and the list cache (ms_*_cached entry points).  row_map[cell] is the row of the
   // nine parameter tensors (and of the cache) that holds logical cell `cell`; X, positions and cell
   // molecules are always indexed by the logical cell.  cache: one record per parameter row with the
@@ -1142,6 +1141,121 @@ __device__ __noinline__ void run_dense(const KinArgs &a, float *X0, float *X1, f
 #include "kinetics_lanes.cuh"
 namespace ms {
 
+// ---------------------------------------------------------------------------
+// The lane path as its own kernel: every warp takes cells from the work counter and integrates them
+// alone (kinetics_lanes.cuh).  Kept apart from kinetics_fused_kernel so that the code the 32
+// independent warps of an SM run through (scan, list building, integration) stays small: with the
+// warps at different places of it, instruction fetch decides the speed.  A cell that does not fit
+// the fixed-format lists is appended to the deferred list (tier 2 of kinetics_fused_kernel).
+// ---------------------------------------------------------------------------
+// X0 of a cell: read, or gathered from cell_molecules and the cell's pixel (world.py:619-621); lane i
+// holds signals i and i + 32.  One copy of the code for both call sites.
+__device__ __noinline__ void load_cell_signals(const KinArgs &a, long long cell, int lane, float &xa, float &xb) {
+  const int s = a.s;
+  float v[2] = {0.0f, 0.0f};
+  if (a.X_in) {
+    const float *x = a.X_in + cell * s;
+    if (lane < s) v[0] = x[lane];
+    if (lane + 32 < s) v[1] = x[lane + 32];
+  } else {
+    const float *cm = a.cell_mols + cell * a.m;
+    const float *px = a.mol_map + (long long)a.pos[2 * cell] * a.W + a.pos[2 * cell + 1];
+    const long long plane = (long long)a.H * a.W;
+#pragma unroll 1
+    for (int r = 0; r < 2; r++) {
+      const int i = lane + 32 * r;
+      if (i < s) v[r] = i < a.m ? cm[i] : px[(long long)(i - a.m) * plane];
+    }
+  }
+  xa = v[0];
+  xb = v[1];
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_kernel(const __grid_constant__ KinArgs a) {
+  extern __shared__ __align__(16) unsigned smem[];
+  __shared__ unsigned sflags[MS_N_FLAGS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < MS_N_FLAGS) sflags[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned raw = (unsigned)__cvta_generic_to_shared(smem);
+  unsigned aligned = (raw + (unsigned)a.smem_align - 1u) & ~((unsigned)a.smem_align - 1u);
+  asm volatile("mov.b32 %0, %0;" : "+r"(aligned));  // held in a register, not recomputed at every use
+  unsigned *b = smem + ((aligned - raw) >> 2) + (size_t)warp * a.words_per_warp;
+  const unsigned sb = aligned + (unsigned)warp * (unsigned)a.words_per_warp * 4u;
+  const int p = a.p, s = a.s;
+  const long long n_items = a.c;
+  const LaneLayout &L = a.lanes;
+  auto grab = [&]() -> long long {
+    int v = 0;
+    if (lane == 0) v = atomicAdd(a.work_counter, 1);
+    return (long long)__shfl_sync(FULL, v, 0);
+  };
+  float xa = 0.0f, xb = 0.0f;
+  unsigned wflags = 0;  // early-exit flags of this warp's cells (bit = index in the flags buffer)
+  long long cell = grab();
+  if (cell < n_items) load_cell_signals(a, cell, lane, xa, xb);
+#pragma unroll 1
+  while (cell < n_items) {
+    const long long next_cell = grab();
+    const long long prm = param_row(a, cell);
+    unsigned *rec = a.cache ? a.cache + prm * (long long)a.rec_words : nullptr;
+    const unsigned hdr = rec ? __ldg(rec) : 0u;
+    const unsigned status = hdr >> 24;
+    LaneCounts cnt = {0, 0, 0};
+    bool ok = false;
+    if (status == REC_VALID) {
+      // a valid record holds exactly what build_lane_lists left in the static arrays
+      const uint4 *src = reinterpret_cast<const uint4 *>(rec + REC_HEADER_WORDS);
+      const int n16 = L.static_words >> 2;
+#pragma unroll 1
+      for (int e = lane; e < n16; e += 32) cp_async16(sb + 16u * (unsigned)e, src + e, 0u);
+      cnt = unpack_counts(hdr);
+      ok = true;
+    } else if (status != REC_OVERFLOW) {
+      const long long tile = prm * (long long)p * s;
+      int nq;
+      if (VEC == 4)
+        nq = scan_tile_lanes(a, sb, sb + 4u * (unsigned)L.oQueue, L.q_cap, tile, lane);
+      else
+        nq = scan_tile<VEC>(a, b + L.oQueue, L.q_cap, tile, lane);
+      __syncwarp();
+      ok = nq >= 0 && build_lane_lists(a, L, b, sb, prm, lane, nq, cnt);
+      if (rec) {  // keep the lists for the next steps
+        if (ok) {
+          cp_async_wait_all();  // scalars and Kmr have landed
+          __syncwarp();
+          uint4 *dst = reinterpret_cast<uint4 *>(rec + REC_HEADER_WORDS);
+          const uint4 *seg = reinterpret_cast<const uint4 *>(b);
+          const int n16 = L.static_words >> 2;
+#pragma unroll 1
+          for (int e = lane; e < n16; e += 32) dst[e] = seg[e];
+        }
+        if (lane == 0) rec[0] = ok ? (REC_VALID << 24) | pack_counts(cnt) : REC_OVERFLOW << 24;
+      }
+    }
+    if (ok) {
+      if (lane < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane), xa);
+      if (lane + 32 < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane + 32), xb);
+    }
+    if (next_cell < n_items) load_cell_signals(a, next_cell, lane, xa, xb);  // in flight during this cell's parts
+    cp_async_wait_all();
+    __syncwarp();
+    if (ok) {
+      run_lanes(a, L, sb, cell, lane, cnt, wflags);
+#pragma unroll 1
+      for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = lds_f(sb + 4u * (unsigned)(L.oX0 + i));
+    } else if (lane == 0) {
+      a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;  // integrated by the tier-2 launch
+    }
+    __syncwarp();
+    cell = next_cell;
+  }
+  if (lane < MS_N_FLAGS && ((wflags >> lane) & 1u)) sflags[lane] = 1u;
+  __syncthreads();
+  if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
+}
+
 template <int VEC>
 __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
                                                                     float *dense_scratch) {
@@ -1178,85 +1292,6 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
     const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
     return a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
   };
-  if (a.lane_enabled) {
-    // ---- lane path: every warp takes cells from the work counter and integrates them alone
-    const LaneLayout &L = a.lanes;
-    unsigned *b = wbase;
-    const unsigned sb = wshared;
-    auto grab = [&]() -> long long {
-      int v = 0;
-      if (lane == 0) v = atomicAdd(a.work_counter, 1);
-      return (long long)__shfl_sync(FULL, v, 0);
-    };
-    float xa = 0.0f, xb = 0.0f;
-    unsigned wflags = 0;  // early-exit flags of this warp's cells (bit = index in the flags buffer)
-    long long cell = grab();
-    if (cell < n_items) {
-      if (lane < s) xa = load_x(cell, lane);
-      if (lane + 32 < s) xb = load_x(cell, lane + 32);
-    }
-    while (cell < n_items) {
-      const long long next_cell = grab();
-      const long long prm = param_row(a, cell);
-      unsigned *rec = a.cache ? a.cache + prm * (long long)a.rec_words : nullptr;
-      const unsigned hdr = rec ? __ldg(rec) : 0u;
-      const unsigned status = hdr >> 24;
-      LaneCounts cnt = {0, 0, 0};
-      bool ok = false;
-      if (status == REC_VALID) {
-        // a valid record holds exactly what build_lane_lists left in the static arrays
-        const uint4 *src = reinterpret_cast<const uint4 *>(rec + REC_HEADER_WORDS);
-        const int n16 = L.static_words >> 2;
-        for (int e = lane; e < n16; e += 32) cp_async16(sb + 16u * (unsigned)e, src + e, 0u);
-        cnt = unpack_counts(hdr);
-        ok = true;
-      } else if (status != REC_OVERFLOW) {
-        const long long tile = prm * (long long)p * s;
-        int nq;
-        if (VEC == 4 && a.scan_staged)
-          nq = scan_tile_lanes(a, sb, sb + 4u * (unsigned)L.oQueue, L.q_cap, tile, lane);
-        else
-          nq = scan_tile<VEC>(a, b + L.oQueue, L.q_cap, tile, lane);
-        __syncwarp();
-        ok = nq >= 0 && build_lane_lists(a, L, b, sb, prm, lane, nq, cnt);
-        if (rec) {  // keep the lists for the next steps
-          if (ok) {
-            cp_async_wait_all();  // scalars and Kmr have landed
-            __syncwarp();
-            uint4 *dst = reinterpret_cast<uint4 *>(rec + REC_HEADER_WORDS);
-            const uint4 *seg = reinterpret_cast<const uint4 *>(b);
-            const int n16 = L.static_words >> 2;
-            for (int e = lane; e < n16; e += 32) dst[e] = seg[e];
-          }
-          if (lane == 0) rec[0] = ok ? (REC_VALID << 24) | pack_counts(cnt) : REC_OVERFLOW << 24;
-        }
-      }
-      float *X0 = reinterpret_cast<float *>(b + (ok ? L.oX0 : 0));
-      if (lane < s) X0[lane] = xa;
-      if (lane + 32 < s) X0[lane + 32] = xb;
-      if (next_cell < n_items) {  // next cell's signals: in flight during this cell's parts
-        if (lane < s) xa = load_x(next_cell, lane);
-        if (lane + 32 < s) xb = load_x(next_cell, lane + 32);
-      }
-      cp_async_wait_all();
-      __syncwarp();
-      if (ok) {
-        run_lanes(a, L, sb, cell, lane, cnt, wflags);
-        for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
-      } else if (a.defer_enabled) {
-        if (lane == 0) a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;
-      } else {
-        run_dense(a, X0, X0 + s32, X0 + 2 * s32, dscr, dscr + round32(p), dscr + 2 * round32(p), cell, lane, sflags);
-        for (int i = lane; i < s; i += 32) a.X_out[cell * s + i] = X0[i];
-      }
-      __syncwarp();
-      cell = next_cell;
-    }
-    if (lane < MS_N_FLAGS && ((wflags >> lane) & 1u)) sflags[lane] = 1u;
-    __syncthreads();
-    if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
-    return;
-  }
   if (a.batch_enabled) {
     // ---- batch mode: 8 cells per CTA at a time, scanned per warp, integrated together
     __shared__ BatchShared bs;
@@ -1778,13 +1813,9 @@ static int launch_one(K kern, const LaunchPlan &pl, KinArgs &a, float *dense, cu
   a.e_ent = pl.e_ent; a.e_nnz = pl.e_nnz; a.e_reg = pl.e_reg; a.words_per_warp = pl.words_per_warp;
   a.region_bytes = (unsigned)pl.words_per_warp * 4u;
   a.smem_align = pl.align;
-  a.lane_enabled = (a.tier == 1 && lanes_possible(a.p, a.s)) ? 1 : 0;
-  a.batch_enabled = (!a.lane_enabled && a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS &&
-                     a.s <= BATCH_MAX_PS && pl.warps_per_cta == BATCH && !switches().no_batch) ? 1 : 0;
-  if (a.lane_enabled) {
-    a.lanes = make_lane_layout(a.p, a.s);
-    a.scan_staged = switches().no_staged_scan ? 0 : 2;
-  } else {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
+  a.batch_enabled = (a.tier == 1 && pl.sparse_enabled && a.p <= BATCH_MAX_PS && a.s <= BATCH_MAX_PS &&
+                     pl.warps_per_cta == BATCH && !switches().no_batch) ? 1 : 0;
+  {  // staging slots of scan_tile_staged: 1024 B in ent, 512 B in reg + regk, 512 B from X1 to colptr's end
     const Layout L = make_layout(a.p, a.s, pl.e_ent, pl.e_nnz, pl.e_reg);
     a.scan_staged = (a.batch_enabled && pl.e_ent >= 256 && 2 * pl.e_reg >= 128 && 3 * L.S2 + 32 >= 128 &&
                      !switches().no_staged_scan) ? 1 : 0;
@@ -1803,6 +1834,27 @@ static int pick_vec(const KinArgs &a) {
   if (a.s % 4 == 0 && (bits & 15) == 0) return 4;
   if (a.s % 2 == 0 && (bits & 7) == 0) return 2;
   return 1;
+}
+
+template <typename K>
+static int launch_lanes_one(K kern, const LaunchPlan &pl, KinArgs &a, cudaStream_t st) {
+  MS_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+  a.words_per_warp = pl.words_per_warp;
+  a.region_bytes = (unsigned)pl.words_per_warp * 4u;
+  a.smem_align = pl.align;
+  a.lanes = make_lane_layout(a.p, a.s);
+  a.sparse_enabled = 1;
+  kern<<<pl.grid, pl.warps_per_cta * 32, pl.smem_bytes, st>>>(a);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+static int launch_lanes(const LaunchPlan &pl, KinArgs &a, cudaStream_t st) {
+  int vec = pick_vec(a);
+  if (vec == 4 && switches().no_staged_scan) vec = 2;  // register scan
+  if (vec == 4) return launch_lanes_one(kinetics_lanes_kernel<4>, pl, a, st);
+  if (vec == 2) return launch_lanes_one(kinetics_lanes_kernel<2>, pl, a, st);
+  return launch_lanes_one(kinetics_lanes_kernel<1>, pl, a, st);
 }
 
 static int launch_plan(const LaunchPlan &pl, KinArgs &a, float *dense, cudaStream_t st) {
@@ -1852,14 +1904,17 @@ static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, 
   a.work_counter = a.defer_count + 1;  // [0] deferred count, [1] tier-1 work, [2] tier-2 work
   a.defer_list = a.defer_count + 64;
 
-  LaunchPlan p1 = lanes_possible(P->p, P->s) ? plan_lanes(P->p, P->s) : plan_tier1(P->p, P->s), p2;
-  const bool two_tiers = p1.sparse_enabled && plan_tier2(P->p, P->s, p2) && p2.e_nnz > p1.e_nnz;
+  // the lane kernel defers what it cannot pack, so it needs a tier 2 (true for every p, s <= 64)
+  LaunchPlan p2;
+  const bool lanes = lanes_possible(P->p, P->s) && plan_tier2(P->p, P->s, p2);
+  LaunchPlan p1 = lanes ? plan_lanes(P->p, P->s) : plan_tier1(P->p, P->s);
+  const bool two_tiers = lanes || (p1.sparse_enabled && plan_tier2(P->p, P->s, p2) && p2.e_nnz > p1.e_nnz);
   const int64_t ctas_needed = ceil_div(P->c, p1.warps_per_cta);
   if (p1.grid > ctas_needed) p1.grid = (int)ctas_needed;
   a.tier = 1;
   a.defer_enabled = two_tiers ? 1 : 0;
   MS_CUDA_CHECK(cudaMemsetAsync(a.defer_count, 0, 4 * sizeof(int), st));
-  int rc = launch_plan(p1, a, dense, st);
+  int rc = lanes ? launch_lanes(p1, a, st) : launch_plan(p1, a, dense, st);
   if (rc != MS_OK || !two_tiers) return rc;
   a.tier = 2;
   a.defer_enabled = 0;

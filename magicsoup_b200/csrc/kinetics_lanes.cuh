@@ -18,6 +18,13 @@
 // The static arrays (col .. csc) are what the list cache keeps per parameter row.
 #pragma once
 
+#ifndef MS_SCAN_STEP_INLINE
+#define MS_SCAN_STEP_INLINE __noinline__  // one copy for both slot sets: the code size matters more than the call
+#endif
+#ifndef MS_PRODUCTS_INLINE
+#define MS_PRODUCTS_INLINE __forceinline__
+#endif
+
 namespace ms {
 
 // header of a lane-path record / of the warp's current cell
@@ -70,7 +77,7 @@ struct ScanState {
   int q0, row, sig0, nq, chk;
 };
 
-__device__ __forceinline__ void scan_step(const KinArgs &a, ScanState &st, unsigned slots, const int *gNf,
+__device__ MS_SCAN_STEP_INLINE void scan_step(const KinArgs &a, ScanState &st, unsigned slots, const int *gNf,
                                           const int *gNb, const int *gN, const int *gA, int total, int drow,
                                           int dsig, unsigned aQueue, int cap, unsigned lt) {
   int nf[4], nb[4], nn[4], na[4];
@@ -188,10 +195,13 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
   const unsigned sigcnt = rowrun + 4u * (unsigned)L.PA;     // [S2]  N entries of a signal, then its first chunk
   const unsigned sigrun = sigcnt + 4u * (unsigned)L.S2;     // [S2]  N entries placed so far
   // (3*PA + 2*S2 <= 2*S2 + RG + 4*CH words between oX0 and oT for every shape of the lane path)
+#pragma unroll 1
   for (int j = lane; j < 3 * L.PA + 2 * L.S2; j += 32) sts_u(rowcnt + 4u * (unsigned)j, 0u);
+#pragma unroll 1
   for (int e = lane; e < 2 * L.PA + 2 * L.EX; e += 32) sts_u(sb + 4u * (unsigned)(L.oEnt8 + e), 0u);  // ent8, ext8
   {
     const unsigned pad = (unsigned)L.PA | ((unsigned)L.PA << 16);  // (dummy protein, N = 0) twice
+#pragma unroll 1
     for (int e = lane; e < 2 * L.CH; e += 32) sts_u(sb + 4u * (unsigned)(L.oCsc + e), pad);
   }
   __syncwarp();
@@ -271,6 +281,7 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
   {
     const long long prow = prm_row * (long long)p;
     const float *gv = a.adj_vmax ? a.adj_vmax : a.Vmax;
+#pragma unroll 1
     for (int t = lane; t < n_act; t += 32) {
       const unsigned j = lds_u(sb + 4u * (unsigned)(L.oPf + t)) >> 21;
       cp_async4(sb + 4u * (unsigned)(L.oKe + t), a.Ke + prow + j);
@@ -361,6 +372,7 @@ __device__ __forceinline__ void table_store(unsigned aT, unsigned S2x4, unsigned
 
 // rare slots: X_sig^n for the entries with n >= 4
 __device__ __forceinline__ void table_rare(unsigned aT, unsigned S2x4, unsigned aRare, unsigned aX, int n_rare, int lane) {
+#pragma unroll 1
   for (int r = lane; r < n_rare; r += 32) {
     const unsigned w = lds_u(aRare + 4u * (unsigned)r);
     sts_f(aT + 4u + 3u * S2x4 + 4u * (unsigned)r, powi(lds_f(aX + 4u * (w & 0xffu)), (int)(w >> 8)));
@@ -368,7 +380,7 @@ __device__ __forceinline__ void table_rare(unsigned aT, unsigned S2x4, unsigned 
 }
 
 // products over a protein's substrate and product entries (kinetics.py:894-918) from the table
-__device__ __forceinline__ void lane_products(unsigned aT, unsigned aEnt8, unsigned aExt8, unsigned t, unsigned pf,
+__device__ MS_PRODUCTS_INLINE void lane_products(unsigned aT, unsigned aEnt8, unsigned aExt8, unsigned t, unsigned pf,
                                               float &xf, float &xb) {
   uint2 e = lds_v2(aEnt8 + 8u * t);
   // byte k of a word -> table address: one PRMT and one shift-add
@@ -425,14 +437,17 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
     const float trim = a.trims[q];
     // table of X0, regulatory factors (kinetics.py:789-799), entry state of the part
     if (q == 0) {  // later parts start from the previous part's X1, whose powers the table already holds
+#pragma unroll 1
       for (int i = lane; i < s; i += 32) table_store(aT, S2x4, (unsigned)i, lds_f(aX0 + 4u * (unsigned)i));
       if (n_rare) table_rare(aT, S2x4, aRare, aX0, n_rare, lane);
     }
+#pragma unroll 1
     for (int e = lane; e < n_reg; e += 32) {
       const unsigned wd = lds_u(aRegw + 4u * (unsigned)e);
       sts_f(aRegf + 4u * (unsigned)e, reg_factor(lds_f(aX0 + 4u * (wd & 0xffu)), (int)(int8_t)((wd >> 8) & 0xff),
                                                  lds_f(aRegk + 4u * (unsigned)e)));
     }
+#pragma unroll 1
     for (int t = lane; t < L.PA2; t += 32) {
       sts_f(aV + 4u * (unsigned)t, 0.0f);  // incl. the dummy protein of the padding entries
       sts_f(aF + 4u * (unsigned)t, 1.0f);
@@ -506,6 +521,7 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
     }
     __syncwarp();
     // the limiting factor of each protein as a float (decoded once per protein, not once per entry)
+#pragma unroll 1
     for (int t = lane; t < L.PA2; t += 32) sts_f(aFk + 4u * (unsigned)t, fkey_decode(lds_u(aFk + 4u * (unsigned)t)));
     __syncwarp();
     // X1 = max(X0 + sum_j NV'_ji, 0)   (kinetics.py:763-764)
@@ -602,11 +618,14 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
 
     if (a.V_out) {  // single-part calls: V of every protein, 0 for those without entries
       float *vrow = a.V_out + cell * (long long)a.p;
+#pragma unroll 1
       for (int j = lane; j < a.p; j += 32) vrow[j] = 0.0f;
       __syncwarp();
+#pragma unroll 1
       for (int t = lane; t < n_act; t += 32) vrow[lds_u(aPf + 4u * (unsigned)t) >> 21] = lds_f(aV + 4u * (unsigned)t);
     }
     // next part starts from this part's result
+#pragma unroll 1
     for (int i = lane; i < s; i += 32) sts_f(aX0 + 4u * (unsigned)i, lds_f(aX1 + 4u * (unsigned)i));
     __syncwarp();
   }

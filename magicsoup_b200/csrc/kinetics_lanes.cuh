@@ -18,9 +18,6 @@
 // The static arrays (col .. csc) are what the list cache keeps per parameter row.
 #pragma once
 
-#ifndef MS_SCAN_STEP_INLINE
-#define MS_SCAN_STEP_INLINE __noinline__  // one copy for both slot sets: the code size matters more than the call
-#endif
 #ifndef MS_PRODUCTS_INLINE
 #define MS_PRODUCTS_INLINE __forceinline__
 #endif
@@ -70,110 +67,91 @@ __device__ __forceinline__ void sts_f4(unsigned addr, float4 v) {
 // per tensor and step, staged through shared memory two steps ahead (cp.async, 16 bytes per lane,
 // two slot sets of 4 x 512 bytes at `stage`), and every element with a non-zero value is pushed onto
 // the queue (2 words per element, row-major order).  Half of the steps of a typical tile are all
-// zero: such a step costs four 128-bit loads, an OR tree and one vote.  The loop is unrolled by the
-// two slot sets, so no slot addresses are swapped.  Returns the queue length or -1 (does not fit).
+// zero: such a step costs four 128-bit loads, an OR tree and one vote.  Returns the queue length or
+// -1 (the tile does not fit the queue or the packing).
 // ---------------------------------------------------------------------------
-struct ScanState {
-  int q0, row, sig0, nq, chk;
-};
-
-__device__ MS_SCAN_STEP_INLINE void scan_step(const KinArgs &a, ScanState &st, unsigned slots, const int *gNf,
-                                          const int *gNb, const int *gN, const int *gA, int total, int drow,
-                                          int dsig, unsigned aQueue, int cap, unsigned lt) {
-  int nf[4], nb[4], nn[4], na[4];
-  lds_vec4(slots, nf);
-  lds_vec4(slots + 512u, nb);
-  lds_vec4(slots + 1024u, nn);
-  lds_vec4(slots + 1536u, na);
-  const bool valid = st.q0 < total;  // past the end the slots hold stale words
-  const int o0 = nf[0] | nb[0] | nn[0] | na[0], o1 = nf[1] | nb[1] | nn[1] | na[1];
-  const int o2 = nf[2] | nb[2] | nn[2] | na[2], o3 = nf[3] | nb[3] | nn[3] | na[3];
-  const unsigned any_l = valid ? (unsigned)(o0 | o1 | o2 | o3) : 0u;
-  {  // refill the slots just read with the step after next (ordered behind the reads by `any_l`)
-    const int q = st.q0 + 256;
-    if (q < total) {
-      cp_async16(slots, gNf + q, any_l);
-      cp_async16(slots + 512u, gNb + q, any_l);
-      cp_async16(slots + 1024u, gN + q, any_l);
-      cp_async16(slots + 1536u, gA + q, any_l);
-    }
-    cp_async_commit();
-  }
-  const unsigned b1 = __ballot_sync(FULL, any_l != 0u);
-  if (b1) {
-    const unsigned m = (o0 != 0 ? 1u : 0u) | (o1 != 0 ? 2u : 0u) | (o2 != 0 ? 4u : 0u) | (o3 != 0 ? 8u : 0u);
-    const unsigned mm = valid ? m : 0u;
-    const int cnt = __popc(mm);
-    // exclusive prefix of cnt over the lanes: most lanes hold no element, few hold more than one
-    int pos = st.nq + __popc(b1 & lt), tot = __popc(b1);
-    const unsigned b2 = __ballot_sync(FULL, cnt >= 2);
-    if (b2) {
-      pos += __popc(b2 & lt);
-      tot += __popc(b2);
-      const unsigned b3 = __ballot_sync(FULL, cnt >= 3);
-      if (b3) {
-        const unsigned b4 = __ballot_sync(FULL, cnt >= 4);
-        pos += __popc(b3 & lt) + __popc(b4 & lt);
-        tot += __popc(b3) + __popc(b4);
-      }
-    }
-#pragma unroll
-    for (int e = 0; e < 4; e++) {
-      if (mm & (1u << e)) {
-        // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
-        st.chk |= ((nf[e] | nb[e]) & 0xffffff00) | ((nn[e] + 32768) & 0xffff0000) | ((na[e] + 128) & 0xffffff00);
-        if (pos < cap)
-          queue_store(aQueue, pos, (unsigned)(st.sig0 + e) | ((unsigned)st.row << 8) | ((unsigned)(na[e] & 0xff) << 16),
-                      ((unsigned)nf[e] & 0xffu) | (((unsigned)nb[e] & 0xffu) << 8) | ((unsigned)nn[e] << 16));
-        pos++;
-      }
-    }
-    st.nq += tot;
-  }
-  st.q0 += 128;
-  st.row += drow;
-  st.sig0 += dsig;
-  if (st.sig0 >= a.s) { st.sig0 -= a.s; st.row++; }
-}
-
 __device__ __noinline__ int scan_tile_lanes(const KinArgs &a, unsigned stage, unsigned aQueue, int cap, long long tile,
                                             int lane) {
   const int s = a.s, total = a.p * s;
   const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
   const unsigned lt = (1u << lane) - 1u;
-  const unsigned setA = stage + 16u * (unsigned)lane, setB = setA + 2048u;
+  const unsigned set0 = stage + 16u * (unsigned)lane;
   const int drow = 128 / s, dsig = 128 - drow * s;
-  ScanState st;
-  st.q0 = 4 * lane;
-  st.row = st.q0 / s;
-  st.sig0 = st.q0 - st.row * s;
-  st.nq = 0;
-  st.chk = 0;
-  if (st.q0 < total) {
-    cp_async16(setA, gNf + st.q0, 0u);
-    cp_async16(setA + 512u, gNb + st.q0, 0u);
-    cp_async16(setA + 1024u, gN + st.q0, 0u);
-    cp_async16(setA + 1536u, gA + st.q0, 0u);
-  }
-  cp_async_commit();
-  if (st.q0 + 128 < total) {
-    cp_async16(setB, gNf + st.q0 + 128, 0u);
-    cp_async16(setB + 512u, gNb + st.q0 + 128, 0u);
-    cp_async16(setB + 1024u, gN + st.q0 + 128, 0u);
-    cp_async16(setB + 1536u, gA + st.q0 + 128, 0u);
-  }
-  cp_async_commit();
-#pragma unroll 1
-  for (int base = 0; base < total; base += 256) {
-    asm volatile("cp.async.wait_group 1;" ::: "memory");
-    scan_step(a, st, setA, gNf, gNb, gN, gA, total, drow, dsig, aQueue, cap, lt);
-    if (base + 128 < total) {
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-      scan_step(a, st, setB, gNf, gNb, gN, gA, total, drow, dsig, aQueue, cap, lt);
+  int q0 = 4 * lane;  // this lane's 4 consecutive elements of the current step (s % 4 == 0: one row)
+  int row = q0 / s, sig0 = q0 - row * s;
+  int nq = 0, chk = 0;
+#pragma unroll
+  for (int g = 0; g < 2; g++) {  // two steps in flight
+    const int q = q0 + 128 * g;
+    const unsigned slots = set0 + 2048u * (unsigned)g;
+    if (q < total) {
+      cp_async16(slots, gNf + q, 0u);
+      cp_async16(slots + 512u, gNb + q, 0u);
+      cp_async16(slots + 1024u, gN + q, 0u);
+      cp_async16(slots + 1536u, gA + q, 0u);
     }
+    cp_async_commit();
   }
-  if (__any_sync(FULL, st.chk != 0) || st.nq > cap) return -1;
-  return st.nq;
+  unsigned toggle = 0;
+#pragma unroll 1
+  for (int base = 0; base < total; base += 128) {
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    const unsigned slots = set0 + toggle;
+    toggle ^= 2048u;
+    int nf[4], nb[4], nn[4], na[4];
+    lds_vec4(slots, nf);
+    lds_vec4(slots + 512u, nb);
+    lds_vec4(slots + 1024u, nn);
+    lds_vec4(slots + 1536u, na);
+    const bool valid = q0 < total;  // past the end the slots hold stale words
+    const int o0 = nf[0] | nb[0] | nn[0] | na[0], o1 = nf[1] | nb[1] | nn[1] | na[1];
+    const int o2 = nf[2] | nb[2] | nn[2] | na[2], o3 = nf[3] | nb[3] | nn[3] | na[3];
+    const unsigned any_l = valid ? (unsigned)(o0 | o1 | o2 | o3) : 0u;
+    {  // refill the slots just read with the step after next (ordered behind the reads by `any_l`)
+      const int q = q0 + 256;
+      if (q < total) {
+        cp_async16(slots, gNf + q, any_l);
+        cp_async16(slots + 512u, gNb + q, any_l);
+        cp_async16(slots + 1024u, gN + q, any_l);
+        cp_async16(slots + 1536u, gA + q, any_l);
+      }
+      cp_async_commit();
+    }
+    const unsigned b1 = __ballot_sync(FULL, any_l != 0u);
+    if (b1) {
+      unsigned mm = (o0 != 0 ? 1u : 0u) | (o1 != 0 ? 2u : 0u) | (o2 != 0 ? 4u : 0u) | (o3 != 0 ? 8u : 0u);
+      if (!valid) mm = 0u;
+      const int cnt = __popc(mm);
+      // exclusive prefix of cnt over the lanes: most lanes hold no element, few hold more than one
+      int pos = nq + __popc(b1 & lt);
+      nq += __popc(b1);
+      const unsigned b2 = __ballot_sync(FULL, cnt >= 2);
+      if (b2) {
+        const unsigned b3 = __ballot_sync(FULL, cnt >= 3), b4 = __ballot_sync(FULL, cnt >= 4);
+        pos += __popc(b2 & lt) + __popc(b3 & lt) + __popc(b4 & lt);
+        nq += __popc(b2) + __popc(b3) + __popc(b4);
+      }
+      // a lane's elements one at a time (usually one): selected with a few SEL, packed, stored
+#pragma unroll 1
+      while (mm) {
+        const int e = __ffs(mm) - 1;
+        mm &= mm - 1u;
+        const int vf = pick<4>(nf, e), vb = pick<4>(nb, e), vn = pick<4>(nn, e), va = pick<4>(na, e);
+        // packing: 0 <= Nf, Nb < 256, |N| < 2^15, |A| < 2^7
+        chk |= ((vf | vb) & 0xffffff00) | ((vn + 32768) & 0xffff0000) | ((va + 128) & 0xffffff00);
+        if (pos < cap)
+          queue_store(aQueue, pos, (unsigned)(sig0 + e) | ((unsigned)row << 8) | ((unsigned)(va & 0xff) << 16),
+                      ((unsigned)vf & 0xffu) | (((unsigned)vb & 0xffu) << 8) | ((unsigned)vn << 16));
+        pos++;
+      }
+    }
+    q0 += 128;
+    row += drow;
+    sig0 += dsig;
+    if (sig0 >= s) { sig0 -= s; row++; }
+  }
+  if (__any_sync(FULL, chk != 0) || nq > cap) return -1;
+  return nq;
 }
 
 // ---------------------------------------------------------------------------

@@ -3,19 +3,29 @@ bench.py -- cell-steps/s of one World.enzymatic_activity() + one World.diffuse_m
 ("step") on synthetic populations (BASELINE.json metric), one process per GPU.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                  [--config c4|c3|c5] [--scaling weak|strong]
   N > 1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload at N = 1: BASELINE.json configs[3], "synthetic 1M cells on 1024x1024 map, 64
-proteins/cell, 32 signals" (42,248 algorithmic bytes per cell-step, 44 GB of parameters
-resident in HBM: far larger than L2, so no flush is needed between iterations).
-N > 1: every rank owns a row slab of the map with its own 1M cells (weak scaling).
+Workloads (BASELINE.json configs)
+  c4 (default, configs[3])  1,048,576 cells on a 1024 x 1024 map, 64 proteins, 32 signals
+       weak   (default)     every rank owns such a population on its own 1024 x 1024 row slab
+       strong               ONE such population and map split over the N ranks
+  c3 (configs[2])           16,384 cells saturating a 128 x 128 map, 35 proteins, 40 signals, 1 GPU
+  c5 (configs[4])           16,777,216 cells on a 4096 x 4096 map over 8 GPUs (2 M cells + 512 rows each)
+The 42 KB of parameters per cell are far larger than L2: no flush between iterations.
 
-Prints ONE JSON line (rank 0).  `value` = cells x K / device time with all state resident
-in HBM; `e2e` = same through the public World API with the per-step state (cell
-molecules, molecule map, cell positions) coming from pinned host memory and the result
-read back every step; `roofline` = algorithmic bytes of the fused kinetics kernel / its
-CUDA-event duration against the measured HBM peak; `cpu_baseline` = the CPU oracle
-(oracle/ms_oracle.c, a port) with all host threads on a bounded sample.
+Prints ONE JSON line (rank 0).
+  value     cells x K / device time, all state resident in HBM, the package's defaults: the kernel's
+            sparse lists are cached per parameter row, so a steady-state step does not re-read the
+            dense tiles (`roofline.scan_path` is the same kernel with the cache off)
+  e2e       the same through the public World API with the per-step state (cell molecules, molecule
+            map, cell positions) coming from pinned host memory and the result read back, every step
+  roofline  kinetics kernel: SURVEY 8(d)'s algorithmic bytes per cell-step x cells / CUDA-event time,
+            against the measured HBM peak; `moved_*` = the bytes a launch actually has to move
+  cpu_baseline / --impl reference: the CPU oracle (oracle/ms_oracle.c, a port), all host threads,
+            full-size steps
+  extra     N = 1: the c3 workload; N > 1: strong scaling of c4 and a bit-exact parity check of the
+            multi-GPU path against the single-domain oracle (the run fails if it mismatches)
 """
 from __future__ import annotations
 
@@ -34,6 +44,13 @@ sys.path.insert(0, str(ROOT))
 PARAMS = ("N", "Nf", "Nb", "A", "Kmr", "Ke", "Kmf", "Kmb", "Vmax")
 METRIC = "cell-steps/sec (enzymatic_activity+diffuse_molecules)"
 FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+CONFIGS = {
+    #        cells    proteins molecules map   BASELINE.json
+    "c4": (1 << 20, 64, 16, 1024, "configs[3]"),
+    "c3": (1 << 14, 35, 20, 128, "configs[2]"),
+    "c5": (1 << 24, 64, 16, 4096, "configs[4]"),
+}
+CPU_CHUNK = 65536  # cells per oracle pass of the CPU legs
 
 
 def parse_args():
@@ -42,18 +59,27 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cells", type=int, default=1 << 20)
-    ap.add_argument("--proteins", type=int, default=64)
-    ap.add_argument("--molecules", type=int, default=16)
-    ap.add_argument("--map", type=int, default=1024)
-    ap.add_argument("--cpu-sample-cells", type=int, default=65536)
+    ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--cells", type=int, default=None, help="override the config's cell count (per GPU when weak)")
+    ap.add_argument("--proteins", type=int, default=None)
+    ap.add_argument("--molecules", type=int, default=None)
+    ap.add_argument("--map", type=int, default=None)
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--scan-steps", type=int, default=5, help="steps timed with the list cache off (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true")
     ap.add_argument("--no-list-cache", action="store_true",
                     help="scan the dense parameter tiles in every step (Kinetics.list_cache = False)")
     ap.add_argument("--energies", default="modest", choices=["modest", "survey"],
-                    help="molecule energies of the synthetic chemistry: U(10,50) kJ (default) or SURVEY §8(d)'s U(10,500) kJ")
-    return ap.parse_args()
+                    help="molecule energies of the synthetic chemistry: U(10,50) kJ (default) or SURVEY 8(d)'s U(10,500) kJ")
+    args = ap.parse_args()
+    cells, p, m, size, _ = CONFIGS[args.config]
+    args.cells = args.cells or cells
+    args.proteins = args.proteins or p
+    args.molecules = args.molecules or m
+    args.map = args.map or size
+    return args
 
 
 def hbm_peak() -> tuple[float, str]:
@@ -67,8 +93,12 @@ def hbm_peak() -> tuple[float, str]:
 
 
 def kinetics_bytes_per_cell(p: int, s: int) -> int:
-    """SURVEY.md §8(d): every parameter once, X in/out, positions"""
+    """SURVEY.md 8(d): every parameter once, X in/out, positions"""
     return 20 * p * s + 16 * p + 8 * s + 8
+
+
+def energy_range(args):
+    return (10e3, 500e3) if args.energies == "survey" else (10e3, 50e3)
 
 
 class ClockSampler:
@@ -125,28 +155,27 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def energy_range(args):
-    return (10e3, 500e3) if args.energies == "survey" else (10e3, 50e3)
-
-
-def build_world(args, device, seed, world_size=1):
+# ---------------------------------------------------------------------------------- worlds
+def build_world(cells, proteins, molecules, map_rows, map_cols, device, seed, world_size, erange, list_cache=True):
+    """a World (one GPU) or the rank's SlabWorld of a (world_size * map_rows) x map_cols torus"""
     import torch
     import magicsoup_b200 as ms
     from magicsoup_b200.synthetic import make_population
 
-    pop = make_population(args.cells, args.proteins, args.molecules, args.map, seed=seed, device=device,
-                          energy_range=energy_range(args))
+    pop = make_population(cells, proteins, molecules, (map_rows, map_cols), seed=seed, device=device,
+                          energy_range=erange)
     mols = [ms.Molecule(f"b{i}", 10e3, diffusivity=pop.diffusivities[i], permeability=pop.permeabilities[i])
             for i in range(pop.m)]
     chem = ms.Chemistry(molecules=mols, reactions=[])
     if world_size > 1:
-        # every rank owns one (map x map) row slab of a (world_size*map x map) torus and the
-        # cells on it: halo rows, plane sums and early-exit flags go over NCCL every step
+        # every rank owns one row slab and the cells on it: halo rows, plane sums and early-exit
+        # flags go over NCCL every step
         from magicsoup_b200.distributed import SlabWorld
 
-        world = SlabWorld(chemistry=chem, global_map_size=(args.map * world_size, args.map), device=str(device))
+        world = SlabWorld(chemistry=chem, global_map_size=(map_rows * world_size, map_cols), device=str(device))
     else:
-        world = ms.World(chemistry=chem, map_size=args.map, device=str(device))
+        world = ms.World(chemistry=chem, map_size=map_rows if map_rows == map_cols else (map_rows, map_cols),
+                         device=str(device))
     # install the population without the (c,p,s)-sized copies the append path would make
     world.molecule_map = pop.molecule_map
     world.cell_positions = pop.cell_positions
@@ -159,60 +188,136 @@ def build_world(args, device, seed, world_size=1):
     world.cell_labels = [""] * pop.c
     for k in PARAMS:
         setattr(world.kinetics, k, getattr(pop, k))
-    world.kinetics.list_cache = not args.no_list_cache
+    world.kinetics.list_cache = list_cache
     return world, pop
 
 
-def cpu_leg(args, pop_params_host, X0_host, map_host, cm_host, pos_host, diffs, perms, full_cells):
-    """times the CPU oracle on a bounded sample; returns (cell-steps/s extrapolated, description, cores)"""
-    import numpy as np
+def timed_steps(world, n_steps, barrier, device, world_size):
+    """(total ms over n_steps as max over ranks, kinetics launch durations in ms)"""
+    import torch
+    import torch.distributed as dist
+
+    world._kernel_events = []
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0.record()
+    for _ in range(n_steps):
+        world.enzymatic_activity()
+        world.diffuse_molecules()
+    t1.record()
+    barrier()
+    kin_ms = [a.elapsed_time(b) for a, b in world._kernel_events]
+    world._kernel_events = None
+    t = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device=device)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    return {"ms_total": ms_total, "ms_per_step": ms_total / n_steps, "kernel_ms": sum(kin_ms) / max(len(kin_ms), 1),
+            "kernel_share_of_step": sum(kin_ms) / ms_total}
+
+
+def measure(world, steps, warmup, barrier, device, world_size):
+    for _ in range(warmup):
+        world.enzymatic_activity()
+        world.diffuse_molecules()
+    return timed_steps(world, steps, barrier, device, world_size)
+
+
+def roofline_block(c, p, s, res, scan, rec_words, traffic):
+    """res / scan: timed_steps() of the default run (cached lists) and of the scan path"""
+    peak, peak_src = hbm_peak()
+    alg = kinetics_bytes_per_cell(p, s) * c
+    moved = (4 * rec_words + 8 * s + 8) * c if rec_words else alg
+    out = {
+        "bound": "hbm", "kernel": "kinetics_lanes_kernel" if p <= 64 and s <= 64 else "kinetics_fused_kernel",
+        "achieved": alg / (res["kernel_ms"] / 1e3) / 1e9, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+        "frac": alg / (res["kernel_ms"] / 1e3) / 1e9 / peak, "traffic": traffic,
+        "algorithmic_bytes_per_launch": alg, "kernel_ms": res["kernel_ms"],
+        "kernel_share_of_step": res["kernel_share_of_step"],
+        "definition": "achieved = SURVEY 8(d)'s algorithmic bytes (dense dtypes: 20ps+16p+8s+8 per cell-step) / kernel "
+                      "time.  With the list cache on (default) a launch only has to move moved_bytes_per_launch "
+                      "(one cached record + X in/out per cell); scan_path is the same kernel reading the dense "
+                      "tiles in every step (list cache off)",
+        "moved_bytes_per_launch": moved, "moved_achieved": moved / (res["kernel_ms"] / 1e3) / 1e9,
+        "moved_frac": moved / (res["kernel_ms"] / 1e3) / 1e9 / peak,
+    }
+    if scan is not None:
+        a = alg / (scan["kernel_ms"] / 1e3) / 1e9
+        out["scan_path"] = {"kernel_ms": scan["kernel_ms"], "achieved": a, "frac": a / peak,
+                            "ms_per_step": scan["ms_per_step"], "cell_steps_per_s": c / (scan["ms_per_step"] / 1e3)}
+    return out
+
+
+def traffic_for(c, p, s, cached: bool):
+    try:
+        tj = json.loads((ROOT / "profiles" / "kinetics_traffic.json").read_text())
+        for e in tj.get("entries", []):
+            if (e.get("cells"), e.get("proteins"), e.get("signals"), e.get("cached")) == (c, p, s, cached):
+                return e.get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    return None
+
+
+# ---------------------------------------------------------------------------------- CPU legs
+def cpu_population(args):
+    from magicsoup_b200.synthetic import make_population
+
+    n = min(args.cells, CPU_CHUNK)
+    n_passes = max(1, args.cells // n)
+    pop = make_population(n, args.proteins, args.molecules, args.map, seed=0, device="cpu", energy_range=energy_range(args))
+    return pop, n, n_passes
+
+
+def cpu_step_time(pop, n_passes):
+    """one full-size step of the CPU oracle: n_passes passes over a resident population + the map once"""
     from oracle import oracle as O
 
     cores = os.cpu_count() or 1
-    P = O.Params(*pop_params_host)
-    n = P.c
+    P = O.Params(*[t.numpy() for t in pop.params()])
+    X0 = pop.X0().numpy()
+    cm, mp, pos = pop.cell_molecules.numpy(), pop.molecule_map.numpy(), pop.cell_positions.numpy()
     t0 = time.perf_counter()
-    O.integrate_signals(P, X0_host, n_threads=cores)
+    for _ in range(n_passes):
+        O.integrate_signals(P, X0, n_threads=cores)
     t_kin = time.perf_counter() - t0
     t0 = time.perf_counter()
-    O.diffuse_molecules(cm_host, map_host, pos_host, diffs, perms)
+    mm = O.diffuse(mp, pop.diffusivities)
+    for _ in range(n_passes):
+        O.permeate(cm, mm, pos, pop.permeabilities)
     t_diff = time.perf_counter() - t0
-    # kinetics scales with cells; diffusion was timed on the full map, permeation on the sample
-    t_step = t_kin * (full_cells / n) + t_diff
-    desc = (f"kinetics on the first {n} of {full_cells} cells ({t_kin:.2f} s, {cores} OpenMP threads, "
-            f"scaled linearly) + diffusion of the full {map_host.shape[0]}x{map_host.shape[1]}x{map_host.shape[2]} "
-            f"map and permeation of the sample ({t_diff:.2f} s, 1 thread)")
-    return full_cells / t_step, desc, cores
+    return t_kin, t_diff, cores
+
+
+def cpu_sample_text(args, n, n_passes, t_kin, t_diff, cores):
+    gb = kinetics_bytes_per_cell(args.proteins, 2 * args.molecules) * args.cells / 1e9
+    return (f"one full-size step = {n_passes} oracle passes over a resident population of {n} cells "
+            f"({n * n_passes} cell-steps of kinetics: {t_kin:.2f} s on {cores} OpenMP threads) + one diffusion of the "
+            f"{args.molecules}x{args.map}x{args.map} map and the permeation of every pass ({t_diff:.2f} s, 1 thread); "
+            f"nothing is extrapolated (distinct parameters for all {args.cells} cells would be {gb:.0f} GB of host memory)")
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path = the oracle port"""
-    import numpy as np
-    import torch
-    from magicsoup_b200.synthetic import make_population
-
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    """--impl reference: the reference's CPU implementation of the path = the oracle port, full-size steps"""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    n = min(args.cells, args.cpu_sample_cells // 4)  # ~2 s of CPU work per step
-    pop = make_population(n, args.proteins, args.molecules, args.map, seed=0, device="cpu",
-                          energy_range=energy_range(args))
-    par = [t.numpy() for t in pop.params()]
-    X0 = pop.X0().numpy()
-    vals = []
-    desc = ""
-    cores = os.cpu_count() or 1
+    pop, n, n_passes = cpu_population(args)
+    times, desc, cores = [], "", 1
     for i in range(args.warmup + args.steps):
-        v, desc, cores = cpu_leg(args, par, X0, pop.molecule_map.numpy(), pop.cell_molecules.numpy(),
-                                 pop.cell_positions.numpy(), pop.diffusivities, pop.permeabilities, args.cells)
+        t_kin, t_diff, cores = cpu_step_time(pop, n_passes)
         if i >= args.warmup:
-            vals.append(v)
-    value = sum(vals) / len(vals)
+            times.append(t_kin + t_diff)
+            desc = cpu_sample_text(args, n, n_passes, t_kin, t_diff, cores)
+    step_s = sum(times) / len(times)
+    value = n * n_passes / step_s
+    cfg = workload_config(args, 1)
+    if args.gpus > 1:
+        cfg["workload"] += " -- the CPU arm always runs the 1-GPU size, on rank 0"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "cell-steps/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * args.cells / value,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * step_s,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": cfg,
         "cpu_baseline": {"value": value, "unit": "cell-steps/s", "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "cell-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -220,14 +325,65 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def split_over_ranks(args, n_gpus) -> bool:
+    return n_gpus > 1 and (args.scaling == "strong" or args.config == "c5")
+
+
 def workload_config(args, n_gpus):
+    _, _, _, _, where = CONFIGS[args.config]
+    s = 2 * args.molecules
+    if split_over_ranks(args, n_gpus):
+        what = (f"synthetic {args.cells} cells on a {args.map}x{args.map} map split over {n_gpus} GPUs "
+                f"({args.cells // n_gpus} cells and {args.map // n_gpus} map rows each)")
+    else:
+        what = f"synthetic {args.cells} cells/GPU on {args.map}x{args.map} map slab/GPU"
     return {
-        "workload": f"synthetic {args.cells} cells/GPU on {args.map}x{args.map} map slab/GPU, {args.proteins} "
-                    f"proteins/cell, {2 * args.molecules} signals (BASELINE.json configs[3])",
-        "cells_per_gpu": args.cells, "proteins": args.proteins, "signals": 2 * args.molecules,
-        "map": [args.map, args.map], "parallelism": f"cells+map-slab x{n_gpus}",
-        "l2": "inputs (44 GB of parameters at the default size) exceed L2; no flush needed",
+        "workload": f"{what}, {args.proteins} proteins/cell, {s} signals (BASELINE.json {where})",
+        "cells_per_gpu": args.cells // n_gpus if split_over_ranks(args, n_gpus) else args.cells,
+        "proteins": args.proteins, "signals": s, "map": [args.map, args.map],
+        "parallelism": f"cells+map-slab x{n_gpus}", "energies": args.energies, "list_cache": not args.no_list_cache,
+        "l2": "parameters (42 KB per cell) exceed L2 by orders of magnitude; no flush needed",
     }
+
+
+def per_rank_shape(args, world_size):
+    """(cells, map rows, map cols) of one rank"""
+    if split_over_ranks(args, world_size):
+        if args.map % world_size or args.cells % world_size:
+            raise SystemExit(f"{args.map} rows / {args.cells} cells do not split over {world_size} ranks")
+        return args.cells // world_size, args.map // world_size, args.map
+    if args.config == "c5":
+        raise SystemExit("c5 (16M cells, 700 GB of parameters) needs --gpus 8")
+    return args.cells, args.map, args.map
+
+
+def pin_to_own_cpus(local_rank, local_world):
+    """spread the ranks over the host cores (the e2e leg is a host-memory copy loop per rank)"""
+    try:
+        cpus = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cpus) // max(local_world, 1))
+        mine = cpus[local_rank * per:(local_rank + 1) * per] or cpus
+        os.sched_setaffinity(0, mine)
+        return len(mine)
+    except Exception:
+        return None
+
+
+def slab_parity_check(world_size):
+    """bit-exact comparison of the N-rank SlabWorld with the single-domain CPU oracle (small problem)"""
+    from tests import dist_worker
+
+    t0 = time.perf_counter()
+    try:
+        dist_worker.run("nccl", steps=3, cells=20000, rows_per_rank=128, cols=128, seed=5, quiet=True)
+        ok, err = True, ""
+    except AssertionError as e:
+        ok, err = False, str(e)[:300]
+    return {"ranks": world_size, "ok": ok,
+            "problem": f"20000 cells x 12 proteins x 8 signals on a {128 * world_size}x128 map: 3 steps "
+                       "(activity, degradation, diffusion), then kill + a cell migrating across a slab boundary + 1 step",
+            "result": "bit-identical to the single-domain oracle" if ok else "MISMATCH: " + err,
+            "seconds": round(time.perf_counter() - t0, 2)}
 
 
 def main():
@@ -246,7 +402,9 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world_size}")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    n_cpus = None
     if world_size > 1:
+        n_cpus = pin_to_own_cpus(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world_size)))
         dist.init_process_group("nccl", device_id=device)
 
     def barrier():
@@ -254,39 +412,34 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    world, pop = build_world(args, device, seed=rank, world_size=world_size)
+    cells, rows, cols = per_rank_shape(args, world_size)
+    erange = energy_range(args)
+    world, pop = build_world(cells, args.proteins, args.molecules, rows, cols, device, seed=rank,
+                             world_size=world_size, erange=erange, list_cache=not args.no_list_cache)
     c, p, m = pop.c, pop.p, pop.m
     s = 2 * m
     torch.cuda.synchronize()
 
-    def step():
+    for _ in range(args.warmup):
         world.enzymatic_activity()
         world.diffuse_molecules()
-
-    for _ in range(args.warmup):
-        step()
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    world._kernel_events = []
-    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    t_start.record()
-    for _ in range(args.steps):
-        step()
-    t_end.record()
-    barrier()
+    res = timed_steps(world, args.steps, barrier, device, world_size)
     clocks = sampler.stop() if rank == 0 else None
-    ms_total = t_start.elapsed_time(t_end)
-    kin_ms = [a.elapsed_time(b) for a, b in world._kernel_events]
-    n_kin_launches = len(kin_ms)
-    world._kernel_events = None
-    t = torch.tensor([ms_total], dtype=torch.float64, device=device)
-    if world_size > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
-    value = c * world_size * args.steps / (ms_total / 1e3)
+    value = c * world_size * args.steps / (res["ms_total"] / 1e3)
+    rec_words = int(world.kinetics._cache.shape[1]) if world.kinetics._cache is not None else 0
+
+    # ---- the same kernel reading the dense tiles in every step (list cache off)
+    scan = None
+    if args.scan_steps > 0 and not args.no_list_cache:
+        world.kinetics.list_cache = False
+        scan = measure(world, args.scan_steps, 2, barrier, device, world_size)
+        world.kinetics.list_cache = True
+        world.enzymatic_activity()  # rebuilds the records
+    roofline = roofline_block(c, p, s, res, scan, rec_words, traffic_for(c, p, s, rec_words > 0))
 
     # ---- end to end through the public API with host-resident per-step state
     host_cm = world.cell_molecules.cpu().pin_memory()
@@ -301,7 +454,8 @@ def main():
         world.cell_molecules = host_cm.to(device, non_blocking=True)
         world.molecule_map = host_map.to(device, non_blocking=True)
         world.cell_positions = host_pos.to(device, non_blocking=True)
-        step()
+        world.enzymatic_activity()
+        world.diffuse_molecules()
         out_cm.copy_(world.cell_molecules, non_blocking=True)
         out_map.copy_(world.molecule_map, non_blocking=True)
         torch.cuda.synchronize()
@@ -319,48 +473,71 @@ def main():
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = c * world_size * args.e2e_steps / (float(t.item()) / 1e3)
+    del host_cm, host_map, host_pos, out_cm, out_map
+
+    # ---- extras (outside the timed regions above)
+    extra = {}
+    if not args.no_extra and world_size > 1:
+        extra["parity_check"] = slab_parity_check(world_size)
+        if args.config == "c4" and args.scaling == "weak" and args.map % world_size == 0:
+            del world, pop  # strong scaling: ONE c4 population and map split over the ranks
+            torch.cuda.empty_cache()
+            w2, _ = build_world(args.cells // world_size, p, m, args.map // world_size, args.map, device,
+                                seed=100 + rank, world_size=world_size, erange=erange)
+            r2 = measure(w2, max(args.steps, 10), max(args.warmup, 3), barrier, device, world_size)
+            extra["c4_strong"] = {
+                "workload": f"{args.cells} cells on a {args.map}x{args.map} map split over {world_size} GPUs "
+                            f"({args.cells // world_size} cells and {args.map // world_size} rows each)",
+                "scaling": "strong", "ms_per_step": r2["ms_per_step"], "kernel_ms": r2["kernel_ms"],
+                "value": args.cells / (r2["ms_per_step"] / 1e3), "unit": "cell-steps/s"}
+            del w2
+    if not args.no_extra and world_size == 1 and args.config == "c4":
+        del world, pop
+        torch.cuda.empty_cache()
+        cc, cp, cmol, cmap, where = CONFIGS["c3"]
+        w3, _ = build_world(cc, cp, cmol, cmap, cmap, device, seed=3, world_size=1, erange=erange)
+        r3 = measure(w3, 200, 20, barrier, device, 1)
+        w3.kinetics.list_cache = False
+        r3s = measure(w3, 100, 10, barrier, device, 1)
+        b3 = kinetics_bytes_per_cell(cp, 2 * cmol) * cc
+        extra["c3"] = {
+            "workload": f"{cc} cells saturating a {cmap}x{cmap} map, {cp} proteins, {2 * cmol} signals (BASELINE.json {where})",
+            "value": cc / (r3["ms_per_step"] / 1e3), "unit": "cell-steps/s", "ms_per_step": r3["ms_per_step"],
+            "kernel_ms": r3["kernel_ms"], "roofline_frac": b3 / (r3["kernel_ms"] / 1e3) / 1e9 / hbm_peak()[0],
+            "scan_path": {"ms_per_step": r3s["ms_per_step"], "kernel_ms": r3s["kernel_ms"],
+                          "value": cc / (r3s["ms_per_step"] / 1e3),
+                          "roofline_frac": b3 / (r3s["kernel_ms"] / 1e3) / 1e9 / hbm_peak()[0]}}
+        del w3
+    if "parity_check" in extra and not extra["parity_check"]["ok"]:
+        if rank == 0:
+            print(json.dumps({"error": "multi-GPU parity check failed", "parity_check": extra["parity_check"]}))
+        dist.destroy_process_group()
+        sys.exit(2)
 
     if rank != 0:
         if world_size > 1:
             dist.destroy_process_group()
         return
 
-    peak, peak_src = hbm_peak()
-    kin_avg_ms = sum(kin_ms) / max(len(kin_ms), 1)
-    bytes_per_launch = kinetics_bytes_per_cell(p, s) * c
-    achieved = bytes_per_launch / (kin_avg_ms / 1e3) / 1e9
-    traffic = None
-    tf = ROOT / "profiles" / "kinetics_traffic.json"
-    if tf.exists():
-        try:
-            tj = json.loads(tf.read_text())
-            if tj.get("cells") == c and tj.get("proteins") == p and tj.get("signals") == s:
-                traffic = tj.get("dram_bytes_per_launch")
-        except Exception:
-            pass
     line = {
         "metric": METRIC, "value": value, "unit": "cell-steps/s", "n_gpus": world_size, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, world_size),
-        "roofline": {"bound": "hbm", "kernel": "kinetics_fused_kernel", "achieved": achieved, "peak": peak,
-                     "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "algorithmic_bytes_per_launch": bytes_per_launch, "kernel_ms": kin_avg_ms,
-                     "kernel_share_of_step": kin_avg_ms * n_kin_launches / ms_total},
+        "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong" if split_over_ranks(args, world_size) else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, world_size), "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": "cell-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": args.e2e_steps},
-        "gpu_launches": 4 * args.steps + n_kin_launches,
+                "steps": args.e2e_steps, "host_cpus_per_rank": n_cpus},
+        # per step: kinetics (lane kernel + the launch for deferred cells), scatter, stencil, correct, permeate
+        "gpu_launches": 6 * args.steps,
         "clocks": clocks,
     }
+    if extra:
+        line["extra"] = extra
     if not args.no_cpu_baseline:
-        n = min(c, args.cpu_sample_cells)
-        par = [getattr(pop, k)[:n].cpu().numpy() for k in PARAMS]
-        cm = host_cm[:n].numpy()
-        pos = host_pos[:n].numpy()
-        mp = host_map.numpy()
-        X0 = torch.cat([host_cm[:n], host_map[:, host_pos[:n, 0].long(), host_pos[:n, 1].long()].T], 1).numpy()
-        v, desc, cores = cpu_leg(args, par, X0, mp, cm, pos, pop.diffusivities, pop.permeabilities, c)
-        line["cpu_baseline"] = {"value": v, "unit": "cell-steps/s", "cores": cores, "kind": "port", "sample": desc}
+        cpop, n, n_passes = cpu_population(args)
+        t_kin, t_diff, cores = cpu_step_time(cpop, n_passes)
+        line["cpu_baseline"] = {"value": n * n_passes / (t_kin + t_diff), "unit": "cell-steps/s", "cores": cores,
+                                "kind": "port", "sample": cpu_sample_text(args, n, n_passes, t_kin, t_diff, cores)}
     print(json.dumps(line))
     if world_size > 1:
         dist.destroy_process_group()

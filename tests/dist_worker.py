@@ -92,7 +92,7 @@ def gather_world(world: SlabWorld):
     return mm, cm, pos
 
 
-def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, seed: int) -> None:
+def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, seed: int, quiet: bool = False) -> None:
     rank, ws = dist.get_rank(), dist.get_world_size()
     if backend == "nccl":
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -162,7 +162,7 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
         assert len({(int(a), int(b)) for a, b in pos}) <= total
         assert np.isfinite(mm).all() and np.isfinite(cm).all() and (mm >= 0).all()
     assert world.kinetics.N.shape[0] == world.n_cells == world.cell_molecules.shape[0]
-    if rank == 0:
+    if rank == 0 and not quiet:
         print(f"dist_worker ok: backend={backend} ranks={ws} steps={steps} cells={cells} received={received}")
 
 

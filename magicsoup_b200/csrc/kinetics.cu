@@ -1149,26 +1149,27 @@ namespace ms {
 // the fixed-format lists is appended to the deferred list (tier 2 of kinetics_fused_kernel).
 // ---------------------------------------------------------------------------
 // X0 of a cell: read, or gathered from cell_molecules and the cell's pixel (world.py:619-621); lane i
-// holds signals i and i + 32.  One copy of the code for both call sites.
-__device__ __noinline__ void load_cell_signals(const KinArgs &a, long long cell, int lane, float &xa, float &xb) {
-  const int s = a.s;
-  float v[2] = {0.0f, 0.0f};
-  if (a.X_in) {
-    const float *x = a.X_in + cell * s;
-    if (lane < s) v[0] = x[lane];
-    if (lane + 32 < s) v[1] = x[lane + 32];
-  } else {
-    const float *cm = a.cell_mols + cell * a.m;
-    const float *px = a.mol_map + (long long)a.pos[2 * cell] * a.W + a.pos[2 * cell + 1];
-    const long long plane = (long long)a.H * a.W;
-#pragma unroll 1
-    for (int r = 0; r < 2; r++) {
-      const int i = lane + 32 * r;
-      if (i < s) v[r] = i < a.m ? cm[i] : px[(long long)(i - a.m) * plane];
-    }
+// holds signals i (.x) and i + 32 (.y).  One copy of the code for both call sites; everything is
+// passed by value (a reference to the kernel parameters would turn into generic loads and a stack
+// frame in a function that is not inlined).
+__device__ __noinline__ float2 load_cell_signals(const float *X_in, const float *cell_mols, const float *mol_map,
+                                                 const int *pos_all, int s, int m, int H, int W, long long cell,
+                                                 int lane) {
+  float2 v = make_float2(0.0f, 0.0f);
+  if (X_in) {
+    const float *x = X_in + cell * s;
+    if (lane < s) v.x = x[lane];
+    if (lane + 32 < s) v.y = x[lane + 32];
+    return v;
   }
-  xa = v[0];
-  xb = v[1];
+  // lane i < m: intracellular molecule i; lane m + k: the cell's pixel of map plane k
+  const int2 pos = *reinterpret_cast<const int2 *>(pos_all + 2 * cell);
+  const unsigned plane = (unsigned)H * (unsigned)W;  // < 2^31 pixels per plane (ms_enzymatic_activity checks)
+  const float *px = mol_map + (size_t)pos.x * W + pos.y;
+  const float *cm = cell_mols + cell * m;
+  if (lane < s) v.x = lane < m ? cm[lane] : px[(size_t)(unsigned)(lane - m) * plane];
+  if (lane + 32 < s) v.y = lane + 32 < m ? cm[lane + 32] : px[(size_t)(unsigned)(lane + 32 - m) * plane];
+  return v;
 }
 
 template <int VEC>
@@ -1194,7 +1195,11 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_
   float xa = 0.0f, xb = 0.0f;
   unsigned wflags = 0;  // early-exit flags of this warp's cells (bit = index in the flags buffer)
   long long cell = grab();
-  if (cell < n_items) load_cell_signals(a, cell, lane, xa, xb);
+  if (cell < n_items) {
+    const float2 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, cell, lane);
+    xa = v.x;
+    xb = v.y;
+  }
 #pragma unroll 1
   while (cell < n_items) {
     const long long next_cell = grab();
@@ -1216,7 +1221,8 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_
       const long long tile = prm * (long long)p * s;
       int nq;
       if (VEC == 4)
-        nq = scan_tile_lanes(a, sb, sb + 4u * (unsigned)L.oQueue, L.q_cap, tile, lane);
+        nq = scan_tile_lanes(a.Nf + tile, a.Nb + tile, a.N + tile, a.A + tile, p, s, sb,
+                             sb + 4u * (unsigned)L.oQueue, L.q_cap, lane);
       else
         nq = scan_tile<VEC>(a, b + L.oQueue, L.q_cap, tile, lane);
       __syncwarp();
@@ -1238,7 +1244,11 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_
       if (lane < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane), xa);
       if (lane + 32 < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane + 32), xb);
     }
-    if (next_cell < n_items) load_cell_signals(a, next_cell, lane, xa, xb);  // in flight during this cell's parts
+    if (next_cell < n_items) {  // in flight during this cell's parts
+      const float2 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, next_cell, lane);
+      xa = v.x;
+      xb = v.y;
+    }
     cp_async_wait_all();
     __syncwarp();
     if (ok) {
@@ -1999,6 +2009,7 @@ static int enzymatic_activity_impl(const ms_kinetics_params *params, const ms_ki
                                    const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
                                    size_t scratch_bytes, void *stream) {
   if (!params || !flags || params->s != 2 * m || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX ||
+      H * W > INT32_MAX ||
       (params->c > 0 && (!cell_positions || !cell_molecules || !molecule_map || !X_out)))
     return MS_ERR_INVALID_ARGUMENT;
   KinArgs a = {};

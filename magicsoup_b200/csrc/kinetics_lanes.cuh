@@ -70,10 +70,9 @@ __device__ __forceinline__ void sts_f4(unsigned addr, float4 v) {
 // zero: such a step costs four 128-bit loads, an OR tree and one vote.  Returns the queue length or
 // -1 (the tile does not fit the queue or the packing).
 // ---------------------------------------------------------------------------
-__device__ __noinline__ int scan_tile_lanes(const KinArgs &a, unsigned stage, unsigned aQueue, int cap, long long tile,
-                                            int lane) {
-  const int s = a.s, total = a.p * s;
-  const int *gN = a.N + tile, *gNf = a.Nf + tile, *gNb = a.Nb + tile, *gA = a.A + tile;
+__device__ __noinline__ int scan_tile_lanes(const int *gNf, const int *gNb, const int *gN, const int *gA, int p, int s,
+                                            unsigned stage, unsigned aQueue, int cap, int lane) {
+  const int total = p * s;
   const unsigned lt = (1u << lane) - 1u;
   const unsigned set0 = stage + 16u * (unsigned)lane;
   const int drow = 128 / s, dsig = 128 - drow * s;
@@ -349,7 +348,7 @@ __device__ __forceinline__ void table_store(unsigned aT, unsigned S2x4, unsigned
 }
 
 // rare slots: X_sig^n for the entries with n >= 4
-__device__ __forceinline__ void table_rare(unsigned aT, unsigned S2x4, unsigned aRare, unsigned aX, int n_rare, int lane) {
+__device__ __noinline__ void table_rare(unsigned aT, unsigned S2x4, unsigned aRare, unsigned aX, int n_rare, int lane) {
 #pragma unroll 1
   for (int r = lane; r < n_rare; r += 32) {
     const unsigned w = lds_u(aRare + 4u * (unsigned)r);
@@ -391,6 +390,15 @@ __device__ MS_PRODUCTS_INLINE void lane_products(unsigned aT, unsigned aEnt8, un
 #undef MS_T
   xf = fix_product(xf);
   xb = fix_product(xb);
+}
+
+// V of every protein of a cell, 0 for those without entries (single-part calls; kept out of line)
+__device__ __noinline__ void store_velocities(float *vrow, int p, int lane, unsigned aPf, unsigned aV, int n_act) {
+#pragma unroll 1
+  for (int j = lane; j < p; j += 32) vrow[j] = 0.0f;
+  __syncwarp();
+#pragma unroll 1
+  for (int t = lane; t < n_act; t += 32) vrow[lds_u(aPf + 4u * (unsigned)t) >> 21] = lds_f(aV + 4u * (unsigned)t);
 }
 
 __device__ __forceinline__ int csc_n(unsigned h) { return (int)(short)(unsigned short)h >> 7; }
@@ -594,14 +602,7 @@ __device__ void run_lanes(const KinArgs &a, const LaneLayout &L, unsigned sb, lo
       }
     }
 
-    if (a.V_out) {  // single-part calls: V of every protein, 0 for those without entries
-      float *vrow = a.V_out + cell * (long long)a.p;
-#pragma unroll 1
-      for (int j = lane; j < a.p; j += 32) vrow[j] = 0.0f;
-      __syncwarp();
-#pragma unroll 1
-      for (int t = lane; t < n_act; t += 32) vrow[lds_u(aPf + 4u * (unsigned)t) >> 21] = lds_f(aV + 4u * (unsigned)t);
-    }
+    if (a.V_out) store_velocities(a.V_out + cell * (long long)a.p, a.p, lane, aPf, aV, n_act);  // single-part calls only
     // next part starts from this part's result
 #pragma unroll 1
     for (int i = lane; i < s; i += 32) sts_f(aX0 + 4u * (unsigned)i, lds_f(aX1 + 4u * (unsigned)i));

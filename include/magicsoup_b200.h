@@ -226,6 +226,28 @@ int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, i
                        int64_t W, int64_t n_pxls_total, void *stream);
 
 /*
+ * World.degrade_molecules()                                    world.py:667-678
+ * molecule_map[k] *= decay[k], cell_molecules[:, k] *= decay[k], in place, one launch
+ * (decay[k] = exp(-ln 2 / half_life_k), world.py:184).
+ */
+int ms_degrade_molecules(float *molecule_map, float *cell_molecules, const float *decay, int64_t c,
+                         int64_t m, int64_t H, int64_t W, void *stream);
+
+/*
+ * degrade_molecules() folded into the next diffuse_molecules(): the stencil
+ * multiplies every value it reads (slab and halo rows) by decay[k], the permeation multiplies the
+ * cell molecules it reads by decay[k]; with ms_diffuse_correct in between the result is
+ * bit-identical to ms_degrade_molecules followed by ms_diffuse_stencil / _correct / ms_permeate,
+ * without the extra read and write of the map.
+ */
+int ms_degrade_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
+                               const float *a, const float *b, const float *decay, int64_t m, int64_t H,
+                               int64_t W, float *out, int64_t *sums, void *stream);
+int ms_degrade_permeate(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
+                        const int32_t *cell_positions, const float *perm, const float *decay, int64_t c,
+                        int64_t m, int64_t H, int64_t W, void *stream);
+
+/*
  * ms_diffuse_molecules without scratch from the caller -- no counterpart in the reference.
  * For hosts that cannot allocate device memory around the call (all memory already handed to
  * their own pool, or a step loop that must avoid the device-wide synchronisation that

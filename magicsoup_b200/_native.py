@@ -63,6 +63,9 @@ _SIGNATURES = {
     "ms_diffuse_static_max_floats": (_i64, []),
     "ms_diffuse_static_last_error": (C.c_char_p, []),
     "ms_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "ms_degrade_molecules": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "ms_degrade_diffuse_stencil": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "ms_degrade_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
 }
 
 _lib: C.CDLL | None = None

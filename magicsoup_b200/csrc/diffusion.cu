@@ -76,9 +76,11 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
                                                                  float *__restrict__ out,
                                                                  const float *__restrict__ wa,
                                                                  const float *__restrict__ wb, int H,
-                                                                 int W, unsigned long long *sums) {
+                                                                 int W, unsigned long long *sums,
+                                                                 const float *__restrict__ decay) {
   __shared__ __align__(16) float tile[(TH + 2) * TSTRIDE];
   const int k = blockIdx.z;
+  const float dk = decay ? decay[k] : 1.0f;  // World.degrade_molecules folded in (x * 1 is exact)
   const int x0 = blockIdx.y * TH, y0 = blockIdx.x * TW;
   const float *plane = map + (size_t)k * H * W;
   float *oplane = out + (size_t)k * H * W;
@@ -87,7 +89,8 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
   // interior columns of rows -1..TH: one float4 per lane per row
   for (int r = warp; r < TH + 2; r += DTHREADS / 32) {
     const float *src = slab_row(plane, halo_top, halo_bot, k, x0 + r - 1, H, W);
-    const float4 v = *reinterpret_cast<const float4 *>(src + y0 + 4 * lane);
+    float4 v = *reinterpret_cast<const float4 *>(src + y0 + 4 * lane);
+    v.x = v.x * dk; v.y = v.y * dk; v.z = v.z * dk; v.w = v.w * dk;
     *reinterpret_cast<float4 *>(&tile[r * TSTRIDE + 4 + 4 * lane]) = v;
   }
   // halo columns -1 and TW
@@ -96,7 +99,7 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
     const float *src = slab_row(plane, halo_top, halo_bot, k, x0 + r - 1, H, W);
     int gy = side ? y0 + TW : y0 - 1;
     gy = gy < 0 ? gy + W : (gy >= W ? gy - W : gy);
-    tile[r * TSTRIDE + (side ? 4 + TW : 3)] = src[gy];
+    tile[r * TSTRIDE + (side ? 4 + TW : 3)] = src[gy] * dk;
   }
   __syncthreads();
 
@@ -140,11 +143,13 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
                                                                    float *__restrict__ out,
                                                                    const float *__restrict__ wa,
                                                                    const float *__restrict__ wb, int H,
-                                                                   int W, unsigned long long *sums) {
+                                                                   int W, unsigned long long *sums,
+                                                                   const float *__restrict__ decay) {
   const int k = blockIdx.z;
   const float *plane = map + (size_t)k * H * W;
   float *oplane = out + (size_t)k * H * W;
   const float a = wa[k], b = wb[k];
+  const float dk = decay ? decay[k] : 1.0f;
   FixSum sin = {0, 0}, sout = {0, 0};
   const long long n = (long long)H * W;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n;
@@ -154,8 +159,9 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
     const float *rm = slab_row(plane, halo_top, halo_bot, k, x - 1, H, W);
     const float *r0 = plane + (size_t)x * W;
     const float *rp = slab_row(plane, halo_top, halo_bot, k, x + 1, H, W);
-    const float c = r0[y];
-    const float o = stencil_point(rm[ym], rm[y], rm[yp], r0[ym], c, r0[yp], rp[ym], rp[y], rp[yp], a, b);
+    const float c = r0[y] * dk;
+    const float o = stencil_point(rm[ym] * dk, rm[y] * dk, rm[yp] * dk, r0[ym] * dk, c, r0[yp] * dk, rp[ym] * dk,
+                                  rp[y] * dk, rp[yp] * dk, a, b);
     oplane[t] = o;
     sin.add(c);
     sout.add(o);
@@ -193,17 +199,29 @@ __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restri
 
 // pass 3: world.py:654-665, one thread per (cell, molecule)
 __global__ void permeate_kernel(const float *cm_in, float *cm_out, float *map, const int *pos,
-                                const float *perm, long long c, int m, int H, int W) {
+                                const float *perm, long long c, int m, int H, int W, const float *decay) {
   const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= c * m) return;
   const long long cell = r / m;
   const int k = (int)(r % m);
   const int x = pos[2 * cell], y = pos[2 * cell + 1];
   const size_t mi = ((size_t)k * H + x) * W + y;
-  const float xi = cm_in[r], xe = map[mi], q = perm[k];
+  const float xi = decay ? cm_in[r] * decay[k] : cm_in[r], xe = map[mi], q = perm[k];
   const float di = xi * q, de = xe * q;
   cm_out[r] = xi + (de - di);
   map[mi] = xe + (di - de);
+}
+
+// World.degrade_molecules, world.py:667-678: map[k] *= f[k], cell_molecules[:, k] *= f[k]
+__global__ void degrade_kernel(float *map, long long n_pxls, float *cm, long long c, int m, const float *f) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (int k = 0; k < m; k++) {
+    const float fk = f[k];
+    float *plane = map + (size_t)k * n_pxls;
+    for (long long t = t0; t < n_pxls; t += stride) plane[t] = plane[t] * fk;
+  }
+  for (long long t = t0; t < c * m; t += stride) cm[t] = cm[t] * f[t % m];
 }
 
 // world.py:624-625, one thread per (cell, signal)
@@ -252,7 +270,7 @@ static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 static int stencil_launch(const float *map, const float *halo_top, const float *halo_bot,
                           const float *a, const float *b, int64_t m, int64_t H, int64_t W, float *tmp,
-                          unsigned long long *sums, cudaStream_t st) {
+                          unsigned long long *sums, cudaStream_t st, const float *decay = nullptr) {
   MS_CUDA_CHECK(cudaMemsetAsync(sums, 0, (size_t)m * 4 * sizeof(long long), st));
   const long long n = (long long)H * W;
   // the tiled kernel moves float4: rows must start 16-byte aligned in every buffer it touches
@@ -260,12 +278,12 @@ static int stencil_launch(const float *map, const float *halo_top, const float *
                       (!halo_bot || aligned16(halo_bot));
   if (W % TW == 0 && H % TH == 0 && vec_ok) {
     dim3 grid((unsigned)(W / TW), (unsigned)(H / TH), (unsigned)m);
-    stencil_tiled_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums);
+    stencil_tiled_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums, decay);
   } else {
     unsigned blocks = (unsigned)((n + DTHREADS - 1) / DTHREADS);
     if (blocks > 1024) blocks = 1024;
     dim3 grid(blocks, 1, (unsigned)m);
-    stencil_generic_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums);
+    stencil_generic_kernel<<<grid, DTHREADS, 0, st>>>(map, halo_top, halo_bot, tmp, a, b, (int)H, (int)W, sums, decay);
   }
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
@@ -302,14 +320,27 @@ extern "C" int ms_diffuse_molecules(float *molecule_map, const float *a, const f
   return correct_launch(tmp, molecule_map, m, H, W, (long long)H * W, sums, (cudaStream_t)stream);
 }
 
-extern "C" int ms_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
-                                  const float *a, const float *b, int64_t m, int64_t H, int64_t W,
-                                  float *out, int64_t *sums, void *stream) {
+static int diffuse_stencil_impl(const float *map_slab, const float *halo_top, const float *halo_bottom,
+                                const float *a, const float *b, const float *decay, int64_t m, int64_t H,
+                                int64_t W, float *out, int64_t *sums, void *stream) {
   if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
   if (m == 0) return MS_OK;
   if (!map_slab || !a || !b || !out || !sums || out == map_slab) return MS_ERR_INVALID_ARGUMENT;
   return stencil_launch(map_slab, halo_top, halo_bottom, a, b, m, H, W, out, (unsigned long long *)sums,
-                        (cudaStream_t)stream);
+                        (cudaStream_t)stream, decay);
+}
+
+extern "C" int ms_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
+                                  const float *a, const float *b, int64_t m, int64_t H, int64_t W,
+                                  float *out, int64_t *sums, void *stream) {
+  return diffuse_stencil_impl(map_slab, halo_top, halo_bottom, a, b, nullptr, m, H, W, out, sums, stream);
+}
+
+extern "C" int ms_degrade_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
+                                          const float *a, const float *b, const float *decay, int64_t m,
+                                          int64_t H, int64_t W, float *out, int64_t *sums, void *stream) {
+  if (!decay && m > 0) return MS_ERR_INVALID_ARGUMENT;
+  return diffuse_stencil_impl(map_slab, halo_top, halo_bottom, a, b, decay, m, H, W, out, sums, stream);
 }
 
 extern "C" int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, int64_t m,
@@ -321,16 +352,42 @@ extern "C" int ms_diffuse_correct(const float *out, float *map_slab, const int64
                         (cudaStream_t)stream);
 }
 
-extern "C" int ms_permeate(const float *cell_molecules_in, float *cell_molecules_out,
-                           float *molecule_map, const int32_t *cell_positions, const float *perm,
-                           int64_t c, int64_t m, int64_t H, int64_t W, void *stream) {
+static int permeate_impl(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
+                         const int32_t *cell_positions, const float *perm, const float *decay, int64_t c, int64_t m,
+                         int64_t H, int64_t W, void *stream) {
   if (c < 0 || m < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX) return MS_ERR_INVALID_ARGUMENT;
   if (c * m == 0) return MS_OK;
   if (!cell_molecules_in || !cell_molecules_out || !molecule_map || !cell_positions || !perm)
     return MS_ERR_INVALID_ARGUMENT;
   const long long n = c * m;
   permeate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, c, (int)m, (int)H, (int)W);
+      cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, c, (int)m, (int)H, (int)W, decay);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_permeate(const float *cell_molecules_in, float *cell_molecules_out,
+                           float *molecule_map, const int32_t *cell_positions, const float *perm,
+                           int64_t c, int64_t m, int64_t H, int64_t W, void *stream) {
+  return permeate_impl(cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, nullptr, c, m, H, W,
+                       stream);
+}
+
+extern "C" int ms_degrade_permeate(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
+                                   const int32_t *cell_positions, const float *perm, const float *decay, int64_t c,
+                                   int64_t m, int64_t H, int64_t W, void *stream) {
+  if (!decay && c * m > 0) return MS_ERR_INVALID_ARGUMENT;
+  return permeate_impl(cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, decay, c, m, H, W,
+                       stream);
+}
+
+extern "C" int ms_degrade_molecules(float *molecule_map, float *cell_molecules, const float *decay, int64_t c,
+                                    int64_t m, int64_t H, int64_t W, void *stream) {
+  if (bad_map(m, H, W) || c < 0) return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!molecule_map || !decay || (c > 0 && !cell_molecules)) return MS_ERR_INVALID_ARGUMENT;
+  degrade_kernel<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(molecule_map, (long long)H * W, cell_molecules, c, (int)m,
+                                                           decay);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }

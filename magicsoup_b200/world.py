@@ -211,15 +211,21 @@ class World:
                                                nat.ptr(mm), nat.stream_ptr(dev)))
         return new_cm
 
-    def _launch_stencil(self, dev, mm, top, bottom) -> tuple[torch.Tensor, torch.Tensor]:
-        """ms_diffuse_stencil -> (stencil output in scratch, int64 plane sums (4*m))"""
+    def _launch_stencil(self, dev, mm, top, bottom, decay=None) -> tuple[torch.Tensor, torch.Tensor]:
+        """ms_diffuse_stencil -> (stencil output in scratch, int64 plane sums (4*m)); decay: degradation folded in"""
         m, H, W = mm.shape
         a = self._const_f32("diff_a", [w[0] for w in self._diffusion], dev)
         b = self._const_f32("diff_b", [w[1] for w in self._diffusion], dev)
         out = self._buffer("diffuse", m * H * W * 4, dev)
         sums = self._buffer("diffuse_sums", 4 * m * 8, dev)[: 4 * m * 8].view(torch.int64)
-        nat.check(nat.lib().ms_diffuse_stencil(nat.ptr(mm), nat.ptr(top), nat.ptr(bottom), nat.ptr(a), nat.ptr(b),
-                                               m, H, W, nat.ptr(out), nat.ptr(sums), nat.stream_ptr(dev)))
+        if decay is None:
+            rc = nat.lib().ms_diffuse_stencil(nat.ptr(mm), nat.ptr(top), nat.ptr(bottom), nat.ptr(a), nat.ptr(b),
+                                              m, H, W, nat.ptr(out), nat.ptr(sums), nat.stream_ptr(dev))
+        else:
+            rc = nat.lib().ms_degrade_diffuse_stencil(nat.ptr(mm), nat.ptr(top), nat.ptr(bottom), nat.ptr(a), nat.ptr(b),
+                                                      nat.ptr(decay), m, H, W, nat.ptr(out), nat.ptr(sums),
+                                                      nat.stream_ptr(dev))
+        nat.check(rc)
         return out, sums
 
     def _launch_correct(self, dev, out, mm, sums, n_total: int):
@@ -227,13 +233,24 @@ class World:
         nat.check(nat.lib().ms_diffuse_correct(nat.ptr(out), nat.ptr(mm), nat.ptr(sums), m, H, W, n_total,
                                                nat.stream_ptr(dev)))
 
-    def _launch_permeate(self, dev, cm, mm, pos) -> torch.Tensor:
+    def _launch_permeate(self, dev, cm, mm, pos, decay=None) -> torch.Tensor:
         m, H, W = mm.shape
         perm = self._const_f32("perm", list(self._permeation), dev)
         new_cm = torch.empty_like(cm)
-        nat.check(nat.lib().ms_permeate(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pos), nat.ptr(perm),
-                                        self.n_cells, m, H, W, nat.stream_ptr(dev)))
+        if decay is None:
+            rc = nat.lib().ms_permeate(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pos), nat.ptr(perm),
+                                       self.n_cells, m, H, W, nat.stream_ptr(dev))
+        else:
+            rc = nat.lib().ms_degrade_permeate(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pos), nat.ptr(perm),
+                                               nat.ptr(decay), self.n_cells, m, H, W, nat.stream_ptr(dev))
+        nat.check(rc)
         return new_cm
+
+    def _launch_degrade(self, dev, mm, cm):
+        m, H, W = mm.shape
+        decay = self._const_f32("decay", list(self._mol_degrads), dev)
+        nat.check(nat.lib().ms_degrade_molecules(nat.ptr(mm), nat.ptr(cm), nat.ptr(decay), cm.shape[0], m, H, W,
+                                                 nat.stream_ptr(dev)))
 
     def _device_for_step(self) -> torch.device:
         return self._cuda()
@@ -264,27 +281,31 @@ class World:
         return self.n_cells == 0
 
     @torch.no_grad()
-    def diffuse_molecules(self):
-        """world.py:627-665"""
+    def diffuse_molecules(self, degrade_first: bool = False):
+        """
+        world.py:627-665.  degrade_first=True folds a preceding degrade_molecules() (world.py:667-678)
+        into the stencil and permeation reads: same bits as calling both, one pass over the map less.
+        """
         dev = self._device_for_step()
         mm, cm, pos = self._state_on_device(dev)
         m, H, W = mm.shape
         if m == 0:
             return
+        decay = self._const_f32("decay", list(self._mol_degrads), dev) if degrade_first else None
         top, bottom = self._exchange_halos(mm)
-        out, sums = self._launch_stencil(dev, mm, top, bottom)
+        out, sums = self._launch_stencil(dev, mm, top, bottom, decay)
         sums = self._reduce_sums(sums)
         self._launch_correct(dev, out, mm, sums, self._n_pixels_total(H, W))
         if self.n_cells == 0:
             return
-        self.cell_molecules = self._launch_permeate(dev, cm, mm, pos)
+        self.cell_molecules = self._launch_permeate(dev, cm, mm, pos, decay)
 
     def degrade_molecules(self):
-        """world.py:667-678 (per-molecule scalar decay; plain tensor ops, not a kernel of this package)"""
-        dev = self.molecule_map.device
-        f = torch.tensor(self._mol_degrads, dtype=torch.float32, device=dev)
-        self.molecule_map *= f[:, None, None]
-        self.cell_molecules *= f.to(self.cell_molecules.device)[None, :]
+        """world.py:667-678: per-molecule decay of the map and of the cell molecules, in place, one launch"""
+        dev = self._device_for_step()
+        mm, cm, _ = self._state_on_device(dev)
+        self.cell_molecules = cm
+        self._launch_degrade(dev, mm, cm)
 
     def increment_cell_lifetimes(self):
         """world.py:680-687"""

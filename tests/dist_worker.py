@@ -55,19 +55,35 @@ class OracleSlabWorld(SlabWorld):
         mm[:, xs, ys] = X[:, m:].T
         return X[:, :m].clone()
 
-    def _launch_stencil(self, dev, mm, top, bottom):
+    def _const_f32(self, key, values, dev):
+        return torch.tensor(values, dtype=torch.float32)
+
+    def _launch_degrade(self, dev, mm, cm):
+        f = torch.tensor(self._mol_degrads, dtype=torch.float32)
+        mm *= f[:, None, None]
+        cm *= f[None, :]
+
+    def _launch_stencil(self, dev, mm, top, bottom, decay=None):
         a = np.array([w[0] for w in self._diffusion], dtype=np.float32)
         b = np.array([w[1] for w in self._diffusion], dtype=np.float32)
-        out, sums = O.diffuse_stencil(mm.numpy(), None if top is None else top.numpy(),
+        mmn = mm.numpy()
+        if decay is not None:  # degradation folded in: every value the stencil reads is decayed first
+            f = decay.numpy()
+            mmn = mmn * f[:, None, None]
+            top = None if top is None else top * decay[:, None]
+            bottom = None if bottom is None else bottom * decay[:, None]
+        out, sums = O.diffuse_stencil(mmn, None if top is None else top.numpy(),
                                       None if bottom is None else bottom.numpy(), a, b)
         return torch.from_numpy(out), torch.from_numpy(sums)
 
     def _launch_correct(self, dev, out, mm, sums, n_total):
         mm.copy_(torch.from_numpy(O.diffuse_correct(out.numpy(), sums.numpy(), n_total)))
 
-    def _launch_permeate(self, dev, cm, mm, pos):
+    def _launch_permeate(self, dev, cm, mm, pos, decay=None):
         q = np.array(self._permeation, dtype=np.float32)
         cm2, mm2 = cm.numpy().copy(), mm.numpy()
+        if decay is not None:
+            cm2 = cm2 * decay.numpy()[None, :]
         import ctypes as C
         lib = O._lib(np.float32)
         m, H, W = mm2.shape
@@ -125,8 +141,11 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
 
     for step in range(steps):
         world.enzymatic_activity()
-        world.degrade_molecules()
-        world.diffuse_molecules()
+        if step % 2 == 0:
+            world.degrade_molecules()
+            world.diffuse_molecules()
+        else:  # the same, with the degradation folded into the diffusion kernels
+            world.diffuse_molecules(degrade_first=True)
         o_cm, o_mm = O.enzymatic_activity(P, o_pos, o_cm, o_mm)
         f = np.array(world._mol_degrads, dtype=np.float32)
         o_cm, o_mm = o_cm * f[None, :], o_mm * f[:, None, None]

@@ -145,15 +145,19 @@ def test_full_step_bit_exact(ms, shape):
     c, p, m, size, seed = shape
     pop = make_population(c, p, m, size, seed=seed)
     w = _world_from_pop(ms, pop)
+    w._mol_degrads = [0.99 - 0.03 * i for i in range(m)]  # the reference's tests poke this list too (test_world.py:68)
     P = oracle_params(pop)
     cm, mm, pos = pop.cell_molecules.numpy(), pop.molecule_map.numpy(), pop.cell_positions.numpy()
-    for step in range(3):
+    for step in range(4):
         w.enzymatic_activity()
         cm, mm = O.enzymatic_activity(P, pos, cm, mm)
         assert bits_equal(w.cell_molecules, cm), describe_mismatch(w.cell_molecules, cm, f"ea cm {step}")
         assert bits_equal(w.molecule_map, mm), describe_mismatch(w.molecule_map, mm, f"ea map {step}")
-        w.degrade_molecules()
-        w.diffuse_molecules()
+        if step % 2 == 0:
+            w.degrade_molecules()  # world.py:667-678: one launch, in place
+            w.diffuse_molecules()
+        else:  # the same with the degradation folded into the diffusion kernels
+            w.diffuse_molecules(degrade_first=True)
         f = np.array(w._mol_degrads, dtype=np.float32)
         cm, mm = cm * f[None, :], mm * f[:, None, None]
         cm, mm = O.diffuse_molecules(cm, mm, pos, pop.diffusivities, pop.permeabilities)

@@ -122,7 +122,9 @@ def test_world_bookkeeping_on_cpu():
     free = torch.nonzero(~w.cell_map)[:1].int()
     assert w.divide_cells_at([0], free) == [(0, 3)]
     assert w.n_cells == 4 and int(w.cell_divisions[0]) == 1 and int(w.cell_divisions[3]) == 1
-    w.degrade_molecules()
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            w.degrade_molecules()  # a kernel launch like the other step methods
     w.increment_cell_lifetimes()
     assert int(w.cell_lifetimes[1]) == 1
     with pytest.raises(ValueError):

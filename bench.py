@@ -65,7 +65,7 @@ def parse_args():
     ap.add_argument("--proteins", type=int, default=None)
     ap.add_argument("--molecules", type=int, default=None)
     ap.add_argument("--map", type=int, default=None)
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--scan-steps", type=int, default=5, help="steps timed with the list cache off (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
@@ -450,29 +450,65 @@ def main():
     h2d = host_cm.numel() * 4 + host_map.numel() * 4 + host_pos.numel() * 4
     d2h = out_cm.numel() * 4 + out_map.numel() * 4
 
-    def e2e_step():
-        world.cell_molecules = host_cm.to(device, non_blocking=True)
-        world.molecule_map = host_map.to(device, non_blocking=True)
-        world.cell_positions = host_pos.to(device, non_blocking=True)
-        world.enzymatic_activity()
-        world.diffuse_molecules()
-        out_cm.copy_(world.cell_molecules, non_blocking=True)
-        out_map.copy_(world.molecule_map, non_blocking=True)
+    # Every step copies its inputs from pinned host memory and reads its results back.  The copies run
+    # on their own streams, two input slots deep: the upload of step t+1 and the read-back of step
+    # t-1 overlap the kernels of step t (the host blocks once per step, on the early-exit flags).
+    compute = torch.cuda.current_stream(device)
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    slots = [dict(cm=torch.empty_like(host_cm, device=device), map=torch.empty_like(host_map, device=device),
+                  pos=torch.empty_like(host_pos, device=device), ev_in=torch.cuda.Event(), ev_free=torch.cuda.Event())
+             for _ in range(2)]
+    for sl in slots:
+        sl["ev_free"].record(compute)
+
+    def upload(t):
+        sl = slots[t % 2]
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(sl["ev_free"])  # the slot's previous step has been computed and read back
+            sl["cm"].copy_(host_cm, non_blocking=True)
+            sl["map"].copy_(host_map, non_blocking=True)
+            sl["pos"].copy_(host_pos, non_blocking=True)
+            sl["ev_in"].record(s_in)
+
+    keep = []
+
+    def run(n):
+        upload(0)
+        for t in range(n):
+            sl = slots[t % 2]
+            if t + 1 < n:
+                upload(t + 1)
+            compute.wait_event(sl["ev_in"])
+            world.cell_molecules, world.molecule_map, world.cell_positions = sl["cm"], sl["map"], sl["pos"]
+            world.enzymatic_activity()
+            world.diffuse_molecules()
+            done = torch.cuda.Event()
+            done.record(compute)
+            res_cm = world.cell_molecules  # a new tensor of this step (world.py:625, 664-665)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done)
+                out_cm.copy_(res_cm, non_blocking=True)
+                out_map.copy_(sl["map"], non_blocking=True)
+                sl["ev_free"].record(s_out)
+            keep.append(res_cm)
+            del keep[:-3]
         torch.cuda.synchronize()
 
-    for _ in range(2):
-        e2e_step()
+    run(3)
     barrier()
+    t_wall = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.e2e_steps):
-        e2e_step()
+    run(args.e2e_steps)
     e1.record()
+    torch.cuda.synchronize()
+    t_wall = (time.perf_counter() - t_wall) * 1e3
     barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    t = torch.tensor([max(e0.elapsed_time(e1), t_wall)], dtype=torch.float64, device=device)
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = c * world_size * args.e2e_steps / (float(t.item()) / 1e3)
+    del slots, keep
     del host_cm, host_map, host_pos, out_cm, out_map
 
     # ---- extras (outside the timed regions above)
@@ -526,7 +562,11 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world_size), "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": "cell-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": args.e2e_steps, "host_cpus_per_rank": n_cpus},
+                "steps": args.e2e_steps, "host_cpus_per_rank": n_cpus,
+                "how": "every step uploads its inputs (cell molecules, molecule map, positions) from pinned host "
+                       "memory and reads its results back; copies on their own streams, so the upload of step t+1 and "
+                       "the read-back of step t-1 overlap the kernels of step t; timed with CUDA events and the host "
+                       "clock around all steps (the larger of the two)"},
         # per step: kinetics (lane kernel + the launch for deferred cells), scatter, stencil, correct, permeate
         "gpu_launches": 6 * args.steps,
         "clocks": clocks,

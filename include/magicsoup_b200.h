@@ -226,6 +226,23 @@ int ms_diffuse_correct(const float *out, float *map_slab, const int64_t *sums, i
                        int64_t W, int64_t n_pxls_total, void *stream);
 
 /*
+ * Pixel-ordered write-back and permeation for densely populated maps -- same results as
+ * ms_scatter_signals (world.py:624-625) and ms_permeate / ms_degrade_permeate (world.py:651-665),
+ * with coalesced map accesses: one thread per pixel walks the m planes.
+ * ms_build_pixel_index fills pixel_cell (H*W int32) with the index of the cell at each pixel, -1
+ * where there is none (the reference's cell_map, world.py:194, with the index instead of a bool);
+ * rebuild it whenever cell_positions or the cell order change.  decay may be NULL.  m <= 32
+ * (MS_ERR_TOO_LARGE otherwise).
+ */
+int ms_build_pixel_index(const int32_t *cell_positions, int64_t c, int64_t H, int64_t W, int32_t *pixel_cell,
+                         void *stream);
+int ms_scatter_signals_by_pixel(const float *X, const int32_t *pixel_cell, int64_t m, int64_t H, int64_t W,
+                                float *cell_molecules_out, float *molecule_map, void *stream);
+int ms_permeate_by_pixel(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
+                         const int32_t *pixel_cell, const float *perm, const float *decay, int64_t m,
+                         int64_t H, int64_t W, void *stream);
+
+/*
  * World.degrade_molecules()                                    world.py:667-678
  * molecule_map[k] *= decay[k], cell_molecules[:, k] *= decay[k], in place, one launch
  * (decay[k] = exp(-ln 2 / half_life_k), world.py:184).

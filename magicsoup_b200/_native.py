@@ -64,6 +64,9 @@ _SIGNATURES = {
     "ms_diffuse_static_last_error": (C.c_char_p, []),
     "ms_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
     "ms_degrade_molecules": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "ms_build_pixel_index": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
+    "ms_scatter_signals_by_pixel": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "ms_permeate_by_pixel": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp]),
     "ms_degrade_diffuse_stencil": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "ms_degrade_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
 }

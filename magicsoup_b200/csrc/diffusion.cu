@@ -224,6 +224,78 @@ __global__ void degrade_kernel(float *map, long long n_pxls, float *cm, long lon
   for (long long t = t0; t < c * m; t += stride) cm[t] = cm[t] * f[t % m];
 }
 
+// ---------------------------------------------------------------------------
+// Pixel-ordered variants for densely populated maps.  The kernels above take one thread per (cell,
+// molecule): neighbouring threads touch planes H*W apart, i.e. one 4-byte value per 32-byte sector
+// on the map side.  With a pixel -> cell index (ms_build_pixel_index) one thread takes one PIXEL and
+// walks the m planes, so every plane access of a warp is one coalesced row segment and the cell side
+// is the cell's whole m-float row.  Same arithmetic per (cell, molecule), so the same bits.  m <= 32.
+// ---------------------------------------------------------------------------
+__global__ void pixel_index_kernel(const int *pos, long long c, int W, int *pixel_cell) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < c) pixel_cell[(size_t)pos[2 * r] * W + pos[2 * r + 1]] = (int)r;
+}
+
+// A warp takes 32 consecutive pixels.  Map side: lane L owns pixel L, one coalesced 128-byte
+// access per plane.  Cell side: the 32 lanes read / write ONE cell's row together (coalesced), pixel
+// after pixel.  A (32 x 33)-float tile in shared memory transposes between the two.  m <= 32.
+constexpr int PIX_WARPS = 8;
+
+__global__ void __launch_bounds__(32 * PIX_WARPS) permeate_pixel_kernel(const float *cm_in, float *cm_out, float *map,
+                                                                        const int *pixel_cell, const float *perm, int m,
+                                                                        long long n_pxls, const float *decay) {
+  __shared__ float tile[PIX_WARPS][32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long px0 = ((long long)blockIdx.x * PIX_WARPS + warp) * 32;
+  if (px0 >= n_pxls) return;
+  const long long px = px0 + lane;
+  const bool inside = px < n_pxls;
+  const int cell = inside ? pixel_cell[px] : -1;
+  if (__ballot_sync(0xffffffffu, cell >= 0) == 0u) return;
+  float (*t)[33] = tile[warp];
+  for (int k = 0; k < m; k++) t[lane][k] = inside ? map[(size_t)k * n_pxls + px] : 0.0f;
+  __syncwarp();
+  const float q = lane < m ? perm[lane] : 0.0f, dk = (decay && lane < m) ? decay[lane] : 1.0f;
+  for (int j = 0; j < 32; j++) {
+    const int cj = __shfl_sync(0xffffffffu, cell, j);
+    if (cj < 0 || lane >= m) continue;
+    const float raw = cm_in[(size_t)cj * m + lane];
+    const float xi = decay ? raw * dk : raw, xe = t[j][lane];
+    const float di = xi * q, de = xe * q;
+    cm_out[(size_t)cj * m + lane] = xi + (de - di);
+    t[j][lane] = xe + (di - de);
+  }
+  __syncwarp();
+  if (inside && cell >= 0)
+    for (int k = 0; k < m; k++) map[(size_t)k * n_pxls + px] = t[lane][k];
+}
+
+__global__ void __launch_bounds__(32 * PIX_WARPS) scatter_pixel_kernel(const float *X, const int *pixel_cell, int m,
+                                                                       long long n_pxls, float *cm_out, float *map) {
+  __shared__ float tile[PIX_WARPS][32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long px0 = ((long long)blockIdx.x * PIX_WARPS + warp) * 32;
+  if (px0 >= n_pxls) return;
+  const long long px = px0 + lane;
+  const int cell = px < n_pxls ? pixel_cell[px] : -1;
+  if (__ballot_sync(0xffffffffu, cell >= 0) == 0u) return;
+  float (*t)[33] = tile[warp];
+  const int s = 2 * m;
+  for (int j = 0; j < 32; j++) {
+    const int cj = __shfl_sync(0xffffffffu, cell, j);
+    if (cj < 0) continue;
+    const float *x = X + (size_t)cj * s;
+    for (int i = lane; i < s; i += 32) {
+      const float v = x[i];
+      if (i < m) cm_out[(size_t)cj * m + i] = v;
+      else t[j][i - m] = v;
+    }
+  }
+  __syncwarp();
+  if (cell >= 0)
+    for (int k = 0; k < m; k++) map[(size_t)k * n_pxls + px] = t[lane][k];
+}
+
 // world.py:624-625, one thread per (cell, signal)
 __global__ void scatter_kernel(const float *X, const int *pos, long long c, int m, int H, int W,
                                float *cm_out, float *map) {
@@ -379,6 +451,47 @@ extern "C" int ms_degrade_permeate(const float *cell_molecules_in, float *cell_m
   if (!decay && c * m > 0) return MS_ERR_INVALID_ARGUMENT;
   return permeate_impl(cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, decay, c, m, H, W,
                        stream);
+}
+
+extern "C" int ms_build_pixel_index(const int32_t *cell_positions, int64_t c, int64_t H, int64_t W,
+                                    int32_t *pixel_cell, void *stream) {
+  if (c < 0 || H <= 0 || W <= 0 || H > INT32_MAX || W > INT32_MAX || c > INT32_MAX || !pixel_cell ||
+      (c > 0 && !cell_positions))
+    return MS_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  MS_CUDA_CHECK(cudaMemsetAsync(pixel_cell, 0xff, (size_t)H * W * sizeof(int32_t), st));  // -1: no cell
+  if (c > 0) pixel_index_kernel<<<(unsigned)((c + 255) / 256), 256, 0, st>>>(cell_positions, c, (int)W, pixel_cell);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_permeate_by_pixel(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
+                                    const int32_t *pixel_cell, const float *perm, const float *decay, int64_t m,
+                                    int64_t H, int64_t W, void *stream) {
+  if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!cell_molecules_in || !cell_molecules_out || !molecule_map || !pixel_cell || !perm)
+    return MS_ERR_INVALID_ARGUMENT;
+  if (m > 32) return MS_ERR_TOO_LARGE;  // the transposing tile holds 32 planes; use ms_permeate
+  const long long n = (long long)H * W;
+  permeate_pixel_kernel<<<(unsigned)((n + 32 * PIX_WARPS - 1) / (32 * PIX_WARPS)), 32 * PIX_WARPS, 0, (cudaStream_t)stream>>>(
+      cell_molecules_in, cell_molecules_out, molecule_map, pixel_cell, perm, (int)m, n, decay);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
+}
+
+extern "C" int ms_scatter_signals_by_pixel(const float *X, const int32_t *pixel_cell, int64_t m, int64_t H,
+                                           int64_t W, float *cell_molecules_out, float *molecule_map,
+                                           void *stream) {
+  if (bad_map(m, H, W)) return MS_ERR_INVALID_ARGUMENT;
+  if (m == 0) return MS_OK;
+  if (!X || !pixel_cell || !cell_molecules_out || !molecule_map) return MS_ERR_INVALID_ARGUMENT;
+  if (m > 32) return MS_ERR_TOO_LARGE;  // the transposing tile holds 32 planes; use ms_scatter_signals
+  const long long n = (long long)H * W;
+  scatter_pixel_kernel<<<(unsigned)((n + 32 * PIX_WARPS - 1) / (32 * PIX_WARPS)), 32 * PIX_WARPS, 0,
+                         (cudaStream_t)stream>>>(X, pixel_cell, (int)m, n, cell_molecules_out, molecule_map);
+  MS_CUDA_CHECK(cudaGetLastError());
+  return MS_OK;
 }
 
 extern "C" int ms_degrade_molecules(float *molecule_map, float *cell_molecules, const float *decay, int64_t c,

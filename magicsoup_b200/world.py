@@ -203,10 +203,33 @@ class World:
             self._kernel_events.append(ev)
         return flags[: nat.N_FLAGS * 4].view(torch.int32)
 
+    def _pixel_index(self, dev, pos, H: int, W: int) -> torch.Tensor | None:
+        """
+        pixel -> cell index for the pixel-ordered kernels, or None on sparsely populated maps (there
+        the per-cell kernels touch less memory).  Rebuilt when cell_positions change (tensor identity
+        and version) -- one small launch.
+        """
+        c = self.n_cells
+        if 4 * c < H * W or self.n_molecules > 32:
+            return None
+        # the stamp holds the tensor itself, so its address cannot be recycled for another one
+        stamp = (pos, pos._version, c, H, W)
+        old = self._scratch.get("pixel_index_stamp")
+        if old is None or old[0] is not pos or old[1:] != stamp[1:]:
+            buf = self._buffer("pixel_index", 4 * H * W, dev)
+            nat.check(nat.lib().ms_build_pixel_index(nat.ptr(pos), c, H, W, nat.ptr(buf), nat.stream_ptr(dev)))
+            self._scratch["pixel_index_stamp"] = stamp  # type: ignore[assignment]
+        return self._scratch["pixel_index"]
+
     def _launch_scatter(self, dev, X, pos, mm) -> torch.Tensor:
         m = self.n_molecules
         _, H, W = mm.shape
         new_cm = torch.empty(self.n_cells, m, dtype=torch.float32, device=dev)
+        pix = self._pixel_index(dev, pos, H, W)
+        if pix is not None:
+            nat.check(nat.lib().ms_scatter_signals_by_pixel(nat.ptr(X), nat.ptr(pix), m, H, W, nat.ptr(new_cm),
+                                                            nat.ptr(mm), nat.stream_ptr(dev)))
+            return new_cm
         nat.check(nat.lib().ms_scatter_signals(nat.ptr(X), nat.ptr(pos), self.n_cells, m, H, W, nat.ptr(new_cm),
                                                nat.ptr(mm), nat.stream_ptr(dev)))
         return new_cm
@@ -237,6 +260,11 @@ class World:
         m, H, W = mm.shape
         perm = self._const_f32("perm", list(self._permeation), dev)
         new_cm = torch.empty_like(cm)
+        pix = self._pixel_index(dev, pos, H, W)
+        if pix is not None:
+            nat.check(nat.lib().ms_permeate_by_pixel(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pix), nat.ptr(perm),
+                                                     nat.ptr(decay), m, H, W, nat.stream_ptr(dev)))
+            return new_cm
         if decay is None:
             rc = nat.lib().ms_permeate(nat.ptr(cm), nat.ptr(new_cm), nat.ptr(mm), nat.ptr(pos), nat.ptr(perm),
                                        self.n_cells, m, H, W, nat.stream_ptr(dev))

@@ -171,7 +171,8 @@ __device__ bool build_lane_lists(const KinArgs &a, const LaneLayout &L, unsigned
   const unsigned rowrun = rowmap + 4u * (unsigned)L.PA;     // [PA]  entries placed so far: substrate | product << 8
   const unsigned sigcnt = rowrun + 4u * (unsigned)L.PA;     // [S2]  N entries of a signal, then its first chunk
   const unsigned sigrun = sigcnt + 4u * (unsigned)L.S2;     // [S2]  N entries placed so far
-  // (3*PA + 2*S2 <= 2*S2 + RG + 4*CH words between oX0 and oT for every shape of the lane path)
+  // (3*PA + 2*S2 words from oX0 on: working arrays that are initialised after the build; the queue starts
+  // behind them, make_lane_layout)
 #pragma unroll 1
   for (int j = lane; j < 3 * L.PA + 2 * L.S2; j += 32) sts_u(rowcnt + 4u * (unsigned)j, 0u);
 #pragma unroll 1

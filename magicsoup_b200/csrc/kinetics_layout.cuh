@@ -59,6 +59,11 @@ __host__ __device__ inline LaneLayout make_lane_layout(int p, int s) {
   // the queue and the scan's staging slots (8 x 512 B) share the region while the tile is scanned
   if (o < 1024 + 2 * L.q_cap) o = 1024 + 2 * L.q_cap;
   L.words = (o + 31) & ~31;
+  {  // the queue gets whatever the region leaves behind the staging slots and behind the static
+     // arrays + the list builder's temporaries (3*PA + 2*S2 words from oX0): costs nothing
+    const int busy = L.static_words + 3 * L.PA + 2 * L.S2;
+    L.q_cap = (L.words - (busy > 1024 ? busy : 1024)) / 2;
+  }
   L.oQueue = L.words - 2 * L.q_cap;
   return L;
 }

@@ -38,7 +38,10 @@ extern "C" {
 #define MS_ERR_TOO_LARGE (-5)
 
 /* Number of uint32 words in a flags buffer (see ms_integrate_signals). */
-#define MS_N_FLAGS 24
+#define MS_N_FLAGS 32
+/* flags[MS_FLAG_BAD_POSITION] != 0: some cell_positions entry lay outside the map (the gather read
+ * pixel (0,0) instead; the reference raises IndexError, world.py:621) */
+#define MS_FLAG_BAD_POSITION 24
 
 /* The nine Kinetics parameter tensors, kinetics.py:399-409. */
 typedef struct ms_kinetics_params {

@@ -13,7 +13,8 @@ import torch
 
 _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libmagicsoup_b200.so"
-N_FLAGS = 24
+N_FLAGS = 32
+FLAG_BAD_POSITION = 24
 
 _vp, _i64, _i32, _sz = C.c_void_p, C.c_int64, C.c_int32, C.c_size_t
 

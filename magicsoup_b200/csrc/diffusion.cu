@@ -205,6 +205,10 @@ __global__ void permeate_kernel(const float *cm_in, float *cm_out, float *map, c
   const long long cell = r / m;
   const int k = (int)(r % m);
   const int x = pos[2 * cell], y = pos[2 * cell + 1];
+  if ((unsigned)x >= (unsigned)H || (unsigned)y >= (unsigned)W) {  // outside the map: no exchange, no stray write
+    cm_out[r] = decay ? cm_in[r] * decay[k] : cm_in[r];
+    return;
+  }
   const size_t mi = ((size_t)k * H + x) * W + y;
   const float xi = decay ? cm_in[r] * decay[k] : cm_in[r], xe = map[mi], q = perm[k];
   const float di = xi * q, de = xe * q;
@@ -231,9 +235,11 @@ __global__ void degrade_kernel(float *map, long long n_pxls, float *cm, long lon
 // walks the m planes, so every plane access of a warp is one coalesced row segment and the cell side
 // is the cell's whole m-float row.  Same arithmetic per (cell, molecule), so the same bits.  m <= 32.
 // ---------------------------------------------------------------------------
-__global__ void pixel_index_kernel(const int *pos, long long c, int W, int *pixel_cell) {
+__global__ void pixel_index_kernel(const int *pos, long long c, int H, int W, int *pixel_cell) {
   const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r < c) pixel_cell[(size_t)pos[2 * r] * W + pos[2 * r + 1]] = (int)r;
+  if (r >= c) return;
+  const int x = pos[2 * r], y = pos[2 * r + 1];
+  if ((unsigned)x < (unsigned)H && (unsigned)y < (unsigned)W) pixel_cell[(size_t)x * W + y] = (int)r;  // else: no pixel
 }
 
 // A warp takes 32 consecutive pixels.  Map side: lane L owns pixel L, one coalesced 128-byte
@@ -309,7 +315,7 @@ __global__ void scatter_kernel(const float *X, const int *pos, long long c, int 
     cm_out[cell * m + i] = v;
   } else {
     const int x = pos[2 * cell], y = pos[2 * cell + 1];
-    map[((size_t)(i - m) * H + x) * W + y] = v;
+    if ((unsigned)x < (unsigned)H && (unsigned)y < (unsigned)W) map[((size_t)(i - m) * H + x) * W + y] = v;
   }
 }
 
@@ -460,7 +466,7 @@ extern "C" int ms_build_pixel_index(const int32_t *cell_positions, int64_t c, in
     return MS_ERR_INVALID_ARGUMENT;
   cudaStream_t st = (cudaStream_t)stream;
   MS_CUDA_CHECK(cudaMemsetAsync(pixel_cell, 0xff, (size_t)H * W * sizeof(int32_t), st));  // -1: no cell
-  if (c > 0) pixel_index_kernel<<<(unsigned)((c + 255) / 256), 256, 0, st>>>(cell_positions, c, (int)W, pixel_cell);
+  if (c > 0) pixel_index_kernel<<<(unsigned)((c + 255) / 256), 256, 0, st>>>(cell_positions, c, (int)H, (int)W, pixel_cell);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }

@@ -1152,10 +1152,10 @@ namespace ms {
 // holds signals i (.x) and i + 32 (.y).  One copy of the code for both call sites; everything is
 // passed by value (a reference to the kernel parameters would turn into generic loads and a stack
 // frame in a function that is not inlined).
-__device__ __noinline__ float2 load_cell_signals(const float *X_in, const float *cell_mols, const float *mol_map,
+__device__ __noinline__ float4 load_cell_signals(const float *X_in, const float *cell_mols, const float *mol_map,
                                                  const int *pos_all, int s, int m, int H, int W, long long cell,
                                                  int lane) {
-  float2 v = make_float2(0.0f, 0.0f);
+  float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);  // .z != 0: the cell's position is outside the map
   if (X_in) {
     const float *x = X_in + cell * s;
     if (lane < s) v.x = x[lane];
@@ -1163,7 +1163,11 @@ __device__ __noinline__ float2 load_cell_signals(const float *X_in, const float 
     return v;
   }
   // lane i < m: intracellular molecule i; lane m + k: the cell's pixel of map plane k
-  const int2 pos = *reinterpret_cast<const int2 *>(pos_all + 2 * cell);
+  int2 pos = *reinterpret_cast<const int2 *>(pos_all + 2 * cell);
+  if ((unsigned)pos.x >= (unsigned)H || (unsigned)pos.y >= (unsigned)W) {
+    pos = make_int2(0, 0);  // never read outside the map; reported through MS_FLAG_BAD_POSITION
+    v.z = 1.0f;
+  }
   const unsigned plane = (unsigned)H * (unsigned)W;  // < 2^31 pixels per plane (ms_enzymatic_activity checks)
   const float *px = mol_map + (size_t)pos.x * W + pos.y;
   const float *cm = cell_mols + cell * m;
@@ -1193,12 +1197,13 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_
     return (long long)__shfl_sync(FULL, v, 0);
   };
   float xa = 0.0f, xb = 0.0f;
-  unsigned wflags = 0;  // early-exit flags of this warp's cells (bit = index in the flags buffer)
+  unsigned wflags = 0;  // flags of this warp's cells (bit = index in the flags buffer)
   long long cell = grab();
   if (cell < n_items) {
-    const float2 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, cell, lane);
+    const float4 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, cell, lane);
     xa = v.x;
     xb = v.y;
+    if (v.z != 0.0f) wflags |= 1u << MS_FLAG_BAD_POSITION;
   }
 #pragma unroll 1
   while (cell < n_items) {
@@ -1245,9 +1250,10 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_
       if (lane + 32 < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane + 32), xb);
     }
     if (next_cell < n_items) {  // in flight during this cell's parts
-      const float2 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, next_cell, lane);
+      const float4 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, next_cell, lane);
       xa = v.x;
       xb = v.y;
+      if (v.z != 0.0f) wflags |= 1u << MS_FLAG_BAD_POSITION;
     }
     cp_async_wait_all();
     __syncwarp();
@@ -1299,7 +1305,11 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_
   auto load_x = [&](long long cell, int i) -> float {
     if (a.X_in) return a.X_in[cell * s + i];
     if (i < a.m) return a.cell_mols[cell * a.m + i];
-    const int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
+    int px = a.pos[2 * cell], py = a.pos[2 * cell + 1];
+    if ((unsigned)px >= (unsigned)a.H || (unsigned)py >= (unsigned)a.W) {
+      px = py = 0;  // never read outside the map; reported through MS_FLAG_BAD_POSITION
+      sflags[MS_FLAG_BAD_POSITION] = 1u;
+    }
     return a.mol_map[((long long)(i - a.m) * a.H + px) * a.W + py];
   };
   if (a.batch_enabled) {

@@ -181,41 +181,88 @@ class SlabWorld(World):
         `cell_positions`, e.g. a division or move across the slab boundary -- to the rank
         that owns its pixel.  Collective: every rank must call it.  Returns the number of
         cells received.  Local indices are compacted exactly like `kill_cells` does
-        (world.py:527-540); received cells are appended.
+        (world.py:527-540); received cells are appended (sender ranks in order).
+
+        One small all-to-all of per-destination counts, then the per-cell tensors and parameter
+        slices of the leaving cells go rank to rank as packed device buffers (`batch_isend_irecv`,
+        only between pairs that exchange cells): no pickling, no per-cell host work.
         """
-        H = self.global_map_size[0]
+        ws, H = self.world_size, self.global_map_size[0]
+        comm = self._comm_device()
         gpos = self.global_positions()
         gpos[:, 0] = gpos[:, 0] % H  # the map is a torus
         owner = self.owner_of_rows(gpos[:, 0].long())
-        leaving = torch.nonzero(owner != self.rank).flatten().tolist()
-        outgoing: list[dict[str, torch.Tensor] | None] = [None] * self.world_size
-        for dst in range(self.world_size):
-            idxs = [i for i in leaving if int(owner[i]) == dst]
-            if idxs:
-                payload = self.export_cells(idxs)
-                payload["positions"][:, 0] = payload["positions"][:, 0] % H
-                outgoing[dst] = {k: v.cpu() for k, v in payload.items()}
-        if leaving:
-            self._drop_cells(leaving)
-        gathered: list[Any] = [None] * self.world_size
-        dist.all_gather_object(gathered, outgoing, group=self.group)
+        leaving = torch.nonzero(owner != self.rank).flatten()
+        order = leaving[torch.argsort(owner[leaving], stable=True)]  # grouped by destination, cell order kept
+        # per destination: (cells to send, my protein dimension); the protein dimension only ever grows
+        # per rank (kinetics.py:705-723), so the receiver sizes its buffers by the sender's
+        p_mine = int(self.kinetics._buf["N"].shape[1])
+        send_meta = torch.stack([torch.bincount(owner[order], minlength=ws).to(torch.int64).cpu(),
+                                 torch.full((ws,), p_mine, dtype=torch.int64)], dim=1).contiguous()
+        recv_meta = send_meta.clone()
+        if ws > 1:
+            sc = send_meta.to(comm)
+            rc = torch.empty_like(sc)
+            dist.all_to_all_single(rc, sc, group=self.group)
+            recv_meta = rc.cpu()
+        send_counts = send_meta[:, 0].tolist()
+        recv_counts, recv_p = recv_meta[:, 0].tolist(), recv_meta[:, 1].tolist()
+
+        payload = self.export_cells(order) if order.numel() else None
+        if payload is not None:
+            payload["positions"][:, 0] = payload["positions"][:, 0] % H
+        names = ["positions", "molecules", "lifetimes", "divisions", *_ALL_PARAMS]
+        ops, inbox, keep_alive = [], {}, []
+        offset = 0
+        for dst in range(ws):
+            n = send_counts[dst]
+            if n and dst != self.rank:
+                for k in names:
+                    buf = payload[k][offset:offset + n].contiguous().to(comm)
+                    keep_alive.append(buf)
+                    ops.append(dist.P2POp(dist.isend, buf, self._global_rank(dst), group=self.group))
+            offset += n
+        for src in range(ws):
+            n = recv_counts[src]
+            if n and src != self.rank:
+                inbox[src] = {k: torch.empty((n,) + shape, dtype=dt, device=comm)
+                              for k, (shape, dt) in self._payload_templates(recv_p[src]).items()}
+                for k in names:
+                    ops.append(dist.P2POp(dist.irecv, inbox[src][k], self._global_rank(src), group=self.group))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        if order.numel():
+            self._drop_cells(order)
         received = 0
-        for src in range(self.world_size):
-            payload = gathered[src][self.rank]
-            if payload is not None:
-                received += len(self.import_cells(payload))
+        for src in sorted(inbox):
+            received += len(self.import_cells(inbox[src]))
         return received
 
-    def _drop_cells(self, cell_idxs: list[int]):
+    def _global_rank(self, r: int) -> int:
+        return dist.get_global_rank(self.group, r) if self.group is not None else r
+
+    def _payload_templates(self, p: int) -> dict[str, tuple[tuple[int, ...], torch.dtype]]:
+        """trailing shape and dtype of every per-cell tensor that travels with a cell (p: the sender's proteins)"""
+        s = 2 * self.n_molecules
+        out = {"positions": ((2,), torch.int32), "molecules": ((self.n_molecules,), torch.float32),
+               "lifetimes": ((), torch.int32), "divisions": ((), torch.int32)}
+        for k in _ALL_PARAMS:
+            out[k] = ((p, s) if k in ("N", "Nf", "Nb", "A", "Kmr") else (p,),
+                      torch.int32 if k in ("N", "Nf", "Nb", "A") else torch.float32)
+        return out
+
+    def _drop_cells(self, cell_idxs):
         """kill_cells' compaction (world.py:527-540) without the spill and cell_map update"""
+        idx = torch.as_tensor(cell_idxs, dtype=torch.long, device=self.cell_lifetimes.device)
         keep = torch.ones(self.cell_lifetimes.size(0), dtype=torch.bool, device=self.cell_lifetimes.device)
-        keep[cell_idxs] = False
+        keep[idx] = False
         self.cell_lifetimes = self.cell_lifetimes[keep]
         self.cell_positions = self.cell_positions[keep]
         self.cell_divisions = self.cell_divisions[keep]
         self.cell_molecules = self.cell_molecules[keep]
         self.kinetics.remove_cell_params(keep=keep)
-        for idx in sorted(cell_idxs, reverse=True):
-            self.cell_genomes.pop(idx)
-            self.cell_labels.pop(idx)
-        self.n_cells -= len(cell_idxs)
+        gone = set(idx.tolist())
+        self.cell_genomes = [g for i, g in enumerate(self.cell_genomes) if i not in gone]
+        self.cell_labels = [g for i, g in enumerate(self.cell_labels) if i not in gone]
+        self.n_cells -= len(gone)

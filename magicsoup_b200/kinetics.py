@@ -43,11 +43,16 @@ _STAGE_METHODS = ("_integrate_signals_part", "_get_velocities", "_multiply_signa
 
 def _settle_early_exit(flags: list[int], eq: list[int], n_parts: int) -> bool:
     """
+    Also raises IndexError if the kernel met a cell position outside the map (flag word 24), as the
+    reference's advanced indexing does (world.py:621).
+
     kinetics.py:846-847: the reference leaves a part's adjustment loop at the first
     iteration where NO cell has an adjustable protein with |V| > 0.1.  `flags` come from
     a launch that applied eq[q] iterations in part q.  Returns True if eq was lowered
     (the launch must be repeated), False if the launch already equals the reference.
     """
+    if len(flags) > nat.FLAG_BAD_POSITION and flags[nat.FLAG_BAD_POSITION]:
+        raise IndexError("cell_positions holds a pixel outside the molecule map")
     for q in range(n_parts):
         for k in range(eq[q]):
             if flags[q * 4 + k] == 0:

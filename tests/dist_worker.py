@@ -181,6 +181,37 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
         assert len({(int(a), int(b)) for a, b in pos}) <= total
         assert np.isfinite(mm).all() and np.isfinite(cm).all() and (mm >= 0).all()
     assert world.kinetics.N.shape[0] == world.n_cells == world.cell_molecules.shape[0]
+
+    # bulk migration: every cell in a slab's first row steps up onto the neighbour's last row where
+    # that pixel is free; cells keep their molecules and parameters (checked by global position)
+    def snapshot():
+        parts = [None] * ws
+        payload = {"pos": world.global_positions().cpu().numpy() % np.array([[H, cols]]),
+                   "cm": world.cell_molecules.cpu().numpy(), "vmax": world.kinetics.cell_params(
+                       list(range(world.n_cells)))["Vmax"].cpu().numpy()}
+        dist.all_gather_object(parts, payload, group=world.group)
+        return {(int(a), int(b)): (c.tobytes(), v.tobytes())
+                for p_ in parts for (a, b), c, v in zip(p_["pos"], p_["cm"], p_["vmax"])}
+
+    last_rows = [None] * ws
+    dist.all_gather_object(last_rows, world.cell_map[-1].cpu().tolist(), group=world.group)
+    above = last_rows[(rank - 1) % ws]
+    movers = [i for i in range(world.n_cells)
+              if int(world.cell_positions[i, 0]) == 0 and not above[int(world.cell_positions[i, 1])]]
+    if ws > 1:
+        for i in movers:
+            world.cell_map[0, int(world.cell_positions[i, 1])] = False
+            world.cell_positions[i, 0] = -1
+    before = snapshot()
+    n_moved = [None] * ws
+    dist.all_gather_object(n_moved, len(movers) if ws > 1 else 0, group=world.group)
+    received = world.migrate_cells()
+    assert received == (n_moved[(rank + 1) % ws] if ws > 1 else 0), (received, n_moved)
+    after = snapshot()
+    assert before == after and len(after) == int(sum(world.global_n_cells()))
+    assert bool((world.cell_positions[:, 0] >= 0).all()) and bool((world.cell_positions[:, 0] < world.slab_rows).all())
+    world.enzymatic_activity()
+    world.diffuse_molecules()
     if rank == 0 and not quiet:
         print(f"dist_worker ok: backend={backend} ranks={ws} steps={steps} cells={cells} received={received}")
 

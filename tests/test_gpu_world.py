@@ -216,3 +216,18 @@ def test_world_pickles_without_device_handles(ms):
     w.enzymatic_activity()
     w2.enzymatic_activity()
     assert torch.equal(w.cell_molecules, w2.cell_molecules)
+
+
+def test_position_outside_the_map_raises_like_the_reference(ms):
+    # the reference's advanced indexing raises IndexError (world.py:621); here the kernels never touch
+    # memory outside the map and the step reports it
+    pop = make_population(64, 8, 4, 16, seed=71)
+    w = _world_from_pop(ms, pop)
+    before = w.molecule_map.clone()
+    w.cell_positions[5, 0] = 16
+    with pytest.raises(IndexError):
+        w.enzymatic_activity()
+    assert torch.equal(w.molecule_map, before)  # nothing was committed
+    w.cell_positions[5, 0] = -3
+    w.diffuse_molecules()  # permeation skips the cell, the map stays finite
+    assert torch.isfinite(w.molecule_map).all() and torch.isfinite(w.cell_molecules).all()

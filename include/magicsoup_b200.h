@@ -201,8 +201,8 @@ int ms_scatter_signals(const float *X, const int32_t *cell_positions, int64_t c,
  * += (sum_before - sum_after) / (H*W) and clamp(0).  In place on molecule_map.
  * scratch: ms_diffuse_scratch_bytes(m,H,W) bytes (stencil output + plane sums).
  * Value range: the plane sums are exact 2^-32 fixed point, which holds finite |x| < 2^31; a NaN,
- * Inf or larger value in a plane is left out of / saturates its sums (the reference's float32
- * torch.sum would turn the whole plane NaN instead).  Pointers need only float alignment; the
+ * Inf or larger value turns its whole plane NaN (NaN / Inf: as the reference's float32 torch.sum
+ * does, world.py:640-648).  Pointers need only float alignment; the
  * float4 paths are taken when the buffers are 16-byte aligned.
  */
 int ms_diffuse_molecules(float *molecule_map, const float *a, const float *b, int64_t m, int64_t H,
@@ -216,11 +216,14 @@ size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W);
  * world.py:638-649 on the whole map).
  * ms_diffuse_stencil: stencil of the slab (m,H,W) into `out` (m,H,W); the rows above
  *   row 0 and below row H-1 come from halo_top / halo_bottom (m,W) (the neighbouring
- *   slabs' edge rows; NULL = wrap around inside the slab); sums (4*m int64, zeroed by
- *   the call) receive the slab's exact plane sums before/after as 2^-32 fixed point
- *   {hi_before, lo_before, hi_after, lo_after}: add them over all slabs (integers, so
- *   the order does not matter) before the second pass.
- * ms_diffuse_correct: map_slab = clamp(out + (sum_before - sum_after)/n_pxls_total, 0).
+ *   slabs' edge rows; NULL = wrap around inside the slab); sums (5*m int64, zeroed by
+ *   the call) receive the slab's exact plane sums before/after as 2^-32 fixed point,
+ *   {hi_before, lo_before, hi_after, lo_after} per plane in the first 4*m words, and in word
+ *   4*m + k the number of blocks that met a value the fixed point cannot hold in plane k (NaN,
+ *   Inf, |x| >= 2^31): add all 5*m words over all slabs (integers, so the order does not
+ *   matter) before the second pass.
+ * ms_diffuse_correct: map_slab = clamp(out + (sum_before - sum_after)/n_pxls_total, 0); a plane
+ *   whose flag word is non-zero becomes NaN, as with the reference's float32 torch.sum.
  */
 int ms_diffuse_stencil(const float *map_slab, const float *halo_top, const float *halo_bottom,
                        const float *a, const float *b, int64_t m, int64_t H, int64_t W, float *out,

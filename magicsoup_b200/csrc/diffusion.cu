@@ -22,7 +22,9 @@ constexpr int DTHREADS = 256;
 
 struct FixSum {
   long long hi, lo;
+  int bad;  // a value the fixed point cannot hold: NaN, Inf or |x| >= 2^31
   __device__ __forceinline__ void add(float x) {
+    bad |= !(fabsf(x) < 2147483648.0f);
     const long long q = __double2ll_rn((double)x * 4294967296.0);
     hi += q >> 32;
     lo += q & 0xffffffffLL;
@@ -46,7 +48,9 @@ __device__ __forceinline__ float stencil_point(float nw, float n, float ne, floa
 }
 
 // block-level reduction of the four fixed-point accumulators + one atomic each
-__device__ void block_commit_sums(FixSum in, FixSum out, unsigned long long *sums /* 4 per plane */) {
+__device__ void block_commit_sums(FixSum in, FixSum out, unsigned long long *sums /* 4 per plane */,
+                                  unsigned long long *bad_flag /* 1 per plane */) {
+  if (__syncthreads_or(in.bad | out.bad) && threadIdx.x == 0) atomicAdd(bad_flag, 1ull);
   __shared__ long long red[4][DTHREADS / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   long long v0 = warp_sum_ll(in.hi), v1 = warp_sum_ll(in.lo), v2 = warp_sum_ll(out.hi),
@@ -104,7 +108,7 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
   __syncthreads();
 
   const float a = wa[k], b = wb[k];
-  FixSum sin = {0, 0}, sout = {0, 0};
+  FixSum sin = {0, 0, 0}, sout = {0, 0, 0};
   const int c0 = 4 + 4 * lane;
   // rolling 3-row window: rows r-1, r, r+1 of the tile; each row = left, 4 centre, right
   float prev[6], cur[6], nxt[6];
@@ -133,7 +137,7 @@ __global__ void __launch_bounds__(DTHREADS) stencil_tiled_kernel(const float *__
 #pragma unroll
     for (int q = 0; q < 6; q++) { prev[q] = cur[q]; cur[q] = nxt[q]; }
   }
-  block_commit_sums(sin, sout, sums + 4 * k);
+  block_commit_sums(sin, sout, sums + 4 * k, sums + 4 * gridDim.z + k);
 }
 
 // generic path: any H, W (e.g. the 5x5 map of the reference's test).  grid = (blocks, 1, m)
@@ -150,7 +154,7 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
   float *oplane = out + (size_t)k * H * W;
   const float a = wa[k], b = wb[k];
   const float dk = decay ? decay[k] : 1.0f;
-  FixSum sin = {0, 0}, sout = {0, 0};
+  FixSum sin = {0, 0, 0}, sout = {0, 0, 0};
   const long long n = (long long)H * W;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n;
        t += (long long)gridDim.x * blockDim.x) {
@@ -166,7 +170,7 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
     sin.add(c);
     sout.add(o);
   }
-  block_commit_sums(sin, sout, sums + 4 * k);
+  block_commit_sums(sin, sout, sums + 4 * k, sums + 4 * gridDim.z + k);
 }
 
 // pass 2: world.py:648-649.  grid = (blocks, 1, m)
@@ -178,7 +182,9 @@ __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restri
   const long long *sk = reinterpret_cast<const long long *>(sums) + 4 * k;
   const float s0 = (float)((double)sk[0] + (double)sk[1] * 2.3283064365386963e-10);
   const float s1 = (float)((double)sk[2] + (double)sk[3] * 2.3283064365386963e-10);
-  const float corr = (s0 - s1) / (float)n_pxls_total;
+  float corr = (s0 - s1) / (float)n_pxls_total;
+  // a NaN / Inf in the plane makes the reference's float32 torch.sum NaN (world.py:640-648): whole plane NaN
+  if (reinterpret_cast<const long long *>(sums)[4 * gridDim.z + k] != 0) corr = __int_as_float(0x7fc00000);
   const float *src = out + (size_t)k * n_pxls;
   float *dst = map + (size_t)k * n_pxls;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -341,7 +347,7 @@ extern "C" size_t ms_diffuse_scratch_bytes(int64_t m, int64_t H, int64_t W) {
   if (m <= 0 || H <= 0 || W <= 0) return 256;
   int64_t vol = 0;
   if (!volume_fits(m, H, W, (int64_t)1 << 58, &vol)) return SIZE_MAX;  // no buffer is ever large enough
-  return align256((size_t)vol * sizeof(float)) + align256((size_t)m * 4 * sizeof(long long));
+  return align256((size_t)vol * sizeof(float)) + align256((size_t)m * 5 * sizeof(long long));
 }
 
 static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
@@ -349,7 +355,7 @@ static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 static int stencil_launch(const float *map, const float *halo_top, const float *halo_bot,
                           const float *a, const float *b, int64_t m, int64_t H, int64_t W, float *tmp,
                           unsigned long long *sums, cudaStream_t st, const float *decay = nullptr) {
-  MS_CUDA_CHECK(cudaMemsetAsync(sums, 0, (size_t)m * 4 * sizeof(long long), st));
+  MS_CUDA_CHECK(cudaMemsetAsync(sums, 0, (size_t)m * 5 * sizeof(long long), st));
   const long long n = (long long)H * W;
   // the tiled kernel moves float4: rows must start 16-byte aligned in every buffer it touches
   const bool vec_ok = aligned16(map) && aligned16(tmp) && (!halo_top || aligned16(halo_top)) &&
@@ -547,7 +553,7 @@ extern "C" int ms_scatter_signals(const float *X, const int32_t *cell_positions,
 #define MS_STATIC_DIFFUSE_MAX_PLANES 256
 
 static __device__ __align__(256) float g_static_diffuse_out[MS_STATIC_DIFFUSE_MAX_FLOATS];
-static __device__ __align__(256) unsigned long long g_static_diffuse_sums[4 * MS_STATIC_DIFFUSE_MAX_PLANES];
+static __device__ __align__(256) unsigned long long g_static_diffuse_sums[5 * MS_STATIC_DIFFUSE_MAX_PLANES];
 
 namespace {
 constexpr int kMaxDevices = 64;

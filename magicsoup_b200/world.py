@@ -235,12 +235,12 @@ class World:
         return new_cm
 
     def _launch_stencil(self, dev, mm, top, bottom, decay=None) -> tuple[torch.Tensor, torch.Tensor]:
-        """ms_diffuse_stencil -> (stencil output in scratch, int64 plane sums (4*m)); decay: degradation folded in"""
+        """ms_diffuse_stencil -> (stencil output in scratch, int64 plane sums + flags (5*m)); decay: degradation folded in"""
         m, H, W = mm.shape
         a = self._const_f32("diff_a", [w[0] for w in self._diffusion], dev)
         b = self._const_f32("diff_b", [w[1] for w in self._diffusion], dev)
         out = self._buffer("diffuse", m * H * W * 4, dev)
-        sums = self._buffer("diffuse_sums", 4 * m * 8, dev)[: 4 * m * 8].view(torch.int64)
+        sums = self._buffer("diffuse_sums", 5 * m * 8, dev)[: 5 * m * 8].view(torch.int64)
         if decay is None:
             rc = nat.lib().ms_diffuse_stencil(nat.ptr(mm), nat.ptr(top), nat.ptr(bottom), nat.ptr(a), nat.ptr(b),
                                               m, H, W, nat.ptr(out), nat.ptr(sums), nat.stream_ptr(dev))

@@ -231,3 +231,22 @@ def test_position_outside_the_map_raises_like_the_reference(ms):
     w.cell_positions[5, 0] = -3
     w.diffuse_molecules()  # permeation skips the cell, the map stays finite
     assert torch.isfinite(w.molecule_map).all() and torch.isfinite(w.cell_molecules).all()
+
+
+@pytest.mark.parametrize("size", [24, 128], ids=["generic-stencil", "tiled-stencil"])
+def test_non_finite_value_poisons_its_plane_like_torch_sum(ms, size):
+    # world.py:640-648: total_before / total_after are float32 torch.sum results, so one NaN or Inf
+    # in a plane makes the correction NaN and with it the whole plane; other planes are untouched
+    m = 3
+    mols = [ms.Molecule(f"nf{size}_{i}", 10e3, diffusivity=[1.0, 0.1, 0.5][i]) for i in range(m)]
+    w = ms.World(chemistry=ms.Chemistry(molecules=mols, reactions=[]), map_size=size, device="cuda")
+    g = torch.Generator().manual_seed(3)
+    mm = (torch.randn(m, size, size, generator=g) + 10.0).abs()
+    clean = O.diffuse(mm.numpy(), [1.0, 0.1, 0.5])
+    mm[0, 3, 5] = float("nan")
+    mm[2, 7, 1] = float("inf")
+    w.molecule_map = mm.cuda()
+    w.diffuse_molecules()
+    out = w.molecule_map.cpu()
+    assert torch.isnan(out[0]).all() and torch.isnan(out[2]).all()
+    assert bits_equal(out[1], clean[1])

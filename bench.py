@@ -69,6 +69,8 @@ def parse_args():
     ap.add_argument("--scan-steps", type=int, default=5, help="steps timed with the list cache off (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--skew", type=float, default=0.0,
+                    help="N > 1: also time a run where rank 0 holds SKEW x the cells of every other rank (extra.density_skew)")
     ap.add_argument("--no-list-cache", action="store_true",
                     help="scan the dense parameter tiles in every step (Kinetics.list_cache = False)")
     ap.add_argument("--energies", default="modest", choices=["modest", "survey"],
@@ -527,6 +529,24 @@ def main():
                 "scaling": "strong", "ms_per_step": r2["ms_per_step"], "kernel_ms": r2["kernel_ms"],
                 "value": args.cells / (r2["ms_per_step"] / 1e3), "unit": "cell-steps/s"}
             del w2
+    if args.skew > 1.0 and world_size > 1:
+        # cells live with their pixels, so a crowded slab is a slow rank: rank 0 gets SKEW x the cells
+        torch.cuda.empty_cache()
+        base = int(args.cells / args.skew)
+        n_mine = int(base * args.skew) if rank == 0 else base
+        w4, _ = build_world(n_mine, p, m, args.map, args.map, device, seed=200 + rank, world_size=world_size, erange=erange)
+        r4 = measure(w4, max(args.steps, 10), max(args.warmup, 3), barrier, device, world_size)
+        total = int(base * args.skew) + base * (world_size - 1)
+        w5, _ = build_world(total // world_size, p, m, args.map, args.map, device, seed=300 + rank, world_size=world_size,
+                            erange=erange)
+        r5 = measure(w5, max(args.steps, 10), max(args.warmup, 3), barrier, device, world_size)
+        extra["density_skew"] = {
+            "workload": f"rank 0: {int(base * args.skew)} cells, every other rank: {base} cells, {args.map}x{args.map} slab each",
+            "ms_per_step": r4["ms_per_step"], "value": total / (r4["ms_per_step"] / 1e3),
+            "balanced_ms_per_step": r5["ms_per_step"], "balanced_value": world_size * (total // world_size) / (r5["ms_per_step"] / 1e3),
+            "note": "the step takes as long as the fullest slab's cells; slabs have equal heights and cells are not "
+                    "rebalanced across ranks"}
+        del w4, w5
     if not args.no_extra and world_size == 1 and args.config == "c4":
         del world, pop
         torch.cuda.empty_cache()

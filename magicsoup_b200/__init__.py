@@ -7,3 +7,6 @@ from magicsoup_b200.kinetics import Kinetics  # noqa: F401
 from magicsoup_b200.world import World, Molecule, Chemistry  # noqa: F401
 
 __version__ = "0.1.0"
+from magicsoup_b200.genetics import Genetics  # noqa: F401,E402
+from magicsoup_b200.mutations import point_mutations, recombinations  # noqa: F401,E402
+from magicsoup_b200.util import random_genome, randstr, variants, codons  # noqa: F401,E402

@@ -61,6 +61,46 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB
 
 
+# ---------------------------------------------------------------- host helpers (_lib, C++ / pybind11)
+def lib_path() -> Path:
+    import sysconfig
+
+    return HERE / ("_lib" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
+
+
+LIB_STAMP = HERE / "_lib.srchash"
+
+
+def _lib_hash() -> str:
+    import hashlib
+
+    return hashlib.sha256((CSRC / "lib_host.cpp").read_bytes()).hexdigest()
+
+
+def build_host_lib(force: bool = False) -> Path:
+    """magicsoup_b200._lib: the interface of the reference's Rust extension, in C++ (g++, pybind11, OpenMP)"""
+    import sys
+
+    out = lib_path()
+    if not force and out.exists() and LIB_STAMP.exists() and LIB_STAMP.read_text().strip() == _lib_hash():
+        return out
+    import pybind11
+    import sysconfig
+
+    cxx = shutil.which("g++")
+    if cxx is None:
+        raise RuntimeError("g++ not found")
+    cmd = [cxx, "-O2", "-std=c++17", "-shared", "-fPIC", "-fopenmp", "-fvisibility=hidden",
+           f"-I{pybind11.get_include()}", f"-I{sysconfig.get_paths()['include']}",
+           str(CSRC / "lib_host.cpp"), "-o", str(out)]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + res.stdout + res.stderr)
+    LIB_STAMP.write_text(_lib_hash())
+    return out
+
+
 if __name__ == "__main__":
     import sys
     print(build(force=True, verbose="-v" in sys.argv))
+    print(build_host_lib(force=True))

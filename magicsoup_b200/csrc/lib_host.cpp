@@ -1,0 +1,461 @@
+// magicsoup_b200._lib -- host-side helpers with the interface of the reference's Rust extension
+// `magicsoup._lib` (mRcSchwering/magic-soup 1.0.5, rust/lib.rs:18-176): genome translation, point
+// mutations and recombinations on strings, and the neighbourhood / division / movement searches on
+// the cell map.  C++17 + pybind11, OpenMP over genomes, the GIL released while working.
+//
+// Not a translation of the Rust sources: the map searches use an occupancy grid (hash of pixel ->
+// cells), so a query costs O(1) instead of the reference's linear scans over all positions
+// (rust/world.rs:9-146, rust/util.rs:45-64: O(n^2) per call), and coding regions are found with
+// per-frame stacks over a 2-bit codon code instead of string compares.  Same results for the same
+// inputs wherever the reference is deterministic; where it draws random numbers (choice of a free
+// pixel, mutations) the distributions are the same and `seed()` makes them reproducible, which
+// the reference's thread_rng is not.
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <algorithm>
+#include <array>
+#include <cstdint>
+#include <mutex>
+#include <random>
+#include <string>
+#include <tuple>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+
+namespace py = pybind11;
+
+namespace {
+
+constexpr size_t CODON = 3;
+
+using DomainSpec = std::tuple<std::tuple<int, int, int, int, int>, size_t, size_t>;
+using ProteinSpec = std::tuple<std::vector<DomainSpec>, size_t, size_t, bool>;
+using Cds = std::tuple<size_t, size_t, bool>;
+using Pos = std::pair<uint16_t, uint16_t>;
+
+// ---------------------------------------------------------------------------- random numbers
+std::mutex g_rng_mutex;
+std::mt19937_64 g_rng{std::random_device{}()};
+
+uint64_t next_seed() {
+  std::lock_guard<std::mutex> lock(g_rng_mutex);
+  return g_rng();
+}
+
+// ---------------------------------------------------------------------------- genetics
+// nucleotide -> 2 bits (anything else: 4, never part of a known codon)
+inline unsigned nt_code(char c) {
+  switch (c) {
+    case 'T': return 0;
+    case 'C': return 1;
+    case 'G': return 2;
+    case 'A': return 3;
+    default: return 4;
+  }
+}
+
+// codon membership table over the 64 codon codes
+std::array<bool, 64> codon_table(const std::vector<std::string> &codons) {
+  std::array<bool, 64> t{};
+  for (const auto &c : codons) {
+    if (c.size() != CODON) continue;
+    const unsigned a = nt_code(c[0]), b = nt_code(c[1]), d = nt_code(c[2]);
+    if (a < 4 && b < 4 && d < 4) t[a * 16 + b * 4 + d] = true;
+  }
+  return t;
+}
+
+// rust/genetics.rs:13-50: every start codon opens a CDS in its frame, the first in-frame stop
+// codon closes all CDSs open in that frame (most recent first); CDSs shorter than min_size are
+// dropped, unstopped ones too.  One pass, a rolling 6-bit codon code.
+std::vector<Cds> coding_regions(const std::string &seq, size_t min_size, const std::array<bool, 64> &starts,
+                                const std::array<bool, 64> &stops, bool is_fwd) {
+  std::vector<Cds> out;
+  const size_t n = seq.size();
+  if (n < min_size || n < CODON) return out;
+  std::array<std::vector<size_t>, 3> open;
+  unsigned code = 0, bad = 0;  // bad: how many of the last 3 characters are not nucleotides
+  for (size_t j = 0; j < n; j++) {
+    const unsigned c = nt_code(seq[j]);
+    code = ((code << 2) | (c & 3u)) & 63u;
+    bad = ((bad << 1) | (c > 3 ? 1u : 0u)) & 7u;
+    if (j + 1 < CODON || bad) continue;
+    const size_t i = j + 1 - CODON, frame = i % CODON;
+    if (starts[code]) {
+      open[frame].push_back(i);
+    } else if (stops[code]) {
+      auto &st = open[frame];
+      while (!st.empty()) {
+        const size_t d = st.back();
+        st.pop_back();
+        if (j + 1 - d >= min_size) out.emplace_back(d, j + 1, is_fwd);
+      }
+    }
+  }
+  return out;
+}
+
+struct CodonMaps {
+  std::unordered_map<std::string, int> dom_type, one, two;
+};
+
+// rust/genetics.rs:58-123: walk each CDS; a known domain-type prefix consumes a whole domain
+// (type, 3 one-codon tokens, 1 two-codon token), anything else one codon; proteins without a
+// catalytic or transporter domain are dropped
+std::vector<ProteinSpec> domains_of(const std::string &genome, const std::vector<Cds> &cdss, size_t dom_size,
+                                    size_t dom_type_size, const CodonMaps &maps) {
+  std::vector<ProteinSpec> out;
+  out.reserve(cdss.size());
+  for (const auto &[cds_start, cds_stop, is_fwd] : cdss) {
+    const size_t n = cds_stop - cds_start;
+    std::vector<DomainSpec> doms;
+    bool useful = false;
+    size_t i = 0;
+    while (i + dom_size <= n) {
+      const size_t d0 = cds_start + i;
+      auto it = maps.dom_type.find(genome.substr(d0, dom_type_size));
+      if (it == maps.dom_type.end()) {
+        i += CODON;
+        continue;
+      }
+      const int type = it->second;
+      if (type != 3) useful = true;  // 1 = catalytic, 2 = transporter, 3 = regulatory
+      const size_t t0 = d0 + dom_type_size;
+      const auto tok1 = [&](size_t k) -> int {
+        auto f = maps.one.find(genome.substr(t0 + k * CODON, CODON));
+        if (f == maps.one.end()) throw std::runtime_error("Incomplete one_codon_map");
+        return f->second;
+      };
+      auto f2 = maps.two.find(genome.substr(t0 + 3 * CODON, 2 * CODON));
+      if (f2 == maps.two.end()) throw std::runtime_error("Incomplete two_codon_map");
+      doms.emplace_back(std::make_tuple(type, tok1(0), tok1(1), tok1(2), f2->second), i, i + dom_size);
+      i += dom_size;
+    }
+    if (useful) out.emplace_back(std::move(doms), cds_start, cds_stop, is_fwd);
+  }
+  return out;
+}
+
+std::string reverse_complement(const std::string &seq) {
+  std::string out;
+  out.reserve(seq.size());
+  for (auto it = seq.rbegin(); it != seq.rend(); ++it) {
+    switch (*it) {
+      case 'A': out.push_back('T'); break;
+      case 'C': out.push_back('G'); break;
+      case 'T': out.push_back('A'); break;
+      case 'G': out.push_back('C'); break;
+      default: break;  // dropped, like the reference
+    }
+  }
+  return out;
+}
+
+std::vector<std::vector<ProteinSpec>> translate_genomes(const std::vector<std::string> &genomes,
+                                                        const std::vector<std::string> &start_codons,
+                                                        const std::vector<std::string> &stop_codons,
+                                                        const CodonMaps &maps, size_t dom_size,
+                                                        size_t dom_type_size) {
+  const auto starts = codon_table(start_codons), stops = codon_table(stop_codons);
+  std::vector<std::vector<ProteinSpec>> out(genomes.size());
+  std::string error;
+#pragma omp parallel for schedule(dynamic, 16)
+  for (long long g = 0; g < (long long)genomes.size(); g++) {
+    try {
+      const std::string &fwd = genomes[g];
+      auto prots = domains_of(fwd, coding_regions(fwd, dom_size, starts, stops, true), dom_size, dom_type_size, maps);
+      const std::string bwd = reverse_complement(fwd);
+      auto more = domains_of(bwd, coding_regions(bwd, dom_size, starts, stops, false), dom_size, dom_type_size, maps);
+      prots.insert(prots.end(), std::make_move_iterator(more.begin()), std::make_move_iterator(more.end()));
+      out[g] = std::move(prots);
+    } catch (const std::exception &e) {
+#pragma omp critical
+      error = e.what();
+    }
+  }
+  if (!error.empty()) throw std::runtime_error(error);
+  return out;
+}
+
+// ---------------------------------------------------------------------------- mutations
+const char NTS[4] = {'A', 'C', 'T', 'G'};
+
+// k distinct indices out of n, ascending
+std::vector<size_t> sample_sorted(std::mt19937_64 &rng, size_t n, size_t k) {
+  std::vector<size_t> idx;
+  if (k * 4 >= n) {  // dense: partial shuffle
+    std::vector<size_t> all(n);
+    for (size_t i = 0; i < n; i++) all[i] = i;
+    for (size_t i = 0; i < k; i++) std::swap(all[i], all[i + std::uniform_int_distribution<size_t>(0, n - 1 - i)(rng)]);
+    idx.assign(all.begin(), all.begin() + k);
+  } else {  // sparse: rejection
+    std::unordered_set<size_t> seen;
+    std::uniform_int_distribution<size_t> pick(0, n - 1);
+    while (seen.size() < k) seen.insert(pick(rng));
+    idx.assign(seen.begin(), seen.end());
+  }
+  std::sort(idx.begin(), idx.end());
+  return idx;
+}
+
+size_t poisson_count(std::mt19937_64 &rng, double lambda, size_t cap) {
+  if (!(lambda > 0.0)) return 0;
+  const size_t n = (size_t)std::poisson_distribution<long long>(lambda)(rng);
+  return std::min(n, cap);
+}
+
+// rust/mutations.rs:11-72: Poisson(p * len) positions; each an indel with p_indel (deletion with
+// p_del, else insertion of a random nucleotide before it), else a substitution
+std::vector<std::pair<std::string, size_t>> point_mutations(const std::vector<std::string> &seqs, double p,
+                                                            double p_indel, double p_del) {
+  const uint64_t seed = next_seed();
+  std::vector<std::string> mutated(seqs.size());
+  std::vector<char> hit(seqs.size(), 0);
+#pragma omp parallel for schedule(dynamic, 64)
+  for (long long s = 0; s < (long long)seqs.size(); s++) {
+    const std::string &src = seqs[s];
+    if (src.empty()) continue;
+    std::mt19937_64 rng(seed ^ (0x9e3779b97f4a7c15ull * (uint64_t)(s + 1)));
+    const size_t n_muts = poisson_count(rng, p * (double)src.size(), src.size());
+    if (n_muts == 0) continue;
+    const auto where = sample_sorted(rng, src.size(), n_muts);
+    std::bernoulli_distribution indel(std::clamp(p_indel, 0.0, 1.0)), del(std::clamp(p_del, 0.0, 1.0));
+    std::uniform_int_distribution<int> nt(0, 3);
+    std::string out;
+    out.reserve(src.size() + n_muts);
+    size_t next = 0;
+    for (size_t i = 0; i < src.size(); i++) {
+      if (next < where.size() && where[next] == i) {
+        next++;
+        if (indel(rng)) {
+          if (del(rng)) continue;          // deletion
+          out.push_back(NTS[nt(rng)]);     // insertion before position i
+          out.push_back(src[i]);
+        } else {
+          out.push_back(NTS[nt(rng)]);     // substitution (may draw the same nucleotide, like the reference)
+        }
+      } else {
+        out.push_back(src[i]);
+      }
+    }
+    mutated[s] = std::move(out);
+    hit[s] = 1;
+  }
+  std::vector<std::pair<std::string, size_t>> res;
+  for (size_t s = 0; s < seqs.size(); s++)
+    if (hit[s]) res.emplace_back(std::move(mutated[s]), s);
+  return res;
+}
+
+// rust/mutations.rs:78-154: Poisson(p * (n0 + n1)) strand breaks over both sequences, the
+// fragments are shuffled and re-joined into two sequences at a random cut of the fragment list
+std::vector<std::tuple<std::string, std::string, size_t>> recombinations(
+    const std::vector<std::pair<std::string, std::string>> &pairs, double p) {
+  const uint64_t seed = next_seed();
+  std::vector<std::tuple<std::string, std::string, size_t>> slots(pairs.size());
+  std::vector<char> hit(pairs.size(), 0);
+#pragma omp parallel for schedule(dynamic, 64)
+  for (long long s = 0; s < (long long)pairs.size(); s++) {
+    const std::string &a = pairs[s].first, &b = pairs[s].second;
+    const size_t n0 = a.size(), n_both = a.size() + b.size();
+    if (n_both == 0) continue;
+    std::mt19937_64 rng(seed ^ (0xd1b54a32d192ed03ull * (uint64_t)(s + 1)));
+    const size_t n_breaks = poisson_count(rng, p * (double)n_both, n_both);
+    if (n_breaks == 0) continue;
+    const auto where = sample_sorted(rng, n_both, n_breaks);
+    std::vector<std::string> parts;
+    parts.reserve(n_breaks + 2);
+    size_t i = 0, k = 0;
+    for (; k < where.size() && where[k] < n0; k++) {
+      parts.push_back(a.substr(i, where[k] - i));
+      i = where[k];
+    }
+    parts.push_back(a.substr(i));
+    i = 0;
+    for (; k < where.size(); k++) {
+      parts.push_back(b.substr(i, where[k] - n0 - i));
+      i = where[k] - n0;
+    }
+    parts.push_back(b.substr(i));
+    std::shuffle(parts.begin(), parts.end(), rng);
+    const size_t cut = std::uniform_int_distribution<size_t>(0, parts.size() - 1)(rng);
+    std::string x, y;
+    for (size_t q = 0; q < parts.size(); q++) (q < cut ? x : y) += parts[q];
+    slots[s] = std::make_tuple(std::move(x), std::move(y), (size_t)s);
+    hit[s] = 1;
+  }
+  std::vector<std::tuple<std::string, std::string, size_t>> res;
+  for (size_t s = 0; s < pairs.size(); s++)
+    if (hit[s]) res.push_back(std::move(slots[s]));
+  return res;
+}
+
+// ---------------------------------------------------------------------------- world
+inline uint32_t pixel_key(uint16_t x, uint16_t y) { return ((uint32_t)x << 16) | y; }
+
+uint16_t dist_1d(uint16_t a, uint16_t b, uint16_t m) {
+  const uint16_t hi = std::max(a, b), lo = std::min(a, b);
+  const uint16_t d0 = hi - lo, d1 = (uint16_t)(m - hi + lo);
+  return std::min(d0, d1);
+}
+
+// rust/util.rs:27-43: W-N, W, W-S, N, S, E-N, E, E-S with "east" = x + 1, "south" = y + 1
+std::array<Pos, 8> moore(uint16_t x, uint16_t y, uint16_t m) {
+  const uint16_t e = (uint16_t)(x + 1 == m ? 0 : x + 1), w = (uint16_t)(x == 0 ? m - 1 : x - 1);
+  const uint16_t s = (uint16_t)(y + 1 == m ? 0 : y + 1), n = (uint16_t)(y == 0 ? m - 1 : y - 1);
+  return {{{w, n}, {w, y}, {w, s}, {x, n}, {x, s}, {e, n}, {e, y}, {e, s}}};
+}
+
+std::vector<Pos> free_moores_nghbhd(uint16_t x, uint16_t y, const std::vector<Pos> &positions, uint16_t map_size) {
+  std::unordered_set<uint32_t> occ;
+  occ.reserve(positions.size() * 2);
+  for (const auto &p : positions) occ.insert(pixel_key(p.first, p.second));
+  std::vector<Pos> out;
+  for (const auto &p : moore(x, y, map_size))
+    if (!occ.count(pixel_key(p.first, p.second))) out.push_back(p);
+  return out;
+}
+
+// rust/world.rs:9-56: unique pairs (smaller index first) of cells from `from_idxs` and `to_idxs` at
+// torus distance <= 1 in both coordinates, in the reference's order (from_idxs order, then
+// to_idxs order, first occurrence kept)
+std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &from_idxs,
+                                                     const std::vector<size_t> &to_idxs,
+                                                     const std::vector<Pos> &positions, uint16_t map_size) {
+  std::unordered_map<uint32_t, std::vector<size_t>> grid;  // pixel -> ranks in to_idxs
+  grid.reserve(to_idxs.size() * 2);
+  for (size_t r = 0; r < to_idxs.size(); r++) {
+    const Pos &p = positions.at(to_idxs[r]);
+    grid[pixel_key(p.first, p.second)].push_back(r);
+  }
+  std::vector<std::pair<size_t, size_t>> out;
+  std::unordered_set<uint64_t> seen;
+  std::vector<size_t> ranks;
+  for (const size_t from : from_idxs) {
+    const Pos &p0 = positions.at(from);
+    ranks.clear();
+    std::unordered_set<uint32_t> pixels;  // the 3 x 3 block, without duplicates on tiny maps
+    pixels.insert(pixel_key(p0.first, p0.second));
+    for (const auto &p : moore(p0.first, p0.second, map_size)) pixels.insert(pixel_key(p.first, p.second));
+    for (const uint32_t key : pixels) {
+      auto it = grid.find(key);
+      if (it != grid.end()) ranks.insert(ranks.end(), it->second.begin(), it->second.end());
+    }
+    std::sort(ranks.begin(), ranks.end());
+    for (const size_t r : ranks) {
+      const size_t to = to_idxs[r];
+      if (to == from) continue;
+      const size_t a = std::min(from, to), b = std::max(from, to);
+      if (seen.insert(((uint64_t)a << 32) | (uint64_t)b).second) out.emplace_back(a, b);
+    }
+  }
+  return out;
+}
+
+// rust/world.rs:59-99: in the order of cell_idxs, every cell picks one free Moore pixel at random
+// (free of all current cells and of the children placed before it); children get indices n_cells..
+std::tuple<std::vector<size_t>, std::vector<size_t>, std::vector<Pos>> divide_cells_if_possible(
+    const std::vector<size_t> &cell_idxs, const std::vector<Pos> &positions, size_t n_cells, uint16_t map_size) {
+  std::unordered_set<uint32_t> occ;
+  occ.reserve((positions.size() + cell_idxs.size()) * 2);
+  for (const auto &p : positions) occ.insert(pixel_key(p.first, p.second));
+  std::mt19937_64 rng(next_seed());
+  std::vector<size_t> parents, children;
+  std::vector<Pos> child_pos;
+  size_t next = n_cells;
+  for (const size_t idx : cell_idxs) {
+    const Pos &p0 = positions.at(idx);
+    std::vector<Pos> opts;
+    for (const auto &p : moore(p0.first, p0.second, map_size))
+      if (!occ.count(pixel_key(p.first, p.second))) opts.push_back(p);
+    if (opts.empty()) continue;
+    const Pos pick = opts[std::uniform_int_distribution<size_t>(0, opts.size() - 1)(rng)];
+    occ.insert(pixel_key(pick.first, pick.second));
+    parents.push_back(idx);
+    children.push_back(next++);
+    child_pos.push_back(pick);
+  }
+  return {parents, children, child_pos};
+}
+
+// rust/world.rs:102-146: in the order of cell_idxs, every cell moves to one free Moore pixel at
+// random: free of the cells that do not move and of the moving cells' current pixels
+std::tuple<std::vector<Pos>, std::vector<size_t>> move_cells(const std::vector<size_t> &cell_idxs,
+                                                             const std::vector<Pos> &positions,
+                                                             uint16_t map_size) {
+  std::unordered_map<uint32_t, int> occ;  // pixel -> number of cells on it (all cells, current positions)
+  occ.reserve(positions.size() * 2);
+  for (const auto &p : positions) occ[pixel_key(p.first, p.second)]++;
+  std::mt19937_64 rng(next_seed());
+  std::vector<Pos> new_pos;
+  std::vector<size_t> moved;
+  for (const size_t idx : cell_idxs) {
+    const Pos p0 = positions.at(idx);
+    std::vector<Pos> opts;
+    for (const auto &p : moore(p0.first, p0.second, map_size)) {
+      auto it = occ.find(pixel_key(p.first, p.second));
+      if (it == occ.end() || it->second == 0) opts.push_back(p);
+    }
+    if (opts.empty()) continue;
+    const Pos pick = opts[std::uniform_int_distribution<size_t>(0, opts.size() - 1)(rng)];
+    occ[pixel_key(p0.first, p0.second)]--;
+    occ[pixel_key(pick.first, pick.second)]++;
+    new_pos.push_back(pick);
+    moved.push_back(idx);
+  }
+  return {new_pos, moved};
+}
+
+CodonMaps make_maps(const std::unordered_map<std::string, int> &dom_type, const std::unordered_map<std::string, int> &one,
+                    const std::unordered_map<std::string, int> &two) {
+  return CodonMaps{dom_type, one, two};
+}
+
+}  // namespace
+
+PYBIND11_MODULE(_lib, m) {
+  m.doc() = "host-side helpers with the interface of magicsoup._lib (C++17, pybind11)";
+  m.def("seed", [](uint64_t s) {
+    std::lock_guard<std::mutex> lock(g_rng_mutex);
+    g_rng.seed(s);
+  }, py::arg("seed"), "seed the generator behind the random choices (the reference's is not seedable)");
+  m.def("dist_1d", &dist_1d, py::arg("a"), py::arg("b"), py::arg("m"));
+  m.def("free_moores_nghbhd", &free_moores_nghbhd, py::arg("x"), py::arg("y"), py::arg("positions"), py::arg("map_size"));
+  m.def("point_mutations", &point_mutations, py::arg("seqs"), py::arg("p"), py::arg("p_indel"), py::arg("p_del"),
+        py::call_guard<py::gil_scoped_release>());
+  m.def("recombinations", &recombinations, py::arg("seq_pairs"), py::arg("p"), py::call_guard<py::gil_scoped_release>());
+  m.def("get_coding_regions",
+        [](const std::string &seq, size_t min_cds_size, const std::vector<std::string> &start_codons,
+           const std::vector<std::string> &stop_codons, bool is_fwd) {
+          return coding_regions(seq, min_cds_size, codon_table(start_codons), codon_table(stop_codons), is_fwd);
+        },
+        py::arg("seq"), py::arg("min_cds_size"), py::arg("start_codons"), py::arg("stop_codons"), py::arg("is_fwd"));
+  m.def("extract_domains",
+        [](const std::string &genome, const std::vector<Cds> &cdss, size_t dom_size, size_t dom_type_size,
+           const std::unordered_map<std::string, int> &dom_type_map, const std::unordered_map<std::string, int> &one_codon_map,
+           const std::unordered_map<std::string, int> &two_codon_map) {
+          return domains_of(genome, cdss, dom_size, dom_type_size, make_maps(dom_type_map, one_codon_map, two_codon_map));
+        },
+        py::arg("genome"), py::arg("cdss"), py::arg("dom_size"), py::arg("dom_type_size"), py::arg("dom_type_map"),
+        py::arg("one_codon_map"), py::arg("two_codon_map"));
+  m.def("reverse_complement", &reverse_complement, py::arg("seq"));
+  m.def("translate_genomes",
+        [](const std::vector<std::string> &genomes, const std::vector<std::string> &start_codons,
+           const std::vector<std::string> &stop_codons, const std::unordered_map<std::string, int> &domain_map,
+           const std::unordered_map<std::string, int> &one_codon_map,
+           const std::unordered_map<std::string, int> &two_codon_map, size_t dom_size, size_t dom_type_size) {
+          const CodonMaps maps = make_maps(domain_map, one_codon_map, two_codon_map);
+          py::gil_scoped_release release;
+          return translate_genomes(genomes, start_codons, stop_codons, maps, dom_size, dom_type_size);
+        },
+        py::arg("genomes"), py::arg("start_codons"), py::arg("stop_codons"), py::arg("domain_map"),
+        py::arg("one_codon_map"), py::arg("two_codon_map"), py::arg("dom_size"), py::arg("dom_type_size"));
+  m.def("get_neighbors", &get_neighbors, py::arg("from_idxs"), py::arg("to_idxs"), py::arg("positions"),
+        py::arg("map_size"), py::call_guard<py::gil_scoped_release>());
+  m.def("divide_cells_if_possible", &divide_cells_if_possible, py::arg("cell_idxs"), py::arg("positions"),
+        py::arg("n_cells"), py::arg("map_size"), py::call_guard<py::gil_scoped_release>());
+  m.def("move_cells", &move_cells, py::arg("cell_idxs"), py::arg("positions"), py::arg("map_size"),
+        py::call_guard<py::gil_scoped_release>());
+}

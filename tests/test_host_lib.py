@@ -1,0 +1,204 @@
+"""
+CPU tests of magicsoup_b200._lib (C++ / pybind11, csrc/lib_host.cpp), the counterpart of the
+reference's Rust extension (rust/lib.rs:18-176), and of the Genetics / util / mutations modules on
+top of it.  Golden vectors are the ones the reference's own tests hold
+(/root/reference/tests/fast/test_genetics.py:10-201, test_util.py:95-125, test_world.py:650-732);
+random inputs are checked against the plain restatements in oracle/host_oracle.py.
+"""
+import random
+from collections import Counter
+
+import pytest
+
+import magicsoup_b200 as ms
+from magicsoup_b200 import mutations, util
+from magicsoup_b200._hostlib import lib
+from magicsoup_b200.genetics import Genetics
+from oracle import host_oracle as HO
+
+STARTS, STOPS = ["TTG", "GTG", "ATG"], ["TGA", "TAG", "TAA"]
+
+# (genome, [(start, stop)]), min CDS size 18 -- test_genetics.py:10-59
+_CDS = [
+    ("""TACCGGATA GCAGCTTTT CTTGGAATA GCCAAGGGT CGCCTTTAT ACCTATCTA CAACTACTA CTCGGTTGG
+        TAACAAAGG TTAAAACGC CAAACGAGT ATCGGCCAA TCCTGTCAC TGTGAGAAG TTTCAATTA TAGATTCCT
+        GGGGCGATT GGCGATGGT""", [(68, 122)]),
+    ("""AACATATCC ACCATCCCT TAAGGGGCG ATGAATTAC GAAAGCGGG CGTACTACT TCTGGGGAT ACGATTAGT
+        GTACTCGGT TCTCTTAAC GACTACCCT GTGTTACGT TATTGAAAG AGCAAATTG CGAGCTCCC CGTGACACT
+        TGTGCGGCG CTATACACC CCTGCAGTT ATTTAAGGG CTTAGGCGA GAAGTTCCG CCTGCTAAG GAGTCCCTG
+        TTGGGTGAA GTAACGCAC AGCCAGGCC TTGGCAGGA CGTTTCCGT TCTCGT""",
+     [(27, 114), (70, 229), (110, 140), (123, 177), (136, 229), (143, 185), (145, 229)]),
+    ("TTGAAAGA GCAAATTT GA", [(0, 18)]),
+    ("GTGTGCTCG AAAGAGAAC GCAAATTCG TAACCTAG", [(0, 30), (2, 35)]),
+]
+
+
+def test_reverse_complement():
+    assert lib().reverse_complement("ACTGG") == "CCAGT"
+
+
+@pytest.mark.parametrize("seq, exp", _CDS)
+def test_get_coding_regions_golden(seq, exp):
+    seq = "".join(seq.split())
+    res = lib().get_coding_regions(seq, 18, STARTS, STOPS, False)
+    assert sorted((a, b) for a, b, _ in res) == sorted(exp)
+    assert all(f is False for _, _, f in res)
+    assert res == HO.get_coding_regions(seq, 18, STARTS, STOPS, False)  # same order as the reference's algorithm
+
+
+def test_extract_domains_golden():
+    # test_genetics.py:122-201
+    dom_type_map = {"AAA": 1, "GGG": 2, "CCC": 3}
+    two = {"ACTGAT": 1, "CTGTAT": 2, "CCGCGA": 3, "GGAATC": 4, "TGTCGA": 5}
+    one = {"ACT": 1, "CTG": 2, "CCG": 3, "GGA": 4, "TGT": 5}
+    genome = ("AGACAAAAACTGTGTACTCCGCGATAGACTAGACG" "AGACTATAGCTAGAAGCCCCTGTACTCCGTGTCGATAGACG"
+              "AGACTAGGGCCGGGACTGCCGCGACTAGAAGCTAGACTAACG" "AAACCGGGATGTCTGTAT" "CCCCCGGGACTGCCGCGAGGGACTCTGCCGGGAATC")
+    cdss = [(0, 35, True), (35, 76, False), (76, 118, True), (118, 136, False), (136, 172, True)]
+    res = lib().extract_domains(genome, cdss, 18, 3, dom_type_map, one, two)
+    assert [(r[1], r[2], r[3]) for r in res] == [(0, 35, True), (76, 118, True), (118, 136, False), (136, 172, True)]
+    assert [len(r[0]) for r in res] == [1, 1, 1, 2]
+    assert res[0][0][0] == ((1, 2, 5, 1, 3), 6, 24)
+    assert res[1][0][0] == ((2, 3, 4, 2, 3), 6, 24)
+    assert res[2][0][0] == ((1, 3, 4, 5, 2), 0, 18)
+    assert res[3][0][0] == ((3, 3, 4, 2, 3), 0, 18)
+    assert res[3][0][1] == ((2, 1, 2, 3, 4), 18, 36)
+    assert res == HO.extract_domains(genome, cdss, 18, 3, dom_type_map, one, two)
+
+
+def test_translate_genomes_matches_the_plain_restatement():
+    random.seed(5)
+    gen = Genetics()
+    genomes = [util.random_genome(s=random.choice([0, 10, 200, 500, 1000, 3000])) for _ in range(200)]
+    res = gen.translate_genomes(genomes)
+    assert len(res) == 200
+    n_prot = 0
+    for g, prots in zip(genomes, res):
+        exp = HO.translate_genome(g, gen.start_codons, gen.stop_codons, gen.domain_map, gen.one_codon_map,
+                                  gen.two_codon_map, gen.dom_size, gen.dom_type_size)
+        assert prots == exp
+        n_prot += len(prots)
+    assert n_prot > 100
+    assert gen.translate_genomes([]) == []
+
+
+def test_genetics_maps_and_domain_frequencies():
+    # genetics.py:104-122 and the reference's statistical check (test_genetics.py:204-246)
+    random.seed(1)
+    gen = Genetics(p_catal_dom=0.1, p_transp_dom=0.1, p_reg_dom=0.1)
+    assert len(gen.one_codon_map) == 61 and len(gen.two_codon_map) == 3904
+    assert set(gen.domain_map.values()) == {1, 2, 3} and gen.dom_size == 21 and gen.dom_type_size == 6
+    assert not any(c[:3] in gen.start_codons or c[3:] in gen.start_codons for c in gen.domain_map)
+    kinds = Counter()
+    for prots in gen.translate_genomes([util.random_genome(1000) for _ in range(300)]):
+        for doms, start, stop, _ in prots:
+            assert stop - start >= gen.dom_size and any(d[0][0] != 3 for d in doms)
+            kinds.update(d[0][0] for d in doms)
+    tot = sum(kinds.values())
+    assert all(0.2 < kinds[k] / tot < 0.5 for k in (1, 2, 3)), kinds
+    with pytest.warns(UserWarning):
+        Genetics(n_dom_type_codons=1)
+    with pytest.raises(ValueError):
+        Genetics(start_codons=("TTG",), stop_codons=("TTG",))
+
+
+@pytest.mark.parametrize("a, b, exp", [(0, 1, 1), (0, 2, 2), (0, 3, 2), (0, 4, 1), (0, 0, 0)])
+def test_dist_1d(a, b, exp):
+    assert util.dist_1d(a=a, b=b, m=5) == exp  # test_util.py:95-107
+
+
+@pytest.mark.parametrize("x, y, exp", [
+    (2, 2, [(1, 1), (1, 2), (1, 3), (3, 1), (3, 2), (3, 3), (2, 1), (2, 3)]),
+    (0, 0, [(4, 4), (4, 0), (4, 1), (1, 4), (1, 0), (1, 1), (0, 4), (0, 1)]),
+    (4, 4, [(3, 3), (3, 4), (3, 0), (0, 3), (0, 4), (0, 0), (4, 3), (4, 0)]),
+    (0, 4, [(4, 3), (4, 4), (4, 0), (1, 3), (1, 4), (1, 0), (0, 3), (0, 0)]),
+    (4, 0, [(3, 4), (4, 4), (0, 4), (3, 1), (4, 1), (0, 1), (3, 0), (0, 0)]),
+])
+def test_free_moores_nghbhd(x, y, exp):
+    res = util.free_moores_nghbhd(x=x, y=y, positions=[], map_size=5)  # test_util.py:110-125
+    assert res == HO.moores_nghbhd(x, y, 5) and set(res) == set(exp)
+    assert set(util.free_moores_nghbhd(x=x, y=y, positions=[res[0]], map_size=5)) == set(exp) - {res[0]}
+    assert util.free_moores_nghbhd(x=x, y=y, positions=res, map_size=5) == []
+
+
+def test_get_neighbors_golden_and_random():
+    # test_world.py:650-732
+    pos = [(1, 1), (1, 2), (0, 1), (2, 1), (8, 8), (0, 8), (2, 0), (8, 6), (8, 7)]
+    nghbrs = [{(0, 2), (0, 1), (0, 6), (0, 3)}, {(1, 2), (0, 1), (1, 3)}, {(0, 2), (1, 2)}, {(0, 3), (1, 3), (3, 6)},
+              {(4, 8), (4, 5)}, {(5, 8), (4, 5)}, {(0, 6), (3, 6)}, {(7, 8)}, {(7, 8), (4, 8), (5, 8)}]
+    everyone = list(range(9))
+    for i, exp in enumerate(nghbrs):
+        res = lib().get_neighbors([i], everyone, pos, 9)
+        assert len(res) == len(exp) and set(res) == exp
+    res = lib().get_neighbors([1, 4, 8], everyone, pos, 9)
+    assert len(res) == len(set(res)) and set(res) == nghbrs[1] | nghbrs[4] | nghbrs[8]
+    res = lib().get_neighbors([0, 3], [6, 2], pos, 9)
+    assert set(res) == {d for d in nghbrs[0] | nghbrs[3] if d[0] in (6, 2) or d[1] in (6, 2)}
+    rnd = random.Random(3)
+    for size in (2, 3, 7, 40):
+        cells = rnd.sample([(x, y) for x in range(size) for y in range(size)], k=min(size * size, 60))
+        frm = rnd.sample(range(len(cells)), k=max(1, len(cells) // 2))
+        to = rnd.sample(range(len(cells)), k=max(1, len(cells) * 2 // 3))
+        assert lib().get_neighbors(frm, to, cells, size) == HO.get_neighbors(frm, to, cells, size)
+
+
+def test_divide_and_move_keep_the_map_consistent():
+    rnd = random.Random(7)
+    lib().seed(11)
+    size = 12
+    cells = rnd.sample([(x, y) for x in range(size) for y in range(size)], k=90)
+    movers = sorted(rnd.sample(range(90), k=60))
+    parents, children, child_pos = lib().divide_cells_if_possible(movers, cells, 90, size)
+    assert children == list(range(90, 90 + len(parents))) and len(set(child_pos)) == len(child_pos)
+    assert not set(child_pos) & set(cells) and parents == [i for i in movers if i in set(parents)]
+    for p, c in zip(parents, child_pos):
+        assert c in HO.moores_nghbhd(*cells[p], size)
+    # a cell that is not divided had no free pixel left when its turn came
+    taken = set(cells)
+    for i in movers:
+        if i in parents:
+            taken.add(child_pos[parents.index(i)])
+        else:
+            assert all(q in taken for q in HO.moores_nghbhd(*cells[i], size))
+    new_pos, moved = lib().move_cells(movers, cells, size)
+    after = list(cells)
+    for i, q in zip(moved, new_pos):
+        assert q in HO.moores_nghbhd(*cells[i], size)
+        after[i] = q
+    assert len(set(after)) == 90 and moved == [i for i in movers if i in set(moved)]
+    # a full map: nobody divides, nobody moves
+    full = [(x, y) for x in range(4) for y in range(4)]
+    assert lib().divide_cells_if_possible(list(range(16)), full, 16, 4) == ([], [], [])
+    assert lib().move_cells(list(range(16)), full, 4) == ([], [])
+    # the choice among free pixels is uniform (reference: slice.choose, rust/world.rs:90)
+    seen = Counter(lib().divide_cells_if_possible([0], [(5, 5)], 1, 11)[2][0] for _ in range(1600))
+    assert len(seen) == 8 and min(seen.values()) > 120
+
+
+def test_point_mutations_and_recombinations_statistics():
+    # tests/fast/test_mutations.py, tests/slow/test_mutations.py: statistical, the generator is random
+    lib().seed(3)
+    seqs = [util.random_genome(1000) for _ in range(400)]
+    res = mutations.point_mutations(seqs, p=1e-3)
+    assert 200 < len(res) < 320  # P(no mutation) = exp(-1)
+    idxs = [i for _, i in res]
+    assert idxs == sorted(set(idxs)) and all(set(s) <= set("ACTG") for s, _ in res)
+    diffs = Counter(len(s) - 1000 for s, _ in res)
+    assert diffs[0] > 0 and sum(v for k, v in diffs.items() if k < 0) > sum(v for k, v in diffs.items() if k > 0)
+    assert mutations.point_mutations(seqs, p=0.0) == [] and mutations.point_mutations([], p=0.5) == []
+    only_sub = mutations.point_mutations(seqs, p=1e-2, p_indel=0.0)
+    assert len(only_sub) == 400 and all(len(s) == 1000 for s, _ in only_sub)
+    n_changed = sum(a != b for a, b in zip(only_sub[0][0], seqs[only_sub[0][1]]))
+    assert 1 <= n_changed <= 30
+    everything = mutations.point_mutations(["ACGT" * 5], p=10.0, p_indel=1.0, p_del=1.0)
+    assert everything == [("", 0)]  # more mutations than nucleotides: capped at one per nucleotide, all deleted
+    pairs = [(util.random_genome(500), util.random_genome(700)) for _ in range(300)]
+    rec = mutations.recombinations(pairs, p=1e-3)
+    assert 150 < len(rec) < 260  # P(no break) = exp(-1.2)
+    for a, b, i in rec:
+        assert len(a) + len(b) == 1200 and Counter(a + b) == Counter(pairs[i][0] + pairs[i][1])
+    assert mutations.recombinations(pairs, p=0.0) == [] and mutations.recombinations([], p=0.1) == []
+
+
+def test_package_surface():
+    assert ms.Genetics is Genetics and ms.random_genome is util.random_genome
+    assert ms.point_mutations is mutations.point_mutations and ms.recombinations is mutations.recombinations

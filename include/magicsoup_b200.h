@@ -139,6 +139,39 @@ int ms_enzymatic_activity_cached(const ms_kinetics_params *params, const ms_kine
                                  const int32_t *eq_iters_host, uint32_t *flags, void *scratch,
                                  size_t scratch_bytes, void *stream);
 
+/*
+ * Kinetics.set_cell_params(cell_idxs, proteomes)               kinetics.py:521-625
+ * Domain tokens -> the nine parameter tensors, written into the given parameter rows.
+ *   tables: the reference's token maps as device arrays: vmax_map.weights, km_map.weights
+ *     (float, NaN at token 0), sign_map.signs, hill_map.numbers (int32), reaction_map.M,
+ *     transport_map.M, effector_map.M (int32, (tokens, s), zero vector at token 0)
+ *     (kinetics.py:16-289, 418-449);
+ *   proteomes flattened (device, int32): rows[k] = parameter row of proteome k; its proteins are
+ *     prot_offsets[k] .. prot_offsets[k+1]; protein q's domains are dom_offsets[q] ..
+ *     dom_offsets[q+1]; doms[5*d ..] = (domain type, i0, i1, i2, i3) (constants.py:9);
+ *   every protein slot 0 .. p-1 of the rows is written (slots beyond a proteome get the
+ *     reference's padding: N = Nf = Nb = A = 0, Vmax = 0, Ke = 1, Kmf = Kmb = 1e-36, Kmr = 1).
+ * Integer results are exact; float results follow the reference's float32 formulas (the energy
+ * sum of kinetics.py:612 is accumulated in float64).  Tokens must index inside the tables.
+ */
+typedef struct ms_token_tables {
+  const float *vmax_weights, *km_weights;
+  const int32_t *signs, *hill_numbers;
+  const int32_t *reaction_M, *transport_M, *effector_M;
+} ms_token_tables;
+
+typedef struct ms_kinetics_params_out {
+  int32_t *N, *Nf, *Nb, *A; /* (rows,p,s) */
+  float *Kmr;               /* (rows,p,s) */
+  float *Ke, *Kmf, *Kmb, *Vmax; /* (rows,p) */
+  int64_t p, s;
+} ms_kinetics_params_out;
+
+int ms_set_cell_params(const ms_token_tables *tables, const float *mol_energies, float abs_temp,
+                       const int32_t *rows, const int32_t *prot_offsets, const int32_t *dom_offsets,
+                       const int32_t *doms, int64_t n_cells, const ms_kinetics_params_out *out,
+                       void *stream);
+
 /* Kinetics._multiply_signals(X, N) -> (xx (c,p), involved (c,p) as uint8)  kinetics.py:894-918 */
 int ms_multiply_signals(const float *X, const int32_t *K, int64_t c, int64_t p, int64_t s,
                         float *xx, uint8_t *involved, void *stream);

@@ -32,6 +32,19 @@ class KineticsCache(C.Structure):
     _fields_ = [("records", _vp), ("rec_words", _i64), ("row_map", _vp)]
 
 
+class TokenTables(C.Structure):
+    """struct ms_token_tables"""
+
+    _fields_ = [(k, _vp) for k in ("vmax_weights", "km_weights", "signs", "hill_numbers", "reaction_M", "transport_M",
+                                   "effector_M")]
+
+
+class KineticsParamsOut(C.Structure):
+    """struct ms_kinetics_params_out"""
+
+    _fields_ = [(k, _vp) for k in ("N", "Nf", "Nb", "A", "Kmr", "Ke", "Kmf", "Kmb", "Vmax")] + [("p", _i64), ("s", _i64)]
+
+
 _PP = C.POINTER(KineticsParams)
 _PC = C.POINTER(KineticsCache)
 _SIGNATURES = {
@@ -48,6 +61,8 @@ _SIGNATURES = {
     "ms_integrate_signals_cached": (C.c_int, [_PP, _PC, _vp, _vp, C.POINTER(_i32), _vp, _vp, _sz, _vp]),
     "ms_enzymatic_activity_cached": (C.c_int, [_PP, _PC, _vp, _vp, _vp, _i64, _i64, _i64, _vp, C.POINTER(_i32), _vp,
                                                _vp, _sz, _vp]),
+    "ms_set_cell_params": (C.c_int, [C.POINTER(TokenTables), _vp, C.c_float, _vp, _vp, _vp, _vp, _i64,
+                                     C.POINTER(KineticsParamsOut), _vp]),
     "ms_multiply_signals": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "ms_get_quotient": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
     "ms_get_velocities": (C.c_int, [_PP, _vp, _vp, _vp, _vp]),

@@ -10,6 +10,7 @@
 // inputs wherever the reference is deterministic; where it draws random numbers (choice of a free
 // pixel, mutations) the distributions are the same and `seed()` makes them reproducible, which
 // the reference's thread_rng is not.
+#include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
@@ -452,6 +453,26 @@ PYBIND11_MODULE(_lib, m) {
         },
         py::arg("genomes"), py::arg("start_codons"), py::arg("stop_codons"), py::arg("domain_map"),
         py::arg("one_codon_map"), py::arg("two_codon_map"), py::arg("dom_size"), py::arg("dom_type_size"));
+  m.def("flatten_proteomes",
+        [](const py::list &proteomes) {
+          // nested (proteome -> protein -> domain) lists of translate_genomes -> three int32 arrays:
+          // protein offsets per proteome, domain offsets per protein, (type, i0, i1, i2, i3) per domain
+          std::vector<int32_t> prot_off{0}, dom_off{0}, doms;
+          for (const auto &proteome : proteomes) {
+            for (const auto &protein : py::reinterpret_borrow<py::sequence>(proteome)) {
+              const auto prot = py::reinterpret_borrow<py::sequence>(protein);
+              for (const auto &dom : py::reinterpret_borrow<py::sequence>(prot[0])) {
+                const auto spec = py::reinterpret_borrow<py::sequence>(py::reinterpret_borrow<py::sequence>(dom)[0]);
+                for (int q = 0; q < 5; q++) doms.push_back(spec[q].cast<int32_t>());
+              }
+              dom_off.push_back((int32_t)(doms.size() / 5));
+            }
+            prot_off.push_back((int32_t)(dom_off.size() - 1));
+          }
+          auto arr = [](const std::vector<int32_t> &v) { return py::array_t<int32_t>(v.size(), v.data()); };
+          return py::make_tuple(arr(prot_off), arr(dom_off), arr(doms));
+        },
+        py::arg("proteomes"), "no counterpart in the reference (which pads nested lists into (c,p,d) tensors, kinetics.py:920-970)");
   m.def("get_neighbors", &get_neighbors, py::arg("from_idxs"), py::arg("to_idxs"), py::arg("positions"),
         py::arg("map_size"), py::call_guard<py::gil_scoped_release>());
   m.def("divide_cells_if_possible", &divide_cells_if_possible, py::arg("cell_idxs"), py::arg("positions"),

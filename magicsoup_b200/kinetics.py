@@ -29,6 +29,7 @@ from typing import Any, Sequence
 import torch
 
 from magicsoup_b200 import _native as nat
+from magicsoup_b200 import tokens as tk
 
 _EPS = 1e-36
 _MAX = 1e36
@@ -86,6 +87,19 @@ class Kinetics:
         self.mol_names = [d.name for d in molecules]
         self.mol_energies = torch.tensor([d.energy for d in molecules] * 2, dtype=torch.float32, device=device)
         n_signals = 2 * len(molecules)
+        # token maps (kinetics.py:418-449), drawn like the reference's; set_cell_params reads them
+        mol_2_idx = {d: i for i, d in enumerate(molecules)}
+        self.km_map = tk.LogNormWeightMap(max_token=scalar_enc_size, weight_range=km_range, device=device)
+        self.vmax_map = tk.LogNormWeightMap(max_token=scalar_enc_size, weight_range=vmax_range, device=device)
+        self.sign_map = tk.SignMap(max_token=scalar_enc_size, device=device)
+        self.hill_map = tk.HillMap(max_token=scalar_enc_size, device=device)
+        self.reaction_map = tk.VectorMap(
+            max_token=vector_enc_size, n_signals=n_signals, device=device,
+            vectors=tk.reaction_vectors(mol_2_idx, list(getattr(chemistry, "reactions", [])), n_signals))
+        self.transport_map = tk.VectorMap(max_token=vector_enc_size, n_signals=n_signals, device=device,
+                                          vectors=tk.transport_vectors(len(molecules)))
+        self.effector_map = tk.VectorMap(max_token=vector_enc_size, n_signals=n_signals, device=device,
+                                         vectors=tk.effector_vectors(len(molecules)))
         z_i = lambda: self._zeros_i32_tensor(0, 0, n_signals)  # noqa: E731
         z_f = lambda: self._zeros_f32_tensor(0, 0)  # noqa: E731
         self._buf: dict[str, torch.Tensor] = {
@@ -485,10 +499,53 @@ class Kinetics:
             self._stale(phys)
         self._stamp()
 
-    def set_cell_params(self, cell_idxs, proteomes):
-        raise NotImplementedError(
-            "genome -> parameter translation (reference kinetics.py:521-625) is host-side genetics "
-            "outside this package's hot path; use set_cell_params_from_tensors")
+    def set_cell_params(self, cell_idxs: list[int], proteomes: list):
+        """
+        kinetics.py:521-625: translate proteomes (Genetics.translate_genomes) into the nine parameter
+        tensors of the given cells.  One kernel launch (ms_set_cell_params) writes the cells' rows
+        from the flattened domain tokens and the token maps; nothing of size (c,p,d,s) is built.
+        """
+        if len(cell_idxs) == 0:
+            return
+        if len(cell_idxs) != len(proteomes):
+            raise ValueError("cell_idxs and proteomes differ in length")
+        from magicsoup_b200._hostlib import lib as hostlib
+
+        dev = self._cuda()
+        if not self._managed() or self._buf["N"].device != dev or not all(t.is_contiguous() for t in self._buf.values()):
+            self._materialize()
+            for k in _ALL_PARAMS:  # user-assigned or CPU tensors: adopt normalised device copies
+                t = self._view(k)
+                self._adopt(k, (self._i32(t, dev) if k in _INT_PARAMS else self._f32(t, dev)).clone())
+            if not self._managed():
+                raise ValueError("the parameter tensors do not describe the same cells; cannot set cell parameters")
+        prot_off, dom_off, doms = hostlib().flatten_proteomes(list(proteomes))
+        p, s = int(self._buf["N"].shape[1]), int(self._buf["N"].shape[2])
+        n_max = int((prot_off[1:] - prot_off[:-1]).max()) if len(prot_off) > 1 else 0
+        if n_max > p:
+            raise ValueError(f"a proteome has {n_max} proteins, the parameter tensors hold {p}: call increase_max_proteins first")
+        doms2 = doms.reshape(-1, 5)
+        tables = {"vmax_weights": self._f32(self.vmax_map.weights, dev), "km_weights": self._f32(self.km_map.weights, dev),
+                  "signs": self._i32(self.sign_map.signs, dev), "hill_numbers": self._i32(self.hill_map.numbers, dev),
+                  "reaction_M": self._i32(self.reaction_map.M, dev), "transport_M": self._i32(self.transport_map.M, dev),
+                  "effector_M": self._i32(self.effector_map.M, dev)}
+        if doms2.shape[0]:
+            n_scalar = min(int(tables[k].shape[0]) for k in ("vmax_weights", "km_weights", "signs", "hill_numbers"))
+            n_vector = min(int(tables[k].shape[0]) for k in ("reaction_M", "transport_M", "effector_M"))
+            if doms2.min() < 0 or doms2[:, 1:4].max() >= n_scalar or doms2[:, 4].max() >= n_vector:
+                raise IndexError("a domain token lies outside the token maps")
+        for k in ("reaction_M", "transport_M", "effector_M"):
+            if tables[k].dim() != 2 or int(tables[k].shape[1]) != s:
+                raise ValueError(f"{k} has shape {tuple(tables[k].shape)}, expected (tokens, {s})")
+        rows = self._phys(cell_idxs).to(torch.int32).contiguous()
+        d_prot, d_dom, d_doms = (torch.from_numpy(a).to(dev) for a in (prot_off, dom_off, doms))
+        energies = self._f32(self.mol_energies, dev)
+        tt = nat.TokenTables(**{k: nat.ptr(v) for k, v in tables.items()})
+        out = nat.KineticsParamsOut(**{k: nat.ptr(self._buf[k]) for k in _ALL_PARAMS}, p=p, s=s)
+        nat.check(nat.lib().ms_set_cell_params(
+            C.byref(tt), nat.ptr(energies), float(self.abs_temp), nat.ptr(rows), nat.ptr(d_prot), nat.ptr(d_dom),
+            nat.ptr(d_doms), len(cell_idxs), C.byref(out), nat.stream_ptr(dev)))
+        self._stale(rows.long())  # the kernel wrote the rows behind torch's back: no version stamp moved
 
     def unset_cell_params(self, cell_idxs: list[int]):
         """kinetics.py:627-644"""

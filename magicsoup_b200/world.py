@@ -31,6 +31,10 @@ from typing import Any
 import torch
 
 from magicsoup_b200 import _native as nat
+from magicsoup_b200._hostlib import lib as _hostlib
+from magicsoup_b200.genetics import Genetics
+from magicsoup_b200.mutations import point_mutations, recombinations
+from magicsoup_b200.util import randstr
 from magicsoup_b200.kinetics import Kinetics, _settle_early_exit, _ALL_PARAMS, _STAGE_METHODS
 
 
@@ -95,6 +99,7 @@ class World:
         self.start_codons = start_codons
         self.stop_codons = stop_codons
         self.kinetics = Kinetics(chemistry=chemistry, abs_temp=abs_temp, device=device)
+        self.genetics = Genetics(start_codons=start_codons, stop_codons=stop_codons)
 
         molecules = list(chemistry.molecules)
         self.n_molecules = len(molecules)
@@ -426,6 +431,152 @@ class World:
         self.cell_divisions[descendants] += 1
         self.cell_lifetimes[descendants] = 0
         return list(zip(parent_idxs, child_idxs))
+
+    # ------------------------------------------------------------------ genome-driven lifecycle
+    # (world.py:229-608, 689-745, 880-920; string and map searches in magicsoup_b200._lib)
+    def _positions_list(self) -> list[tuple[int, int]]:
+        return [(int(x), int(y)) for x, y in self.cell_positions.tolist()]
+
+    def _square_size(self) -> int:
+        if not isinstance(self.map_size, int):
+            raise ValueError("neighbour, division and movement searches need a square map (map_size: int)")
+        return self.map_size
+
+    def get_neighbors(self, cell_idxs: list[int], nghbr_idxs: list[int] | None = None) -> list[tuple[int, int]]:
+        """world.py:229-285: unique pairs (lower index first) of cells in each other's Moore neighbourhood"""
+        if len(cell_idxs) == 0:
+            return []
+        from_idxs = list(set(cell_idxs))
+        to_idxs = list(set(cell_idxs)) if nghbr_idxs is None else list(set(nghbr_idxs))
+        if len(to_idxs) == 0:
+            return []
+        return _hostlib().get_neighbors(from_idxs, to_idxs, self._positions_list(), self._square_size())
+
+    def spawn_cells(self, genomes: list[str]) -> list[int]:
+        """world.py:287-341: new cells on random free pixels, each takes half of its pixel's molecules"""
+        n = len(genomes)
+        if n == 0:
+            return []
+        free = self._find_free_random_positions(n_cells=n)
+        if free.size(0) == 0:
+            return []
+        if free.size(0) < n:
+            n = int(free.size(0))
+            genomes = random.sample(list(genomes), k=n)
+        pos = free[:n]
+        new_idxs = list(range(self.n_cells, self.n_cells + n))
+        self.n_cells += n
+        self.cell_genomes.extend(genomes)
+        self.cell_labels.extend(randstr(n=12) for _ in range(n))
+        self.cell_lifetimes = self._expand_c(self.cell_lifetimes, n)
+        self.cell_positions = self._expand_c(self.cell_positions, n)
+        self.cell_divisions = self._expand_c(self.cell_divisions, n)
+        self.cell_molecules = self._expand_c(self.cell_molecules, n)
+        self.kinetics.increase_max_cells(by_n=n)
+        xs, ys = pos[:, 0].long(), pos[:, 1].long()
+        self.cell_map[xs, ys] = True
+        self.cell_positions[new_idxs] = pos.to(self.cell_positions.device)
+        pickup = self.molecule_map[:, xs, ys] * 0.5
+        self.cell_molecules[new_idxs, :] += pickup.T.to(self.cell_molecules.device)
+        self.molecule_map[:, xs, ys] -= pickup
+        self._update_cell_params(genomes=list(genomes), idxs=new_idxs)
+        return new_idxs
+
+    def divide_cells(self, cell_idxs: list[int]) -> list[tuple[int, int]]:
+        """world.py:406-475: every cell with a free Moore pixel puts a clone there; (ancestor, new) pairs"""
+        if len(cell_idxs) == 0:
+            return []
+        parents, children, child_pos = _hostlib().divide_cells_if_possible(
+            list(set(cell_idxs)), self._positions_list(), self.n_cells, self._square_size())
+        if len(children) == 0:
+            return []
+        pos = torch.tensor(child_pos, dtype=torch.int32, device=self.cell_positions.device)
+        return self.divide_cells_at(list(parents), pos)
+
+    def update_cells(self, genome_idx_pairs: list[tuple[str, int]]):
+        """world.py:476-492: new genomes for existing cells, parameters re-derived"""
+        if len(genome_idx_pairs) == 0:
+            return
+        last = {}
+        for genome, idx in genome_idx_pairs:  # a cell named twice keeps its last genome, and the matching parameters
+            self.cell_genomes[idx] = genome
+            last[idx] = genome
+        self._update_cell_params(genomes=list(last.values()), idxs=list(last.keys()))
+
+    def move_cells(self, cell_idxs: list[int] | None = None):
+        """world.py:543-574: every cell steps onto a random free pixel of its Moore neighbourhood, if any"""
+        if cell_idxs is None:
+            cell_idxs = list(range(self.n_cells))
+        if len(cell_idxs) == 0:
+            return
+        new_pos, moved = _hostlib().move_cells(sorted(set(cell_idxs)), self._positions_list(), self._square_size())
+        if len(moved) == 0:
+            return
+        old = self.cell_positions[moved].long()
+        self.cell_map[old[:, 0], old[:, 1]] = False
+        new = torch.tensor(new_pos, dtype=torch.int32, device=self.cell_positions.device)
+        self.cell_map[new[:, 0].long(), new[:, 1].long()] = True
+        self.cell_positions[moved] = new
+
+    def reposition_cells(self, cell_idxs: list[int] | None = None):
+        """world.py:576-608: the cells are taken off the map and put on random free pixels"""
+        if cell_idxs is None:
+            cell_idxs = list(range(self.n_cells))
+        if len(cell_idxs) == 0:
+            return
+        cell_idxs = list(set(cell_idxs))
+        old = self.cell_positions[cell_idxs].long()
+        self.cell_map[old[:, 0], old[:, 1]] = False
+        new = self._find_free_random_positions(n_cells=len(cell_idxs))
+        self.cell_map[new[:, 0].long(), new[:, 1].long()] = True
+        self.cell_positions[cell_idxs] = new.to(self.cell_positions.device)
+
+    def mutate_cells(self, cell_idxs: list[int] | None = None, p: float = 1e-6, p_indel: float = 0.4, p_del: float = 0.66):
+        """world.py:689-714: point mutations in the genomes, parameters of the changed cells re-derived"""
+        if cell_idxs is None:
+            mutated = point_mutations(seqs=self.cell_genomes, p=p, p_indel=p_indel, p_del=p_del)
+            self.update_cells(genome_idx_pairs=mutated)
+        else:
+            seqs = [self.cell_genomes[d] for d in cell_idxs]
+            mutated = point_mutations(seqs=seqs, p=p, p_indel=p_indel, p_del=p_del)
+            self.update_cells(genome_idx_pairs=[(g, cell_idxs[i]) for g, i in mutated])
+
+    def recombinate_cells(self, cell_idxs: list[int] | None = None, p: float = 1e-7):
+        """world.py:716-745: recombinations between the genomes of neighbouring cells"""
+        if cell_idxs is None:
+            cell_idxs = list(range(self.n_cells))
+        if len(cell_idxs) == 0:
+            return
+        nghbrs = self.get_neighbors(cell_idxs=cell_idxs)
+        pairs = [(self.cell_genomes[a], self.cell_genomes[b]) for a, b in nghbrs]
+        changed = []
+        for g0, g1, idx in recombinations(seq_pairs=pairs, p=p):
+            a, b = nghbrs[idx]
+            changed += [(g0, a), (g1, b)]
+        self.update_cells(genome_idx_pairs=changed)
+
+    def _update_cell_params(self, genomes: list[str], idxs: list[int]):
+        """world.py:880-908: translate, unset cells without proteins, grow the protein axis, set the rest"""
+        proteomes = self.genetics.translate_genomes(genomes=genomes)
+        set_idxs, set_proteomes, unset_idxs = [], [], []
+        for idx, proteome in zip(idxs, proteomes):
+            if len(proteome) > 0:
+                set_idxs.append(idx)
+                set_proteomes.append(proteome)
+            else:
+                unset_idxs.append(idx)
+        if unset_idxs:
+            self.kinetics.unset_cell_params(cell_idxs=unset_idxs)
+        if not set_idxs:
+            return
+        self.kinetics.increase_max_proteins(max_n=max(len(p) for p in set_proteomes))
+        self.kinetics.set_cell_params(cell_idxs=set_idxs, proteomes=set_proteomes)
+
+    def _find_free_random_positions(self, n_cells: int) -> torch.Tensor:
+        """world.py:910-920: up to n_cells distinct free pixels, int32 (n,2)"""
+        pxls = torch.nonzero(~self.cell_map).int()
+        n = min(n_cells, int(pxls.size(0)))
+        return pxls[random.sample(range(int(pxls.size(0))), k=n)]
 
     # ------------------------------------------------------------------ helpers
     def _get_molecule_map(self, n: int, size, init: str) -> torch.Tensor:

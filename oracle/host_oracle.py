@@ -92,3 +92,61 @@ def get_neighbors(from_idxs, to_idxs, positions, map_size):
                 if pair not in out:
                     out.append(pair)
     return out
+
+
+def set_cell_params(prot_off, dom_off, doms, tables, mol_energies, abs_temp, p, s):
+    """
+    Kinetics.set_cell_params (python/magicsoup/kinetics.py:521-625) as plain loops over the
+    flattened domain tokens; returns the nine (c,p[,s]) arrays.  Means are sum / count in
+    float32 in domain order, the energy sum in float64 (as the CUDA kernel does).
+    """
+    import numpy as np
+
+    f32 = np.float32
+    c = len(prot_off) - 1
+    doms = np.asarray(doms).reshape(-1, 5)
+    out = {k: np.zeros((c, p, s), dtype=np.int32) for k in ("N", "Nf", "Nb", "A")}
+    out["Kmr"] = np.ones((c, p, s), dtype=f32)
+    out.update(Ke=np.ones((c, p), f32), Kmf=np.full((c, p), 1e-36, f32), Kmb=np.full((c, p), 1e-36, f32),
+               Vmax=np.zeros((c, p), f32))
+    R = f32(8.31446261815324)
+    with np.errstate(all="ignore"):
+        for k in range(c):
+            for j, q in enumerate(range(prot_off[k], prot_off[k + 1])):
+                vs, ks = [], []
+                N = np.zeros(s, np.int32); Nf = np.zeros(s, np.int32); Nb = np.zeros(s, np.int32)
+                Af = np.zeros(s, f32); rsum = np.zeros(s, f32); rcnt = np.zeros(s, np.int32)
+                for dt, i0, i1, i2, i3 in doms[dom_off[q]:dom_off[q + 1]]:
+                    reg = dt == 3
+                    vm = tables["vmax_weights"][0 if reg else i0]
+                    km = tables["km_weights"][i1]
+                    if not np.isnan(vm):
+                        vs.append(vm)
+                    if not reg and not np.isnan(km):
+                        ks.append(km)
+                    sign = int(tables["signs"][i2])
+                    nd = (tables["reaction_M"][i3 if dt == 1 else 0] + tables["transport_M"][i3 if dt == 2 else 0]) * sign
+                    N += nd; Nf += np.where(nd < 0, -nd, 0); Nb += np.where(nd > 0, nd, 0)
+                    eff = tables["effector_M"][i3 if reg else 0].astype(f32)
+                    hill = int(tables["hill_numbers"][i0 if reg else 0])
+                    Af = Af + eff * f32(sign * hill)
+                    kv = eff * (km if reg else f32(np.nan))
+                    use = (kv != 0) & ~np.isnan(kv)
+                    rsum = np.where(use, rsum + kv, rsum).astype(f32); rcnt += use
+                A = Af.astype(np.int32)
+                kmr = np.where(rcnt > 0, rsum / np.maximum(rcnt, 1).astype(f32), f32(0)).astype(f32)
+                vmax = f32(0) if not vs else f32(sum(vs[1:], start=f32(vs[0]))) / f32(len(vs))
+                acc = f32(0)
+                for x in ks:
+                    acc = f32(acc + x)
+                kmn = f32(0) if not ks else acc / f32(len(ks))
+                E = f32(np.dot(N.astype(np.float64), mol_energies.astype(np.float64)))
+                ke = np.exp((-E / f32(abs_temp)) / R).astype(f32)
+                ke = np.clip(ke, f32(1e-36), f32(1e36))
+                fwd = ke >= 1
+                out["N"][k, j], out["Nf"][k, j], out["Nb"][k, j], out["A"][k, j] = N, Nf, Nb, A
+                out["Kmr"][k, j] = np.power(kmr, A.astype(f32)).astype(f32)
+                out["Vmax"][k, j], out["Ke"][k, j] = vmax, ke
+                out["Kmf"][k, j] = np.clip(kmn if fwd else kmn / ke, f32(1e-36), f32(1e36))
+                out["Kmb"][k, j] = np.clip(kmn * ke if fwd else kmn, f32(1e-36), f32(1e36))
+    return out

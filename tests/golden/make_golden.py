@@ -17,6 +17,8 @@ Fixtures
                            (small) and c4, c4e, c3, s82 (the benchmarked tile shapes).
   ref_drift_1000.npz       population statistics of a 1000-step reference trajectory (and of
                            the reference with permuted proteins) every 100 steps.
+  ref_set_cell_params.npz  Kinetics.set_cell_params on random proteomes: token tables, flattened
+                           domain tokens, the nine tensors the reference derives from them.
   ref_world.npz            World.diffuse_molecules / enzymatic_activity on small
                            maps incl. the 5x5 known-answer map of
                            tests/fast/test_world.py:8-51.
@@ -298,11 +300,48 @@ def world_fixture(ms):
     print("world fixture written")
 
 
+def set_cell_params_fixture(ms):
+    """
+    Kinetics.set_cell_params of the reference (kinetics.py:521-625) on random proteomes: the
+    reference's token tables, the flattened domain tokens and the nine tensors it derives.
+    Proteomes come from magicsoup_b200's own genome translation (the reference's Rust extension
+    cannot be built here; tests/test_host_lib.py pins that translation to the reference's vectors).
+    """
+    import random
+    from magicsoup_b200 import Genetics, random_genome
+    from magicsoup_b200._hostlib import lib as hostlib
+
+    random.seed(17)
+    ms.Molecule._instances = {}
+    mols = [ms.Molecule(f"scp{i}", e) for i, e in enumerate((10e3, 25e3, 60e3, 150e3, 8e3))]
+    reactions = [([mols[0]], [mols[1]]), ([mols[1], mols[2]], [mols[3]]), ([mols[4], mols[4]], [mols[0], mols[2]])]
+    chem = ms.Chemistry(molecules=mols, reactions=reactions)
+    kin = ms.kinetics.Kinetics(chemistry=chem)
+    gen = Genetics(p_catal_dom=0.1, p_transp_dom=0.1, p_reg_dom=0.1)  # many domains per protein
+    genomes = [random_genome(random.choice((300, 1000, 2000))) for _ in range(80)]
+    proteomes = [p for p in gen.translate_genomes(genomes) if len(p) > 0]
+    n, p_max = len(proteomes), max(len(p) for p in proteomes)
+    kin.increase_max_cells(by_n=n)
+    kin.increase_max_proteins(max_n=p_max)
+    kin.set_cell_params(cell_idxs=list(range(n)), proteomes=proteomes)
+    prot_off, dom_off, doms = hostlib().flatten_proteomes(proteomes)
+    d = {k: _np(getattr(kin, k)) for k in PARAMS}
+    d.update(prot_off=prot_off, dom_off=dom_off, doms=doms, abs_temp=np.array(kin.abs_temp),
+             mol_energies=_np(kin.mol_energies), km_weights=_np(kin.km_map.weights), vmax_weights=_np(kin.vmax_map.weights),
+             signs=_np(kin.sign_map.signs), hill_numbers=_np(kin.hill_map.numbers), reaction_M=_np(kin.reaction_map.M),
+             transport_M=_np(kin.transport_map.M), effector_M=_np(kin.effector_map.M))
+    np.savez_compressed(OUT / "ref_set_cell_params.npz", **d)
+    print(f"set_cell_params fixture: {n} cells, up to {p_max} proteins, {doms.size // 5} domains")
+
+
 def main():
     ms = ref_loader.load()
     torch.manual_seed(0)
     if sys.argv[1:] == ["bench"]:
         bench_shape_fixtures(ms)
+        return
+    if sys.argv[1:] == ["params"]:
+        set_cell_params_fixture(ms)
         return
     store = record_reference_tests(ms)
     np.savez_compressed(OUT / "ref_tests_kinetics.npz", **store)
@@ -313,6 +352,7 @@ def main():
     bench_shape_fixtures(ms)
     drift_fixture(ms)
     world_fixture(ms)
+    set_cell_params_fixture(ms)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,126 @@
+"""
+GPU tests of Kinetics.set_cell_params on the device (ms_set_cell_params, reference
+python/magicsoup/kinetics.py:521-625) and of the genome-driven World loop built on it
+(spawn / divide / mutate / recombinate, reference performance/run_simulation.py:56-100).
+"""
+import random
+
+import numpy as np
+import pytest
+import torch
+
+import magicsoup_b200 as ms
+from oracle import host_oracle as HO
+from oracle import oracle as O
+from tests.helpers import PARAMS, bits_equal, describe_mismatch
+from tests.test_host_lib import _params_fixture, check_params_against_reference, unflatten
+
+pytestmark = pytest.mark.gpu
+
+
+def _chem(n_mols=5, tag="gp"):
+    mols = [ms.Molecule(f"{tag}{i}", e, diffusivity=d, permeability=q)
+            for i, (e, d, q) in enumerate(zip((10e3, 25e3, 60e3, 150e3, 8e3, 40e3)[:n_mols], (1.0, 0.1, 0.01, 0.0, 0.5, 1.0),
+                                              (1.0, 0.1, 0.0, 0.5, 0.0, 0.2)))]
+    reactions = [([mols[0]], [mols[1]]), ([mols[1], mols[2]], [mols[3]]), ([mols[4], mols[4]], [mols[0], mols[2]])]
+    return ms.Chemistry(molecules=mols, reactions=reactions)
+
+
+def test_set_cell_params_kernel_against_the_reference_fixture():
+    z, tables = _params_fixture()
+    c, p, s = z["N"].shape
+    kin = ms.Kinetics(chemistry=_chem(), abs_temp=float(z["abs_temp"]), device="cuda")
+    kin.mol_energies = torch.from_numpy(z["mol_energies"])
+    kin.km_map.weights = torch.from_numpy(tables["km_weights"])      # the reference's tests overwrite the maps
+    kin.vmax_map.weights = torch.from_numpy(tables["vmax_weights"])  # the same way (test_kinetics.py:103-109)
+    kin.sign_map.signs = torch.from_numpy(tables["signs"])
+    kin.hill_map.numbers = torch.from_numpy(tables["hill_numbers"])
+    kin.reaction_map.M = torch.from_numpy(tables["reaction_M"])
+    kin.transport_map.M = torch.from_numpy(tables["transport_M"])
+    kin.effector_map.M = torch.from_numpy(tables["effector_M"])
+    kin.increase_max_cells(by_n=c + 3)
+    kin.increase_max_proteins(max_n=p)
+    proteomes = unflatten(z["prot_off"], z["dom_off"], z["doms"])
+    order = list(range(c + 2, 2, -1))  # cells c+2 .. 3 get proteomes 0 .. c-1: rows need not be in order
+    kin.set_cell_params(cell_idxs=order, proteomes=proteomes)
+    got = {k: getattr(kin, k)[order].cpu().numpy() for k in PARAMS}
+    check_params_against_reference(got, z)
+    mine = HO.set_cell_params(z["prot_off"], z["dom_off"], z["doms"], tables, z["mol_energies"], float(z["abs_temp"]), p, s)
+    for k in ("N", "Nf", "Nb", "A"):
+        assert np.array_equal(got[k], mine[k])
+    for k in ("Vmax", "Kmr", "Ke", "Kmf", "Kmb"):
+        assert np.allclose(got[k], mine[k], rtol=2e-5, atol=0, equal_nan=True), k
+    assert float(kin.N[:3].abs().sum()) == 0  # untouched cells stay unset
+    # setting again after unsetting reproduces the same bits (tests/slow/test_kinetics.py:18-78)
+    kin.unset_cell_params(cell_idxs=order)
+    kin.set_cell_params(cell_idxs=order, proteomes=proteomes)
+    for k in PARAMS:
+        again = getattr(kin, k)[order].cpu().numpy()
+        assert np.array_equal(again, got[k], equal_nan=k not in ("N", "Nf", "Nb", "A")), k
+    with pytest.raises(ValueError):
+        kin.set_cell_params(cell_idxs=[0], proteomes=[proteomes[0] * 50])
+    bad = [([((1, 1, 1, 1, 9999), 0, 21)], 0, 30, True)]
+    with pytest.raises(IndexError):
+        kin.set_cell_params(cell_idxs=[0], proteomes=[bad])
+
+
+def test_genome_driven_world_loop_matches_oracle():
+    random.seed(23)
+    torch.manual_seed(23)
+    chem = _chem(tag="gw")
+    w = ms.World(chemistry=chem, map_size=32, device="cuda")
+    w.genetics = ms.Genetics(p_catal_dom=0.1, p_transp_dom=0.1, p_reg_dom=0.1)
+    idxs = w.spawn_cells(genomes=[ms.random_genome(random.choice((300, 500, 1000))) for _ in range(300)])
+    assert idxs == list(range(300)) and w.n_cells == 300 and int(w.cell_map.sum()) == 300
+    assert w.kinetics.N.shape[0] == 300 and w.kinetics.N.shape[2] == 10
+    n_active = int((w.kinetics.N.abs().sum((1, 2)) > 0).sum())
+    assert n_active > 200  # most random genomes encode a working protein
+    for step in range(6):
+        # kinetics against the CPU oracle on the parameters the store shows
+        P = O.Params(*[getattr(w.kinetics, k).cpu().numpy() for k in PARAMS])
+        pos = w.cell_positions.cpu().numpy()
+        cm, mm = O.enzymatic_activity(P, pos, w.cell_molecules.cpu().numpy(), w.molecule_map.cpu().numpy())
+        w.enzymatic_activity()
+        assert bits_equal(w.cell_molecules, cm), f"step {step}: " + describe_mismatch(w.cell_molecules, cm)
+        assert bits_equal(w.molecule_map, mm), f"step {step}"
+        # the reference's loop (performance/run_simulation.py:56-100)
+        w.kill_cells(cell_idxs=[i for i in range(w.n_cells) if i % 11 == step])
+        pairs = w.divide_cells(cell_idxs=[i for i in range(w.n_cells) if i % 3 == 0])
+        assert len(pairs) > 0 and all(w.cell_genomes[a] == w.cell_genomes[b] for a, b in pairs)
+        w.recombinate_cells(p=1e-4)
+        w.mutate_cells(p=1e-3)
+        w.move_cells(cell_idxs=list(range(0, w.n_cells, 5)))
+        w.degrade_molecules()
+        w.diffuse_molecules()
+        w.increment_cell_lifetimes()
+        n = w.n_cells
+        assert len(w.cell_genomes) == len(w.cell_labels) == n == w.cell_molecules.shape[0] == w.kinetics.N.shape[0]
+        assert w.cell_positions.shape == (n, 2) and int(w.cell_map.sum()) == n
+        xs, ys = w.cell_positions[:, 0].long(), w.cell_positions[:, 1].long()
+        assert bool(w.cell_map[xs, ys].all()) and len({(int(a), int(b)) for a, b in w.cell_positions.tolist()}) == n
+        assert torch.isfinite(w.molecule_map).all() and (w.molecule_map >= 0).all() and (w.cell_molecules >= 0).all()
+    # parameters follow the genomes: re-deriving them from scratch gives the same tensors
+    fresh = ms.Kinetics(chemistry=chem, device="cuda")
+    for name in ("km_map", "vmax_map", "sign_map", "hill_map", "reaction_map", "transport_map", "effector_map"):
+        setattr(fresh, name, getattr(w.kinetics, name))
+    proteomes = w.genetics.translate_genomes(w.cell_genomes)
+    fresh.increase_max_cells(by_n=w.n_cells)
+    fresh.increase_max_proteins(max_n=int(w.kinetics.N.shape[1]))
+    keep = [i for i, p in enumerate(proteomes) if p]
+    fresh.set_cell_params(cell_idxs=keep, proteomes=[proteomes[i] for i in keep])
+    # (as in the reference, protein slots added later by increase_max_proteins hold zeros where a
+    # fresh derivation writes the no-op values Kmr = 0^0 = 1, Ke = 1 ...: compare each cell's own
+    # proteins in all nine tensors, the padding only where it matters to the kinetics)
+    n_prots = torch.tensor([len(p) for p in proteomes], device="cuda")
+    own = torch.arange(fresh.N.shape[1], device="cuda")[None, :] < n_prots[:, None]
+    for k in PARAMS:
+        a, b = getattr(w.kinetics, k), getattr(fresh, k)
+        assert a.shape == b.shape, (k, tuple(a.shape), tuple(b.shape))
+        differ = (a != b) & ~(torch.isnan(a) & torch.isnan(b)) if a.is_floating_point() else a != b
+        if k in ("Kmr", "Ke", "Kmf", "Kmb"):
+            differ &= own[:, :, None] if differ.dim() == 3 else own
+        assert not bool(differ.any()), (k, int(differ.sum()), differ.nonzero()[:5].tolist())
+    w.reposition_cells(cell_idxs=list(range(10)))
+    assert int(w.cell_map.sum()) == w.n_cells
+    nb = w.get_neighbors(cell_idxs=list(range(w.n_cells)))
+    assert all(a < b for a, b in nb) and len(nb) == len(set(nb))

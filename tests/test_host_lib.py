@@ -202,3 +202,52 @@ def test_point_mutations_and_recombinations_statistics():
 def test_package_surface():
     assert ms.Genetics is Genetics and ms.random_genome is util.random_genome
     assert ms.point_mutations is mutations.point_mutations and ms.recombinations is mutations.recombinations
+
+
+def _params_fixture():
+    import numpy as np
+    from pathlib import Path
+
+    z = np.load(Path(__file__).resolve().parent / "golden" / "ref_set_cell_params.npz")
+    tables = {k: z[k] for k in ("vmax_weights", "km_weights", "signs", "hill_numbers", "reaction_M", "transport_M", "effector_M")}
+    return z, tables
+
+
+def unflatten(prot_off, dom_off, doms):
+    """flattened tokens back into the nested lists translate_genomes returns (positions are not kept)"""
+    doms = doms.reshape(-1, 5)
+    return [[([(tuple(int(x) for x in doms[d]), 0, 0) for d in range(dom_off[q], dom_off[q + 1])], 0, 0, True)
+             for q in range(prot_off[k], prot_off[k + 1])] for k in range(len(prot_off) - 1)]
+
+
+PARAM_TOLERANCES = {"Vmax": 2e-6, "Kmr": 2e-5, "Ke": 2e-4, "Kmf": 2e-4, "Kmb": 2e-4}
+
+
+def check_params_against_reference(got, z):
+    """
+    integers exact; floats relative: means of a few float32 2e-6, powf with exponents up to 25 2e-5,
+    exp of an energy sum of magnitude 1e2 (float32 rounding of the sum enters the exponent) 2e-4
+    """
+    import numpy as np
+
+    for k in ("N", "Nf", "Nb", "A"):
+        assert np.array_equal(got[k], z[k]), k
+    for k, tol in PARAM_TOLERANCES.items():
+        a, b = np.asarray(got[k], dtype=np.float64), z[k].astype(np.float64)
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(np.isinf(a), np.isinf(b)), k
+        fin = np.isfinite(b)
+        sat = fin & ((b == np.float32(1e36)) | (b == np.float32(1e-36)))
+        assert np.array_equal(a[sat], b[sat]), k  # clamped values are exact
+        assert (np.abs(a[fin] - b[fin]) <= tol * np.abs(b[fin])).all(), (k, np.abs(a[fin] / b[fin] - 1).max())
+
+
+def test_set_cell_params_restatement_matches_the_reference():
+    # pins oracle/host_oracle.py::set_cell_params to the reference's Kinetics.set_cell_params
+    # (tests/golden/make_golden.py::set_cell_params_fixture); the CUDA kernel is held to both in
+    # tests/test_gpu_params.py
+    z, tables = _params_fixture()
+    c, p, s = z["N"].shape
+    got = HO.set_cell_params(z["prot_off"], z["dom_off"], z["doms"], tables, z["mol_energies"], float(z["abs_temp"]), p, s)
+    check_params_against_reference(got, z)
+    assert unflatten(z["prot_off"], z["dom_off"], z["doms"])[0][0][0][0][0] == tuple(z["doms"][:5])
+    assert lib().flatten_proteomes(unflatten(z["prot_off"], z["dom_off"], z["doms"]))[2].tolist() == z["doms"].tolist()

@@ -24,8 +24,9 @@ Prints ONE JSON line (rank 0).
             against the measured HBM peak; `moved_*` = the bytes a launch actually has to move
   cpu_baseline / --impl reference: the CPU oracle (oracle/ms_oracle.c, a port), all host threads,
             full-size steps
-  extra     N = 1: the c3 workload; N > 1: strong scaling of c4 and a bit-exact parity check of the
-            multi-GPU path against the single-domain oracle (the run fails if it mismatches)
+  extra     N = 1: the c3 workload and the cost of kill + divide of 1 % of the cells per step at c4;
+            N > 1: strong scaling of c4 and a bit-exact parity check of the multi-GPU path against the
+            single-domain oracle (the run fails if it mismatches)
 """
 from __future__ import annotations
 
@@ -223,6 +224,44 @@ def measure(world, steps, warmup, barrier, device, world_size):
         world.enzymatic_activity()
         world.diffuse_molecules()
     return timed_steps(world, steps, barrier, device, world_size)
+
+
+def lifecycle_rounds(world, device, step_ms, rounds=4, frac=0.01):
+    """
+    The reference's per-step bookkeeping (performance/run_simulation.py:56-100) at the bench size: kill
+    `frac` of the cells, let as many divide onto the freed pixels, step once.  Host clock around
+    each call with a device synchronize on both sides (these calls are host work + small launches).
+    """
+    import torch
+
+    g = torch.Generator()
+    g.manual_seed(5)
+    out = []
+    for _ in range(rounds):
+        n = world.n_cells
+        k = max(1, int(n * frac))
+        kill = torch.randperm(n, generator=g)[:k].tolist()
+        freed = world.cell_positions[kill].clone()
+        parents = torch.randperm(n - k, generator=g)[:k].tolist()
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        world.kill_cells(cell_idxs=kill)
+        torch.cuda.synchronize(device)
+        t1 = time.perf_counter()
+        world.divide_cells_at(parents, freed)
+        torch.cuda.synchronize(device)
+        t2 = time.perf_counter()
+        world.enzymatic_activity()
+        world.diffuse_molecules()
+        torch.cuda.synchronize(device)
+        t3 = time.perf_counter()
+        out.append({"kill_ms": (t1 - t0) * 1e3, "divide_ms": (t2 - t1) * 1e3, "step_after_ms": (t3 - t2) * 1e3})
+    k = max(1, int(world.n_cells * frac))
+    return {"what": f"kill {k} random cells, divide {k} random cells onto the freed pixels, one step; {rounds} rounds "
+                    "(the first one includes the one-off growth of the parameter buffers by half)",
+            "rounds": out, "steady_step_ms": step_ms,
+            "parameter_bytes_per_cell": kinetics_bytes_per_cell(int(world.kinetics._buf["N"].shape[1]),
+                                                                int(world.kinetics._buf["N"].shape[2]))}
 
 
 def roofline_block(c, p, s, res, scan, rec_words, traffic):
@@ -548,6 +587,7 @@ def main():
                     "rebalanced across ranks"}
         del w4, w5
     if not args.no_extra and world_size == 1 and args.config == "c4":
+        extra["lifecycle"] = lifecycle_rounds(world, device, res["ms_per_step"])
         del world, pop
         torch.cuda.empty_cache()
         cc, cp, cmol, cmap, where = CONFIGS["c3"]

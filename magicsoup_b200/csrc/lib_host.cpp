@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <array>
 #include <cstdint>
+#include <cstring>
 #include <mutex>
 #include <random>
 #include <string>
@@ -473,6 +474,36 @@ PYBIND11_MODULE(_lib, m) {
           return py::make_tuple(arr(prot_off), arr(dom_off), arr(doms));
         },
         py::arg("proteomes"), "no counterpart in the reference (which pads nested lists into (c,p,d) tensors, kinetics.py:920-970)");
+  m.def("remove_items",
+        [](py::list items, const std::vector<int64_t> &dead_sorted) {
+          // order-preserving removal from a Python list in place (World.kill_cells' genome and
+          // label lists, world.py:527-540): the kept pointers slide down in one pass and only the
+          // removed objects are touched; a pop per index moves the tail every time, and building
+          // a new list touches the reference count of every kept object (a cache miss each)
+          PyListObject *lst = (PyListObject *)items.ptr();
+          const int64_t n = (int64_t)Py_SIZE(lst);
+          int64_t prev = -1;
+          for (int64_t i : dead_sorted) {
+            if (i < 0 || i >= n) throw py::index_error("index out of range");
+            if (i <= prev) throw py::value_error("indices must be strictly ascending");
+            prev = i;
+          }
+          std::vector<PyObject *> removed;
+          removed.reserve(dead_sorted.size());
+          PyObject **it = lst->ob_item;
+          int64_t o = 0, a = 0;
+          for (int64_t i : dead_sorted) {
+            if (i > a) std::memmove(it + o, it + a, (size_t)(i - a) * sizeof(PyObject *));
+            o += i - a;
+            removed.push_back(it[i]);
+            a = i + 1;
+          }
+          if (n > a) std::memmove(it + o, it + a, (size_t)(n - a) * sizeof(PyObject *));
+          o += n - a;
+          Py_SET_SIZE(lst, o);
+          for (PyObject *r : removed) Py_DECREF(r);  // after the list is consistent again
+        },
+        py::arg("items"), py::arg("dead_sorted"));
   m.def("get_neighbors", &get_neighbors, py::arg("from_idxs"), py::arg("to_idxs"), py::arg("positions"),
         py::arg("map_size"), py::call_guard<py::gil_scoped_release>());
   m.def("divide_cells_if_possible", &divide_cells_if_possible, py::arg("cell_idxs"), py::arg("positions"),

@@ -77,6 +77,17 @@ def diffusion_weights(mol_diff_rate: float) -> tuple[float, float]:
     return a, b
 
 
+def _remove_items(items: list, dead_sorted: list[int]):
+    """drop the (ascending, unique) indices from `items` in place"""
+    if len(dead_sorted) < 16:
+        for i in reversed(dead_sorted):
+            del items[i]
+        return
+    from magicsoup_b200._hostlib import lib as hostlib
+
+    hostlib().remove_items(items, dead_sorted)
+
+
 class World:
     """see module docstring; constructor signature of world.py:147-157"""
 
@@ -386,22 +397,22 @@ class World:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
             return
-        cell_idxs = list(set(cell_idxs))
-        xs = self.cell_positions[cell_idxs, 0].long()
-        ys = self.cell_positions[cell_idxs, 1].long()
+        dead = sorted(set(cell_idxs))
+        idx = torch.as_tensor(dead, dtype=torch.long, device=self.cell_positions.device)  # one upload
+        xs = self.cell_positions[idx, 0].long()
+        ys = self.cell_positions[idx, 1].long()
         self.cell_map[xs, ys] = False
-        self.molecule_map[:, xs, ys] += self.cell_molecules[cell_idxs, :].T
-        keep = torch.ones(self.cell_lifetimes.size(0), dtype=torch.bool, device=self.cell_lifetimes.device)
-        keep[cell_idxs] = False
+        self.molecule_map[:, xs, ys] += self.cell_molecules[idx, :].T
+        keep = torch.ones(self.cell_lifetimes.size(0), dtype=torch.bool, device=idx.device)
+        keep[idx] = False
         self.cell_lifetimes = self.cell_lifetimes[keep]
         self.cell_positions = self.cell_positions[keep]
         self.cell_divisions = self.cell_divisions[keep]
         self.cell_molecules = self.cell_molecules[keep]
         self.kinetics.remove_cell_params(keep=keep)
-        for idx in sorted(cell_idxs, reverse=True):
-            self.cell_genomes.pop(idx)
-            self.cell_labels.pop(idx)
-        self.n_cells -= len(cell_idxs)
+        _remove_items(self.cell_genomes, dead)
+        _remove_items(self.cell_labels, dead)
+        self.n_cells -= len(dead)
 
     def divide_cells_at(self, parent_idxs: list[int], child_positions: torch.Tensor) -> list[tuple[int, int]]:
         """
@@ -411,25 +422,29 @@ class World:
         n = len(parent_idxs)
         if n == 0:
             return []
+        dev = self.cell_positions.device
         child_idxs = list(range(self.n_cells, self.n_cells + n))
+        parents = torch.as_tensor(parent_idxs, dtype=torch.long, device=dev)  # one upload, reused below
+        children = torch.arange(self.n_cells, self.n_cells + n, dtype=torch.long, device=dev)
+        both = torch.cat([parents, children])
         self.n_cells += n
-        self.cell_genomes.extend(self.cell_genomes[d] for d in parent_idxs)
-        self.cell_labels.extend(self.cell_labels[d] for d in parent_idxs)
+        genomes, labels = self.cell_genomes, self.cell_labels
+        genomes.extend([genomes[d] for d in parent_idxs])
+        labels.extend([labels[d] for d in parent_idxs])
         self.cell_lifetimes = self._expand_c(self.cell_lifetimes, n)
         self.cell_positions = self._expand_c(self.cell_positions, n)
         self.cell_divisions = self._expand_c(self.cell_divisions, n)
         self.cell_molecules = self._expand_c(self.cell_molecules, n)
         self.kinetics.increase_max_cells(by_n=n)
-        self.kinetics.copy_cell_params(from_idxs=parent_idxs, to_idxs=child_idxs)
-        pos = child_positions.to(device=self.cell_positions.device, dtype=torch.int32)
+        self.kinetics.copy_cell_params(from_idxs=parents, to_idxs=children)
+        pos = child_positions.to(device=dev, dtype=torch.int32)
         self.cell_map[pos[:, 0].long(), pos[:, 1].long()] = True
-        self.cell_positions[child_idxs] = pos
-        descendants = parent_idxs + child_idxs
-        self.cell_molecules[child_idxs] = self.cell_molecules[parent_idxs]
-        self.cell_molecules[descendants] *= 0.5
-        self.cell_divisions[child_idxs] = self.cell_divisions[parent_idxs]
-        self.cell_divisions[descendants] += 1
-        self.cell_lifetimes[descendants] = 0
+        self.cell_positions[children] = pos
+        self.cell_molecules[children] = self.cell_molecules[parents]
+        self.cell_molecules[both] *= 0.5
+        self.cell_divisions[children] = self.cell_divisions[parents]
+        self.cell_divisions[both] += 1
+        self.cell_lifetimes[both] = 0
         return list(zip(parent_idxs, child_idxs))
 
     # ------------------------------------------------------------------ genome-driven lifecycle

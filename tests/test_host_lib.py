@@ -251,3 +251,23 @@ def test_set_cell_params_restatement_matches_the_reference():
     check_params_against_reference(got, z)
     assert unflatten(z["prot_off"], z["dom_off"], z["doms"])[0][0][0][0][0] == tuple(z["doms"][:5])
     assert lib().flatten_proteomes(unflatten(z["prot_off"], z["dom_off"], z["doms"]))[2].tolist() == z["doms"].tolist()
+
+
+def test_remove_items_in_place():
+    """the list edit behind World.kill_cells (world.py:527-540 pops genome and label per index)"""
+    import random as _r
+
+    rng = _r.Random(4)
+    for n, k in ((0, 0), (1, 1), (40, 17), (5000, 300), (5000, 5000)):
+        items = [f"g{i}" for i in range(n)]
+        same = items
+        dead = sorted(rng.sample(range(n), k))
+        want = [v for i, v in enumerate(items) if i not in set(dead)]
+        lib().remove_items(items, dead)
+        assert items == want and items is same
+        items.append("tail")  # the list stays a working list
+        assert items[-1] == "tail" and len(items) == n - k + 1
+    with pytest.raises(ValueError):
+        lib().remove_items([1, 2, 3], [1, 1])
+    with pytest.raises(IndexError):
+        lib().remove_items([1, 2, 3], [3])

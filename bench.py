@@ -264,6 +264,55 @@ def lifecycle_rounds(world, device, step_ms, rounds=4, frac=0.01):
                                                                 int(world.kinetics._buf["N"].shape[2]))}
 
 
+def genome_update_times(device, n_cells=10_000, genome_size=1000):
+    """
+    World.update_cells' work for `n_cells` random genomes (translate_genomes + set_cell_params,
+    world.py:880-908; the reference quotes 5.95 s per 10,000 cells on a T4, performance/check.py:15):
+    host translation (C++ / OpenMP), flattening, one kernel launch.  14 molecules / 28 signals like
+    the reference's Wood-Ljungdahl chemistry.
+    """
+    import random
+
+    import numpy as np
+    import torch
+
+    import magicsoup_b200 as ms
+
+    random.seed(11)
+    mols = [ms.Molecule(f"bench-g{i}", 10e3 + 15e3 * i, diffusivity=1.0, permeability=0.1) for i in range(14)]
+    reactions = [([mols[i]], [mols[i + 1]]) for i in range(0, 12, 2)] + \
+                [([mols[i], mols[i + 2]], [mols[i + 1], mols[i + 3]]) for i in range(0, 10, 2)]
+    kin = ms.Kinetics(chemistry=ms.Chemistry(molecules=mols, reactions=reactions), device=str(device))
+    gen = ms.Genetics()
+    genomes = [ms.random_genome(genome_size) for _ in range(n_cells)]
+    out = {"cells": n_cells, "genome_size": genome_size, "host_threads": len(os.sched_getaffinity(0))}
+    for rep in range(2):  # the second round is the warm one
+        t0 = time.perf_counter()
+        prot_off, dom_off, doms = gen.translate_genomes_flat(genomes)
+        t1 = time.perf_counter()
+        counts = prot_off[1:] - prot_off[:-1]
+        p_max = int(counts.max())
+        if rep == 0:
+            kin.increase_max_cells(by_n=n_cells)
+        kin.increase_max_proteins(max_n=p_max)
+        has = counts > 0
+        keep = [i for i, h in enumerate(has.tolist()) if h]
+        offsets = np.concatenate([prot_off[:1], prot_off[1:][has]])
+        torch.cuda.synchronize(device)
+        t2 = time.perf_counter()
+        kin.set_cell_params_flat(keep, offsets, dom_off, doms)
+        torch.cuda.synchronize(device)
+        t3 = time.perf_counter()
+        t4 = time.perf_counter()
+        nested = gen.translate_genomes(genomes)  # the reference's interface: nested lists of tuples
+        t5 = time.perf_counter()
+        del nested
+    out.update(translate_genomes_flat_ms=(t1 - t0) * 1e3, set_cell_params_ms=(t3 - t2) * 1e3, proteins_max=p_max,
+               translate_genomes_nested_ms=(t5 - t4) * 1e3,
+               reference_quote="5.95 s per 10,000 cells for update_cells on a T4 (performance/check.py:15)")
+    return out
+
+
 def roofline_block(c, p, s, res, scan, rec_words, traffic):
     """res / scan: timed_steps() of the default run (cached lists) and of the scan path"""
     peak, peak_src = hbm_peak()
@@ -604,6 +653,7 @@ def main():
                           "value": cc / (r3s["ms_per_step"] / 1e3),
                           "roofline_frac": b3 / (r3s["kernel_ms"] / 1e3) / 1e9 / hbm_peak()[0]}}
         del w3
+        extra["genome_update"] = genome_update_times(device)
     if "parity_check" in extra and not extra["parity_check"]["ok"]:
         if rank == 0:
             print(json.dumps({"error": "multi-GPU parity check failed", "parity_check": extra["parity_check"]}))

@@ -101,13 +101,50 @@ std::vector<Cds> coding_regions(const std::string &seq, size_t min_size, const s
 
 struct CodonMaps {
   std::unordered_map<std::string, int> dom_type, one, two;
+  // dense tables over codon codes, usable when the domain type is two codons long (the
+  // reference's default) and every key is made of nucleotides; -1 = not in the map
+  bool dense = false;
+  std::vector<int> type_tab, one_tab, two_tab;
 };
+
+// 6-bit code of a codon string, -1 if it holds anything but T, C, G, A
+inline int codon_code(const char *c) {
+  const unsigned a = nt_code(c[0]), b = nt_code(c[1]), d = nt_code(c[2]);
+  return (a | b | d) > 3 ? -1 : (int)(a * 16 + b * 4 + d);
+}
+
+void make_dense_tables(CodonMaps &m) {
+  m.type_tab.assign(4096, -1);
+  m.one_tab.assign(64, -1);
+  m.two_tab.assign(4096, -1);
+  const auto two_code = [](const std::string &k) {
+    if (k.size() != 2 * CODON) return -1;
+    const int a = codon_code(k.data()), b = codon_code(k.data() + CODON);
+    return a < 0 || b < 0 ? -1 : a * 64 + b;
+  };
+  for (const auto &[k, v] : m.dom_type) {
+    const int c = two_code(k);
+    if (c < 0 || v < 0) return;
+    m.type_tab[c] = v;
+  }
+  for (const auto &[k, v] : m.one) {
+    const int c = k.size() == CODON ? codon_code(k.data()) : -1;
+    if (c < 0 || v < 0) return;
+    m.one_tab[c] = v;
+  }
+  for (const auto &[k, v] : m.two) {
+    const int c = two_code(k);
+    if (c < 0 || v < 0) return;
+    m.two_tab[c] = v;
+  }
+  m.dense = true;
+}
 
 // rust/genetics.rs:58-123: walk each CDS; a known domain-type prefix consumes a whole domain
 // (type, 3 one-codon tokens, 1 two-codon token), anything else one codon; proteins without a
-// catalytic or transporter domain are dropped
-std::vector<ProteinSpec> domains_of(const std::string &genome, const std::vector<Cds> &cdss, size_t dom_size,
-                                    size_t dom_type_size, const CodonMaps &maps) {
+// catalytic or transporter domain are dropped.  Map look-ups by substring (any key length).
+std::vector<ProteinSpec> domains_of_by_key(const std::string &genome, const std::vector<Cds> &cdss, size_t dom_size,
+                                           size_t dom_type_size, const CodonMaps &maps) {
   std::vector<ProteinSpec> out;
   out.reserve(cdss.size());
   for (const auto &[cds_start, cds_stop, is_fwd] : cdss) {
@@ -133,6 +170,51 @@ std::vector<ProteinSpec> domains_of(const std::string &genome, const std::vector
       auto f2 = maps.two.find(genome.substr(t0 + 3 * CODON, 2 * CODON));
       if (f2 == maps.two.end()) throw std::runtime_error("Incomplete two_codon_map");
       doms.emplace_back(std::make_tuple(type, tok1(0), tok1(1), tok1(2), f2->second), i, i + dom_size);
+      i += dom_size;
+    }
+    if (useful) out.emplace_back(std::move(doms), cds_start, cds_stop, is_fwd);
+  }
+  return out;
+}
+
+// the same walk over per-position codon codes and dense tables: CDSs nest (every start codon
+// before a stop opens one), so a genome's codons are visited many times and a table look-up per
+// visit instead of a substring + hash is what makes translation cheap
+std::vector<ProteinSpec> domains_of(const std::string &genome, const std::vector<Cds> &cdss, size_t dom_size,
+                                    size_t dom_type_size, const CodonMaps &maps) {
+  if (!maps.dense || dom_type_size != 2 * CODON || dom_size != dom_type_size + 5 * CODON)
+    return domains_of_by_key(genome, cdss, dom_size, dom_type_size, maps);
+  std::vector<ProteinSpec> out;
+  if (cdss.empty()) return out;
+  const size_t len = genome.size();
+  std::vector<int8_t> code(len, -1);  // codon starting at each position
+  for (size_t i = 0; i + CODON <= len; i++) code[i] = (int8_t)codon_code(genome.data() + i);
+  out.reserve(cdss.size());
+  for (const auto &[cds_start, cds_stop, is_fwd] : cdss) {
+    const size_t n = cds_stop - cds_start;
+    std::vector<DomainSpec> doms;
+    bool useful = false;
+    size_t i = 0;
+    while (i + dom_size <= n) {
+      const size_t d0 = cds_start + i;
+      const int c0 = code[d0], c1 = code[d0 + CODON];
+      const int type = (c0 | c1) < 0 ? -1 : maps.type_tab[c0 * 64 + c1];
+      if (type < 0) {
+        i += CODON;
+        continue;
+      }
+      if (type != 3) useful = true;
+      const size_t t0 = d0 + dom_type_size;
+      int tok[3];
+      for (size_t k = 0; k < 3; k++) {
+        const int c = code[t0 + k * CODON];
+        tok[k] = c < 0 ? -1 : maps.one_tab[c];
+        if (tok[k] < 0) throw std::runtime_error("Incomplete one_codon_map");
+      }
+      const int e0 = code[t0 + 3 * CODON], e1 = code[t0 + 4 * CODON];
+      const int tok2 = (e0 | e1) < 0 ? -1 : maps.two_tab[e0 * 64 + e1];
+      if (tok2 < 0) throw std::runtime_error("Incomplete two_codon_map");
+      doms.emplace_back(std::make_tuple(type, tok[0], tok[1], tok[2], tok2), i, i + dom_size);
       i += dom_size;
     }
     if (useful) out.emplace_back(std::move(doms), cds_start, cds_stop, is_fwd);
@@ -412,7 +494,9 @@ std::tuple<std::vector<Pos>, std::vector<size_t>> move_cells(const std::vector<s
 
 CodonMaps make_maps(const std::unordered_map<std::string, int> &dom_type, const std::unordered_map<std::string, int> &one,
                     const std::unordered_map<std::string, int> &two) {
-  return CodonMaps{dom_type, one, two};
+  CodonMaps m{dom_type, one, two};
+  make_dense_tables(m);
+  return m;
 }
 
 }  // namespace
@@ -454,6 +538,36 @@ PYBIND11_MODULE(_lib, m) {
         },
         py::arg("genomes"), py::arg("start_codons"), py::arg("stop_codons"), py::arg("domain_map"),
         py::arg("one_codon_map"), py::arg("two_codon_map"), py::arg("dom_size"), py::arg("dom_type_size"));
+  m.def("translate_genomes_flat",
+        [](const std::vector<std::string> &genomes, const std::vector<std::string> &start_codons,
+           const std::vector<std::string> &stop_codons, const std::unordered_map<std::string, int> &domain_map,
+           const std::unordered_map<std::string, int> &one_codon_map,
+           const std::unordered_map<std::string, int> &two_codon_map, size_t dom_size, size_t dom_type_size) {
+          // translate_genomes + flatten_proteomes without the nested Python lists in between
+          // (half a million objects per 10,000 genomes): what World._update_cell_params needs
+          const CodonMaps maps = make_maps(domain_map, one_codon_map, two_codon_map);
+          std::vector<int32_t> prot_off{0}, dom_off{0}, doms;
+          {
+            py::gil_scoped_release release;
+            const auto all = translate_genomes(genomes, start_codons, stop_codons, maps, dom_size, dom_type_size);
+            for (const auto &proteome : all) {
+              for (const auto &protein : proteome) {
+                for (const auto &dom : std::get<0>(protein)) {
+                  const auto &t = std::get<0>(dom);
+                  doms.insert(doms.end(), {(int32_t)std::get<0>(t), (int32_t)std::get<1>(t), (int32_t)std::get<2>(t),
+                                           (int32_t)std::get<3>(t), (int32_t)std::get<4>(t)});
+                }
+                dom_off.push_back((int32_t)(doms.size() / 5));
+              }
+              prot_off.push_back((int32_t)(dom_off.size() - 1));
+            }
+          }
+          auto arr = [](const std::vector<int32_t> &v) { return py::array_t<int32_t>(v.size(), v.data()); };
+          return py::make_tuple(arr(prot_off), arr(dom_off), arr(doms));
+        },
+        py::arg("genomes"), py::arg("start_codons"), py::arg("stop_codons"), py::arg("domain_map"),
+        py::arg("one_codon_map"), py::arg("two_codon_map"), py::arg("dom_size"), py::arg("dom_type_size"),
+        "no counterpart in the reference: the three int32 arrays of flatten_proteomes(translate_genomes(...))");
   m.def("flatten_proteomes",
         [](const py::list &proteomes) {
           // nested (proteome -> protein -> domain) lists of translate_genomes -> three int32 arrays:

@@ -69,6 +69,15 @@ class Genetics:
         return _lib().translate_genomes(genomes, self.start_codons, self.stop_codons, self.domain_map,
                                         self.one_codon_map, self.two_codon_map, self.dom_size, self.dom_type_size)
 
+    def translate_genomes_flat(self, genomes: list[str]):
+        """
+        translate_genomes as three int32 arrays (protein offsets per genome, domain offsets per
+        protein, (type, i0, i1, i2, i3) per domain) instead of nested lists: what
+        Kinetics.set_cell_params_flat takes.  No counterpart in the reference.
+        """
+        return _lib().translate_genomes_flat(list(genomes), self.start_codons, self.stop_codons, self.domain_map,
+                                             self.one_codon_map, self.two_codon_map, self.dom_size, self.dom_type_size)
+
     def _get_single_codons(self) -> list[str]:
         return [d for d in codons(n=1) if d not in self.stop_codons]  # no premature stop
 

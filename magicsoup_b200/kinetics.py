@@ -511,6 +511,19 @@ class Kinetics:
             raise ValueError("cell_idxs and proteomes differ in length")
         from magicsoup_b200._hostlib import lib as hostlib
 
+        prot_off, dom_off, doms = hostlib().flatten_proteomes(list(proteomes))
+        self.set_cell_params_flat(cell_idxs, prot_off, dom_off, doms)
+
+    def set_cell_params_flat(self, cell_idxs: list[int], prot_off, dom_off, doms):
+        """
+        set_cell_params on flattened proteomes (int32 numpy arrays: protein offsets per cell, domain
+        offsets per protein, 5 tokens per domain; `_lib.flatten_proteomes` / `translate_genomes_flat`).
+        No counterpart in the reference, which pads nested lists into (c,p,d) tensors (kinetics.py:920-970).
+        """
+        if len(cell_idxs) == 0:
+            return
+        if len(prot_off) != len(cell_idxs) + 1:
+            raise ValueError("cell_idxs and proteomes differ in length")
         dev = self._cuda()
         if not self._managed() or self._buf["N"].device != dev or not all(t.is_contiguous() for t in self._buf.values()):
             self._materialize()
@@ -519,7 +532,6 @@ class Kinetics:
                 self._adopt(k, (self._i32(t, dev) if k in _INT_PARAMS else self._f32(t, dev)).clone())
             if not self._managed():
                 raise ValueError("the parameter tensors do not describe the same cells; cannot set cell parameters")
-        prot_off, dom_off, doms = hostlib().flatten_proteomes(list(proteomes))
         p, s = int(self._buf["N"].shape[1]), int(self._buf["N"].shape[2])
         n_max = int((prot_off[1:] - prot_off[:-1]).max()) if len(prot_off) > 1 else 0
         if n_max > p:

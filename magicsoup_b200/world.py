@@ -28,6 +28,7 @@ import random
 from dataclasses import dataclass
 from typing import Any
 
+import numpy as np
 import torch
 
 from magicsoup_b200 import _native as nat
@@ -572,6 +573,24 @@ class World:
 
     def _update_cell_params(self, genomes: list[str], idxs: list[int]):
         """world.py:880-908: translate, unset cells without proteins, grow the protein axis, set the rest"""
+        if len(genomes) == 0:
+            return
+        if type(self.genetics).translate_genomes is Genetics.translate_genomes and \
+                type(self.kinetics).set_cell_params is Kinetics.set_cell_params:
+            # flat arrays from the translation straight into the kernel: no nested Python lists
+            prot_off, dom_off, doms = self.genetics.translate_genomes_flat(genomes)
+            counts = prot_off[1:] - prot_off[:-1]
+            has = counts > 0
+            unset_idxs = [i for i, h in zip(idxs, has.tolist()) if not h]
+            set_idxs = [i for i, h in zip(idxs, has.tolist()) if h]
+            if unset_idxs:
+                self.kinetics.unset_cell_params(cell_idxs=unset_idxs)
+            if not set_idxs:
+                return
+            self.kinetics.increase_max_proteins(max_n=int(counts.max()))
+            offsets = np.concatenate([prot_off[:1], prot_off[1:][has]])  # cells without proteins own no entries
+            self.kinetics.set_cell_params_flat(set_idxs, offsets, dom_off, doms)
+            return
         proteomes = self.genetics.translate_genomes(genomes=genomes)
         set_idxs, set_proteomes, unset_idxs = [], [], []
         for idx, proteome in zip(idxs, proteomes):

@@ -81,6 +81,29 @@ def test_translate_genomes_matches_the_plain_restatement():
     assert gen.translate_genomes([]) == []
 
 
+@pytest.mark.parametrize("n_type_codons, probs", [(2, 0.05), (1, 0.3), (3, 0.1)])
+def test_translation_paths_agree(n_type_codons, probs):
+    """table-driven walk (two type codons) vs the look-ups by key (any other size) vs the plain
+    restatement, and the flat arrays vs flatten_proteomes of the nested lists"""
+    import numpy as np
+
+    random.seed(8 + n_type_codons)
+    gen = Genetics(p_catal_dom=probs, p_transp_dom=probs, p_reg_dom=probs, n_dom_type_codons=n_type_codons)
+    genomes = [util.random_genome(s=random.choice([0, 2, 30, 200, 700])) for _ in range(150)]
+    genomes += ["", "ATG", "ATGNNNNNNTGA" * 20, genomes[5].lower()]  # characters that are no nucleotides
+    res = gen.translate_genomes(genomes)
+    for g, prots in zip(genomes, res):
+        exp = HO.translate_genome(g, gen.start_codons, gen.stop_codons, gen.domain_map, gen.one_codon_map,
+                                  gen.two_codon_map, gen.dom_size, gen.dom_type_size)
+        assert prots == exp
+    assert sum(len(p) for p in res) > 50
+    nested = lib().flatten_proteomes(res)
+    flat = gen.translate_genomes_flat(genomes)
+    for a, b in zip(nested, flat):
+        assert a.dtype == b.dtype == np.int32 and np.array_equal(a, b)
+    assert len(flat[0]) == len(genomes) + 1 and flat[0][-1] == len(flat[1]) - 1 and flat[1][-1] * 5 == len(flat[2])
+
+
 def test_genetics_maps_and_domain_frequencies():
     # genetics.py:104-122 and the reference's statistical check (test_genetics.py:204-246)
     random.seed(1)

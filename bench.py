@@ -24,7 +24,8 @@ Prints ONE JSON line (rank 0).
             against the measured HBM peak; `moved_*` = the bytes a launch actually has to move
   cpu_baseline / --impl reference: the CPU oracle (oracle/ms_oracle.c, a port), all host threads,
             full-size steps
-  extra     N = 1: the c3 workload and the cost of kill + divide of 1 % of the cells per step at c4;
+  extra     N = 1: the c3 workload, the cost of kill + divide of 1 % of the cells per step at c4, and the
+            reference's own benchmark scripts (performance/check.py, run_simulation.py; bench_workloads.py);
             N > 1: strong scaling of c4 and a bit-exact parity check of the multi-GPU path against the
             single-domain oracle (the run fails if it mismatches)
 """
@@ -654,6 +655,9 @@ def main():
                           "roofline_frac": b3 / (r3s["kernel_ms"] / 1e3) / 1e9 / hbm_peak()[0]}}
         del w3
         extra["genome_update"] = genome_update_times(device)
+        from bench_workloads import reference_workloads
+
+        extra["reference_workloads"] = reference_workloads(device)
     if "parity_check" in extra and not extra["parity_check"]["ok"]:
         if rank == 0:
             print(json.dumps({"error": "multi-GPU parity check failed", "parity_check": extra["parity_check"]}))

@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <array>
 #include <cstdint>
+#include <cmath>
 #include <cstring>
 #include <mutex>
 #include <random>
@@ -45,6 +46,38 @@ uint64_t next_seed() {
   std::lock_guard<std::mutex> lock(g_rng_mutex);
   return g_rng();
 }
+
+// One small generator per sequence (xoshiro256**, seeded through splitmix64 from the call's seed
+// and the sequence's index): the streams are independent of the thread schedule, and setting one
+// up costs a few instructions where a Mersenne twister initialises 312 words.
+struct SeqRng {
+  using result_type = uint64_t;
+  uint64_t s[4];
+  SeqRng(uint64_t seed, uint64_t index) {
+    uint64_t x = seed ^ (0x9e3779b97f4a7c15ull * (index + 1));
+    for (auto &w : s) {
+      x += 0x9e3779b97f4a7c15ull;
+      uint64_t z = x;
+      z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+      z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+      w = z ^ (z >> 31);
+    }
+  }
+  static constexpr uint64_t min() { return 0; }
+  static constexpr uint64_t max() { return ~0ull; }
+  static uint64_t rotl(uint64_t v, int k) { return (v << k) | (v >> (64 - k)); }
+  uint64_t operator()() {
+    const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
+    s[2] ^= s[0];
+    s[3] ^= s[1];
+    s[1] ^= s[2];
+    s[0] ^= s[3];
+    s[2] ^= t;
+    s[3] = rotl(s[3], 45);
+    return r;
+  }
+  double uniform() { return (double)((*this)() >> 11) * (1.0 / 9007199254740992.0); }  // [0, 1)
+};
 
 // ---------------------------------------------------------------------------- genetics
 // nucleotide -> 2 bits (anything else: 4, never part of a known codon)
@@ -267,7 +300,8 @@ std::vector<std::vector<ProteinSpec>> translate_genomes(const std::vector<std::s
 const char NTS[4] = {'A', 'C', 'T', 'G'};
 
 // k distinct indices out of n, ascending
-std::vector<size_t> sample_sorted(std::mt19937_64 &rng, size_t n, size_t k) {
+template <class Rng>
+std::vector<size_t> sample_sorted(Rng &rng, size_t n, size_t k) {
   std::vector<size_t> idx;
   if (k * 4 >= n) {  // dense: partial shuffle
     std::vector<size_t> all(n);
@@ -284,96 +318,178 @@ std::vector<size_t> sample_sorted(std::mt19937_64 &rng, size_t n, size_t k) {
   return idx;
 }
 
-size_t poisson_count(std::mt19937_64 &rng, double lambda, size_t cap) {
+// number of events ~ Poisson(lambda), at most cap.  Small rates (the usual case: 1e-6 per base)
+// by inversion of the distribution function from one uniform number.
+template <class Rng>
+size_t poisson_count(Rng &rng, double lambda, size_t cap) {
   if (!(lambda > 0.0)) return 0;
+  if (lambda < 16.0) {
+    const double u = std::generate_canonical<double, 53>(rng);
+    double pk = std::exp(-lambda), cdf = pk;
+    size_t n = 0;
+    while (u >= cdf && n < cap && pk > 0.0) {
+      n++;
+      pk *= lambda / (double)n;
+      cdf += pk;
+    }
+    return std::min(n, cap);
+  }
   const size_t n = (size_t)std::poisson_distribution<long long>(lambda)(rng);
   return std::min(n, cap);
 }
 
 // rust/mutations.rs:11-72: Poisson(p * len) positions; each an indel with p_indel (deletion with
-// p_del, else insertion of a random nucleotide before it), else a substitution
-std::vector<std::pair<std::string, size_t>> point_mutations(const std::vector<std::string> &seqs, double p,
-                                                            double p_indel, double p_del) {
-  const uint64_t seed = next_seed();
-  std::vector<std::string> mutated(seqs.size());
-  std::vector<char> hit(seqs.size(), 0);
-#pragma omp parallel for schedule(dynamic, 64)
-  for (long long s = 0; s < (long long)seqs.size(); s++) {
-    const std::string &src = seqs[s];
-    if (src.empty()) continue;
-    std::mt19937_64 rng(seed ^ (0x9e3779b97f4a7c15ull * (uint64_t)(s + 1)));
-    const size_t n_muts = poisson_count(rng, p * (double)src.size(), src.size());
-    if (n_muts == 0) continue;
-    const auto where = sample_sorted(rng, src.size(), n_muts);
-    std::bernoulli_distribution indel(std::clamp(p_indel, 0.0, 1.0)), del(std::clamp(p_del, 0.0, 1.0));
-    std::uniform_int_distribution<int> nt(0, 3);
-    std::string out;
-    out.reserve(src.size() + n_muts);
-    size_t next = 0;
-    for (size_t i = 0; i < src.size(); i++) {
-      if (next < where.size() && where[next] == i) {
-        next++;
-        if (indel(rng)) {
-          if (del(rng)) continue;          // deletion
-          out.push_back(NTS[nt(rng)]);     // insertion before position i
-          out.push_back(src[i]);
-        } else {
-          out.push_back(NTS[nt(rng)]);     // substitution (may draw the same nucleotide, like the reference)
-        }
-      } else {
+// p_del, else insertion of a random nucleotide before it), else a substitution.
+// The number of events depends on the length alone, so the callers below draw it for every
+// sequence first and copy only the sequences that are hit out of their Python strings: at the
+// reference's default rates (1e-6 per base) that is a handful of genomes out of thousands.
+std::string mutate_one(const std::string &src, SeqRng &rng, size_t n_muts, double p_indel, double p_del) {
+  const auto where = sample_sorted(rng, src.size(), std::min(n_muts, src.size()));
+  const double q_indel = std::clamp(p_indel, 0.0, 1.0), q_del = std::clamp(p_del, 0.0, 1.0);
+  std::string out;
+  out.reserve(src.size() + n_muts);
+  size_t next = 0;
+  for (size_t i = 0; i < src.size(); i++) {
+    if (next < where.size() && where[next] == i) {
+      next++;
+      if (rng.uniform() < q_indel) {
+        if (rng.uniform() < q_del) continue;  // deletion
+        out.push_back(NTS[rng() >> 62]);      // insertion before position i
         out.push_back(src[i]);
+      } else {
+        out.push_back(NTS[rng() >> 62]);      // substitution (may draw the same nucleotide, like the reference)
       }
+    } else {
+      out.push_back(src[i]);
     }
-    mutated[s] = std::move(out);
-    hit[s] = 1;
   }
-  std::vector<std::pair<std::string, size_t>> res;
-  for (size_t s = 0; s < seqs.size(); s++)
-    if (hit[s]) res.emplace_back(std::move(mutated[s]), s);
-  return res;
+  return out;
 }
 
 // rust/mutations.rs:78-154: Poisson(p * (n0 + n1)) strand breaks over both sequences, the
 // fragments are shuffled and re-joined into two sequences at a random cut of the fragment list
-std::vector<std::tuple<std::string, std::string, size_t>> recombinations(
-    const std::vector<std::pair<std::string, std::string>> &pairs, double p) {
-  const uint64_t seed = next_seed();
-  std::vector<std::tuple<std::string, std::string, size_t>> slots(pairs.size());
-  std::vector<char> hit(pairs.size(), 0);
-#pragma omp parallel for schedule(dynamic, 64)
-  for (long long s = 0; s < (long long)pairs.size(); s++) {
-    const std::string &a = pairs[s].first, &b = pairs[s].second;
-    const size_t n0 = a.size(), n_both = a.size() + b.size();
-    if (n_both == 0) continue;
-    std::mt19937_64 rng(seed ^ (0xd1b54a32d192ed03ull * (uint64_t)(s + 1)));
-    const size_t n_breaks = poisson_count(rng, p * (double)n_both, n_both);
-    if (n_breaks == 0) continue;
-    const auto where = sample_sorted(rng, n_both, n_breaks);
-    std::vector<std::string> parts;
-    parts.reserve(n_breaks + 2);
-    size_t i = 0, k = 0;
-    for (; k < where.size() && where[k] < n0; k++) {
-      parts.push_back(a.substr(i, where[k] - i));
-      i = where[k];
-    }
-    parts.push_back(a.substr(i));
-    i = 0;
-    for (; k < where.size(); k++) {
-      parts.push_back(b.substr(i, where[k] - n0 - i));
-      i = where[k] - n0;
-    }
-    parts.push_back(b.substr(i));
-    std::shuffle(parts.begin(), parts.end(), rng);
-    const size_t cut = std::uniform_int_distribution<size_t>(0, parts.size() - 1)(rng);
-    std::string x, y;
-    for (size_t q = 0; q < parts.size(); q++) (q < cut ? x : y) += parts[q];
-    slots[s] = std::make_tuple(std::move(x), std::move(y), (size_t)s);
-    hit[s] = 1;
+std::pair<std::string, std::string> recombine_one(const std::string &a, const std::string &b, SeqRng &rng,
+                                                  size_t n_breaks) {
+  const size_t n0 = a.size(), n_both = a.size() + b.size();
+  const auto where = sample_sorted(rng, n_both, std::min(n_breaks, n_both));
+  std::vector<std::string> parts;
+  parts.reserve(where.size() + 2);
+  size_t i = 0, k = 0;
+  for (; k < where.size() && where[k] < n0; k++) {
+    parts.push_back(a.substr(i, where[k] - i));
+    i = where[k];
   }
-  std::vector<std::tuple<std::string, std::string, size_t>> res;
-  for (size_t s = 0; s < pairs.size(); s++)
-    if (hit[s]) res.push_back(std::move(slots[s]));
+  parts.push_back(a.substr(i));
+  i = 0;
+  for (; k < where.size(); k++) {
+    parts.push_back(b.substr(i, where[k] - n0 - i));
+    i = where[k] - n0;
+  }
+  parts.push_back(b.substr(i));
+  std::shuffle(parts.begin(), parts.end(), rng);
+  const size_t cut = (size_t)(rng.uniform() * (double)parts.size());
+  std::string x, y;
+  for (size_t q = 0; q < parts.size(); q++) (q < cut ? x : y) += parts[q];
+  return {std::move(x), std::move(y)};
+}
+
+// a Python str as (length in code points) / (UTF-8 copy); genomes are ASCII, so both agree
+size_t str_len(PyObject *o) {
+  if (!PyUnicode_Check(o)) throw py::type_error("expected str");
+  return (size_t)PyUnicode_GET_LENGTH(o);
+}
+std::string str_copy(PyObject *o) {
+  Py_ssize_t n = 0;
+  const char *d = PyUnicode_AsUTF8AndSize(o, &n);
+  if (!d) throw py::error_already_set();
+  return std::string(d, (size_t)n);
+}
+
+std::vector<std::pair<std::string, size_t>> point_mutations(const py::sequence &seqs, double p, double p_indel,
+                                                            double p_del) {
+  const py::object fast = py::reinterpret_steal<py::object>(PySequence_Fast(seqs.ptr(), "seqs must be a sequence of str"));
+  if (!fast) throw py::error_already_set();
+  const size_t n = (size_t)PySequence_Fast_GET_SIZE(fast.ptr());
+  const uint64_t seed = next_seed();
+  std::vector<size_t> hit, hit_len;
+  std::vector<std::string> src;
+  for (size_t s = 0; s < n; s++) {
+    PyObject *o = PySequence_Fast_GET_ITEM(fast.ptr(), (Py_ssize_t)s);
+    const size_t len = str_len(o);
+    if (len == 0) continue;
+    SeqRng rng(seed, s);
+    if (poisson_count(rng, p * (double)len, len) == 0) continue;
+    hit.push_back(s);
+    hit_len.push_back(len);
+    src.push_back(str_copy(o));
+  }
+  std::vector<std::pair<std::string, size_t>> res(hit.size());
+  {
+    py::gil_scoped_release release;
+#pragma omp parallel for schedule(dynamic, 16) if (hit.size() > 64)
+    for (long long h = 0; h < (long long)hit.size(); h++) {
+      SeqRng rng(seed, hit[h]);
+      const size_t n_muts = poisson_count(rng, p * (double)hit_len[h], hit_len[h]);  // the same draw again
+      res[h] = {mutate_one(src[h], rng, n_muts, p_indel, p_del), hit[h]};
+    }
+  }
   return res;
+}
+
+// `pair_at(s)` yields the two Python strings of pair s
+template <class PairAt>
+std::vector<std::tuple<std::string, std::string, size_t>> recombine_pairs(size_t n_pairs, double p, PairAt pair_at) {
+  const uint64_t seed = next_seed();
+  std::vector<size_t> hit, hit_len;
+  std::vector<std::pair<std::string, std::string>> src;
+  for (size_t s = 0; s < n_pairs; s++) {
+    const std::pair<PyObject *, PyObject *> ab = pair_at(s);
+    const size_t n_both = str_len(ab.first) + str_len(ab.second);
+    if (n_both == 0) continue;
+    SeqRng rng(seed, s);
+    if (poisson_count(rng, p * (double)n_both, n_both) == 0) continue;
+    hit.push_back(s);
+    hit_len.push_back(n_both);
+    src.emplace_back(str_copy(ab.first), str_copy(ab.second));
+  }
+  std::vector<std::tuple<std::string, std::string, size_t>> res(hit.size());
+  {
+    py::gil_scoped_release release;
+#pragma omp parallel for schedule(dynamic, 16) if (hit.size() > 64)
+    for (long long h = 0; h < (long long)hit.size(); h++) {
+      SeqRng rng(seed, hit[h]);
+      const size_t n_breaks = poisson_count(rng, p * (double)hit_len[h], hit_len[h]);
+      auto xy = recombine_one(src[h].first, src[h].second, rng, n_breaks);
+      res[h] = std::make_tuple(std::move(xy.first), std::move(xy.second), hit[h]);
+    }
+  }
+  return res;
+}
+
+std::vector<std::tuple<std::string, std::string, size_t>> recombinations(const py::sequence &seq_pairs, double p) {
+  const py::object fast = py::reinterpret_steal<py::object>(PySequence_Fast(seq_pairs.ptr(), "seq_pairs must be a sequence"));
+  if (!fast) throw py::error_already_set();
+  const size_t n = (size_t)PySequence_Fast_GET_SIZE(fast.ptr());
+  return recombine_pairs(n, p, [&](size_t s) {
+    PyObject *pair = PySequence_Fast_GET_ITEM(fast.ptr(), (Py_ssize_t)s);
+    if (PyTuple_Check(pair) && PyTuple_GET_SIZE(pair) == 2)
+      return std::pair<PyObject *, PyObject *>(PyTuple_GET_ITEM(pair, 0), PyTuple_GET_ITEM(pair, 1));
+    if (PyList_Check(pair) && PyList_GET_SIZE(pair) == 2)
+      return std::pair<PyObject *, PyObject *>(PyList_GET_ITEM(pair, 0), PyList_GET_ITEM(pair, 1));
+    throw py::type_error("seq_pairs must hold pairs of str");
+  });
+}
+
+// recombinations((genomes[a], genomes[b]) for a, b in pairs) without building the pairs of strings
+std::vector<std::tuple<std::string, std::string, size_t>> recombinations_indexed(
+    const py::list &genomes, const std::vector<std::pair<size_t, size_t>> &pairs, double p) {
+  const size_t n_genomes = (size_t)py::len(genomes);
+  for (const auto &ab : pairs)
+    if (ab.first >= n_genomes || ab.second >= n_genomes) throw py::index_error("genome index out of range");
+  return recombine_pairs(pairs.size(), p, [&](size_t s) {
+    return std::pair<PyObject *, PyObject *>(PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)pairs[s].first),
+                                             PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)pairs[s].second));
+  });
 }
 
 // ---------------------------------------------------------------------------- world
@@ -402,61 +518,106 @@ std::vector<Pos> free_moores_nghbhd(uint16_t x, uint16_t y, const std::vector<Po
   return out;
 }
 
-// rust/world.rs:9-56: unique pairs (smaller index first) of cells from `from_idxs` and `to_idxs` at
-// torus distance <= 1 in both coordinates, in the reference's order (from_idxs order, then
-// to_idxs order, first occurrence kept)
-std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &from_idxs,
-                                                     const std::vector<size_t> &to_idxs,
-                                                     const std::vector<Pos> &positions, uint16_t map_size) {
-  std::unordered_map<uint32_t, std::vector<size_t>> grid;  // pixel -> ranks in to_idxs
-  grid.reserve(to_idxs.size() * 2);
-  for (size_t r = 0; r < to_idxs.size(); r++) {
-    const Pos &p = positions.at(to_idxs[r]);
-    grid[pixel_key(p.first, p.second)].push_back(r);
-  }
-  std::vector<std::pair<size_t, size_t>> out;
-  std::unordered_set<uint64_t> seen;
-  std::vector<size_t> ranks;
-  for (const size_t from : from_idxs) {
-    const Pos &p0 = positions.at(from);
-    ranks.clear();
-    std::unordered_set<uint32_t> pixels;  // the 3 x 3 block, without duplicates on tiny maps
-    pixels.insert(pixel_key(p0.first, p0.second));
-    for (const auto &p : moore(p0.first, p0.second, map_size)) pixels.insert(pixel_key(p.first, p.second));
-    for (const uint32_t key : pixels) {
-      auto it = grid.find(key);
-      if (it != grid.end()) ranks.insert(ranks.end(), it->second.begin(), it->second.end());
-    }
-    std::sort(ranks.begin(), ranks.end());
-    for (const size_t r : ranks) {
-      const size_t to = to_idxs[r];
-      if (to == from) continue;
-      const size_t a = std::min(from, to), b = std::max(from, to);
-      if (seen.insert(((uint64_t)a << 32) | (uint64_t)b).second) out.emplace_back(a, b);
+// first occurrences of a list of indices, order kept
+std::vector<size_t> unique_in_order(const std::vector<size_t> &idxs, size_t n) {
+  std::vector<char> seen(n, 0);
+  std::vector<size_t> out;
+  out.reserve(idxs.size());
+  for (const size_t i : idxs) {
+    if (i >= n) throw py::index_error("cell index out of range");
+    if (!seen[i]) {
+      seen[i] = 1;
+      out.push_back(i);
     }
   }
   return out;
 }
 
+// rust/world.rs:9-56: unique pairs (smaller index first) of cells from `from_idxs` and `to_idxs` at
+// torus distance <= 1 in both coordinates, in the reference's order (from_idxs order, then
+// to_idxs order, first occurrence kept).  The reference compares every `from` with every `to`;
+// here the `to` cells are chained per pixel of an occupancy grid and a `from` cell looks at its
+// 3 x 3 block.  A pair is found twice exactly when both cells are in both lists: the second find
+// is recognised by the ranks of the two cells in from_idxs, no set of seen pairs is kept.
+std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &from_raw,
+                                                     const std::vector<size_t> &to_raw,
+                                                     const std::vector<Pos> &positions, uint16_t map_size) {
+  const size_t n = positions.size();
+  const std::vector<size_t> from_idxs = unique_in_order(from_raw, n), to_idxs = unique_in_order(to_raw, n);
+  constexpr int64_t NONE = -1;
+  std::vector<int64_t> from_rank(n, NONE), to_rank(n, NONE);
+  for (size_t r = 0; r < from_idxs.size(); r++) from_rank[from_idxs[r]] = (int64_t)r;
+  for (size_t r = 0; r < to_idxs.size(); r++) to_rank[to_idxs[r]] = (int64_t)r;
+  // pixel -> chain of ranks in to_idxs (ascending rank along the chain)
+  const size_t m = map_size;
+  for (const size_t i : to_idxs)
+    if (positions[i].first >= m || positions[i].second >= m) throw py::index_error("position outside the map");
+  std::vector<int64_t> head(m * m, NONE), next(to_idxs.size(), NONE);
+  for (size_t r = to_idxs.size(); r-- > 0;) {
+    const Pos &q = positions[to_idxs[r]];
+    const size_t px = (size_t)q.first * m + q.second;
+    next[r] = head[px];
+    head[px] = (int64_t)r;
+  }
+  std::vector<std::pair<size_t, size_t>> out;
+  std::vector<int64_t> ranks;
+  for (const size_t from : from_idxs) {
+    const Pos &p0 = positions[from];
+    if (p0.first >= m || p0.second >= m) throw py::index_error("position outside the map");
+    std::array<uint32_t, 9> pixels;  // the 3 x 3 block, without duplicates on tiny maps
+    size_t n_px = 0;
+    pixels[n_px++] = pixel_key(p0.first, p0.second);
+    for (const auto &q : moore(p0.first, p0.second, map_size)) pixels[n_px++] = pixel_key(q.first, q.second);
+    if (m < 3) {
+      std::sort(pixels.begin(), pixels.begin() + n_px);
+      n_px = (size_t)(std::unique(pixels.begin(), pixels.begin() + n_px) - pixels.begin());
+    }
+    ranks.clear();
+    for (size_t k = 0; k < n_px; k++)
+      for (int64_t r = head[(size_t)(pixels[k] >> 16) * m + (pixels[k] & 0xffffu)]; r != NONE; r = next[r]) ranks.push_back(r);
+    std::sort(ranks.begin(), ranks.end());
+    for (const int64_t r : ranks) {
+      const size_t to = to_idxs[(size_t)r];
+      if (to == from) continue;
+      // found before, from the other side: `to` came earlier in from_idxs and `from` is a `to` cell
+      if (from_rank[to] != NONE && from_rank[to] < from_rank[from] && to_rank[from] != NONE) continue;
+      out.emplace_back(std::min(from, to), std::max(from, to));
+    }
+  }
+  return out;
+}
+
+// cells per pixel of a square map
+struct Occupancy {
+  size_t m;
+  std::vector<int32_t> count;
+  Occupancy(const std::vector<Pos> &positions, uint16_t map_size) : m(map_size), count((size_t)map_size * map_size, 0) {
+    for (const auto &p : positions) {
+      if (p.first >= m || p.second >= m) throw py::index_error("position outside the map");
+      count[(size_t)p.first * m + p.second]++;
+    }
+  }
+  int32_t &at(const Pos &p) { return count[(size_t)p.first * m + p.second]; }
+};
+
 // rust/world.rs:59-99: in the order of cell_idxs, every cell picks one free Moore pixel at random
 // (free of all current cells and of the children placed before it); children get indices n_cells..
 std::tuple<std::vector<size_t>, std::vector<size_t>, std::vector<Pos>> divide_cells_if_possible(
     const std::vector<size_t> &cell_idxs, const std::vector<Pos> &positions, size_t n_cells, uint16_t map_size) {
-  std::unordered_set<uint32_t> occ;
-  occ.reserve((positions.size() + cell_idxs.size()) * 2);
-  for (const auto &p : positions) occ.insert(pixel_key(p.first, p.second));
-  std::mt19937_64 rng(next_seed());
+  Occupancy occ(positions, map_size);
+  SeqRng rng(next_seed(), 0);
   std::vector<size_t> parents, children;
   std::vector<Pos> child_pos;
   size_t next = n_cells;
   for (const size_t idx : cell_idxs) {
     const Pos &p0 = positions.at(idx);
-    std::vector<Pos> opts;
+    std::array<Pos, 8> opts;
+    size_t n_opts = 0;
     for (const auto &p : moore(p0.first, p0.second, map_size))
-      if (!occ.count(pixel_key(p.first, p.second))) opts.push_back(p);
-    if (opts.empty()) continue;
-    const Pos pick = opts[std::uniform_int_distribution<size_t>(0, opts.size() - 1)(rng)];
-    occ.insert(pixel_key(pick.first, pick.second));
+      if (occ.at(p) == 0) opts[n_opts++] = p;
+    if (n_opts == 0) continue;
+    const Pos pick = opts[(size_t)(rng.uniform() * (double)n_opts)];
+    occ.at(pick)++;
     parents.push_back(idx);
     children.push_back(next++);
     child_pos.push_back(pick);
@@ -469,27 +630,40 @@ std::tuple<std::vector<size_t>, std::vector<size_t>, std::vector<Pos>> divide_ce
 std::tuple<std::vector<Pos>, std::vector<size_t>> move_cells(const std::vector<size_t> &cell_idxs,
                                                              const std::vector<Pos> &positions,
                                                              uint16_t map_size) {
-  std::unordered_map<uint32_t, int> occ;  // pixel -> number of cells on it (all cells, current positions)
-  occ.reserve(positions.size() * 2);
-  for (const auto &p : positions) occ[pixel_key(p.first, p.second)]++;
-  std::mt19937_64 rng(next_seed());
+  Occupancy occ(positions, map_size);
+  SeqRng rng(next_seed(), 0);
   std::vector<Pos> new_pos;
   std::vector<size_t> moved;
   for (const size_t idx : cell_idxs) {
     const Pos p0 = positions.at(idx);
-    std::vector<Pos> opts;
-    for (const auto &p : moore(p0.first, p0.second, map_size)) {
-      auto it = occ.find(pixel_key(p.first, p.second));
-      if (it == occ.end() || it->second == 0) opts.push_back(p);
-    }
-    if (opts.empty()) continue;
-    const Pos pick = opts[std::uniform_int_distribution<size_t>(0, opts.size() - 1)(rng)];
-    occ[pixel_key(p0.first, p0.second)]--;
-    occ[pixel_key(pick.first, pick.second)]++;
+    std::array<Pos, 8> opts;
+    size_t n_opts = 0;
+    for (const auto &p : moore(p0.first, p0.second, map_size))
+      if (occ.at(p) == 0) opts[n_opts++] = p;
+    if (n_opts == 0) continue;
+    const Pos pick = opts[(size_t)(rng.uniform() * (double)n_opts)];
+    occ.at(p0)--;
+    occ.at(pick)++;
     new_pos.push_back(pick);
     moved.push_back(idx);
   }
   return {new_pos, moved};
+}
+
+// positions as a list of (x, y) pairs (the reference's interface) or as an (n, 2) integer array
+std::vector<Pos> positions_from(const py::object &obj) {
+  if (py::isinstance<py::array>(obj)) {
+    const auto arr = py::array_t<int64_t, py::array::c_style | py::array::forcecast>::ensure(obj);
+    if (!arr || arr.ndim() != 2 || arr.shape(1) != 2) throw py::value_error("positions must have shape (n, 2)");
+    const auto v = arr.unchecked<2>();
+    std::vector<Pos> out((size_t)arr.shape(0));
+    for (py::ssize_t i = 0; i < arr.shape(0); i++) {
+      if (v(i, 0) < 0 || v(i, 0) > 0xffff || v(i, 1) < 0 || v(i, 1) > 0xffff) throw py::index_error("position outside the map");
+      out[(size_t)i] = {(uint16_t)v(i, 0), (uint16_t)v(i, 1)};
+    }
+    return out;
+  }
+  return obj.cast<std::vector<Pos>>();
 }
 
 CodonMaps make_maps(const std::unordered_map<std::string, int> &dom_type, const std::unordered_map<std::string, int> &one,
@@ -509,9 +683,10 @@ PYBIND11_MODULE(_lib, m) {
   }, py::arg("seed"), "seed the generator behind the random choices (the reference's is not seedable)");
   m.def("dist_1d", &dist_1d, py::arg("a"), py::arg("b"), py::arg("m"));
   m.def("free_moores_nghbhd", &free_moores_nghbhd, py::arg("x"), py::arg("y"), py::arg("positions"), py::arg("map_size"));
-  m.def("point_mutations", &point_mutations, py::arg("seqs"), py::arg("p"), py::arg("p_indel"), py::arg("p_del"),
-        py::call_guard<py::gil_scoped_release>());
-  m.def("recombinations", &recombinations, py::arg("seq_pairs"), py::arg("p"), py::call_guard<py::gil_scoped_release>());
+  m.def("point_mutations", &point_mutations, py::arg("seqs"), py::arg("p"), py::arg("p_indel"), py::arg("p_del"));
+  m.def("recombinations", &recombinations, py::arg("seq_pairs"), py::arg("p"));
+  m.def("recombinations_indexed", &recombinations_indexed, py::arg("genomes"), py::arg("pairs"), py::arg("p"),
+        "no counterpart in the reference: recombinations() over index pairs into one list of genomes");
   m.def("get_coding_regions",
         [](const std::string &seq, size_t min_cds_size, const std::vector<std::string> &start_codons,
            const std::vector<std::string> &stop_codons, bool is_fwd) {
@@ -618,10 +793,43 @@ PYBIND11_MODULE(_lib, m) {
           for (PyObject *r : removed) Py_DECREF(r);  // after the list is consistent again
         },
         py::arg("items"), py::arg("dead_sorted"));
-  m.def("get_neighbors", &get_neighbors, py::arg("from_idxs"), py::arg("to_idxs"), py::arg("positions"),
-        py::arg("map_size"), py::call_guard<py::gil_scoped_release>());
-  m.def("divide_cells_if_possible", &divide_cells_if_possible, py::arg("cell_idxs"), py::arg("positions"),
-        py::arg("n_cells"), py::arg("map_size"), py::call_guard<py::gil_scoped_release>());
-  m.def("move_cells", &move_cells, py::arg("cell_idxs"), py::arg("positions"), py::arg("map_size"),
-        py::call_guard<py::gil_scoped_release>());
+  m.def("get_neighbors",
+        [](const std::vector<size_t> &from_idxs, const std::vector<size_t> &to_idxs, const py::object &positions,
+           uint16_t map_size) {
+          const auto pos = positions_from(positions);
+          py::gil_scoped_release release;
+          return get_neighbors(from_idxs, to_idxs, pos, map_size);
+        },
+        py::arg("from_idxs"), py::arg("to_idxs"), py::arg("positions"), py::arg("map_size"));
+  m.def("neighbor_recombinations",
+        [](const py::list &genomes, const std::vector<size_t> &cell_idxs, const py::object &positions, uint16_t map_size,
+           double p) {
+          // World.recombinate_cells in one call (world.py:716-745): neighbour pairs among cell_idxs,
+          // recombinations between their genomes; only the pairs that were hit come back, as
+          // (genome a, genome b, a, b).  No list of pairs crosses the language boundary.
+          const auto pos = positions_from(positions);
+          if ((size_t)py::len(genomes) != pos.size()) throw py::value_error("one genome per position expected");
+          const auto pairs = get_neighbors(cell_idxs, cell_idxs, pos, map_size);
+          const auto hits = recombinations_indexed(genomes, pairs, p);
+          std::vector<std::tuple<std::string, std::string, size_t, size_t>> out;
+          out.reserve(hits.size());
+          for (const auto &[x, y, s] : hits) out.emplace_back(x, y, pairs[s].first, pairs[s].second);
+          return out;
+        },
+        py::arg("genomes"), py::arg("cell_idxs"), py::arg("positions"), py::arg("map_size"), py::arg("p"),
+        "no counterpart in the reference");
+  m.def("divide_cells_if_possible",
+        [](const std::vector<size_t> &cell_idxs, const py::object &positions, size_t n_cells, uint16_t map_size) {
+          const auto pos = positions_from(positions);
+          py::gil_scoped_release release;
+          return divide_cells_if_possible(cell_idxs, pos, n_cells, map_size);
+        },
+        py::arg("cell_idxs"), py::arg("positions"), py::arg("n_cells"), py::arg("map_size"));
+  m.def("move_cells",
+        [](const std::vector<size_t> &cell_idxs, const py::object &positions, uint16_t map_size) {
+          const auto pos = positions_from(positions);
+          py::gil_scoped_release release;
+          return move_cells(cell_idxs, pos, map_size);
+        },
+        py::arg("cell_idxs"), py::arg("positions"), py::arg("map_size"));
 }

@@ -450,8 +450,9 @@ class World:
 
     # ------------------------------------------------------------------ genome-driven lifecycle
     # (world.py:229-608, 689-745, 880-920; string and map searches in magicsoup_b200._lib)
-    def _positions_list(self) -> list[tuple[int, int]]:
-        return [(int(x), int(y)) for x, y in self.cell_positions.tolist()]
+    def _positions_array(self):
+        """cell positions as an (n, 2) host array for the map searches of `_lib`"""
+        return self.cell_positions.cpu().numpy()
 
     def _square_size(self) -> int:
         if not isinstance(self.map_size, int):
@@ -466,7 +467,7 @@ class World:
         to_idxs = list(set(cell_idxs)) if nghbr_idxs is None else list(set(nghbr_idxs))
         if len(to_idxs) == 0:
             return []
-        return _hostlib().get_neighbors(from_idxs, to_idxs, self._positions_list(), self._square_size())
+        return _hostlib().get_neighbors(from_idxs, to_idxs, self._positions_array(), self._square_size())
 
     def spawn_cells(self, genomes: list[str]) -> list[int]:
         """world.py:287-341: new cells on random free pixels, each takes half of its pixel's molecules"""
@@ -503,7 +504,7 @@ class World:
         if len(cell_idxs) == 0:
             return []
         parents, children, child_pos = _hostlib().divide_cells_if_possible(
-            list(set(cell_idxs)), self._positions_list(), self.n_cells, self._square_size())
+            list(set(cell_idxs)), self._positions_array(), self.n_cells, self._square_size())
         if len(children) == 0:
             return []
         pos = torch.tensor(child_pos, dtype=torch.int32, device=self.cell_positions.device)
@@ -525,7 +526,7 @@ class World:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
             return
-        new_pos, moved = _hostlib().move_cells(sorted(set(cell_idxs)), self._positions_list(), self._square_size())
+        new_pos, moved = _hostlib().move_cells(sorted(set(cell_idxs)), self._positions_array(), self._square_size())
         if len(moved) == 0:
             return
         old = self.cell_positions[moved].long()
@@ -563,12 +564,17 @@ class World:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
             return
-        nghbrs = self.get_neighbors(cell_idxs=cell_idxs)
-        pairs = [(self.cell_genomes[a], self.cell_genomes[b]) for a, b in nghbrs]
-        changed = []
-        for g0, g1, idx in recombinations(seq_pairs=pairs, p=p):
-            a, b = nghbrs[idx]
-            changed += [(g0, a), (g1, b)]
+        if type(self).get_neighbors is World.get_neighbors and isinstance(self.cell_genomes, list):
+            hits = _hostlib().neighbor_recombinations(self.cell_genomes, list(set(cell_idxs)), self._positions_array(),
+                                                     self._square_size(), p)
+            changed = [pair for g0, g1, a, b in hits for pair in ((g0, a), (g1, b))]
+        else:
+            nghbrs = self.get_neighbors(cell_idxs=cell_idxs)
+            pairs = [(self.cell_genomes[a], self.cell_genomes[b]) for a, b in nghbrs]
+            changed = []
+            for g0, g1, idx in recombinations(seq_pairs=pairs, p=p):
+                a, b = nghbrs[idx]
+                changed += [(g0, a), (g1, b)]
         self.update_cells(genome_idx_pairs=changed)
 
     def _update_cell_params(self, genomes: list[str], idxs: list[int]):

@@ -294,3 +294,44 @@ def test_remove_items_in_place():
         lib().remove_items([1, 2, 3], [1, 1])
     with pytest.raises(IndexError):
         lib().remove_items([1, 2, 3], [3])
+
+
+def test_lazy_mutation_entry_points():
+    """point_mutations / recombinations read only the sequences that are hit; the indexed and the
+    fused neighbour variants give what the reference's two-step composition gives"""
+    import numpy as np
+
+    random.seed(12)
+    genomes = [util.random_genome(s=random.choice([0, 50, 400])) for _ in range(400)]
+    assert lib().point_mutations(genomes, 0.0, 0.4, 0.66) == []
+    assert lib().recombinations([(genomes[0], genomes[1])], 0.0) == []
+    with pytest.raises(TypeError):
+        lib().point_mutations(["ACGT", 5], 0.5, 0.4, 0.66)
+    with pytest.raises(TypeError):
+        lib().recombinations([("ACGT",)], 0.5)
+    # tuples as well as lists, generators of pairs
+    res = lib().recombinations([[genomes[1], genomes[2]], (genomes[3], genomes[4])], 0.05)
+    for a, b, i in res:
+        src = (genomes[1] + genomes[2], genomes[3] + genomes[4])[i]
+        assert sorted(a + b) == sorted(src)
+    # same seed, same pairs: the indexed variant is the same computation
+    pairs = [(random.randrange(400), random.randrange(400)) for _ in range(300)]
+    lib().seed(77)
+    by_string = lib().recombinations([(genomes[a], genomes[b]) for a, b in pairs], 0.01)
+    lib().seed(77)
+    by_index = lib().recombinations_indexed(genomes, pairs, 0.01)
+    assert by_string == by_index and len(by_index) > 20
+    with pytest.raises(IndexError):
+        lib().recombinations_indexed(genomes, [(0, 400)], 0.01)
+    # fused: neighbours among the given cells, then recombinations between them
+    size = 30
+    cells = random.sample([(x, y) for x in range(size) for y in range(size)], 400)
+    pos = np.array(cells, dtype=np.int32)
+    idxs = list(range(0, 400, 2))
+    nghbrs = lib().get_neighbors(idxs, idxs, pos, size)
+    assert nghbrs == lib().get_neighbors(idxs, idxs, cells, size) == HO.get_neighbors(idxs, idxs, cells, size)
+    lib().seed(78)
+    want = [(a, b) + nghbrs[i] for a, b, i in lib().recombinations_indexed(genomes, nghbrs, 0.02)]
+    lib().seed(78)
+    got = lib().neighbor_recombinations(genomes, idxs, pos, size, 0.02)
+    assert got == want and len(got) > 3

@@ -148,8 +148,46 @@ def simulation_loop(device, n_start: int, n_steps: int, map_size: int = 256, gen
             "first_step_s": stages["perStep"][0], "proteins_max": int(world.kinetics.N.shape[1])}
 
 
+def readme_loop(device, n_steps: int = 1000) -> dict:
+    """BASELINE.json configs[0]: the loop of the reference's README (README.md:49-114)"""
+    import torch
+
+    import magicsoup_b200 as ms
+
+    random.seed(23)
+    torch.manual_seed(23)
+    mols = [ms.Molecule("rl-NADPH", 200e3), ms.Molecule("rl-NADP", 100e3), ms.Molecule("rl-formiat", 20e3),
+            ms.Molecule("rl-CO2", 10e3)]
+    chem = ms.Chemistry(molecules=mols, reactions=[([mols[3], mols[0]], [mols[2], mols[1]])])
+    world = ms.World(chemistry=chem, device=str(device))
+    world.spawn_cells(genomes=[ms.random_genome(s=500) for _ in range(100)])
+
+    def sample(p):
+        return torch.argwhere(torch.bernoulli(p)).flatten().tolist()
+
+    def loop():
+        for _ in range(n_steps):
+            world.enzymatic_activity()
+            x = world.cell_molecules[:, 2]
+            sizes = torch.tensor([float(len(g)) for g in world.cell_genomes], device=x.device)
+            too_big = sample(sizes ** 7 / (sizes ** 7 + 3000.0 ** 7))  # docs/tutorials.md:191-208: without it genomes grow without bound
+            world.kill_cells(cell_idxs=sorted(set(sample(0.01 / (0.01 + x)) + too_big)))
+            x = world.cell_molecules[:, 2]
+            world.divide_cells(cell_idxs=sample(x ** 3 / (x ** 3 + 20.0 ** 3)))
+            world.mutate_cells(p=1e-4)
+            world.recombinate_cells(p=1e-6)
+            world.diffuse_molecules()
+
+    t = _Clock(device)(loop)
+    return {"what": "README.md:49-114: CO2 + NADPH <-> formiat + NADP, 100 random 500-bp genomes, 128 x 128 map, "
+                    "activity / kill (+ the size-dependent kill of docs/tutorials.md:191-208) / replicate / mutate / "
+                    "recombinate / diffuse", "steps": n_steps, "total_s": t,
+            "ms_per_step": t / n_steps * 1e3, "cells_end": world.n_cells}
+
+
 def reference_workloads(device) -> dict:
     return {
+        "readme_loop": readme_loop(device),
         "check": check_times(device),
         "simulation_loop": {
             "what": "the step of performance/run_simulation.py:56-100 (BASELINE.json configs[1]): Wood-Ljungdahl "

@@ -1762,6 +1762,7 @@ static LaunchPlan plan_tier1(int64_t p, int64_t s) {
   if (!pl.sparse_enabled || pl.smem_bytes > SMEM_PER_CTA_MAX) {
     pl.sparse_enabled = 0;
     pl.e_ent = pl.e_nnz = pl.e_reg = 0;
+    pl.align = align_bytes(1, s);  // the dense path keeps nothing of size p in shared memory
     pl.words_per_warp = 4 * pow2_at_least_32((int)s);
     pl.smem_bytes = (size_t)pl.words_per_warp * 4 * pl.warps_per_cta + pl.align;
   }

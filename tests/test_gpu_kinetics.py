@@ -172,6 +172,7 @@ _SHAPES = [
     (50, 7, 3, 8, 16),         # ragged: s=6, p=7
     (40, 300, 4, 8, 17),       # p > 256: dense path for every cell
     (30, 12, 70, 8, 18),       # s=140 > 128: dense path for every cell
+    (3, 40000, 4, 4, 20),      # a protein axis grown by runaway genomes (p > 32768), s=8
     (1, 5, 2, 4, 19),          # a single cell: the global early exit fires
     (2, 6, 3, 4, 13),          # two cells (the reference's unit-test regime)
 ]

@@ -124,3 +124,59 @@ def test_genome_driven_world_loop_matches_oracle():
     assert int(w.cell_map.sum()) == w.n_cells
     nb = w.get_neighbors(cell_idxs=list(range(w.n_cells)))
     assert all(a < b for a, b in nb) and len(nb) == len(set(nb))
+
+
+def test_config0_readme_loop_1000_steps():
+    """
+    BASELINE.json configs[0], the reference's README example (README.md:49-114): CO2 + NADPH <->
+    formiat + NADP, 100 random 500-bp genomes on a 128 x 128 map, 1000 steps of activity / kill /
+    replicate / mutate / recombinate / diffuse.  enzymatic_activity and diffuse_molecules are compared
+    bit for bit with the CPU oracle in each of the first 100 steps and in every 10th step after.
+    Without a penalty on genome size this loop lets genomes (and with them the protein axis) grow
+    without bound -- at step 250 the largest genome has 1.4 M bases and 35,000 proteins -- "a technical
+    problem" the reference's docs answer with a size-dependent kill (docs/tutorials.md:191-208,
+    524-540); that selection is part of the loop here.
+    """
+    random.seed(31)
+    torch.manual_seed(31)
+    mols = [ms.Molecule("rd-NADPH", 200e3), ms.Molecule("rd-NADP", 100e3), ms.Molecule("rd-formiat", 20e3),
+            ms.Molecule("rd-CO2", 10e3)]
+    chem = ms.Chemistry(molecules=mols, reactions=[([mols[3], mols[0]], [mols[2], mols[1]])])
+    w = ms.World(chemistry=chem, device="cuda")
+    w.spawn_cells(genomes=[ms.random_genome(s=500) for _ in range(100)])
+    assert w.n_cells == 100 and tuple(w.molecule_map.shape) == (4, 128, 128)
+    diffs, perms = [m.diffusivity for m in mols], [m.permeability for m in mols]
+
+    def sample(p):
+        return torch.argwhere(torch.bernoulli(p)).flatten().tolist()
+
+    checked = 0
+    for step in range(1000):
+        check = step < 100 or step % 10 == 0
+        if check:
+            P = O.Params(*[getattr(w.kinetics, k).cpu().numpy() for k in PARAMS])
+            cm, mm = O.enzymatic_activity(P, w.cell_positions.cpu().numpy(), w.cell_molecules.cpu().numpy(),
+                                          w.molecule_map.cpu().numpy())
+        w.enzymatic_activity()
+        if check:
+            assert bits_equal(w.cell_molecules, cm), f"step {step}: " + describe_mismatch(w.cell_molecules, cm)
+            assert bits_equal(w.molecule_map, mm), f"step {step}"
+        x = w.cell_molecules[:, 2]
+        sizes = torch.tensor([float(len(g)) for g in w.cell_genomes], device="cuda")
+        w.kill_cells(cell_idxs=sorted(set(sample(0.01 / (0.01 + x)) + sample(sizes ** 7 / (sizes ** 7 + 3000.0 ** 7)))))
+        x = w.cell_molecules[:, 2]
+        w.divide_cells(cell_idxs=sample(x ** 3 / (x ** 3 + 20.0 ** 3)))
+        w.mutate_cells(p=1e-4)
+        w.recombinate_cells(p=1e-6)
+        if check:
+            cm, mm = O.diffuse_molecules(w.cell_molecules.cpu().numpy(), w.molecule_map.cpu().numpy(),
+                                         w.cell_positions.cpu().numpy(), diffs, perms)
+        w.diffuse_molecules()
+        if check:
+            assert bits_equal(w.cell_molecules, cm), f"step {step} (diffusion)"
+            assert bits_equal(w.molecule_map, mm), f"step {step} (diffusion)"
+            checked += 1
+        assert len(w.cell_genomes) == w.n_cells == w.cell_molecules.shape[0]
+    assert checked == 190 and w.n_cells > 0
+    assert torch.isfinite(w.molecule_map).all() and (w.molecule_map >= 0).all() and (w.cell_molecules >= 0).all()
+    assert int(w.cell_map.sum()) == w.n_cells

@@ -666,6 +666,77 @@ std::vector<Pos> positions_from(const py::object &obj) {
   return obj.cast<std::vector<Pos>>();
 }
 
+// rust/kinetics.rs:17-201: keyword arguments for the reference's Protein / domain containers
+// (containers.py) from a proteome's index tuples and the values Kinetics looked up for them.
+// Per protein i and domain j: vmaxs[i][j], kms[i][j], hills[i][j], signs[i][j] and the three
+// signal vectors reacts / trnspts / effectors [i][j][:].
+py::list get_proteome(const std::vector<ProteinSpec> &proteome, const std::vector<std::vector<float>> &vmaxs,
+                      const std::vector<std::vector<float>> &kms, const std::vector<std::vector<int>> &hills,
+                      const std::vector<std::vector<int>> &signs,
+                      const std::vector<std::vector<std::vector<int>>> &reacts,
+                      const std::vector<std::vector<std::vector<int>>> &trnspts,
+                      const std::vector<std::vector<std::vector<int>>> &effectors,
+                      const std::vector<std::string> &molecules) {
+  const size_t n_mols = molecules.size();
+  const auto first_nonzero = [](const std::vector<int> &v, const char *what) {
+    for (size_t i = 0; i < v.size(); i++)
+      if (v[i] != 0) return i;
+    throw std::runtime_error(what);
+  };
+  py::list out;
+  for (size_t i = 0; i < proteome.size(); i++) {
+    const auto &[doms, cds_start, cds_end, is_fwd] = proteome[i];
+    py::list domains;
+    for (size_t j = 0; j < doms.size(); j++) {
+      const auto &[idxs, start, end] = doms[j];
+      const int kind = std::get<0>(idxs);  // 1 = catalytic, 2 = transporter, 3 = regulatory
+      const int sign = signs.at(i).at(j);
+      py::dict spec;
+      spec["start"] = start;
+      spec["end"] = end;
+      if (kind == 1) {
+        py::list lhs, rhs;  // a molecule appears |n| times on its side
+        const auto &vec = reacts.at(i).at(j);
+        for (size_t k = 0; k < vec.size(); k++) {
+          const int n = vec[k] * sign;
+          if (n == 0) continue;
+          const py::str name(molecules.at(k));
+          for (int r = 0; r < std::abs(vec[k]); r++) (n > 0 ? rhs : lhs).append(name);
+        }
+        spec["km"] = kms.at(i).at(j);
+        spec["vmax"] = vmaxs.at(i).at(j);
+        spec["reaction"] = py::make_tuple(lhs, rhs);
+      } else if (kind == 2) {
+        const auto &vec = trnspts.at(i).at(j);
+        const size_t k = first_nonzero(vec, "No transporter molecule identified");
+        spec["km"] = kms.at(i).at(j);
+        spec["vmax"] = vmaxs.at(i).at(j);
+        spec["is_exporter"] = vec[k] * sign < 0;
+        spec["molecule"] = molecules.at(k);
+      } else if (kind == 3) {
+        const auto &vec = effectors.at(i).at(j);
+        const size_t k = first_nonzero(vec, "No effector molecule identified");
+        spec["km"] = kms.at(i).at(j);
+        spec["hill"] = hills.at(i).at(j);
+        spec["is_transmembrane"] = k >= n_mols;  // the second half of the signals is extracellular
+        spec["is_inhibiting"] = vec[k] * sign < 0;
+        spec["effector"] = molecules.at(k >= n_mols ? k - n_mols : k);
+      }
+      py::dict dom;
+      dom["spec"] = spec;
+      dom["type"] = kind == 1 ? "C" : kind == 2 ? "T" : kind == 3 ? "R" : " ";
+      domains.append(dom);
+    }
+    py::dict prot;
+    prot["cds_start"] = cds_start;
+    prot["cds_end"] = cds_end;
+    prot["is_fwd"] = is_fwd;
+    prot["domains"] = domains;
+    out.append(prot);
+  }
+  return out;
+}
+
 CodonMaps make_maps(const std::unordered_map<std::string, int> &dom_type, const std::unordered_map<std::string, int> &one,
                     const std::unordered_map<std::string, int> &two) {
   CodonMaps m{dom_type, one, two};
@@ -793,6 +864,8 @@ PYBIND11_MODULE(_lib, m) {
           for (PyObject *r : removed) Py_DECREF(r);  // after the list is consistent again
         },
         py::arg("items"), py::arg("dead_sorted"));
+  m.def("get_proteome", &get_proteome, py::arg("proteome"), py::arg("vmaxs"), py::arg("kms"), py::arg("hills"),
+        py::arg("signs"), py::arg("reacts"), py::arg("trnspts"), py::arg("effectors"), py::arg("molecules"));
   m.def("get_neighbors",
         [](const std::vector<size_t> &from_idxs, const std::vector<size_t> &to_idxs, const py::object &positions,
            uint16_t map_size) {

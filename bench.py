@@ -629,13 +629,24 @@ def main():
         w5, _ = build_world(total // world_size, p, m, args.map, args.map, device, seed=300 + rank, world_size=world_size,
                             erange=erange)
         r5 = measure(w5, max(args.steps, 10), max(args.warmup, 3), barrier, device, world_size)
+        del w5
+        torch.cuda.empty_cache()
+        barrier()
+        t0 = time.perf_counter()
+        heights = w4.rebalance()  # slab boundaries follow the cells; map rows and cells move to their new owners
+        barrier()
+        t_rebalance = time.perf_counter() - t0
+        r6 = measure(w4, max(args.steps, 10), max(args.warmup, 3), barrier, device, world_size)
         extra["density_skew"] = {
             "workload": f"rank 0: {int(base * args.skew)} cells, every other rank: {base} cells, {args.map}x{args.map} slab each",
             "ms_per_step": r4["ms_per_step"], "value": total / (r4["ms_per_step"] / 1e3),
             "balanced_ms_per_step": r5["ms_per_step"], "balanced_value": world_size * (total // world_size) / (r5["ms_per_step"] / 1e3),
-            "note": "the step takes as long as the fullest slab's cells; slabs have equal heights and cells are not "
-                    "rebalanced across ranks"}
-        del w4, w5
+            "rebalanced_ms_per_step": r6["ms_per_step"], "rebalanced_value": total / (r6["ms_per_step"] / 1e3),
+            "rebalance_s": t_rebalance, "slab_heights_after": heights, "cells_per_rank_after": w4.global_n_cells(),
+            "note": "cells live with their pixels, so the step takes as long as the fullest slab's cells; "
+                    "SlabWorld.rebalance() moves the slab boundaries (and the rows and cells behind them) until every "
+                    "rank carries the same share of the step's algorithmic bytes"}
+        del w4
     if not args.no_extra and world_size == 1 and args.config == "c4":
         extra["lifecycle"] = lifecycle_rounds(world, device, res["ms_per_step"])
         del world, pop

@@ -3,7 +3,9 @@ Multi-GPU world: one process per GPU (`torch.distributed`, NCCL over NVLink on t
 box, gloo in the CPU tests).  The reference is single-device; this is the
 sharding north_star asks for:
 
-  * the molecule map (m, H, W) is split into `world_size` row slabs of H / world_size rows;
+  * the molecule map (m, H, W) is split into `world_size` row slabs (as even as H allows by
+    default; any heights >= 1 that add up to H can be given, and `rebalance()` moves the slab
+    boundaries so that every rank carries the same share of the step's memory traffic);
   * every cell lives on the rank that owns its pixel's slab, together with its slice of the
     nine kinetics parameter tensors, so the gather/scatter of `enzymatic_activity`
     (world.py:619-625) and the permeation (world.py:651-665) stay local;
@@ -22,13 +24,39 @@ their new pixel, e.g. after a division or move across a slab boundary.
 """
 from __future__ import annotations
 
-from typing import Any
+from typing import Any, Sequence
 
 import torch
 import torch.distributed as dist
 
 from magicsoup_b200.kinetics import _ALL_PARAMS
 from magicsoup_b200.world import World
+
+
+def even_slab_heights(n_rows: int, world_size: int) -> list[int]:
+    """row slabs as even as n_rows allows (the first n_rows % world_size slabs get one row more)"""
+    base, extra = divmod(n_rows, world_size)
+    return [base + (1 if r < extra else 0) for r in range(world_size)]
+
+
+def balanced_slab_heights(cost_per_row: torch.Tensor, world_size: int) -> list[int]:
+    """
+    Slab heights (>= 1 row each) whose summed per-row cost is as equal as whole rows allow:
+    boundary k sits at the first row where the running cost reaches k / world_size of the total.
+    """
+    H = int(cost_per_row.numel())
+    cum = torch.cumsum(cost_per_row.to(torch.float64).cpu(), 0)
+    total = float(cum[-1])
+    if total <= 0:
+        return even_slab_heights(H, world_size)
+    bounds = [0]
+    for k in range(1, world_size):
+        b = int(torch.searchsorted(cum, torch.tensor(total * k / world_size, dtype=torch.float64)).item()) + 1
+        b = max(b, bounds[-1] + 1)            # at least one row per slab ...
+        b = min(b, H - (world_size - k))      # ... also for the slabs that follow
+        bounds.append(b)
+    bounds.append(H)
+    return [bounds[k + 1] - bounds[k] for k in range(world_size)]
 
 
 class SlabWorld(World):
@@ -42,6 +70,7 @@ class SlabWorld(World):
         abs_temp: float = 310.0,
         mol_map_init: str = "randn",
         device: str = "cpu",
+        slab_heights: Sequence[int] | None = None,
     ):
         if not dist.is_initialized():
             raise RuntimeError("SlabWorld needs an initialised torch.distributed process group")
@@ -49,11 +78,10 @@ class SlabWorld(World):
         self.rank = dist.get_rank(group)
         self.world_size = dist.get_world_size(group)
         H, W = (global_map_size, global_map_size) if isinstance(global_map_size, int) else global_map_size
-        if H % self.world_size != 0:
-            raise ValueError(f"{H} map rows do not split evenly over {self.world_size} ranks")
+        if H < self.world_size:
+            raise ValueError(f"{H} map rows cannot be split over {self.world_size} ranks")
         self.global_map_size = (H, W)
-        self.slab_rows = H // self.world_size
-        self.row0 = self.rank * self.slab_rows  # first global row of this slab
+        self._set_slabs(list(slab_heights) if slab_heights is not None else even_slab_heights(H, self.world_size))
         super().__init__(chemistry=chemistry, map_size=(self.slab_rows, W), abs_temp=abs_temp,
                          mol_map_init=mol_map_init, device=device)
 
@@ -61,6 +89,15 @@ class SlabWorld(World):
         state = super().__getstate__()
         state["group"] = None
         return state
+
+    def _set_slabs(self, heights: list[int]):
+        H = self.global_map_size[0]
+        if len(heights) != self.world_size or any(int(h) < 1 for h in heights) or sum(heights) != H:
+            raise ValueError(f"slab heights {heights} must be {self.world_size} positive numbers adding up to {H}")
+        self.slab_heights = [int(h) for h in heights]
+        self.row_starts = [sum(self.slab_heights[:r]) for r in range(self.world_size + 1)]
+        self.slab_rows = self.slab_heights[self.rank]
+        self.row0 = self.row_starts[self.rank]  # first global row of this slab
 
     # ------------------------------------------------------------------ global bookkeeping
     def global_n_cells(self) -> list[int]:
@@ -81,7 +118,9 @@ class SlabWorld(World):
         return pos
 
     def owner_of_rows(self, rows: torch.Tensor) -> torch.Tensor:
-        return torch.div(rows, self.slab_rows, rounding_mode="floor")
+        """rank that owns each global row"""
+        inner = torch.tensor(self.row_starts[1:-1], dtype=rows.dtype, device=rows.device)
+        return torch.bucketize(rows, inner, right=True)
 
     def _comm_device(self) -> torch.device:
         backend = dist.get_backend(self.group)
@@ -238,6 +277,97 @@ class SlabWorld(World):
         for src in sorted(inbox):
             received += len(self.import_cells(inbox[src]))
         return received
+
+    # ------------------------------------------------------------------ load balance
+    def row_costs(self) -> torch.Tensor:
+        """
+        Algorithmic bytes per step and global map row: B_kin = 20ps + 16p + 8s + 8 per
+        cell on the row plus the row's share of the diffusion, 16 m W + (16 m + 8) per cell.  (H,) float64
+        on the host, the same on every rank.  Collective.
+        """
+        H, W = self.global_map_size
+        comm = self._comm_device()
+        hist = torch.zeros(H, dtype=torch.int64, device=comm)
+        if self.n_cells > 0:
+            rows = (self.cell_positions[:, 0].long() + self.row0) % H
+            hist += torch.bincount(rows, minlength=H).to(comm)
+        p_max = torch.tensor([int(self.kinetics._buf["N"].shape[1]) if self.kinetics._buf["N"].dim() == 3 else 0],
+                             dtype=torch.int64, device=comm)
+        if self.world_size > 1:
+            dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=self.group)
+            dist.all_reduce(p_max, op=dist.ReduceOp.MAX, group=self.group)
+        m, p = self.n_molecules, int(p_max.item())
+        s = 2 * m
+        per_cell = 20 * p * s + 16 * p + 8 * s + 8 + 16 * m + 8
+        return hist.cpu().to(torch.float64) * per_cell + 16.0 * m * W
+
+    def rebalance(self, tolerance: float = 0.05) -> list[int]:
+        """
+        Move the slab boundaries so that every rank carries the same share of the step's memory
+        traffic (`row_costs`), then move map rows and cells to their new owners.  Nothing happens
+        while the fullest slab is within `tolerance` of the mean.  Collective; returns the slab
+        heights in effect afterwards.  The step's results do not depend on where the boundaries are.
+        """
+        cost = self.row_costs()
+        loads = [float(cost[self.row_starts[r]:self.row_starts[r + 1]].sum()) for r in range(self.world_size)]
+        mean = sum(loads) / self.world_size
+        if self.world_size == 1 or mean <= 0 or max(loads) <= (1.0 + tolerance) * mean:
+            return list(self.slab_heights)
+        heights = balanced_slab_heights(cost, self.world_size)
+        new_loads = []
+        at = 0
+        for h in heights:
+            new_loads.append(float(cost[at:at + h].sum()))
+            at += h
+        if max(new_loads) >= max(loads):  # whole rows cannot do better
+            return list(self.slab_heights)
+        self.set_slab_heights(heights)
+        return list(self.slab_heights)
+
+    def set_slab_heights(self, heights: Sequence[int]):
+        """re-cut the map into slabs of the given heights; map rows and cells move to their new owners. Collective."""
+        old_starts = list(self.row_starts)
+        old_r0 = self.row0
+        mm_old = self.molecule_map
+        self._set_slabs([int(h) for h in heights])
+        if self.row_starts == old_starts:
+            return
+        ws, (H, W), m = self.world_size, self.global_map_size, self.n_molecules
+        comm = self._comm_device()
+        new_r0, new_r1 = self.row0, self.row0 + self.slab_rows
+        mm_new = torch.empty(m, self.slab_rows, W, dtype=mm_old.dtype, device=mm_old.device)
+        ops, landing, keep_alive = [], [], []
+        for q in range(ws):
+            # rows I held that rank q holds now / rows rank q held that I hold now
+            a, b = max(old_starts[self.rank], self.row_starts[q]), min(old_starts[self.rank + 1], self.row_starts[q + 1])
+            if a < b:
+                block = mm_old[:, a - old_r0:b - old_r0, :]
+                if q == self.rank:
+                    mm_new[:, a - new_r0:b - new_r0, :] = block
+                else:
+                    buf = block.contiguous().to(comm)
+                    keep_alive.append(buf)
+                    ops.append(dist.P2POp(dist.isend, buf, self._global_rank(q), group=self.group))
+            a, b = max(new_r0, old_starts[q]), min(new_r1, old_starts[q + 1])
+            if a < b and q != self.rank:
+                buf = torch.empty(m, b - a, W, dtype=mm_old.dtype, device=comm)
+                landing.append((a - new_r0, b - new_r0, buf))
+                ops.append(dist.P2POp(dist.irecv, buf, self._global_rank(q), group=self.group))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        for a, b, buf in landing:
+            mm_new[:, a:b, :] = buf.to(mm_new.device)
+        self.molecule_map = mm_new
+        self.map_size = (self.slab_rows, W)
+        # cells: local rows relative to the new first row; the ones outside move to their owners
+        self.cell_positions = self.cell_positions.clone()
+        self.cell_positions[:, 0] += old_r0 - new_r0
+        rows = self.cell_positions[:, 0].long()
+        stay = (rows >= 0) & (rows < self.slab_rows)
+        self.cell_map = torch.zeros(self.slab_rows, W, dtype=torch.bool, device=self.cell_map.device)
+        self.cell_map[rows[stay], self.cell_positions[stay, 1].long()] = True
+        self.migrate_cells()
 
     def _global_rank(self, r: int) -> int:
         return dist.get_global_rank(self.group, r) if self.group is not None else r

@@ -108,7 +108,25 @@ def gather_world(world: SlabWorld):
     return mm, cm, pos
 
 
-def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, seed: int, quiet: bool = False) -> None:
+def gather_params(world: SlabWorld):
+    """the nine parameter tensors of all ranks' cells on every rank (rank order), padded to the widest protein axis"""
+    parts = [None] * world.world_size
+    mine = {k: v.cpu().numpy() for k, v in world.kinetics.cell_params(list(range(world.n_cells))).items()}
+    dist.all_gather_object(parts, mine, group=world.group)
+    p = max(q["N"].shape[1] for q in parts)
+    out = {}
+    for k in PARAMS:
+        padded = []
+        for q in parts:
+            a = q[k]
+            pad = [(0, 0), (0, p - a.shape[1])] + [(0, 0)] * (a.ndim - 2)
+            padded.append(np.pad(a, pad))
+        out[k] = np.concatenate(padded, axis=0)
+    return out
+
+
+def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, seed: int, quiet: bool = False,
+        rows: int | None = None) -> None:
     rank, ws = dist.get_rank(), dist.get_world_size()
     if backend == "nccl":
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -117,7 +135,7 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
     else:
         device = "cpu"
         cls = OracleSlabWorld
-    H = rows_per_rank * ws
+    H = rows if rows else rows_per_rank * ws  # `rows` need not be a multiple of the number of ranks
     # the same seeded global population on every rank; each keeps the cells of its slab
     pop = make_population(cells, 12, 4, (H, cols), seed=seed)
     mols = [Molecule(f"d{i}", 10e3, diffusivity=pop.diffusivities[i], permeability=pop.permeabilities[i])
@@ -134,7 +152,7 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
     assert sum(counts) == cells and world.global_cell_offset() == sum(counts[:rank])
 
     # the oracle on the whole map, cells in rank order (= the gathered order)
-    order = torch.argsort(torch.div(pop.cell_positions[:, 0], rows_per_rank, rounding_mode="floor"), stable=True)
+    order = torch.argsort(world.owner_of_rows(pop.cell_positions[:, 0].long()), stable=True)
     P = O.Params(*[getattr(pop, k)[order].numpy() for k in PARAMS])
     o_pos = pop.cell_positions[order].numpy()
     o_cm, o_mm = pop.cell_molecules[order].numpy(), pop.molecule_map.numpy()
@@ -212,6 +230,42 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
     assert bool((world.cell_positions[:, 0] >= 0).all()) and bool((world.cell_positions[:, 0] < world.slab_rows).all())
     world.enzymatic_activity()
     world.diffuse_molecules()
+
+    # load balance: rank 0 loses most of its cells, the slab boundaries follow the cells; the world is
+    # the same before and after, and the next step equals the single-domain oracle's step on it
+    if rank == 0:
+        world.kill_cells([i for i in range(world.n_cells) if i % 5 != 0])
+    mm0, cm0, pos0 = gather_world(world)
+    before = snapshot()
+    heights0 = list(world.slab_heights)
+    cost = world.row_costs()
+    heights1 = world.rebalance(tolerance=0.01)
+    assert heights1 == world.slab_heights and sum(heights1) == H and min(heights1) >= 1
+    assert world.molecule_map.shape[1] == world.slab_rows == heights1[rank]
+    mm1, cm1, pos1 = gather_world(world)
+    assert before == snapshot()
+    assert np.array_equal(mm0, mm1), "the map changed under rebalance()"
+    assert int(world.cell_map.sum()) == world.n_cells
+    xs, ys = world.cell_positions[:, 0].long(), world.cell_positions[:, 1].long()
+    assert world.n_cells == 0 or bool(world.cell_map[xs, ys].all())
+    if ws > 1:
+        def fullest(hs):
+            at, worst = 0, 0.0
+            for h in hs:
+                worst = max(worst, float(cost[at:at + h].sum()))
+                at += h
+            return worst
+        assert heights1 != heights0 and fullest(heights1) < fullest(heights0), (heights0, heights1)
+    par = gather_params(world)
+    o_cm, o_mm = O.enzymatic_activity(O.Params(*[par[k] for k in PARAMS]), pos1, cm1, mm1)
+    o_cm, o_mm = O.diffuse_molecules(o_cm, o_mm, pos1, pop.diffusivities, pop.permeabilities)
+    world.enzymatic_activity()
+    world.diffuse_molecules()
+    mm2, cm2, pos2 = gather_world(world)
+    if rank == 0:
+        assert np.array_equal(pos2, pos1)
+        assert np.array_equal(mm2, o_mm), "map differs from the single-domain oracle after rebalance()"
+        assert np.array_equal(cm2, o_cm), "cell molecules differ from the oracle after rebalance()"
     if rank == 0 and not quiet:
         print(f"dist_worker ok: backend={backend} ranks={ws} steps={steps} cells={cells} received={received}")
 
@@ -222,12 +276,13 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--cells", type=int, default=300)
     ap.add_argument("--rows-per-rank", type=int, default=16)
+    ap.add_argument("--rows", type=int, default=None, help="total map rows (need not divide by the number of ranks)")
     ap.add_argument("--cols", type=int, default=24)
     ap.add_argument("--seed", type=int, default=5)
     args = ap.parse_args()
     dist.init_process_group(args.backend)
     try:
-        run(args.backend, args.steps, args.cells, args.rows_per_rank, args.cols, args.seed)
+        run(args.backend, args.steps, args.cells, args.rows_per_rank, args.cols, args.seed, rows=args.rows)
     finally:
         dist.destroy_process_group()
 

@@ -21,11 +21,13 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("nproc,cells", [(2, 300), (3, 200), (1, 100)])
-def test_slab_world_matches_single_domain_oracle(nproc, cells):
+@pytest.mark.parametrize("nproc,cells,rows", [(2, 300, None), (3, 200, None), (1, 100, None), (3, 250, 50), (2, 200, 31)])
+def test_slab_world_matches_single_domain_oracle(nproc, cells, rows):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            str(ROOT / "tests" / "dist_worker.py"), "--backend", "gloo", "--cells", str(cells)]
+    if rows:  # slabs of unequal heights
+        cmd += ["--rows", str(rows)]
     env = dict(os.environ, OMP_NUM_THREADS="2")
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=str(ROOT))
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]

@@ -253,3 +253,34 @@ def test_parameter_store_notices_outside_writes_and_assignment():
     kin.remove_cell_params(keep=torch.tensor([True, False] * 4))
     back = pickle.loads(pickle.dumps(kin))
     assert back.N.shape == (4, 3, 4) and torch.equal(back.N, kin.N) and back._cache is None
+
+
+def test_slab_height_rules():
+    """distributed.py: slabs as even as the rows allow; boundaries that follow a per-row cost"""
+    from magicsoup_b200.distributed import balanced_slab_heights, even_slab_heights
+
+    assert even_slab_heights(10, 3) == [4, 3, 3] and even_slab_heights(8, 8) == [1] * 8
+    assert even_slab_heights(1024, 8) == [128] * 8
+    cost = torch.ones(12)
+    assert balanced_slab_heights(cost, 3) == [4, 4, 4]
+    cost = torch.tensor([9.0, 1, 1, 1, 1, 1, 1, 1, 1, 1])  # a crowded first row
+    h = balanced_slab_heights(cost, 2)
+    assert h == [1, 9]
+    cost = torch.tensor([0.0, 0, 0, 0, 0, 0, 100.0, 0])  # everything on one row: every slab still gets a row
+    h = balanced_slab_heights(cost, 4)
+    assert sum(h) == 8 and min(h) >= 1 and len(h) == 4
+    assert balanced_slab_heights(torch.zeros(9), 3) == [3, 3, 3]
+    g = torch.Generator().manual_seed(0)
+    for _ in range(50):
+        H, ws = int(torch.randint(4, 200, (1,), generator=g)), int(torch.randint(1, 9, (1,), generator=g))
+        if H < ws:
+            continue
+        cost = torch.rand(H, generator=g) ** 4 * 100
+        h = balanced_slab_heights(cost, ws)
+        assert sum(h) == H and min(h) >= 1 and len(h) == ws
+        loads, at = [], 0
+        for x in h:
+            loads.append(float(cost[at:at + x].sum()))
+            at += x
+        # no slab exceeds the mean by more than the heaviest single row
+        assert max(loads) <= float(cost.sum()) / ws + float(cost.max()) + 1e-9

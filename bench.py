@@ -472,7 +472,8 @@ def slab_parity_check(world_size):
         ok, err = False, str(e)[:300]
     return {"ranks": world_size, "ok": ok,
             "problem": f"20000 cells x 12 proteins x 8 signals on a {128 * world_size}x128 map: 3 steps "
-                       "(activity, degradation, diffusion), then kill + a cell migrating across a slab boundary + 1 step",
+                       "(activity, degradation, diffusion), kill + cells migrating across slab boundaries + 1 step, "
+                       "then most of rank 0's cells killed + rebalance() of the slab boundaries + 1 step",
             "result": "bit-identical to the single-domain oracle" if ok else "MISMATCH: " + err,
             "seconds": round(time.perf_counter() - t0, 2)}
 

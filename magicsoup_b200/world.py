@@ -23,9 +23,12 @@ raise without a CUDA device.
 from __future__ import annotations
 
 import ctypes as C
+import io
 import math
+import pickle
 import random
 from dataclasses import dataclass
+from pathlib import Path
 from typing import Any
 
 import numpy as np
@@ -76,6 +79,23 @@ def diffusion_weights(mol_diff_rate: float) -> tuple[float, float]:
     b = d * a
     b = b + 1.0 - (8 * a + b)
     return a, b
+
+
+_STATE_TENSORS = {"cell_molecules": torch.float32, "cell_map": torch.bool, "molecule_map": torch.float32,
+                  "cell_lifetimes": torch.int32, "cell_positions": torch.int32, "cell_divisions": torch.int32}
+
+
+class _TensorRehomingUnpickler(pickle.Unpickler):
+    """pickle.load that puts every tensor on `device` (torch pickles storages through one loader function)"""
+
+    def __init__(self, fh, device: str | None):
+        super().__init__(fh)
+        self._device = device
+
+    def find_class(self, module, name):
+        if self._device is not None and (module, name) == ("torch.storage", "_load_from_bytes"):
+            return lambda raw: torch.load(io.BytesIO(raw), map_location=self._device, weights_only=False)
+        return super().find_class(module, name)
 
 
 def _remove_items(items: list, dead_sorted: list[int]):
@@ -619,6 +639,56 @@ class World:
         return pxls[random.sample(range(int(pxls.size(0))), k=n)]
 
     # ------------------------------------------------------------------ helpers
+    # ------------------------------------------------------------------ persistence
+    # (world.py:747-878; same file names and formats, so states written by either package load in the other)
+    def save(self, rundir, name: str = "world.pkl"):
+        """the whole object as one pickle (chemistry, genetics, parameters, state)"""
+        rundir = Path(rundir)
+        rundir.mkdir(parents=True, exist_ok=True)
+        with open(rundir / name, "wb") as fh:
+            pickle.dump(self, fh)
+
+    @classmethod
+    def from_file(cls, rundir, name: str = "world.pkl", device: str | None = None) -> "World":
+        """a world written by save(); `device` re-homes all tensors (e.g. "cpu" for a world saved on a GPU)"""
+        with open(Path(rundir) / name, "rb") as fh:
+            world = _TensorRehomingUnpickler(fh, device).load()
+        if device is not None:
+            world.device = device
+            world.kinetics.device = device
+        return world
+
+    def save_state(self, statedir):
+        """what changes during a simulation: six tensors and the genomes with their labels as FASTA"""
+        statedir = Path(statedir)
+        statedir.mkdir(parents=True, exist_ok=True)
+        for key in _STATE_TENSORS:
+            torch.save(getattr(self, key), statedir / f"{key}.pt")
+        with open(statedir / "cells.fasta", "w", encoding="utf-8") as fh:
+            fh.write("\n".join(f">{i} {label}\n{genome}"
+                               for i, (genome, label) in enumerate(zip(self.cell_genomes, self.cell_labels))))
+
+    def load_state(self, statedir, ignore_cell_params: bool = False):
+        """a state written by save_state(); parameters are re-derived from the genomes unless told otherwise"""
+        statedir = Path(statedir)
+        if not ignore_cell_params:
+            self.kill_cells(cell_idxs=list(range(self.n_cells)))
+        for key, dtype in _STATE_TENSORS.items():
+            setattr(self, key, torch.load(statedir / f"{key}.pt", map_location=self.device).to(dtype))
+        text = (statedir / "cells.fasta").read_text(encoding="utf-8")
+        self.cell_genomes, self.cell_labels = [], []
+        for record in (r.strip() for r in text.split(">")):
+            if not record:
+                continue
+            head, _, seq = record.partition("\n")
+            words = head.split()
+            self.cell_genomes.append(seq.split("\n")[0])
+            self.cell_labels.append(words[1].strip() if len(words) > 1 else "")
+        self.n_cells = len(self.cell_genomes)
+        self.kinetics.increase_max_cells(by_n=self.n_cells)
+        if not ignore_cell_params:
+            self.update_cells(genome_idx_pairs=[(g, i) for i, g in enumerate(self.cell_genomes)])
+
     def _get_molecule_map(self, n: int, size, init: str) -> torch.Tensor:
         """world.py:922-933"""
         rows, cols = (size, size) if isinstance(size, int) else size

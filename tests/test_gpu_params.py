@@ -180,3 +180,47 @@ def test_config0_readme_loop_1000_steps():
     assert checked == 190 and w.n_cells > 0
     assert torch.isfinite(w.molecule_map).all() and (w.molecule_map >= 0).all() and (w.cell_molecules >= 0).all()
     assert int(w.cell_map.sum()) == w.n_cells
+
+
+def test_save_state_load_state_rederives_parameters(tmp_path):
+    """world.py:795-878: a state holds tensors + genomes; loading it re-translates the genomes"""
+    random.seed(41)
+    torch.manual_seed(41)
+    chem = _chem(tag="gs")
+    w = ms.World(chemistry=chem, map_size=24, device="cuda")
+    w.genetics = ms.Genetics(p_catal_dom=0.1, p_transp_dom=0.1, p_reg_dom=0.1)
+    w.spawn_cells(genomes=[ms.random_genome(random.choice((200, 600))) for _ in range(120)])
+    w.enzymatic_activity()
+    w.kill_cells(cell_idxs=list(range(0, w.n_cells, 7)))
+    w.divide_cells(cell_idxs=list(range(0, w.n_cells, 4)))
+    w.save_state(statedir=tmp_path / "s0")
+    w.save(rundir=tmp_path)
+    want = {k: getattr(w.kinetics, k).clone() for k in PARAMS}
+    state = {k: getattr(w, k).clone() for k in ("cell_molecules", "cell_map", "molecule_map", "cell_positions",
+                                                  "cell_lifetimes", "cell_divisions")}
+    genomes, labels = list(w.cell_genomes), list(w.cell_labels)
+    n_prots = torch.tensor([len(p) for p in w.genetics.translate_genomes(genomes)], device="cuda")
+    # go on, then come back
+    w.enzymatic_activity()
+    w.diffuse_molecules()
+    w.kill_cells(cell_idxs=list(range(0, w.n_cells, 3)))
+    w.load_state(statedir=tmp_path / "s0")
+    assert w.cell_genomes == genomes and w.cell_labels == labels and w.n_cells == len(genomes)
+    for k, v in state.items():
+        assert torch.equal(getattr(w, k), v), k
+    own = torch.arange(want["N"].shape[1], device="cuda")[None, :] < n_prots[:, None]
+    for k in PARAMS:
+        a, b = getattr(w.kinetics, k), want[k]
+        assert a.shape == b.shape, k
+        differ = (a != b) & ~(torch.isnan(a) & torch.isnan(b)) if a.is_floating_point() else a != b
+        if k in ("Kmr", "Ke", "Kmf", "Kmb"):  # padding proteins hold zeros or the no-op values, see above
+            differ &= own[:, :, None] if differ.dim() == 3 else own
+        assert not bool(differ.any()), k
+    w.enzymatic_activity()  # and the loaded world steps
+    # the pickled world, on the CPU and back on the GPU
+    w2 = ms.World.from_file(rundir=tmp_path, device="cpu")
+    assert w2.device == "cpu" and w2.molecule_map.device.type == "cpu" and w2.kinetics.N.device.type == "cpu"
+    assert w2.cell_genomes == genomes and torch.equal(w2.kinetics.N, want["N"].cpu())
+    w3 = ms.World.from_file(rundir=tmp_path, device="cuda")
+    w3.enzymatic_activity()
+    assert torch.isfinite(w3.cell_molecules).all()

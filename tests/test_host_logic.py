@@ -284,3 +284,36 @@ def test_slab_height_rules():
             at += x
         # no slab exceeds the mean by more than the heaviest single row
         assert max(loads) <= float(cost.sum()) / ws + float(cost.max()) + 1e-9
+
+
+def test_world_persistence_round_trip(tmp_path):
+    """save / from_file and save_state / load_state (world.py:747-878), incl. the reference's file names"""
+    import magicsoup_b200 as ms
+
+    mols = [ms.Molecule(f"ps{i}", 10e3 * (i + 1)) for i in range(3)]
+    w = ms.World(chemistry=ms.Chemistry(molecules=mols, reactions=[([mols[0]], [mols[1]])]), map_size=8)
+    n, p, s = 5, 2, 6
+    pos = torch.tensor([[0, 0], [1, 2], [3, 3], [7, 7], [4, 0]], dtype=torch.int32)
+    g = torch.Generator().manual_seed(3)
+    params = {k: torch.randint(-2, 3, (n, p, s), generator=g, dtype=torch.int32) for k in ("N", "Nf", "Nb", "A")}
+    params.update(Kmr=torch.rand(n, p, s, generator=g), **{k: torch.rand(n, p, generator=g) for k in ("Ke", "Kmf", "Kmb", "Vmax")})
+    w.add_cells_from_params(pos, **params)
+    w.cell_genomes[:] = ["ACGT" * (i + 1) for i in range(n)]
+    w.kill_cells([1])
+    w.save(rundir=tmp_path / "run")
+    w2 = ms.World.from_file(rundir=tmp_path / "run", device="cpu")
+    assert w2.n_cells == 4 and w2.cell_genomes == w.cell_genomes and w2.cell_labels == w.cell_labels
+    for key in ("cell_molecules", "cell_map", "molecule_map", "cell_lifetimes", "cell_positions", "cell_divisions"):
+        assert torch.equal(getattr(w, key), getattr(w2, key)), key
+    for k in ("N", "Nf", "Nb", "A", "Kmr", "Ke", "Kmf", "Kmb", "Vmax"):
+        assert torch.equal(getattr(w.kinetics, k), getattr(w2.kinetics, k)), k
+    w.save_state(statedir=tmp_path / "run" / "step=0")
+    names = sorted(f.name for f in (tmp_path / "run" / "step=0").iterdir())
+    assert names == ["cell_divisions.pt", "cell_lifetimes.pt", "cell_map.pt", "cell_molecules.pt", "cell_positions.pt",
+                     "cells.fasta", "molecule_map.pt"]
+    assert (tmp_path / "run" / "step=0" / "cells.fasta").read_text().startswith(f">0 {w.cell_labels[0]}\nACGT\n>1 ")
+    w.cell_molecules += 1.0
+    w.cell_genomes[0] = "TTTT"
+    w.load_state(statedir=tmp_path / "run" / "step=0", ignore_cell_params=True)
+    assert w.cell_genomes == w2.cell_genomes and w.cell_labels == w2.cell_labels and w.n_cells == 4
+    assert torch.equal(w.cell_molecules, w2.cell_molecules) and w.cell_positions.dtype == torch.int32

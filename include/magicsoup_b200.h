@@ -282,6 +282,27 @@ int ms_permeate_by_pixel(const float *cell_molecules_in, float *cell_molecules_o
                          int64_t H, int64_t W, void *stream);
 
 /*
+ * Committing the rest of a step before the host has read the early-exit flags (no counterpart in
+ * the reference, whose host blocks on torch.any() inside the loop, kinetics.py:846).
+ *
+ * ms_early_exit_verdict evaluates, on the device, what the host does with the flags of a kinetics
+ * launch that applied eq_iters_host[q] iterations in part q: *gate = 1 if that launch already equals
+ * the reference and met no cell position outside the map, else 0 (the launch has to be repeated
+ * with fewer iterations, see `flags` above).
+ * ms_step_gate(gate) makes every later call BY THE CALLING THREAD of the entry points that commit
+ * results -- ms_scatter_signals[_by_pixel], ms_diffuse_correct, ms_diffuse_molecules,
+ * ms_permeate[_by_pixel], ms_degrade_permeate, ms_degrade_molecules -- launch kernels that leave
+ * without writing anything if *gate == 0 when they run; ms_step_gate(NULL) ends that.  (The stencil
+ * pass writes only scratch and is not gated.)  A host can so enqueue
+ *     kinetics, verdict, [gated: write-back, degradation, diffusion, permeation]
+ * without a synchronisation in between, read the flags afterwards, and, in the rare case that the
+ * verdict was 0, repeat the step from the untouched state.  ms_diffuse_molecules_static ignores it.
+ */
+int ms_early_exit_verdict(const uint32_t *flags, const int32_t *eq_iters_host, int32_t n_parts,
+                          uint32_t *gate, void *stream);
+void ms_step_gate(const uint32_t *gate);
+
+/*
  * World.degrade_molecules()                                    world.py:667-678
  * molecule_map[k] *= decay[k], cell_molecules[:, k] *= decay[k], in place, one launch
  * (decay[k] = exp(-ln 2 / half_life_k), world.py:184).

@@ -85,6 +85,8 @@ _SIGNATURES = {
     "ms_permeate_by_pixel": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp]),
     "ms_degrade_diffuse_stencil": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "ms_degrade_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "ms_early_exit_verdict": (C.c_int, [_vp, C.POINTER(C.c_int32), C.c_int32, _vp, _vp]),
+    "ms_step_gate": (None, [_vp]),
 }
 
 _lib: C.CDLL | None = None
@@ -135,7 +137,13 @@ def ptr(t: torch.Tensor | None):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device: torch.device):
+    """torch's current stream on `device` as a cudaStream_t (called for every launch: the short way if torch has it)"""
+    if _raw_stream is not None and device.index is not None:
+        return C.c_void_p(_raw_stream(device.index))
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 

@@ -177,7 +177,9 @@ __global__ void __launch_bounds__(DTHREADS) stencil_generic_kernel(const float *
 __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restrict__ out,
                                                            float *__restrict__ map, long long n_pxls,
                                                            long long n_pxls_total,
-                                                           const unsigned long long *sums, int vec) {
+                                                           const unsigned long long *sums, int vec,
+                                                           const unsigned *gate) {
+  if (gate_closed(gate)) return;
   const int k = blockIdx.z;
   const long long *sk = reinterpret_cast<const long long *>(sums) + 4 * k;
   const float s0 = (float)((double)sk[0] + (double)sk[1] * 2.3283064365386963e-10);
@@ -205,9 +207,10 @@ __global__ void __launch_bounds__(DTHREADS) correct_kernel(const float *__restri
 
 // pass 3: world.py:654-665, one thread per (cell, molecule)
 __global__ void permeate_kernel(const float *cm_in, float *cm_out, float *map, const int *pos,
-                                const float *perm, long long c, int m, int H, int W, const float *decay) {
+                                const float *perm, long long c, int m, int H, int W, const float *decay,
+                                const unsigned *gate) {
   const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= c * m) return;
+  if (r >= c * m || gate_closed(gate)) return;
   const long long cell = r / m;
   const int k = (int)(r % m);
   const int x = pos[2 * cell], y = pos[2 * cell + 1];
@@ -223,7 +226,9 @@ __global__ void permeate_kernel(const float *cm_in, float *cm_out, float *map, c
 }
 
 // World.degrade_molecules, world.py:667-678: map[k] *= f[k], cell_molecules[:, k] *= f[k]
-__global__ void degrade_kernel(float *map, long long n_pxls, float *cm, long long c, int m, const float *f) {
+__global__ void degrade_kernel(float *map, long long n_pxls, float *cm, long long c, int m, const float *f,
+                               const unsigned *gate) {
+  if (gate_closed(gate)) return;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   for (int k = 0; k < m; k++) {
@@ -255,11 +260,12 @@ constexpr int PIX_WARPS = 8;
 
 __global__ void __launch_bounds__(32 * PIX_WARPS) permeate_pixel_kernel(const float *cm_in, float *cm_out, float *map,
                                                                         const int *pixel_cell, const float *perm, int m,
-                                                                        long long n_pxls, const float *decay) {
+                                                                        long long n_pxls, const float *decay,
+                                                                        const unsigned *gate) {
   __shared__ float tile[PIX_WARPS][32][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long px0 = ((long long)blockIdx.x * PIX_WARPS + warp) * 32;
-  if (px0 >= n_pxls) return;
+  if (px0 >= n_pxls || gate_closed(gate)) return;
   const long long px = px0 + lane;
   const bool inside = px < n_pxls;
   const int cell = inside ? pixel_cell[px] : -1;
@@ -283,11 +289,12 @@ __global__ void __launch_bounds__(32 * PIX_WARPS) permeate_pixel_kernel(const fl
 }
 
 __global__ void __launch_bounds__(32 * PIX_WARPS) scatter_pixel_kernel(const float *X, const int *pixel_cell, int m,
-                                                                       long long n_pxls, float *cm_out, float *map) {
+                                                                       long long n_pxls, float *cm_out, float *map,
+                                                                       const unsigned *gate) {
   __shared__ float tile[PIX_WARPS][32][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long px0 = ((long long)blockIdx.x * PIX_WARPS + warp) * 32;
-  if (px0 >= n_pxls) return;
+  if (px0 >= n_pxls || gate_closed(gate)) return;
   const long long px = px0 + lane;
   const int cell = px < n_pxls ? pixel_cell[px] : -1;
   if (__ballot_sync(0xffffffffu, cell >= 0) == 0u) return;
@@ -310,10 +317,10 @@ __global__ void __launch_bounds__(32 * PIX_WARPS) scatter_pixel_kernel(const flo
 
 // world.py:624-625, one thread per (cell, signal)
 __global__ void scatter_kernel(const float *X, const int *pos, long long c, int m, int H, int W,
-                               float *cm_out, float *map) {
+                               float *cm_out, float *map, const unsigned *gate) {
   const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int s = 2 * m;
-  if (r >= c * s) return;
+  if (r >= c * s || gate_closed(gate)) return;
   const long long cell = r / s;
   const int i = (int)(r % s);
   const float v = X[r];
@@ -331,6 +338,13 @@ using namespace ms;
 
 #include <stdio.h>
 static thread_local char g_static_too_large_msg[320] = "";
+
+// Step gate (ms_step_gate): while one is set for the calling thread, the kernels that COMMIT results
+// (write-back, correction, permeation, degradation) are launched with it and leave without writing
+// when the word it points to is 0 at the time they run.  It lets a host enqueue the rest of a step
+// behind the kinetics launch before it has read the early-exit flags (ms_early_exit_verdict).
+static thread_local const unsigned *g_step_gate = nullptr;
+extern "C" void ms_step_gate(const uint32_t *gate) { g_step_gate = gate; }
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -374,13 +388,14 @@ static int stencil_launch(const float *map, const float *halo_top, const float *
 }
 
 static int correct_launch(const float *tmp, float *map, int64_t m, int64_t H, int64_t W,
-                          long long n_pxls_total, const unsigned long long *sums, cudaStream_t st) {
+                          long long n_pxls_total, const unsigned long long *sums, cudaStream_t st,
+                          const unsigned *gate) {
   const long long n = (long long)H * W;
   const bool vec = (n & 3) == 0 && aligned16(tmp) && aligned16(map);
   long long work = vec ? n / 4 : n;
   unsigned blocks = (unsigned)((work + DTHREADS - 1) / DTHREADS);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, map, n, n_pxls_total, sums, vec ? 1 : 0);
+  correct_kernel<<<dim3(blocks, 1, (unsigned)m), DTHREADS, 0, st>>>(tmp, map, n, n_pxls_total, sums, vec ? 1 : 0, gate);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -401,7 +416,7 @@ extern "C" int ms_diffuse_molecules(float *molecule_map, const float *a, const f
       (unsigned long long *)((char *)scratch + align256((size_t)m * H * W * sizeof(float)));
   int rc = stencil_launch(molecule_map, nullptr, nullptr, a, b, m, H, W, tmp, sums, (cudaStream_t)stream);
   if (rc != MS_OK) return rc;
-  return correct_launch(tmp, molecule_map, m, H, W, (long long)H * W, sums, (cudaStream_t)stream);
+  return correct_launch(tmp, molecule_map, m, H, W, (long long)H * W, sums, (cudaStream_t)stream, g_step_gate);
 }
 
 static int diffuse_stencil_impl(const float *map_slab, const float *halo_top, const float *halo_bottom,
@@ -433,7 +448,7 @@ extern "C" int ms_diffuse_correct(const float *out, float *map_slab, const int64
   if (m == 0) return MS_OK;
   if (!out || !map_slab || !sums) return MS_ERR_INVALID_ARGUMENT;
   return correct_launch(out, map_slab, m, H, W, n_pxls_total, (const unsigned long long *)sums,
-                        (cudaStream_t)stream);
+                        (cudaStream_t)stream, g_step_gate);
 }
 
 static int permeate_impl(const float *cell_molecules_in, float *cell_molecules_out, float *molecule_map,
@@ -445,7 +460,8 @@ static int permeate_impl(const float *cell_molecules_in, float *cell_molecules_o
     return MS_ERR_INVALID_ARGUMENT;
   const long long n = c * m;
   permeate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, c, (int)m, (int)H, (int)W, decay);
+      cell_molecules_in, cell_molecules_out, molecule_map, cell_positions, perm, c, (int)m, (int)H, (int)W, decay,
+      g_step_gate);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -487,7 +503,7 @@ extern "C" int ms_permeate_by_pixel(const float *cell_molecules_in, float *cell_
   if (m > 32) return MS_ERR_TOO_LARGE;  // the transposing tile holds 32 planes; use ms_permeate
   const long long n = (long long)H * W;
   permeate_pixel_kernel<<<(unsigned)((n + 32 * PIX_WARPS - 1) / (32 * PIX_WARPS)), 32 * PIX_WARPS, 0, (cudaStream_t)stream>>>(
-      cell_molecules_in, cell_molecules_out, molecule_map, pixel_cell, perm, (int)m, n, decay);
+      cell_molecules_in, cell_molecules_out, molecule_map, pixel_cell, perm, (int)m, n, decay, g_step_gate);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -501,7 +517,8 @@ extern "C" int ms_scatter_signals_by_pixel(const float *X, const int32_t *pixel_
   if (m > 32) return MS_ERR_TOO_LARGE;  // the transposing tile holds 32 planes; use ms_scatter_signals
   const long long n = (long long)H * W;
   scatter_pixel_kernel<<<(unsigned)((n + 32 * PIX_WARPS - 1) / (32 * PIX_WARPS)), 32 * PIX_WARPS, 0,
-                         (cudaStream_t)stream>>>(X, pixel_cell, (int)m, n, cell_molecules_out, molecule_map);
+                         (cudaStream_t)stream>>>(X, pixel_cell, (int)m, n, cell_molecules_out, molecule_map,
+                                                 g_step_gate);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -512,7 +529,7 @@ extern "C" int ms_degrade_molecules(float *molecule_map, float *cell_molecules, 
   if (m == 0) return MS_OK;
   if (!molecule_map || !decay || (c > 0 && !cell_molecules)) return MS_ERR_INVALID_ARGUMENT;
   degrade_kernel<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(molecule_map, (long long)H * W, cell_molecules, c, (int)m,
-                                                           decay);
+                                                           decay, g_step_gate);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -525,7 +542,7 @@ extern "C" int ms_scatter_signals(const float *X, const int32_t *cell_positions,
   if (!X || !cell_positions || !cell_molecules_out || !molecule_map) return MS_ERR_INVALID_ARGUMENT;
   const long long n = c * 2 * m;
   scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      X, cell_positions, c, (int)m, (int)H, (int)W, cell_molecules_out, molecule_map);
+      X, cell_positions, c, (int)m, (int)H, (int)W, cell_molecules_out, molecule_map, g_step_gate);
   MS_CUDA_CHECK(cudaGetLastError());
   return MS_OK;
 }
@@ -606,7 +623,7 @@ extern "C" int ms_diffuse_molecules_static(float *molecule_map, const float *a, 
   // stencil_launch clears the plane sums (cudaMemsetAsync) before accumulating into them
   rc = stencil_launch(molecule_map, nullptr, nullptr, a, b, m, H, W, sc.out, sc.sums, (cudaStream_t)stream);
   if (rc != MS_OK) return rc;
-  return correct_launch(sc.out, molecule_map, m, H, W, (long long)H * W, sc.sums, (cudaStream_t)stream);
+  return correct_launch(sc.out, molecule_map, m, H, W, (long long)H * W, sc.sums, (cudaStream_t)stream, nullptr);
 }
 
 extern "C" const char *ms_diffuse_static_last_error(void) { return g_static_too_large_msg; }

@@ -21,6 +21,9 @@ constexpr float IMPACT = 0.1f;  // kinetics.py:825
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// step gate (ms_step_gate): a committing kernel leaves without writing when the gate word is 0
+__device__ __forceinline__ bool gate_closed(const unsigned *gate) { return gate != nullptr && *gate == 0u; }
+
 // x^n, n >= 1, right-to-left binary exponentiation
 __device__ __forceinline__ float powi(float x, int n) {
   float r = 1.0f, b = x;

@@ -146,6 +146,16 @@ class SlabWorld(World):
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         return t.tolist()
 
+    def _reduce_flags_device(self, flags: torch.Tensor) -> torch.Tensor:
+        """MAX over ranks in place, enqueued like any other step of the launch sequence (no host round trip)"""
+        if self.world_size > 1:
+            dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=self.group)
+        return flags
+
+    def _can_defer(self) -> bool:
+        # the collectives of the deferred sequence run on the step's device: NCCL only
+        return super()._can_defer() and (self.world_size == 1 or dist.get_backend(self.group) == "nccl")
+
     def _reduce_sums(self, sums: torch.Tensor) -> torch.Tensor:
         if self.world_size > 1:
             if sums.device != self._comm_device():
@@ -189,6 +199,7 @@ class SlabWorld(World):
     # ------------------------------------------------------------------ moving cells between ranks
     def export_cells(self, cell_idxs: list[int]) -> dict[str, torch.Tensor]:
         """per-cell state + parameter slices of the given local cells, positions global"""
+        self._settle()
         idx = torch.as_tensor(cell_idxs, dtype=torch.long, device=self.cell_positions.device)
         out = {
             "positions": self.global_positions()[idx],
@@ -201,6 +212,7 @@ class SlabWorld(World):
 
     def import_cells(self, payload: dict[str, torch.Tensor]) -> list[int]:
         """append cells exported by another rank; their pixels must lie in this slab"""
+        self._settle()
         n = int(payload["positions"].shape[0])
         if n == 0:
             return []
@@ -226,6 +238,7 @@ class SlabWorld(World):
         slices of the leaving cells go rank to rank as packed device buffers (`batch_isend_irecv`,
         only between pairs that exchange cells): no pickling, no per-cell host work.
         """
+        self._settle()
         ws, H = self.world_size, self.global_map_size[0]
         comm = self._comm_device()
         gpos = self.global_positions()
@@ -285,6 +298,7 @@ class SlabWorld(World):
         cell on the row plus the row's share of the diffusion, 16 m W + (16 m + 8) per cell.  (H,) float64
         on the host, the same on every rank.  Collective.
         """
+        self._settle()
         H, W = self.global_map_size
         comm = self._comm_device()
         hist = torch.zeros(H, dtype=torch.int64, device=comm)
@@ -326,6 +340,7 @@ class SlabWorld(World):
 
     def set_slab_heights(self, heights: Sequence[int]):
         """re-cut the map into slabs of the given heights; map rows and cells move to their new owners. Collective."""
+        self._settle()
         old_starts = list(self.row_starts)
         old_r0 = self.row0
         mm_old = self.molecule_map
@@ -384,6 +399,7 @@ class SlabWorld(World):
 
     def _drop_cells(self, cell_idxs):
         """kill_cells' compaction (world.py:527-540) without the spill and cell_map update"""
+        self._settle()
         idx = torch.as_tensor(cell_idxs, dtype=torch.long, device=self.cell_lifetimes.device)
         keep = torch.ones(self.cell_lifetimes.size(0), dtype=torch.bool, device=self.cell_lifetimes.device)
         keep[idx] = False

@@ -115,9 +115,21 @@ class Kinetics:
         self._scratch: dict[str, torch.Tensor] = {}
 
     # ------------------------------------------------------------------ pickling
+    # A World that has enqueued a step behind a kinetics launch whose early-exit flags it has not read
+    # yet (World._settle) hangs itself in here: whoever reads or writes the parameters, or uses the
+    # flag buffer, lets it finish that step first.
+    _guard = None
+
+    def _touch(self):
+        guard = self._guard
+        if guard is not None:
+            guard()
+
     def __getstate__(self):
+        self._touch()
         self._materialize()
         state = dict(self.__dict__)
+        state.pop("_guard", None)
         state["_scratch"] = {}  # device scratch is rebuilt lazily (world.py:747-793 pickles the object)
         state["_cache"] = None
         state["_buf"] = {k: self._view(k).clone() for k in _ALL_PARAMS}  # without the spare capacity
@@ -229,6 +241,7 @@ class Kinetics:
         (plus, only if the reference's global early exit would have fired, a repeat).
         Subclasses that override a stage method get the staged composition instead.
         """
+        self._touch()
         if any(self._overrides(m) for m in _STAGE_METHODS):
             for trim in _TRIMS:
                 X = self._integrate_signals_part(adj_vmax=(self.Vmax * trim).clamp(0.0), X0=X)
@@ -275,6 +288,7 @@ class Kinetics:
         return X1
 
     def _part_kernel(self, adj_vmax, X0d, dev, want_v: bool = False):
+        self._touch()
         c, s = X0d.shape
         st, keep, p = self._params(dev, c, s)
         adj = self._f32(adj_vmax, dev)
@@ -349,6 +363,7 @@ class Kinetics:
     def _get_equilibrium_adjusted_x(self, X0: torch.Tensor, X1: torch.Tensor, NV: torch.Tensor,
                                     V: torch.Tensor) -> torch.Tensor:
         """kinetics.py:808-859 on dense NV (c,p,s)"""
+        self._touch()
         dev = self._cuda()
         X0d, X1d, NVd, Vd = (self._f32(t, dev) for t in (X0, X1, NV, V))
         c, p, s = NVd.shape
@@ -398,12 +413,14 @@ class Kinetics:
         return self._len["N"]
 
     def _view(self, k: str) -> torch.Tensor:
+        self._touch()
         self._materialize()
         t = self._buf[k]
         return t if t.dim() == 0 or t.shape[0] == self._len[k] else t[: self._len[k]]
 
     def _adopt(self, k: str, value: Any):
         """`kinetics.N = tensor` (kinetics.py's attributes are plain tensors that users replace)"""
+        self._touch()
         self._materialize()
         if not isinstance(value, torch.Tensor):
             value = torch.as_tensor(value)
@@ -472,6 +489,7 @@ class Kinetics:
 
     def cell_params(self, cell_idxs) -> dict[str, torch.Tensor]:
         """the nine parameter slices of the given cells (copies), without compacting the store"""
+        self._touch()
         if not self._managed():
             return {k: self._view(k)[cell_idxs] for k in _ALL_PARAMS}
         phys = self._phys(cell_idxs)
@@ -482,6 +500,7 @@ class Kinetics:
         Install ready-made parameters for `cell_idxs` (what set_cell_params derives from
         proteomes, kinetics.py:571-625).  Keyword names are the attribute names.
         """
+        self._touch()
         p_new = int(tensors["N"].shape[1])
         self.increase_max_proteins(max_n=p_new)
         managed = self._managed()
@@ -524,6 +543,7 @@ class Kinetics:
             return
         if len(prot_off) != len(cell_idxs) + 1:
             raise ValueError("cell_idxs and proteomes differ in length")
+        self._touch()
         dev = self._cuda()
         if not self._managed() or self._buf["N"].device != dev or not all(t.is_contiguous() for t in self._buf.values()):
             self._materialize()
@@ -561,6 +581,7 @@ class Kinetics:
 
     def unset_cell_params(self, cell_idxs: list[int]):
         """kinetics.py:627-644"""
+        self._touch()
         managed = self._managed()
         phys = self._phys(cell_idxs) if managed else cell_idxs
         for k in _ALL_PARAMS:
@@ -571,6 +592,7 @@ class Kinetics:
 
     def copy_cell_params(self, from_idxs: list[int], to_idxs: list[int]):
         """kinetics.py:646-665"""
+        self._touch()
         managed = self._managed()
         src = self._phys(from_idxs) if managed else from_idxs
         dst = self._phys(to_idxs) if managed else to_idxs
@@ -583,6 +605,7 @@ class Kinetics:
 
     def remove_cell_params(self, keep: torch.Tensor):
         """kinetics.py:667-686: order-preserving removal; only the row map is edited"""
+        self._touch()
         if not self._managed():
             for k in _ALL_PARAMS:
                 self._adopt(k, self._view(k)[keep])
@@ -599,6 +622,7 @@ class Kinetics:
         """kinetics.py:688-703: by_n new all-zero cells at the end"""
         if by_n <= 0:
             return
+        self._touch()
         if not self._managed():
             for k in _ALL_PARAMS:
                 self._adopt(k, self._expand(self._view(k), dim=0, n=by_n))
@@ -626,6 +650,7 @@ class Kinetics:
         n_prots = int(self._buf["N"].size(1))
         if max_n <= n_prots:
             return
+        self._touch()
         if not self._managed():
             for k in _ALL_PARAMS:
                 self._adopt(k, self._expand(self._view(k), dim=1, n=max_n - n_prots))

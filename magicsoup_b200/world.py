@@ -81,6 +81,26 @@ def diffusion_weights(mol_diff_rate: float) -> tuple[float, float]:
     return a, b
 
 
+_KERNEL_HOOKS = ("_launch_activity", "_launch_scatter", "_launch_stencil", "_launch_correct", "_launch_permeate",
+                 "_launch_degrade", "_device_for_step")
+
+
+class _StepGate:
+    """`with`: the library's committing kernels launched by this thread obey the gate word (ms_step_gate)"""
+
+    def __init__(self, gate: torch.Tensor | None):
+        self.gate = gate
+
+    def __enter__(self):
+        if self.gate is not None:
+            nat.lib().ms_step_gate(nat.ptr(self.gate))
+
+    def __exit__(self, *exc):
+        if self.gate is not None:
+            nat.lib().ms_step_gate(None)
+        return False
+
+
 _STATE_TENSORS = {"cell_molecules": torch.float32, "cell_map": torch.bool, "molecule_map": torch.float32,
                   "cell_lifetimes": torch.int32, "cell_positions": torch.int32, "cell_divisions": torch.int32}
 
@@ -141,6 +161,7 @@ class World:
         self._diffusion = [diffusion_weights(d.diffusivity) for d in molecules]
         self._permeation = [permeation_factor(d.permeability) for d in molecules]
 
+        self._pending = None  # a step enqueued behind a kinetics launch whose flags are not read yet (_settle)
         self.n_cells = 0
         self.cell_genomes: list[str] = []
         self.cell_labels: list[str] = []
@@ -157,9 +178,11 @@ class World:
         self._kernel_events: list | None = None
 
     def __getstate__(self):
+        self._settle()
         state = dict(self.__dict__)
         state["_scratch"] = {}
         state["_kernel_events"] = None
+        state["_pending"] = None
         return state
 
     # ------------------------------------------------------------------ plumbing
@@ -189,13 +212,75 @@ class World:
 
     def _state_on_device(self, dev: torch.device):
         """normalise user-assigned state tensors (tests assign CPU tensors, world.py H5)"""
-        mm = self.molecule_map
+        mm = self._st_molecule_map
         if mm.device != dev or mm.dtype != torch.float32 or not mm.is_contiguous():
             mm = mm.to(device=dev, dtype=torch.float32).contiguous()
-            self.molecule_map = mm
-        cm = self.cell_molecules.to(device=dev, dtype=torch.float32).contiguous()
-        pos = self.cell_positions.to(device=dev, dtype=torch.int32).contiguous()
+            self._st_molecule_map = mm
+        cm = self._st_cell_molecules.to(device=dev, dtype=torch.float32).contiguous()
+        pos = self._st_cell_positions.to(device=dev, dtype=torch.int32).contiguous()
         return mm, cm, pos
+
+    # ------------------------------------------------------------------ deferred early-exit check
+    # The reference's adjustment loop ends on a GLOBAL condition (kinetics.py:846-847), which the
+    # host settles from 24 flag words after the kinetics launch (Kinetics._settle_early_exit); with
+    # realistic populations the answer is always "the launch stands".  Blocking on the flags right
+    # after the launch leaves the GPU idle while the host then enqueues the write-back and the whole
+    # diffusion (nine launches and, on several GPUs, three collectives: ~0.45 ms per step).  Instead
+    # the verdict is also computed on the device (ms_early_exit_verdict) and everything that commits
+    # results until the flags are read is launched behind that gate (ms_step_gate): the host returns
+    # from enzymatic_activity() without a synchronisation, enqueues the rest of the step while the
+    # kinetics kernel runs, and reads the flags at the next touch of the state (_settle: the next
+    # enzymatic_activity(), any access to cell_molecules / molecule_map / cell_positions or to the
+    # kinetics parameters, any lifecycle call).  If the verdict was "repeat" nothing was committed,
+    # and the step is redone from the untouched state the blocking way.  An out-of-map cell position
+    # raises its IndexError at that point, like an asynchronous CUDA error.
+    deferred_settle = True  # False: block on the flags inside enzymatic_activity()
+
+    def _can_defer(self) -> bool:
+        cls = type(self)
+        return bool(self.deferred_settle) and all(getattr(cls, h) is getattr(World, h) for h in _KERNEL_HOOKS)
+
+    def _reduce_flags_device(self, flags: torch.Tensor) -> torch.Tensor:
+        """the flags of all ranks, still on the device (SlabWorld: MAX over ranks, no host round trip)"""
+        return flags
+
+    def _gate(self):
+        """context: launches inside commit only if the pending verdict allows it"""
+        return _StepGate(self._pending["gate"] if self._pending is not None else None)
+
+    def _settle(self):
+        pend = self._pending
+        if pend is None:
+            return
+        self._pending = None
+        pend["kin"]._guard = None
+        flags = pend["flags"].tolist()  # the step's one synchronisation
+        eq = [4, 4, 4]
+        try:
+            redo = _settle_early_exit(flags, eq, 3)
+        except IndexError:
+            self._st_cell_molecules = pend["cm"]  # nothing was committed
+            raise
+        if not redo:
+            return
+        # the reference would have left an adjustment loop early: the gate stayed shut, state is as before the step
+        self._st_cell_molecules = pend["cm"]
+        self._activity_blocking(eq)
+        for op in pend["replay"]:
+            op()
+
+    def _activity_blocking(self, eq: list[int]):
+        """enzymatic_activity with the flags read after every launch (eq is lowered until the launch stands)"""
+        dev = self._device_for_step()
+        mm, cm, pos = self._state_on_device(dev)
+        c, s = self.n_cells, 2 * self.n_molecules
+        X = torch.empty(c, s, dtype=torch.float32, device=dev)
+        while True:
+            flags = self._launch_activity(dev, pos, cm, mm, X, eq) if c > 0 else [0] * nat.N_FLAGS
+            if not _settle_early_exit(self._reduce_flags(flags), eq, 3):
+                break
+        if c > 0:
+            self._st_cell_molecules = self._launch_scatter(dev, X, pos, mm)
 
     # ------------------------------------------------------------------ step methods
     # The step methods are written against a few hooks so that the multi-GPU SlabWorld
@@ -322,25 +407,39 @@ class World:
 
     def enzymatic_activity(self):
         """world.py:610-625"""
+        self._settle()
         if self._all_ranks_empty():
             return
         dev = self._device_for_step()
         kin = self.kinetics
-        mm, cm, pos = self._state_on_device(dev)
         m = self.n_molecules
         c, s = self.n_cells, 2 * m
         if kin._overrides("integrate_signals") or any(kin._overrides(k) for k in _STAGE_METHODS):
+            mm, cm, pos = self._state_on_device(dev)
             xs, ys = pos[:, 0].long(), pos[:, 1].long()
             X = kin.integrate_signals(X=torch.cat([cm, mm[:, xs, ys].T], dim=1))
-        else:
-            X = torch.empty(c, s, dtype=torch.float32, device=dev)
-            eq = [4, 4, 4]
-            while True:
-                flags = self._launch_activity(dev, pos, cm, mm, X, eq) if c > 0 else [0] * nat.N_FLAGS
-                if not _settle_early_exit(self._reduce_flags(flags), eq, 3):
-                    break
+            if c > 0:
+                self._st_cell_molecules = self._launch_scatter(dev, X, pos, mm)
+            return
+        if not self._can_defer():
+            self._activity_blocking([4, 4, 4])
+            return
+        mm, cm, pos = self._state_on_device(dev)
+        X = torch.empty(c, s, dtype=torch.float32, device=dev)
+        eq = [4, 4, 4]
         if c > 0:
-            self.cell_molecules = self._launch_scatter(dev, X, pos, mm)
+            flags = self._launch_activity(dev, pos, cm, mm, X, eq)
+        else:  # a rank without cells still takes part in the other ranks' decision
+            flags = kin._flags(dev)[: nat.N_FLAGS * 4].view(torch.int32)
+            flags.zero_()
+        flags = self._reduce_flags_device(flags)
+        gate = self._buffer("gate", 256, dev)
+        nat.check(nat.lib().ms_early_exit_verdict(nat.ptr(flags), nat.eq_array(eq), 3, nat.ptr(gate), nat.stream_ptr(dev)))
+        self._pending = {"flags": flags, "gate": gate, "cm": cm, "kin": kin, "replay": []}
+        kin._guard = self._settle
+        if c > 0:
+            with self._gate():
+                self._st_cell_molecules = self._launch_scatter(dev, X, pos, mm)
 
     def _all_ranks_empty(self) -> bool:
         return self.n_cells == 0
@@ -357,20 +456,26 @@ class World:
         if m == 0:
             return
         decay = self._const_f32("decay", list(self._mol_degrads), dev) if degrade_first else None
+        if self._pending is not None:  # not committed unless the pending verdict allows it; redone otherwise
+            self._pending["replay"].append(lambda: self.diffuse_molecules(degrade_first=degrade_first))
         top, bottom = self._exchange_halos(mm)
         out, sums = self._launch_stencil(dev, mm, top, bottom, decay)
         sums = self._reduce_sums(sums)
-        self._launch_correct(dev, out, mm, sums, self._n_pixels_total(H, W))
-        if self.n_cells == 0:
-            return
-        self.cell_molecules = self._launch_permeate(dev, cm, mm, pos, decay)
+        with self._gate():
+            self._launch_correct(dev, out, mm, sums, self._n_pixels_total(H, W))
+            if self.n_cells > 0:
+                self._st_cell_molecules = self._launch_permeate(dev, cm, mm, pos, decay)
 
     def degrade_molecules(self):
         """world.py:667-678: per-molecule decay of the map and of the cell molecules, in place, one launch"""
         dev = self._device_for_step()
         mm, cm, _ = self._state_on_device(dev)
-        self.cell_molecules = cm
-        self._launch_degrade(dev, mm, cm)
+        if self._pending is not None:
+            self._pending["replay"].append(self.degrade_molecules)
+            cm = cm.clone() if cm is self._pending["cm"] else cm  # the step's input stays as it was
+        self._st_cell_molecules = cm
+        with self._gate():
+            self._launch_degrade(dev, mm, cm)
 
     def increment_cell_lifetimes(self):
         """world.py:680-687"""
@@ -384,6 +489,7 @@ class World:
         spawn_cells + set_cell_params produce, world.py:287-341).  Without `cell_molecules`
         each new cell takes half of its pixel's molecules (world.py:335-338).
         """
+        self._settle()
         n = int(positions.shape[0])
         if n == 0:
             return []
@@ -414,6 +520,7 @@ class World:
 
     def kill_cells(self, cell_idxs: list[int] | None = None):
         """world.py:495-540: spill molecules, compact every per-cell tensor order-preservingly"""
+        self._settle()
         if cell_idxs is None:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
@@ -440,6 +547,7 @@ class World:
         world.py:446-475 after the reference's Rust helper has picked the children's pixels:
         children are appended, inherit the parents' parameters and half of their molecules.
         """
+        self._settle()
         n = len(parent_idxs)
         if n == 0:
             return []
@@ -491,6 +599,7 @@ class World:
 
     def spawn_cells(self, genomes: list[str]) -> list[int]:
         """world.py:287-341: new cells on random free pixels, each takes half of its pixel's molecules"""
+        self._settle()
         n = len(genomes)
         if n == 0:
             return []
@@ -521,6 +630,7 @@ class World:
 
     def divide_cells(self, cell_idxs: list[int]) -> list[tuple[int, int]]:
         """world.py:406-475: every cell with a free Moore pixel puts a clone there; (ancestor, new) pairs"""
+        self._settle()
         if len(cell_idxs) == 0:
             return []
         parents, children, child_pos = _hostlib().divide_cells_if_possible(
@@ -532,6 +642,7 @@ class World:
 
     def update_cells(self, genome_idx_pairs: list[tuple[str, int]]):
         """world.py:476-492: new genomes for existing cells, parameters re-derived"""
+        self._settle()
         if len(genome_idx_pairs) == 0:
             return
         last = {}
@@ -542,6 +653,7 @@ class World:
 
     def move_cells(self, cell_idxs: list[int] | None = None):
         """world.py:543-574: every cell steps onto a random free pixel of its Moore neighbourhood, if any"""
+        self._settle()
         if cell_idxs is None:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
@@ -557,6 +669,7 @@ class World:
 
     def reposition_cells(self, cell_idxs: list[int] | None = None):
         """world.py:576-608: the cells are taken off the map and put on random free pixels"""
+        self._settle()
         if cell_idxs is None:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
@@ -570,6 +683,7 @@ class World:
 
     def mutate_cells(self, cell_idxs: list[int] | None = None, p: float = 1e-6, p_indel: float = 0.4, p_del: float = 0.66):
         """world.py:689-714: point mutations in the genomes, parameters of the changed cells re-derived"""
+        self._settle()
         if cell_idxs is None:
             mutated = point_mutations(seqs=self.cell_genomes, p=p, p_indel=p_indel, p_del=p_del)
             self.update_cells(genome_idx_pairs=mutated)
@@ -580,6 +694,7 @@ class World:
 
     def recombinate_cells(self, cell_idxs: list[int] | None = None, p: float = 1e-7):
         """world.py:716-745: recombinations between the genomes of neighbouring cells"""
+        self._settle()
         if cell_idxs is None:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
@@ -660,6 +775,7 @@ class World:
 
     def save_state(self, statedir):
         """what changes during a simulation: six tensors and the genomes with their labels as FASTA"""
+        self._settle()
         statedir = Path(statedir)
         statedir.mkdir(parents=True, exist_ok=True)
         for key in _STATE_TENSORS:
@@ -670,6 +786,7 @@ class World:
 
     def load_state(self, statedir, ignore_cell_params: bool = False):
         """a state written by save_state(); parameters are re-derived from the genomes unless told otherwise"""
+        self._settle()
         statedir = Path(statedir)
         if not ignore_cell_params:
             self.kill_cells(cell_idxs=list(range(self.n_cells)))
@@ -704,3 +821,28 @@ class World:
 
     def __repr__(self) -> str:
         return f"{type(self).__name__}(map_size:{self.map_size!r},abs_temp:{self.abs_temp!r},device:{self.device!r})"
+
+
+def _state_property(name: str) -> property:
+    """
+    cell_molecules, molecule_map, cell_positions: plain tensor attributes in the reference
+    (world.py:161-204); here reading or assigning one first finishes a step that is still behind
+    its early-exit check (World._settle), so users always see committed state.
+    """
+    key = "_st_" + name
+
+    def getter(self) -> torch.Tensor:
+        if self._pending is not None:
+            self._settle()
+        return self.__dict__[key]
+
+    def setter(self, value):
+        if self.__dict__.get("_pending") is not None:
+            self._settle()
+        self.__dict__[key] = value
+
+    return property(getter, setter, doc=f"World.{name} (world.py:161-204)")
+
+
+for _name in ("cell_molecules", "molecule_map", "cell_positions"):
+    setattr(World, _name, _state_property(_name))

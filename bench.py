@@ -401,9 +401,10 @@ def run_reference(args):
             desc = cpu_sample_text(args, n, n_passes, t_kin, t_diff, cores)
     step_s = sum(times) / len(times)
     value = n * n_passes / step_s
-    cfg = workload_config(args, 1)
-    if args.gpus > 1:
-        cfg["workload"] += " -- the CPU arm always runs the 1-GPU size, on rank 0"
+    cfg = workload_config(args, args.gpus)  # the same config as our arm at this N
+    if args.gpus > 1 and not split_over_ranks(args, args.gpus):
+        # weak scaling: the N-GPU workload is N such populations; a timed step is a bounded sample of it
+        desc = f"bounded sample: 1/{args.gpus} of the {args.gpus}-GPU workload's cells per step (cell-steps/s does not depend on it); " + desc
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "cell-steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * step_s,

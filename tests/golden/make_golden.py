@@ -15,7 +15,7 @@ Fixtures
                            end, incl. the reference's own summation-order noise
                            floor (same inputs, proteins permuted).  Tags c1, wl, two
                            (small) and c4, c4e, c3, s82 (the benchmarked tile shapes).
-  ref_drift_1000.npz       population statistics of a 1000-step reference trajectory (and of
+  ref_drift_1000[_c4].npz  population statistics of a 1000-step reference trajectory (and of
                            the reference with permuted proteins) every 100 steps.
   ref_set_cell_params.npz  Kinetics.set_cell_params on random proteomes: token tables, flattened
                            domain tokens, the nine tensors the reference derives from them.
@@ -210,7 +210,7 @@ def bench_shape_fixtures(ms):
     synthetic_fixture(ms, "s82", c=256, p=40, m=41, map_size=16, seed=34, n_steps=10)  # 16 x 16 map, every pixel occupied
 
 
-def drift_fixture(ms, c=96, p=20, m=6, n_steps=1000, seed=21):
+def drift_fixture(ms, c=96, p=20, m=6, n_steps=1000, seed=21, name="ref_drift_1000.npz"):
     """
     north_star: "drift over 1000 steps".  Population statistics of the reference's own
     trajectory (and of the same run with its proteins permuted = the reference's own drift)
@@ -237,7 +237,7 @@ def drift_fixture(ms, c=96, p=20, m=6, n_steps=1000, seed=21):
         out[f"{tag}_q99"] = np.stack(q99)
         out[f"{tag}_total"] = np.array(tot)
         out[f"{tag}_final"] = _np(X)
-    np.savez_compressed(OUT / "ref_drift_1000.npz", **out)
+    np.savez_compressed(OUT / name, **out)
     print("drift fixture: total mass ref", out["ref_total"][-1], "perm", out["perm_total"][-1])
 
 
@@ -340,6 +340,9 @@ def main():
     if sys.argv[1:] == ["bench"]:
         bench_shape_fixtures(ms)
         return
+    if sys.argv[1:] == ["drift_c4"]:  # the benchmark's tile shape (p=64, s=32) over 1000 steps
+        drift_fixture(ms, c=256, p=64, m=16, n_steps=1000, seed=22, name="ref_drift_1000_c4.npz")
+        return
     if sys.argv[1:] == ["params"]:
         set_cell_params_fixture(ms)
         return
@@ -351,6 +354,7 @@ def main():
     synthetic_fixture(ms, "two", c=2, p=6, m=3, map_size=4, seed=13, n_steps=30)
     bench_shape_fixtures(ms)
     drift_fixture(ms)
+    drift_fixture(ms, c=256, p=64, m=16, n_steps=1000, seed=22, name="ref_drift_1000_c4.npz")
     world_fixture(ms)
     set_cell_params_fixture(ms)
 

@@ -387,12 +387,13 @@ def test_large_population_invariants(ms):
     assert torch.equal(out, kin.integrate_signals(X=X))
 
 
-def test_drift_over_1000_steps_gpu(ms):
+@pytest.mark.parametrize("name", ["ref_drift_1000.npz", "ref_drift_1000_c4.npz"])
+def test_drift_over_1000_steps_gpu(ms, name):
     # 1000 steps on the device: bit-identical to the oracle every 100 steps, and within the
     # reference's own drift bounds (tests/test_oracle_golden.py::check_drift)
     from tests.test_oracle_golden import drift_population, check_drift
 
-    z, pop, n_steps = drift_population()
+    z, pop, n_steps = drift_population(name)
     kin = install(_kinetics(ms, pop.s), pop)
     P = oracle_params(pop)
     X = pop.X0().cuda()

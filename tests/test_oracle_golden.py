@@ -239,10 +239,13 @@ def test_enzymatic_activity_vs_reference(world):
 
 # ---------------------------------------------------------------- drift over 1000 steps
 
-def drift_population():
+DRIFT_FIXTURES = ["ref_drift_1000.npz", "ref_drift_1000_c4.npz"]  # 96 x 20 x 12, and the benchmark's tile shape 256 x 64 x 32
+
+
+def drift_population(name: str = "ref_drift_1000.npz"):
     from magicsoup_b200.synthetic import make_population
 
-    z = np.load(GOLDEN / "ref_drift_1000.npz")
+    z = np.load(GOLDEN / name)
     c, p, m, size, seed, n_steps = [int(v) for v in z["shape"]]
     pop = make_population(c, p, m, size, seed=seed)
     return z, pop, n_steps
@@ -266,8 +269,9 @@ def check_drift(z, stats):
         2 * np.abs(z["perm_zero_frac"] - z["ref_zero_frac"]).max(), 0.02)
 
 
-def test_drift_over_1000_steps():
-    z, pop, n_steps = drift_population()
+@pytest.mark.parametrize("name", DRIFT_FIXTURES)
+def test_drift_over_1000_steps(name):
+    z, pop, n_steps = drift_population(name)
     P = O.Params(*[t.numpy() for t in pop.params()])
     X = pop.X0().numpy()
     stats = {"mean": [], "q99": [], "total": [], "zero_frac": []}

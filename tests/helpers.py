@@ -26,7 +26,7 @@ def bits_equal(a, b) -> bool:
     if a.shape != b.shape:
         return False
     ai, bi = a.view(np.uint32), b.view(np.uint32)
-    same = (ai == bi) | (np.isnan(a) & np.isnan(b)) | ((a == 0) & (b == 0))
+    same = (ai == bi) | (np.isnan(a) & np.isnan(b))  # bit patterns: +0 and -0 differ
     return bool(same.all())
 
 

@@ -518,6 +518,37 @@ std::vector<Pos> free_moores_nghbhd(uint16_t x, uint16_t y, const std::vector<Po
   return out;
 }
 
+// One value per pixel of a square map: a dense array where that is small next to the number of
+// entries it serves (4 Mi pixels, or 16 per entry), a hash map on huge, sparsely populated maps.
+template <class T>
+struct PixelTable {
+  size_t m;
+  T fill;
+  bool dense;
+  std::vector<T> flat;
+  std::unordered_map<uint64_t, T> sparse;
+  PixelTable(uint16_t map_size, size_t n_entries, T fill_value) : m(map_size), fill(fill_value) {
+    const size_t n_pixels = m * m;
+    dense = n_pixels <= ((size_t)1 << 22) || n_pixels <= 16 * n_entries;
+    if (dense) flat.assign(n_pixels, fill);
+    else sparse.reserve(2 * n_entries);
+  }
+  void check(const Pos &p) const {
+    if (p.first >= m || p.second >= m) throw py::index_error("position outside the map");
+  }
+  T &at(const Pos &p) {  // created with the fill value if absent
+    const size_t k = (size_t)p.first * m + p.second;
+    if (dense) return flat[k];
+    return sparse.try_emplace(k, fill).first->second;
+  }
+  T get(const Pos &p) const {
+    const size_t k = (size_t)p.first * m + p.second;
+    if (dense) return flat[k];
+    const auto it = sparse.find(k);
+    return it == sparse.end() ? fill : it->second;
+  }
+};
+
 // first occurrences of a list of indices, order kept
 std::vector<size_t> unique_in_order(const std::vector<size_t> &idxs, size_t n) {
   std::vector<char> seen(n, 0);
@@ -550,20 +581,20 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
   for (size_t r = 0; r < to_idxs.size(); r++) to_rank[to_idxs[r]] = (int64_t)r;
   // pixel -> chain of ranks in to_idxs (ascending rank along the chain)
   const size_t m = map_size;
-  for (const size_t i : to_idxs)
-    if (positions[i].first >= m || positions[i].second >= m) throw py::index_error("position outside the map");
-  std::vector<int64_t> head(m * m, NONE), next(to_idxs.size(), NONE);
+  PixelTable<int64_t> head(map_size, to_idxs.size(), NONE);
+  std::vector<int64_t> next(to_idxs.size(), NONE);
   for (size_t r = to_idxs.size(); r-- > 0;) {
     const Pos &q = positions[to_idxs[r]];
-    const size_t px = (size_t)q.first * m + q.second;
-    next[r] = head[px];
-    head[px] = (int64_t)r;
+    head.check(q);
+    int64_t &h = head.at(q);
+    next[r] = h;
+    h = (int64_t)r;
   }
   std::vector<std::pair<size_t, size_t>> out;
   std::vector<int64_t> ranks;
   for (const size_t from : from_idxs) {
     const Pos &p0 = positions[from];
-    if (p0.first >= m || p0.second >= m) throw py::index_error("position outside the map");
+    head.check(p0);
     std::array<uint32_t, 9> pixels;  // the 3 x 3 block, without duplicates on tiny maps
     size_t n_px = 0;
     pixels[n_px++] = pixel_key(p0.first, p0.second);
@@ -574,7 +605,8 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
     }
     ranks.clear();
     for (size_t k = 0; k < n_px; k++)
-      for (int64_t r = head[(size_t)(pixels[k] >> 16) * m + (pixels[k] & 0xffffu)]; r != NONE; r = next[r]) ranks.push_back(r);
+      for (int64_t r = head.get({(uint16_t)(pixels[k] >> 16), (uint16_t)(pixels[k] & 0xffffu)}); r != NONE; r = next[r])
+        ranks.push_back(r);
     std::sort(ranks.begin(), ranks.end());
     for (const int64_t r : ranks) {
       const size_t to = to_idxs[(size_t)r];
@@ -589,15 +621,15 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
 
 // cells per pixel of a square map
 struct Occupancy {
-  size_t m;
-  std::vector<int32_t> count;
-  Occupancy(const std::vector<Pos> &positions, uint16_t map_size) : m(map_size), count((size_t)map_size * map_size, 0) {
+  PixelTable<int32_t> count;
+  Occupancy(const std::vector<Pos> &positions, uint16_t map_size) : count(map_size, positions.size(), 0) {
     for (const auto &p : positions) {
-      if (p.first >= m || p.second >= m) throw py::index_error("position outside the map");
-      count[(size_t)p.first * m + p.second]++;
+      count.check(p);
+      count.at(p)++;
     }
   }
-  int32_t &at(const Pos &p) { return count[(size_t)p.first * m + p.second]; }
+  int32_t &at(const Pos &p) { return count.at(p); }
+  int32_t get(const Pos &p) const { return count.get(p); }
 };
 
 // rust/world.rs:59-99: in the order of cell_idxs, every cell picks one free Moore pixel at random
@@ -614,7 +646,7 @@ std::tuple<std::vector<size_t>, std::vector<size_t>, std::vector<Pos>> divide_ce
     std::array<Pos, 8> opts;
     size_t n_opts = 0;
     for (const auto &p : moore(p0.first, p0.second, map_size))
-      if (occ.at(p) == 0) opts[n_opts++] = p;
+      if (occ.get(p) == 0) opts[n_opts++] = p;
     if (n_opts == 0) continue;
     const Pos pick = opts[(size_t)(rng.uniform() * (double)n_opts)];
     occ.at(pick)++;
@@ -639,7 +671,7 @@ std::tuple<std::vector<Pos>, std::vector<size_t>> move_cells(const std::vector<s
     std::array<Pos, 8> opts;
     size_t n_opts = 0;
     for (const auto &p : moore(p0.first, p0.second, map_size))
-      if (occ.at(p) == 0) opts[n_opts++] = p;
+      if (occ.get(p) == 0) opts[n_opts++] = p;
     if (n_opts == 0) continue;
     const Pos pick = opts[(size_t)(rng.uniform() * (double)n_opts)];
     occ.at(p0)--;

@@ -694,8 +694,9 @@ def main():
                        "memory and reads its results back; copies on their own streams, so the upload of step t+1 and "
                        "the read-back of step t-1 overlap the kernels of step t; timed with CUDA events and the host "
                        "clock around all steps (the larger of the two)"},
-        # per step: kinetics (lane kernel + the launch for deferred cells), scatter, stencil, correct, permeate
-        "gpu_launches": 6 * args.steps,
+        # per step: kinetics (lane kernel + the launch for deferred cells), early-exit verdict, write-back, stencil,
+        # correction, permeation
+        "gpu_launches": 7 * args.steps,
         "clocks": clocks,
     }
     if extra:

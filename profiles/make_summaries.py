@@ -42,7 +42,7 @@ def launch_list():
     lines = [
         f"# ncu launch list of `{BENCH_CMD}` (1,048,576 cells, p=64, s=32, one B200)",
         "# ncu --metrics gpu__time_duration.sum --clock-control none "
-        "-k regex:^(kinetics_|stencil_|correct_kernel|permeate_|scatter_|degrade_kernel|pixel_index) -c 200",
+        "-k regex:^(kinetics_|stencil_|correct_kernel|permeate_|scatter_|degrade_kernel|pixel_index|early_exit_verdict) -c 200",
         "# the command runs 5 steps with cached lists (1 builds them) and 4 steps of the scan path; per-launch",
         "# times are cold-cache and serialised: compare SHARES, not absolutes",
         "kernel,launches,total_ms,avg_ms,min_ms,max_ms,share",

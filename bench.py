@@ -177,6 +177,7 @@ def build_world(cells, proteins, molecules, map_rows, map_cols, device, seed, wo
         from magicsoup_b200.distributed import SlabWorld
 
         world = SlabWorld(chemistry=chem, global_map_size=(map_rows * world_size, map_cols), device=str(device))
+        world.deferred_settle = True  # every rank runs the same loop: the early-exit check may trail the step
     else:
         world = ms.World(chemistry=chem, map_size=map_rows if map_rows == map_cols else (map_rows, map_cols),
                          device=str(device))
@@ -434,6 +435,7 @@ def workload_config(args, n_gpus):
         "cells_per_gpu": args.cells // n_gpus if split_over_ranks(args, n_gpus) else args.cells,
         "proteins": args.proteins, "signals": s, "map": [args.map, args.map],
         "parallelism": f"cells+map-slab x{n_gpus}", "energies": args.energies, "list_cache": not args.no_list_cache,
+        "deferred_settle": True,
         "l2": "parameters (42 KB per cell) exceed L2 by orders of magnitude; no flush needed",
     }
 

@@ -30,7 +30,7 @@ import torch
 import torch.distributed as dist
 
 from magicsoup_b200.kinetics import _ALL_PARAMS
-from magicsoup_b200.world import World
+from magicsoup_b200.world import World, _KERNEL_HOOKS
 
 
 def even_slab_heights(n_rows: int, world_size: int) -> list[int]:
@@ -152,9 +152,21 @@ class SlabWorld(World):
             dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=self.group)
         return flags
 
+    # On several ranks the deferred early-exit check (World._settle) is opt-in: when the verdict is
+    # "repeat" (tiny or fully equilibrated populations) the step is redone with collectives at the
+    # rank's next touch of its state, so every rank has to touch its state at the same points of
+    # the program -- true for a plain SPMD loop (bench.py sets it), not for a program where, say,
+    # only rank 0 reads cell_molecules for logging between two steps.
+    deferred_settle = False
+
     def _can_defer(self) -> bool:
+        cls = type(self)
+        hooks_own = all(getattr(cls, h) is getattr(World, h) for h in _KERNEL_HOOKS)
+        if self.world_size == 1:  # one rank: nothing collective in a repeat, World's default applies
+            wanted = self.__dict__.get("deferred_settle", World.deferred_settle)
+            return bool(wanted) and hooks_own
         # the collectives of the deferred sequence run on the step's device: NCCL only
-        return super()._can_defer() and (self.world_size == 1 or dist.get_backend(self.group) == "nccl")
+        return bool(self.deferred_settle) and hooks_own and dist.get_backend(self.group) == "nccl"
 
     def _reduce_sums(self, sums: torch.Tensor) -> torch.Tensor:
         if self.world_size > 1:

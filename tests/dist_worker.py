@@ -126,7 +126,7 @@ def gather_params(world: SlabWorld):
 
 
 def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, seed: int, quiet: bool = False,
-        rows: int | None = None) -> None:
+        rows: int | None = None, deferred: bool = True) -> None:
     rank, ws = dist.get_rank(), dist.get_world_size()
     if backend == "nccl":
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -141,6 +141,7 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
     mols = [Molecule(f"d{i}", 10e3, diffusivity=pop.diffusivities[i], permeability=pop.permeabilities[i])
             for i in range(pop.m)]
     world = cls(chemistry=Chemistry(molecules=mols, reactions=[]), global_map_size=(H, cols), device=device)
+    world.deferred_settle = deferred  # all ranks run the same sequence of calls here (no effect on the gloo hooks)
     r0, r1 = world.row0, world.row0 + world.slab_rows
     world.molecule_map = pop.molecule_map[:, r0:r1].clone().to(device)
     mine = torch.nonzero((pop.cell_positions[:, 0] >= r0) & (pop.cell_positions[:, 0] < r1)).flatten()
@@ -248,7 +249,7 @@ def run(backend: str, steps: int, cells: int, rows_per_rank: int, cols: int, see
     assert int(world.cell_map.sum()) == world.n_cells
     xs, ys = world.cell_positions[:, 0].long(), world.cell_positions[:, 1].long()
     assert world.n_cells == 0 or bool(world.cell_map[xs, ys].all())
-    if ws > 1:
+    if ws > 1 and cells >= 50:  # (a handful of cells leaves nothing to balance)
         def fullest(hs):
             at, worst = 0, 0.0
             for h in hs:
@@ -277,12 +278,14 @@ def main():
     ap.add_argument("--cells", type=int, default=300)
     ap.add_argument("--rows-per-rank", type=int, default=16)
     ap.add_argument("--rows", type=int, default=None, help="total map rows (need not divide by the number of ranks)")
+    ap.add_argument("--blocking", action="store_true", help="SlabWorld.deferred_settle = False (the multi-rank default)")
     ap.add_argument("--cols", type=int, default=24)
     ap.add_argument("--seed", type=int, default=5)
     args = ap.parse_args()
     dist.init_process_group(args.backend)
     try:
-        run(args.backend, args.steps, args.cells, args.rows_per_rank, args.cols, args.seed, rows=args.rows)
+        run(args.backend, args.steps, args.cells, args.rows_per_rank, args.cols, args.seed, rows=args.rows,
+            deferred=not args.blocking)
     finally:
         dist.destroy_process_group()
 

@@ -21,7 +21,8 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("nproc,cells,rows", [(2, 300, None), (3, 200, None), (1, 100, None), (3, 250, 50), (2, 200, 31)])
+@pytest.mark.parametrize("nproc,cells,rows", [(2, 300, None), (3, 200, None), (1, 100, None), (3, 250, 50), (2, 200, 31),
+                                              (2, 5, 8)])  # five cells: the global early exit fires across ranks
 def test_slab_world_matches_single_domain_oracle(nproc, cells, rows):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),

@@ -23,17 +23,21 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("shape", [(300, 16, 24), (20000, 128, 128)], ids=["generic-stencil", "tiled-stencil"])
-def test_nccl_slab_world_matches_oracle(shape):
+@pytest.mark.parametrize("blocking", [False, True], ids=["deferred", "blocking"])
+@pytest.mark.parametrize("shape", [(300, 16, 24), (20000, 128, 128), (5, 4, 8)],
+                         ids=["generic-stencil", "tiled-stencil", "five-cells"])
+def test_nccl_slab_world_matches_oracle(shape, blocking):
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs at least 2 GPUs")
-    nproc = min(n, 4)
     cells, rows, cols = shape
+    nproc = 2 if cells < 100 else min(n, 4)  # five cells: the global early exit fires and steps are repeated
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            str(ROOT / "tests" / "dist_worker.py"), "--backend", "nccl", "--cells", str(cells),
            "--rows-per-rank", str(rows), "--cols", str(cols)]
+    if blocking:  # SlabWorld's multi-rank default; otherwise the early-exit check trails the step (opt-in)
+        cmd.append("--blocking")
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=dict(os.environ))
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "dist_worker ok" in res.stdout

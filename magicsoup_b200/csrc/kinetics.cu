@@ -67,6 +67,8 @@ struct KinArgs {
   // lists build_lists produced for it (batch mode only); rec_seg: the three region segments a record
   // holds, {word offset, words} each.
   const int *row_map;
+  unsigned *phase_recs;   // phased lane kernel: (grid x phase_batch) records of scratch, see kinetics_lanes_phased_kernel
+  int phase_batch, phase_ahead;
   unsigned *cache;
   int rec_words;
   int rec_seg[6];
@@ -1272,6 +1274,152 @@ __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_lanes_
   if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
 }
 
+// ---------------------------------------------------------------------------
+// The lane path with the dense tiles read in every launch (no list cache), phased per SM.
+// In kinetics_lanes_kernel a warp scans, builds and integrates its cell in one go; with 32 warps of an
+// SM at different places of those 46 KB of code the instruction cache (32 KB) misses all the time
+// (28 % of the warp samples wait for instructions).  Here ONE CTA of 32 warps owns the SM and takes
+// rounds of `phase_batch` cells: first all warps scan tiles and build lists (records go to a scratch
+// slot in global memory, i.e. L2), then, after a CTA barrier, all warps integrate from the records.
+// Each phase's code fits the cache; cells are handed out dynamically inside a phase, so a round
+// ends at most one cell's work after its average warp.  Same device functions, same lists, same
+// bits as kinetics_lanes_kernel.
+// ---------------------------------------------------------------------------
+constexpr int PHASED_THREADS = 1024;
+
+// the four dense (p,s) int32 tiles of a parameter row on their way into L2 (this GPU's memory), one
+// bulk prefetch each: the scan that follows a cell-time later finds them there instead of in HBM
+__device__ __forceinline__ void prefetch_tiles(const KinArgs &a, long long cell, int lane) {
+  if (lane >= 4) return;
+  const long long tile = param_row(a, cell) * (long long)a.p * a.s;
+  const int *src = (lane == 0 ? a.Nf : lane == 1 ? a.Nb : lane == 2 ? a.N : a.A) + tile;
+  const unsigned bytes = (unsigned)a.p * (unsigned)a.s * 4u;  // a multiple of 16 (VEC == 4: s % 4 == 0)
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(PHASED_THREADS, 1) kinetics_lanes_phased_kernel(const __grid_constant__ KinArgs a) {
+  extern __shared__ __align__(16) unsigned smem[];
+  __shared__ unsigned sflags[MS_N_FLAGS];
+  __shared__ long long s_base_next;
+  __shared__ int s_next[2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < MS_N_FLAGS) sflags[threadIdx.x] = 0;
+  const unsigned raw = (unsigned)__cvta_generic_to_shared(smem);
+  unsigned aligned = (raw + (unsigned)a.smem_align - 1u) & ~((unsigned)a.smem_align - 1u);
+  asm volatile("mov.b32 %0, %0;" : "+r"(aligned));
+  unsigned *b = smem + ((aligned - raw) >> 2) + (size_t)warp * a.words_per_warp;
+  const unsigned sb = aligned + (unsigned)warp * (unsigned)a.words_per_warp * 4u;
+  const int p = a.p, s = a.s;
+  const long long n_items = a.c;
+  const LaneLayout &L = a.lanes;
+  const int rec_words = REC_HEADER_WORDS + L.static_words;
+  unsigned *slots = a.phase_recs + (size_t)blockIdx.x * (size_t)a.phase_batch * (size_t)rec_words;
+  const int n16 = L.static_words >> 2;
+  const int AHEAD = a.phase_ahead;  // a warp that takes item i sends item i + AHEAD on its way
+  unsigned wflags = 0;
+  auto take = [&](int phase) -> int {
+    int v = 0;
+    if (lane == 0) v = atomicAdd(&s_next[phase], 1);
+    return __shfl_sync(FULL, v, 0);
+  };
+  if (threadIdx.x == 0) s_base_next = (long long)atomicAdd(a.work_counter, a.phase_batch);
+  __syncthreads();
+  {  // the first round starts cold: at least its first items are requested before anything else
+    const long long first = s_base_next + warp;
+    if (warp < AHEAD && first < n_items) prefetch_tiles(a, first, lane);
+  }
+#pragma unroll 1
+  for (;;) {
+    const long long base = s_base_next;
+    __syncthreads();  // everyone holds this round's base; the round before is done (records, counters)
+    if (base >= n_items) break;
+    if (threadIdx.x == 0) {
+      s_next[0] = 0;
+      s_next[1] = 0;
+      s_base_next = (long long)atomicAdd(a.work_counter, a.phase_batch);  // the round after this one
+    }
+    __syncthreads();
+    const int n = (int)(n_items - base < (long long)a.phase_batch ? n_items - base : (long long)a.phase_batch);
+
+    // ---- phase 1: tiles -> lists -> record slots
+#pragma unroll 1
+    for (int i = take(0); i < n; i = take(0)) {
+      if (AHEAD > 0 && i + AHEAD < n) prefetch_tiles(a, base + i + AHEAD, lane);
+      const long long prm = param_row(a, base + i);
+      const long long tile = prm * (long long)p * s;
+      LaneCounts cnt = {0, 0, 0};
+      const int nq = scan_tile_lanes(a.Nf + tile, a.Nb + tile, a.N + tile, a.A + tile, p, s, sb,
+                                     sb + 4u * (unsigned)L.oQueue, L.q_cap, lane);
+      __syncwarp();
+      const bool ok = nq >= 0 && build_lane_lists(a, L, b, sb, prm, lane, nq, cnt);
+      unsigned *rec = slots + (size_t)i * rec_words;
+      if (ok) {
+        cp_async_wait_all();  // scalars and Kmr have landed
+        __syncwarp();
+        uint4 *dst = reinterpret_cast<uint4 *>(rec + REC_HEADER_WORDS);
+        const uint4 *seg = reinterpret_cast<const uint4 *>(b);
+#pragma unroll 1
+        for (int e = lane; e < n16; e += 32) dst[e] = seg[e];
+      }
+      if (lane == 0) rec[0] = ok ? (REC_VALID << 24) | pack_counts(cnt) : REC_OVERFLOW << 24;
+      __syncwarp();
+    }
+    __syncthreads();  // all records of the round are written (and visible to the CTA)
+    {  // the next round's first items travel to L2 while this round is integrated
+      const long long ahead = s_base_next + warp;
+      if (warp < AHEAD && ahead < n_items) prefetch_tiles(a, ahead, lane);
+    }
+
+    // ---- phase 2: records -> three parts -> X_out; the next cell's signals are fetched ahead
+    int i = take(1);
+    float xa = 0.0f, xb = 0.0f;
+    if (i < n) {
+      const float4 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, base + i, lane);
+      xa = v.x;
+      xb = v.y;
+      if (v.z != 0.0f) wflags |= 1u << MS_FLAG_BAD_POSITION;
+    }
+#pragma unroll 1
+    while (i < n) {
+      const int i_next = take(1);
+      const long long cell = base + i;
+      const unsigned *rec = slots + (size_t)i * rec_words;
+      const unsigned hdr = *reinterpret_cast<const volatile unsigned *>(rec);
+      const bool ok = (hdr >> 24) == REC_VALID;
+      LaneCounts cnt = {0, 0, 0};
+      if (ok) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(rec + REC_HEADER_WORDS);
+#pragma unroll 1
+        for (int e = lane; e < n16; e += 32) cp_async16(sb + 16u * (unsigned)e, src + e, 0u);
+        cnt = unpack_counts(hdr);
+        if (lane < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane), xa);
+        if (lane + 32 < s) sts_f(sb + 4u * (unsigned)(L.oX0 + lane + 32), xb);
+      }
+      if (i_next < n) {
+        const float4 v = load_cell_signals(a.X_in, a.cell_mols, a.mol_map, a.pos, s, a.m, a.H, a.W, base + i_next, lane);
+        xa = v.x;
+        xb = v.y;
+        if (v.z != 0.0f) wflags |= 1u << MS_FLAG_BAD_POSITION;
+      }
+      cp_async_wait_all();
+      __syncwarp();
+      if (ok) {
+        run_lanes(a, L, sb, cell, lane, cnt, wflags);
+#pragma unroll 1
+        for (int k = lane; k < s; k += 32) a.X_out[cell * s + k] = lds_f(sb + 4u * (unsigned)(L.oX0 + k));
+      } else if (lane == 0) {
+        a.defer_list[atomicAdd(a.defer_count, 1)] = (int)cell;  // integrated by the tier-2 launch
+      }
+      __syncwarp();
+      i = i_next;
+    }
+  }
+  if (lane < MS_N_FLAGS && ((wflags >> lane) & 1u)) sflags[lane] = 1u;
+  __syncthreads();
+  if (threadIdx.x < MS_N_FLAGS && sflags[threadIdx.x]) a.flags[threadIdx.x] = 1u;
+}
+
 template <int VEC>
 __global__ void __launch_bounds__(MAX_THREADS, MS_TUNE_MIN_CTAS) kinetics_fused_kernel(const __grid_constant__ KinArgs a,
                                                                     float *dense_scratch) {
@@ -1697,9 +1845,12 @@ static int sm_count() {
 
 // Diagnostic switches, read from the environment ONCE, at the first launch of the
 // process; ms_kinetics_reload_switches() re-reads them (tests flip them between launches).
+constexpr int MAX_PHASE_BATCH = 1024, MAX_PHASED_CTAS = 192;
 struct Switches {
-  bool no_lanes, no_batch, no_staged_scan, staged_depth1;
+  bool no_lanes, no_batch, no_staged_scan, staged_depth1, phased;
   int max_ctas_per_sm;  // 0 = no limit
+  int phase_batch;      // cells per round and SM of the phased lane kernel
+  int phase_ahead;      // how many cells ahead of the one a warp takes its tiles are prefetched into L2 (0: never)
 };
 static Switches read_switches() {
   Switches sw;
@@ -1709,6 +1860,15 @@ static Switches read_switches() {
   sw.staged_depth1 = getenv("MS_KIN_STAGED_DEPTH1") != nullptr;
   const char *env = getenv("MS_KIN_MAX_CTAS_PER_SM");
   sw.max_ctas_per_sm = env ? atoi(env) : 0;
+  sw.phased = getenv("MS_KIN_PHASED") != nullptr;
+  env = getenv("MS_KIN_PHASE_BATCH");
+  sw.phase_batch = env ? atoi(env) : 512;
+  if (sw.phase_batch < 32) sw.phase_batch = 32;
+  if (sw.phase_batch > MAX_PHASE_BATCH) sw.phase_batch = MAX_PHASE_BATCH;
+  env = getenv("MS_KIN_PHASE_AHEAD");
+  sw.phase_ahead = env ? atoi(env) : 0;  // measured: any distance > 0 is slower
+  if (sw.phase_ahead < 0) sw.phase_ahead = 0;
+  if (sw.phase_ahead > 32) sw.phase_ahead = 32;
   return sw;
 }
 static Switches &switches() {
@@ -1822,10 +1982,16 @@ using namespace ms;
 
 extern "C" void ms_kinetics_reload_switches(void) { switches() = read_switches(); }
 
+// record slots of the phased lane kernel: one round per CTA
+static size_t phased_scratch_bytes(int64_t p, int64_t s) {
+  if (!lanes_possible(p, s) || !switches().phased) return 0;
+  const size_t rec_words = REC_HEADER_WORDS + (size_t)make_lane_layout((int)p, (int)s).static_words;
+  return align256k((size_t)MAX_PHASED_CTAS * (size_t)switches().phase_batch * rec_words * sizeof(unsigned));
+}
+
 extern "C" size_t ms_kinetics_scratch_bytes(int64_t c, int64_t p, int64_t s) {
-  (void)s;
   if (c < 0) c = 0;
-  return dense_scratch_bytes(p) + 256 + align256k((size_t)c * sizeof(int));
+  return dense_scratch_bytes(p) + 256 + align256k((size_t)c * sizeof(int)) + phased_scratch_bytes(p, s);
 }
 
 template <typename K>
@@ -1870,9 +2036,43 @@ static int launch_lanes_one(K kern, const LaunchPlan &pl, KinArgs &a, cudaStream
   return MS_OK;
 }
 
+// one CTA of 32 warps per SM; false if the shape's regions do not fit 32 times
+static bool launch_lanes_phased(const LaunchPlan &pl, KinArgs &a, cudaStream_t st, int &rc) {
+  const size_t smem = (size_t)pl.words_per_warp * 4 * (PHASED_THREADS / 32) + pl.align;
+  if (smem > SMEM_PER_SM_HW) return false;
+  auto kern = kinetics_lanes_phased_kernel<4>;
+  rc = MS_OK;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  a.words_per_warp = pl.words_per_warp;
+  a.region_bytes = (unsigned)pl.words_per_warp * 4u;
+  a.smem_align = pl.align;
+  a.lanes = make_lane_layout(a.p, a.s);
+  a.sparse_enabled = 1;
+  a.phase_batch = switches().phase_batch;
+  a.phase_ahead = switches().phase_ahead;
+  int grid = sm_count();
+  if (grid > MAX_PHASED_CTAS) grid = MAX_PHASED_CTAS;
+  const long long rounds = ceil_div(a.c, a.phase_batch);
+  if (grid > rounds) grid = (int)rounds;
+  kern<<<grid, PHASED_THREADS, smem, st>>>(a);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    ms_set_cuda_error_(e);
+    rc = MS_ERR_CUDA;
+  }
+  return true;
+}
+
 static int launch_lanes(const LaunchPlan &pl, KinArgs &a, cudaStream_t st) {
   int vec = pick_vec(a);
   if (vec == 4 && switches().no_staged_scan) vec = 2;  // register scan
+  if (vec == 4 && switches().phased && !a.cache && a.phase_recs) {
+    int rc = MS_OK;
+    if (launch_lanes_phased(pl, a, st, rc)) return rc;
+  }
   if (vec == 4) return launch_lanes_one(kinetics_lanes_kernel<4>, pl, a, st);
   if (vec == 2) return launch_lanes_one(kinetics_lanes_kernel<2>, pl, a, st);
   return launch_lanes_one(kinetics_lanes_kernel<1>, pl, a, st);
@@ -1924,6 +2124,9 @@ static int launch_fused(const ms_kinetics_params *P, KinArgs &a, void *scratch, 
   a.defer_count = (int *)((char *)scratch + dense_scratch_bytes(P->p));
   a.work_counter = a.defer_count + 1;  // [0] deferred count, [1] tier-1 work, [2] tier-2 work
   a.defer_list = a.defer_count + 64;
+  a.phase_recs = phased_scratch_bytes(P->p, P->s)
+                     ? (unsigned *)((char *)scratch + dense_scratch_bytes(P->p) + 256 + align256k((size_t)P->c * sizeof(int)))
+                     : nullptr;
 
   // the lane kernel defers what it cannot pack, so it needs a tier 2 (true for every p, s <= 64)
   LaunchPlan p2;

@@ -229,6 +229,40 @@ def test_kernel_paths_agree_bit_for_bit(ms, shape, monkeypatch):
         assert bits_equal(out, ora), f"{env}: " + describe_mismatch(out, ora)
 
 
+@pytest.mark.parametrize("batch", ["32", "96", "512"])
+@pytest.mark.parametrize("shape", [_SHAPES[0], _SHAPES[1], _SHAPES[2], _SHAPES[4]],
+                         ids=[f"c{c}p{p}s{2*m}" for c, p, m, _, _ in [_SHAPES[0], _SHAPES[1], _SHAPES[2], _SHAPES[4]]])
+def test_phased_lane_kernel_gives_the_same_bits(ms, shape, batch, monkeypatch):
+    """MS_KIN_PHASED: the lane path with the list cache off as one CTA per SM that alternates between
+    a build phase and an integration phase (a measured variant); rounds smaller and
+    larger than the population, through the row map as well"""
+    from magicsoup_b200 import _native
+    c, p, m, size, seed = shape
+    pop = make_population(c, p, m, size, seed=seed)
+    kin = install(_kinetics(ms, 2 * m), pop)
+    kin.list_cache = False
+    P = oracle_params(pop)
+    X = pop.X0()
+    monkeypatch.setenv("MS_KIN_PHASED", "1")
+    monkeypatch.setenv("MS_KIN_PHASE_BATCH", batch)
+    _native.lib().ms_kinetics_reload_switches()
+    try:
+        out = kin.integrate_signals(X=X.cuda())
+        ora = O.integrate_signals(P, X.numpy())
+        assert bits_equal(out, ora), describe_mismatch(out, ora)
+        keep = torch.ones(c, dtype=torch.bool)
+        keep[::3] = False
+        kin.remove_cell_params(keep=keep.cuda())  # parameter rows behind a row map
+        out = kin.integrate_signals(X=X[keep].cuda())
+        sub = O.Params(*[t[keep.numpy()] for t in (P.N, P.Nf, P.Nb, P.A, P.Kmr, P.Ke, P.Kmf, P.Kmb, P.Vmax)])
+        ora = O.integrate_signals(sub, X[keep].numpy())
+        assert bits_equal(out, ora), describe_mismatch(out, ora)
+    finally:
+        monkeypatch.delenv("MS_KIN_PHASED", raising=False)
+        monkeypatch.delenv("MS_KIN_PHASE_BATCH", raising=False)
+        _native.lib().ms_kinetics_reload_switches()
+
+
 @pytest.mark.parametrize("shape", _SHAPES[:6], ids=[f"c{c}p{p}s{2*m}" for c, p, m, _, _ in _SHAPES[:6]])
 def test_stages_bit_exact(ms, shape):
     c, p, m, size, seed = shape

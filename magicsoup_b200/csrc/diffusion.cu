@@ -258,9 +258,19 @@ __global__ void pixel_index_kernel(const int *pos, long long c, int H, int W, in
 // after pixel.  A (32 x 33)-float tile in shared memory transposes between the two.  m <= 32.
 constexpr int PIX_WARPS = 8;
 
-__global__ void __launch_bounds__(32 * PIX_WARPS) permeate_pixel_kernel(const float *cm_in, float *cm_out, float *map,
-                                                                        const int *pixel_cell, const float *perm, int m,
-                                                                        long long n_pxls, const float *decay,
+// lanes are split into groups of G = 2^ceil(log2(n)) lanes (n values per cell); a warp handles 32 / G cells
+// per pass, so that no lane idles when a cell's row is shorter than the warp
+__device__ __forceinline__ int lane_group_size(int n) {
+  int g = 1;
+  while (g < n) g <<= 1;
+  return g < 32 ? g : 32;
+}
+
+__global__ void __launch_bounds__(32 * PIX_WARPS) permeate_pixel_kernel(const float *__restrict__ cm_in,
+                                                                        float *__restrict__ cm_out, float *map,
+                                                                        const int *__restrict__ pixel_cell,
+                                                                        const float *__restrict__ perm, int m,
+                                                                        long long n_pxls, const float *__restrict__ decay,
                                                                         const unsigned *gate) {
   __shared__ float tile[PIX_WARPS][32][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -271,26 +281,33 @@ __global__ void __launch_bounds__(32 * PIX_WARPS) permeate_pixel_kernel(const fl
   const int cell = inside ? pixel_cell[px] : -1;
   if (__ballot_sync(0xffffffffu, cell >= 0) == 0u) return;
   float (*t)[33] = tile[warp];
+#pragma unroll 4
   for (int k = 0; k < m; k++) t[lane][k] = inside ? map[(size_t)k * n_pxls + px] : 0.0f;
   __syncwarp();
-  const float q = lane < m ? perm[lane] : 0.0f, dk = (decay && lane < m) ? decay[lane] : 1.0f;
-  for (int j = 0; j < 32; j++) {
+  const int G = lane_group_size(m), li = lane & (G - 1), grp = lane / G, per_pass = 32 / G;
+  const float q = li < m ? perm[li] : 0.0f, dk = (decay && li < m) ? decay[li] : 1.0f;
+#pragma unroll 4
+  for (int j0 = 0; j0 < 32; j0 += per_pass) {
+    const int j = j0 + grp;  // the pixel (of this warp's 32) whose cell this lane group exchanges with
     const int cj = __shfl_sync(0xffffffffu, cell, j);
-    if (cj < 0 || lane >= m) continue;
-    const float raw = cm_in[(size_t)cj * m + lane];
-    const float xi = decay ? raw * dk : raw, xe = t[j][lane];
+    if (cj < 0 || li >= m) continue;
+    const float raw = cm_in[(size_t)cj * m + li];
+    const float xi = decay ? raw * dk : raw, xe = t[j][li];
     const float di = xi * q, de = xe * q;
-    cm_out[(size_t)cj * m + lane] = xi + (de - di);
-    t[j][lane] = xe + (di - de);
+    cm_out[(size_t)cj * m + li] = xi + (de - di);
+    t[j][li] = xe + (di - de);
   }
   __syncwarp();
-  if (inside && cell >= 0)
+  if (inside && cell >= 0) {
+#pragma unroll 4
     for (int k = 0; k < m; k++) map[(size_t)k * n_pxls + px] = t[lane][k];
+  }
 }
 
-__global__ void __launch_bounds__(32 * PIX_WARPS) scatter_pixel_kernel(const float *X, const int *pixel_cell, int m,
-                                                                       long long n_pxls, float *cm_out, float *map,
-                                                                       const unsigned *gate) {
+__global__ void __launch_bounds__(32 * PIX_WARPS) scatter_pixel_kernel(const float *__restrict__ X,
+                                                                       const int *__restrict__ pixel_cell, int m,
+                                                                       long long n_pxls, float *__restrict__ cm_out,
+                                                                       float *__restrict__ map, const unsigned *gate) {
   __shared__ float tile[PIX_WARPS][32][33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long px0 = ((long long)blockIdx.x * PIX_WARPS + warp) * 32;
@@ -300,19 +317,34 @@ __global__ void __launch_bounds__(32 * PIX_WARPS) scatter_pixel_kernel(const flo
   if (__ballot_sync(0xffffffffu, cell >= 0) == 0u) return;
   float (*t)[33] = tile[warp];
   const int s = 2 * m;
-  for (int j = 0; j < 32; j++) {
-    const int cj = __shfl_sync(0xffffffffu, cell, j);
-    if (cj < 0) continue;
-    const float *x = X + (size_t)cj * s;
-    for (int i = lane; i < s; i += 32) {
-      const float v = x[i];
-      if (i < m) cm_out[(size_t)cj * m + i] = v;
-      else t[j][i - m] = v;
+  if (s <= 32) {  // a lane group per cell: 32 / G cells per pass
+    const int G = lane_group_size(s), li = lane & (G - 1), grp = lane / G, per_pass = 32 / G;
+#pragma unroll 4
+    for (int j0 = 0; j0 < 32; j0 += per_pass) {
+      const int j = j0 + grp;
+      const int cj = __shfl_sync(0xffffffffu, cell, j);
+      if (cj < 0 || li >= s) continue;
+      const float v = X[(size_t)cj * s + li];
+      if (li < m) cm_out[(size_t)cj * m + li] = v;
+      else t[j][li - m] = v;
+    }
+  } else {
+    for (int j = 0; j < 32; j++) {
+      const int cj = __shfl_sync(0xffffffffu, cell, j);
+      if (cj < 0) continue;
+      const float *x = X + (size_t)cj * s;
+      for (int i = lane; i < s; i += 32) {
+        const float v = x[i];
+        if (i < m) cm_out[(size_t)cj * m + i] = v;
+        else t[j][i - m] = v;
+      }
     }
   }
   __syncwarp();
-  if (cell >= 0)
+  if (cell >= 0) {
+#pragma unroll 4
     for (int k = 0; k < m; k++) map[(size_t)k * n_pxls + px] = t[lane][k];
+  }
 }
 
 // world.py:624-625, one thread per (cell, signal)

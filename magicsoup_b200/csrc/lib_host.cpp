@@ -325,6 +325,7 @@ size_t poisson_count(Rng &rng, double lambda, size_t cap) {
   if (!(lambda > 0.0)) return 0;
   if (lambda < 16.0) {
     const double u = std::generate_canonical<double, 53>(rng);
+    if (u < 1.0 - lambda) return 0;  // 1 - lambda <= exp(-lambda): the same answer without the exponential
     double pk = std::exp(-lambda), cdf = pk;
     size_t n = 0;
     while (u >= cdf && n < cap && pk > 0.0) {
@@ -480,16 +481,50 @@ std::vector<std::tuple<std::string, std::string, size_t>> recombinations(const p
   });
 }
 
-// recombinations((genomes[a], genomes[b]) for a, b in pairs) without building the pairs of strings
+// recombinations((genomes[a], genomes[b]) for a, b in pairs) without building the pairs of strings.
+// The lengths of all genomes are read once; only the pairs that are hit touch their strings.
 std::vector<std::tuple<std::string, std::string, size_t>> recombinations_indexed(
     const py::list &genomes, const std::vector<std::pair<size_t, size_t>> &pairs, double p) {
   const size_t n_genomes = (size_t)py::len(genomes);
   for (const auto &ab : pairs)
     if (ab.first >= n_genomes || ab.second >= n_genomes) throw py::index_error("genome index out of range");
-  return recombine_pairs(pairs.size(), p, [&](size_t s) {
-    return std::pair<PyObject *, PyObject *>(PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)pairs[s].first),
-                                             PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)pairs[s].second));
-  });
+  std::vector<size_t> len(n_genomes);
+  for (size_t g = 0; g < n_genomes; g++) len[g] = str_len(PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)g));
+  const uint64_t seed = next_seed();
+  std::vector<size_t> hit;
+  {
+    const size_t chunk = 8192, n_chunks = (pairs.size() + chunk - 1) / chunk;
+    std::vector<std::vector<size_t>> parts(n_chunks);
+#pragma omp parallel for schedule(dynamic, 1) if (n_chunks > 2)
+    for (long long c = 0; c < (long long)n_chunks; c++) {
+      const size_t s1 = std::min(pairs.size(), ((size_t)c + 1) * chunk);
+      for (size_t s = (size_t)c * chunk; s < s1; s++) {
+        const size_t n_both = len[pairs[s].first] + len[pairs[s].second];
+        if (n_both == 0) continue;
+        SeqRng rng(seed, s);
+        if (poisson_count(rng, p * (double)n_both, n_both) > 0) parts[(size_t)c].push_back(s);
+      }
+    }
+    for (const auto &part : parts) hit.insert(hit.end(), part.begin(), part.end());
+  }
+  std::vector<std::pair<std::string, std::string>> src;
+  src.reserve(hit.size());
+  for (const size_t s : hit)
+    src.emplace_back(str_copy(PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)pairs[s].first)),
+                     str_copy(PyList_GET_ITEM(genomes.ptr(), (Py_ssize_t)pairs[s].second)));
+  std::vector<std::tuple<std::string, std::string, size_t>> res(hit.size());
+  {
+    py::gil_scoped_release release;
+#pragma omp parallel for schedule(dynamic, 16) if (hit.size() > 64)
+    for (long long h = 0; h < (long long)hit.size(); h++) {
+      const size_t s = hit[h], n_both = len[pairs[s].first] + len[pairs[s].second];
+      SeqRng rng(seed, s);
+      const size_t n_breaks = poisson_count(rng, p * (double)n_both, n_both);  // the same draw again
+      auto xy = recombine_one(src[h].first, src[h].second, rng, n_breaks);
+      res[h] = std::make_tuple(std::move(xy.first), std::move(xy.second), s);
+    }
+  }
+  return res;
 }
 
 // ---------------------------------------------------------------------------- world
@@ -590,32 +625,45 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
     next[r] = h;
     h = (int64_t)r;
   }
-  std::vector<std::pair<size_t, size_t>> out;
-  std::vector<int64_t> ranks;
-  for (const size_t from : from_idxs) {
-    const Pos &p0 = positions[from];
-    head.check(p0);
-    std::array<uint32_t, 9> pixels;  // the 3 x 3 block, without duplicates on tiny maps
-    size_t n_px = 0;
-    pixels[n_px++] = pixel_key(p0.first, p0.second);
-    for (const auto &q : moore(p0.first, p0.second, map_size)) pixels[n_px++] = pixel_key(q.first, q.second);
-    if (m < 3) {
-      std::sort(pixels.begin(), pixels.begin() + n_px);
-      n_px = (size_t)(std::unique(pixels.begin(), pixels.begin() + n_px) - pixels.begin());
-    }
-    ranks.clear();
-    for (size_t k = 0; k < n_px; k++)
-      for (int64_t r = head.get({(uint16_t)(pixels[k] >> 16), (uint16_t)(pixels[k] & 0xffffu)}); r != NONE; r = next[r])
-        ranks.push_back(r);
-    std::sort(ranks.begin(), ranks.end());
-    for (const int64_t r : ranks) {
-      const size_t to = to_idxs[(size_t)r];
-      if (to == from) continue;
-      // found before, from the other side: `to` came earlier in from_idxs and `from` is a `to` cell
-      if (from_rank[to] != NONE && from_rank[to] < from_rank[from] && to_rank[from] != NONE) continue;
-      out.emplace_back(std::min(from, to), std::max(from, to));
+  for (const size_t from : from_idxs) head.check(positions[from]);
+  // the from cells in chunks, one output list per chunk (joined in order: the result does not depend on the threads)
+  const size_t n_from = from_idxs.size(), chunk = 2048, n_chunks = (n_from + chunk - 1) / chunk;
+  std::vector<std::vector<std::pair<size_t, size_t>>> parts(n_chunks);
+#pragma omp parallel for schedule(dynamic, 1) if (n_chunks > 2)
+  for (long long c = 0; c < (long long)n_chunks; c++) {
+    auto &out = parts[(size_t)c];
+    std::vector<int64_t> ranks;
+    const size_t f1 = std::min(n_from, ((size_t)c + 1) * chunk);
+    for (size_t f = (size_t)c * chunk; f < f1; f++) {
+      const size_t from = from_idxs[f];
+      const Pos &p0 = positions[from];
+      std::array<uint32_t, 9> pixels;  // the 3 x 3 block, without duplicates on tiny maps
+      size_t n_px = 0;
+      pixels[n_px++] = pixel_key(p0.first, p0.second);
+      for (const auto &q : moore(p0.first, p0.second, map_size)) pixels[n_px++] = pixel_key(q.first, q.second);
+      if (m < 3) {
+        std::sort(pixels.begin(), pixels.begin() + n_px);
+        n_px = (size_t)(std::unique(pixels.begin(), pixels.begin() + n_px) - pixels.begin());
+      }
+      ranks.clear();
+      for (size_t k = 0; k < n_px; k++)
+        for (int64_t r = head.get({(uint16_t)(pixels[k] >> 16), (uint16_t)(pixels[k] & 0xffffu)}); r != NONE; r = next[r])
+          ranks.push_back(r);
+      std::sort(ranks.begin(), ranks.end());
+      for (const int64_t r : ranks) {
+        const size_t to = to_idxs[(size_t)r];
+        if (to == from) continue;
+        // found before, from the other side: `to` came earlier in from_idxs and `from` is a `to` cell
+        if (from_rank[to] != NONE && from_rank[to] < from_rank[from] && to_rank[from] != NONE) continue;
+        out.emplace_back(std::min(from, to), std::max(from, to));
+      }
     }
   }
+  size_t total = 0;
+  for (const auto &part : parts) total += part.size();
+  std::vector<std::pair<size_t, size_t>> out;
+  out.reserve(total);
+  for (const auto &part : parts) out.insert(out.end(), part.begin(), part.end());
   return out;
 }
 

@@ -126,11 +126,19 @@ def check(rc: int) -> None:
         raise NativeError(f"magicsoup_b200 native call failed ({rc}): {msg}")
 
 
+_cuda_seen = False
+
+
 def require_cuda() -> None:
+    """raises without a CUDA device (checked until one was seen: it is called in every step)"""
+    global _cuda_seen
+    if _cuda_seen:
+        return
     if not torch.cuda.is_available() or lib().ms_device_count() < 1:
         raise RuntimeError(
             "magicsoup_b200 runs its hot path as CUDA kernels on a B200 only: "
             "no CUDA device is visible and there is no CPU fallback")
+    _cuda_seen = True
 
 
 def ptr(t: torch.Tensor | None):

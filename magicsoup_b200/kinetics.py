@@ -199,13 +199,22 @@ class Kinetics:
         goes through _params' normalised copies without a cache.
         """
         b = self._buf
+        # the same store as at the last launch (same tensors at the same versions, same row map, same
+        # cache): the same arguments (this runs in every step; building them costs ~30 us of Python)
+        memo = self._scratch.get("launch_args")
+        rec_now = int(nat.lib().ms_kinetics_cache_record_words(int(b["N"].shape[1]), s)) \
+            if self.list_cache and b["N"].dim() == 3 else 0  # (depends on the library's diagnostic switches)
+        key = (dev, c, s, rec_now, id(self._rows), id(self._cache), self._len["N"],
+               tuple(t.data_ptr() for t in b.values()))
+        if memo is not None and memo[0] == key and not self._written_from_outside():
+            return memo[1]
         if not (self._managed() and b["N"].device == dev and self._len["N"] == c and b["N"].shape[2] == s
                 and all(t.is_contiguous() for t in b.values())):
             st, keep, p = self._params(dev, c, s)
             return st, None, keep, p
         p = int(b["N"].shape[1])
         st = nat.KineticsParams(**{k: nat.ptr(b[k]) for k in _ALL_PARAMS}, c=c, p=p, s=s)
-        rec_words = int(nat.lib().ms_kinetics_cache_record_words(p, s)) if self.list_cache else 0
+        rec_words = rec_now
         if rec_words == 0:
             self._cache = None
         else:
@@ -217,9 +226,14 @@ class Kinetics:
                 self._stale(None)  # someone wrote into an attribute view: every record may be stale
                 self._stamp()
         if self._cache is None and self._rows is None:
-            return st, None, b, p
-        cs = nat.KineticsCache(records=nat.ptr(self._cache), rec_words=rec_words, row_map=nat.ptr(self._rows))
-        return st, cs, (b, self._cache, self._rows), p
+            value = (st, None, b, p)
+        else:
+            cs = nat.KineticsCache(records=nat.ptr(self._cache), rec_words=rec_words, row_map=nat.ptr(self._rows))
+            value = (st, cs, (dict(b), self._cache, self._rows), p)  # holds the tensors: ids in the key stay theirs
+        key = (dev, c, s, rec_now, id(self._rows), id(self._cache), self._len["N"],
+               tuple(t.data_ptr() for t in b.values()))  # (the cache may just have been created)
+        self._scratch["launch_args"] = (key, value)
+        return value
 
     def _kin_scratch(self, dev: torch.device, c: int, p: int, s: int):
         n = int(nat.lib().ms_kinetics_scratch_bytes(c, p, s))

@@ -257,9 +257,21 @@ def lifecycle_rounds(world, device, step_ms, rounds=4, frac=0.01):
         world.diffuse_molecules()
         torch.cuda.synchronize(device)
         t3 = time.perf_counter()
-        out.append({"kill_ms": (t1 - t0) * 1e3, "divide_ms": (t2 - t1) * 1e3, "step_after_ms": (t3 - t2) * 1e3})
+        # genomes of 1 % of the cells changed (mutations): their lists are rebuilt from the dense tiles in the next step
+        kin = world.kinetics
+        stale = torch.randperm(world.n_cells, generator=g)[:k].to(device)
+        kin._stale(kin._phys(stale))
+        torch.cuda.synchronize(device)
+        t4 = time.perf_counter()
+        world.enzymatic_activity()
+        world.diffuse_molecules()
+        torch.cuda.synchronize(device)
+        t5 = time.perf_counter()
+        out.append({"kill_ms": (t1 - t0) * 1e3, "divide_ms": (t2 - t1) * 1e3, "step_after_ms": (t3 - t2) * 1e3,
+                    "step_with_1pct_stale_lists_ms": (t5 - t4) * 1e3})
     k = max(1, int(world.n_cells * frac))
-    return {"what": f"kill {k} random cells, divide {k} random cells onto the freed pixels, one step; {rounds} rounds "
+    return {"what": f"kill {k} random cells, divide {k} random cells onto the freed pixels, one step, then the lists of {k} cells "
+                    f"marked stale (as after mutations) and one more step; {rounds} rounds "
                     "(the first one includes the one-off growth of the parameter buffers by half)",
             "rounds": out, "steady_step_ms": step_ms,
             "parameter_bytes_per_cell": kinetics_bytes_per_cell(int(world.kinetics._buf["N"].shape[1]),

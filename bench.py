@@ -536,6 +536,7 @@ def main():
         sampler.start()
     res = timed_steps(world, args.steps, barrier, device, world_size)
     clocks = sampler.stop() if rank == 0 else None
+    peer_active = world.__dict__.get("_peer_ctx") is not None  # flags, plane sums and halos over peer memory (csrc/peer.cu)
     value = c * world_size * args.steps / (res["ms_total"] / 1e3)
     rec_words = int(world.kinetics._cache.shape[1]) if world.kinetics._cache is not None else 0
 
@@ -701,7 +702,8 @@ def main():
         "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
         "scaling": "strong" if split_over_ranks(args, world_size) else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, world_size), "roofline": roofline,
+        "config": dict(workload_config(args, world_size),
+                       peer_exchange=bool(world_size > 1 and peer_active)), "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": "cell-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": args.e2e_steps, "host_cpus_per_rank": n_cpus,
                 "how": "every step uploads its inputs (cell molecules, molecule map, positions) from pinned host "

@@ -303,6 +303,30 @@ int ms_early_exit_verdict(const uint32_t *flags, const int32_t *eq_iters_host, i
 void ms_step_gate(const uint32_t *gate);
 
 /*
+ * The small exchanges of a multi-GPU step over NVLink peer memory (csrc/peer.cu; no counterpart in the
+ * single-device reference).  `bufs[r]` (r < world <= 16) is the address, in THIS process, of rank r's
+ * exchange buffer of ms_peer_buffer_bytes(world, m, W) bytes, zero-initialised before the first call
+ * (torch.distributed._symmetric_memory or CUDA IPC provide such mappings).  Every rank makes the same
+ * calls in the same order, with `seq` = 1, 2, 3, ... counted separately for the all-reduces and for
+ * the halos.  A rank's kernel stores its contribution into every peer's buffer with plain
+ * peer-to-peer stores, publishes `seq`, waits for the peers' in its own buffer and reduces: one short
+ * launch in stream order instead of a collective call.  If a peer does not show up within ~2 s the
+ * kernel sets *status (device word) and returns.
+ *   ms_peer_allreduce: `data` (n elements, in place) := sum over ranks (op 0, int64) or max (op 1,
+ *     uint32); n * element size <= 16 KB.
+ *   ms_peer_halo: the first row of every plane of `map_slab` (m,H,W) goes to the bottom halo of the rank
+ *     above, the last row to the top halo of the rank below (circular); on return of the kernel this
+ *     rank's own halos of call `seq` are at ms_peer_halo_offset(world, m, W, seq & 1, 0 / 1) bytes
+ *     into its buffer: (m, W) floats each, the halo_top / halo_bottom of ms_diffuse_stencil.
+ */
+size_t ms_peer_buffer_bytes(int32_t world, int64_t m, int64_t W);
+size_t ms_peer_halo_offset(int32_t world, int64_t m, int64_t W, int32_t parity, int32_t bottom);
+int ms_peer_allreduce(const uint64_t *bufs, int32_t world, int32_t rank, uint64_t seq, void *data, int32_t n,
+                      int32_t op, uint32_t *status, void *stream);
+int ms_peer_halo(const uint64_t *bufs, int32_t world, int32_t rank, uint64_t seq, const float *map_slab, int64_t m,
+                 int64_t H, int64_t W, uint32_t *status, void *stream);
+
+/*
  * World.degrade_molecules()                                    world.py:667-678
  * molecule_map[k] *= decay[k], cell_molecules[:, k] *= decay[k], in place, one launch
  * (decay[k] = exp(-ln 2 / half_life_k), world.py:184).

@@ -87,6 +87,10 @@ _SIGNATURES = {
     "ms_degrade_permeate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
     "ms_early_exit_verdict": (C.c_int, [_vp, C.POINTER(C.c_int32), C.c_int32, _vp, _vp]),
     "ms_step_gate": (None, [_vp]),
+    "ms_peer_buffer_bytes": (C.c_size_t, [C.c_int32, _i64, _i64]),
+    "ms_peer_halo_offset": (C.c_size_t, [C.c_int32, _i64, _i64, C.c_int32, C.c_int32]),
+    "ms_peer_allreduce": (C.c_int, [C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_uint64, _vp, C.c_int32, C.c_int32, _vp, _vp]),
+    "ms_peer_halo": (C.c_int, [C.POINTER(C.c_uint64), C.c_int32, C.c_int32, C.c_uint64, _vp, _i64, _i64, _i64, _vp, _vp]),
 }
 
 _lib: C.CDLL | None = None

@@ -11,7 +11,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "libmagicsoup_b200.so"
-SOURCES = ("ms_api.cu", "kinetics.cu", "diffusion.cu", "params.cu")
+SOURCES = ("ms_api.cu", "kinetics.cu", "diffusion.cu", "params.cu", "peer.cu")
 # -fmad=false: the spec order has no fused multiply-add (bit parity with the CPU oracle)
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-fmad=false",

@@ -15,6 +15,11 @@ sharding north_star asks for:
     bit-identical to the single-device result on the whole map;
   * `enzymatic_activity` all-reduces (max) the 24 early-exit flags so that every rank takes the
     same decision about the reference's GLOBAL early exit (kinetics.py:846-847).
+  * With NCCL (i.e. GPUs on one NVLink domain) those three small exchanges do not go through
+    collective calls: every rank's buffer is mapped into every process
+    (torch.distributed._symmetric_memory) and short kernels store a rank's contribution into the
+    peers' buffers, publish a sequence number and reduce what has arrived (csrc/peer.cu,
+    `peer_exchange`); NCCL remains the fallback, and what moves the cells (`migrate_cells`).
 
 Cell indices are local to the rank; the global index of local cell i is
 `global_cell_offset() + i` (ranks in order).  `kill_cells`, `add_cells_from_params` and
@@ -24,11 +29,14 @@ their new pixel, e.g. after a division or move across a slab boundary.
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
 from typing import Any, Sequence
 
 import torch
 import torch.distributed as dist
 
+from magicsoup_b200 import _native as nat
 from magicsoup_b200.kinetics import _ALL_PARAMS
 from magicsoup_b200.world import World, _KERNEL_HOOKS
 
@@ -88,7 +96,14 @@ class SlabWorld(World):
     def __getstate__(self):
         state = super().__getstate__()
         state["group"] = None
+        state.pop("_peer_ctx", None)  # mappings of other processes' memory do not travel
         return state
+
+    def _settle(self):
+        pending = self._pending is not None
+        super()._settle()
+        if pending and self.peer_status():
+            raise RuntimeError("an exchange over peer memory gave up waiting for a rank (see csrc/peer.cu)")
 
     def _set_slabs(self, heights: list[int]):
         H = self.global_map_size[0]
@@ -146,10 +161,70 @@ class SlabWorld(World):
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         return t.tolist()
 
+    # ------------------------------------------------------------------ exchanges over peer memory
+    peer_exchange = True  # False (or MS_NO_PEER=1): NCCL collectives for the flags, the plane sums and the halos
+
+    def _peer(self):
+        """
+        The rank's exchange buffer, mapped by all ranks (csrc/peer.cu), or None: one rank, not NCCL,
+        switched off, more than 16 ranks, or symmetric memory not available here (then NCCL is used).
+        Created collectively at the first step.
+        """
+        ctx = self.__dict__.get("_peer_ctx", False)
+        if ctx is not False:
+            if ctx is not None and ctx["shape"] != (self.n_molecules, self.global_map_size[1]):
+                raise RuntimeError("the map's planes or columns changed under a SlabWorld with peer exchange")
+            return ctx
+        ctx = None
+        if (self.peer_exchange and not os.environ.get("MS_NO_PEER") and 1 < self.world_size <= 16
+                and dist.get_backend(self.group) == "nccl"):
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+
+                dev = self._cuda()
+                m, W = self.n_molecules, self.global_map_size[1]
+                nbytes = int(nat.lib().ms_peer_buffer_bytes(self.world_size, m, W))
+                buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+                buf.zero_()
+                handle = symm_mem.rendezvous(buf, self.group if self.group is not None else dist.group.WORLD)
+                torch.cuda.synchronize(dev)
+                dist.barrier(group=self.group)  # every buffer is zero before anybody stores into it
+                ptrs = (C.c_uint64 * self.world_size)(*[int(p) for p in handle.buffer_ptrs])
+                ctx = {"buf": buf, "handle": handle, "ptrs": ptrs, "seq_reduce": 0, "seq_halo": 0, "shape": (m, W),
+                       "status": torch.zeros(1, dtype=torch.int32, device=dev)}
+            except Exception as err:  # no symmetric memory on this system: the collectives do the same job
+                import warnings
+
+                warnings.warn(f"SlabWorld: peer exchange not available ({err!r}); using NCCL collectives")
+                ctx = None
+        # all ranks must agree (a rank that fell back would wait in a collective for ranks that did not)
+        ok = torch.tensor([1 if ctx is not None else 0], dtype=torch.int32, device=self._comm_device())
+        if self.world_size > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 0:
+            ctx = None
+        self.__dict__["_peer_ctx"] = ctx
+        return ctx
+
+    def _peer_allreduce(self, ctx, data: torch.Tensor, op: int):
+        ctx["seq_reduce"] += 1
+        dev = data.device
+        nat.check(nat.lib().ms_peer_allreduce(ctx["ptrs"], self.world_size, self.rank, ctx["seq_reduce"], nat.ptr(data),
+                                              int(data.numel()), op, nat.ptr(ctx["status"]), nat.stream_ptr(dev)))
+
+    def peer_status(self) -> int:
+        """non-zero if an exchange over peer memory gave up waiting for a rank (synchronises)"""
+        ctx = self.__dict__.get("_peer_ctx")
+        return int(ctx["status"].item()) if ctx else 0
+
     def _reduce_flags_device(self, flags: torch.Tensor) -> torch.Tensor:
         """MAX over ranks in place, enqueued like any other step of the launch sequence (no host round trip)"""
         if self.world_size > 1:
-            dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=self.group)
+            ctx = self._peer()
+            if ctx is not None:
+                self._peer_allreduce(ctx, flags, 1)
+            else:
+                dist.all_reduce(flags, op=dist.ReduceOp.MAX, group=self.group)
         return flags
 
     # On several ranks the deferred early-exit check (World._settle) is opt-in: when the verdict is
@@ -170,7 +245,10 @@ class SlabWorld(World):
 
     def _reduce_sums(self, sums: torch.Tensor) -> torch.Tensor:
         if self.world_size > 1:
-            if sums.device != self._comm_device():
+            ctx = self._peer() if sums.is_cuda else None
+            if ctx is not None:
+                self._peer_allreduce(ctx, sums, 0)
+            elif sums.device != self._comm_device():
                 moved = sums.to(self._comm_device())
                 dist.all_reduce(moved, op=dist.ReduceOp.SUM, group=self.group)
                 sums.copy_(moved)
@@ -189,6 +267,17 @@ class SlabWorld(World):
         """
         if self.world_size == 1:
             return None, None
+        ctx = self._peer() if mm.is_cuda else None
+        if ctx is not None:
+            ctx["seq_halo"] += 1
+            m, H, W = mm.shape
+            nat.check(nat.lib().ms_peer_halo(ctx["ptrs"], self.world_size, self.rank, ctx["seq_halo"], nat.ptr(mm), m, H, W,
+                                             nat.ptr(ctx["status"]), nat.stream_ptr(mm.device)))
+            halos = []
+            for bottom in (0, 1):
+                off = int(nat.lib().ms_peer_halo_offset(self.world_size, m, W, ctx["seq_halo"] & 1, bottom))
+                halos.append(ctx["buf"][off:off + m * W * 4].view(torch.float32).view(m, W))
+            return halos[0], halos[1]
         comm = self._comm_device()
         first = mm[:, 0, :].contiguous().to(comm)
         last = mm[:, -1, :].contiguous().to(comm)

@@ -23,10 +23,11 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("blocking", [False, True], ids=["deferred", "blocking"])
+@pytest.mark.parametrize("blocking,peer", [(False, True), (True, True), (False, False)],
+                         ids=["deferred-peer", "blocking-peer", "deferred-nccl"])
 @pytest.mark.parametrize("shape", [(300, 16, 24), (20000, 128, 128), (5, 4, 8)],
                          ids=["generic-stencil", "tiled-stencil", "five-cells"])
-def test_nccl_slab_world_matches_oracle(shape, blocking):
+def test_nccl_slab_world_matches_oracle(shape, blocking, peer):
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs at least 2 GPUs")
@@ -38,6 +39,9 @@ def test_nccl_slab_world_matches_oracle(shape, blocking):
            "--rows-per-rank", str(rows), "--cols", str(cols)]
     if blocking:  # SlabWorld's multi-rank default; otherwise the early-exit check trails the step (opt-in)
         cmd.append("--blocking")
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=dict(os.environ))
+    env = dict(os.environ)
+    if not peer:  # flags, plane sums and halos through NCCL collectives instead of the peer-memory kernels (csrc/peer.cu)
+        env["MS_NO_PEER"] = "1"
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=env)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "dist_worker ok" in res.stdout

@@ -45,3 +45,18 @@ def test_nccl_slab_world_matches_oracle(shape, blocking, peer):
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=env)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "dist_worker ok" in res.stdout
+
+
+@pytest.mark.parametrize("blocking", [False, True], ids=["deferred", "blocking"])
+def test_slab_world_equals_one_gpu_under_lifecycle_churn(blocking):
+    """24 steps with kills, cells crossing slab boundaries and rebalanced slabs: the N-rank SlabWorld
+    (peer-memory exchanges, deferred or blocking early-exit check) against one World holding everything"""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={min(n, 4)}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           str(ROOT / "tests" / "dist_stress_worker.py")] + (["--blocking"] if blocking else [])
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=dict(os.environ))
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "dist_stress ok" in res.stdout

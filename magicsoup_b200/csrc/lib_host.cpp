@@ -536,14 +536,45 @@ uint16_t dist_1d(uint16_t a, uint16_t b, uint16_t m) {
   return std::min(d0, d1);
 }
 
+// The map the searches run on.  The reference's maps are square tori (`map_size`); a row slab of a
+// map that is split over several GPUs (magicsoup_b200/distributed.py) is `rows x cols`, wraps
+// around in its columns only, and what lies beyond its first and last row belongs to other ranks.
+struct MapShape {
+  uint16_t rows, cols;
+  bool wrap_rows;
+};
+
+struct Moore {
+  std::array<Pos, 8> p;
+  int n;
+  const Pos *begin() const { return p.data(); }
+  const Pos *end() const { return p.data() + n; }
+};
+
 // rust/util.rs:27-43: W-N, W, W-S, N, S, E-N, E, E-S with "east" = x + 1, "south" = y + 1
-std::array<Pos, 8> moore(uint16_t x, uint16_t y, uint16_t m) {
-  const uint16_t e = (uint16_t)(x + 1 == m ? 0 : x + 1), w = (uint16_t)(x == 0 ? m - 1 : x - 1);
-  const uint16_t s = (uint16_t)(y + 1 == m ? 0 : y + 1), n = (uint16_t)(y == 0 ? m - 1 : y - 1);
-  return {{{w, n}, {w, y}, {w, s}, {x, n}, {x, s}, {e, n}, {e, y}, {e, s}}};
+Moore moore(uint16_t x, uint16_t y, const MapShape &m) {
+  const bool has_e = m.wrap_rows || x + 1 < m.rows, has_w = m.wrap_rows || x > 0;
+  const uint16_t e = (uint16_t)(x + 1 >= m.rows ? 0 : x + 1), w = (uint16_t)(x == 0 ? m.rows - 1 : x - 1);
+  const uint16_t s = (uint16_t)(y + 1 >= m.cols ? 0 : y + 1), n = (uint16_t)(y == 0 ? m.cols - 1 : y - 1);
+  Moore out{};
+  out.n = 0;
+  if (has_w) {
+    out.p[out.n++] = {w, n};
+    out.p[out.n++] = {w, y};
+    out.p[out.n++] = {w, s};
+  }
+  out.p[out.n++] = {x, n};
+  out.p[out.n++] = {x, s};
+  if (has_e) {
+    out.p[out.n++] = {e, n};
+    out.p[out.n++] = {e, y};
+    out.p[out.n++] = {e, s};
+  }
+  return out;
 }
 
-std::vector<Pos> free_moores_nghbhd(uint16_t x, uint16_t y, const std::vector<Pos> &positions, uint16_t map_size) {
+std::vector<Pos> free_moores_nghbhd(uint16_t x, uint16_t y, const std::vector<Pos> &positions, uint16_t map_size_) {
+  const MapShape map_size{map_size_, map_size_, true};
   std::unordered_set<uint32_t> occ;
   occ.reserve(positions.size() * 2);
   for (const auto &p : positions) occ.insert(pixel_key(p.first, p.second));
@@ -553,23 +584,23 @@ std::vector<Pos> free_moores_nghbhd(uint16_t x, uint16_t y, const std::vector<Po
   return out;
 }
 
-// One value per pixel of a square map: a dense array where that is small next to the number of
+// One value per pixel of a map: a dense array where that is small next to the number of
 // entries it serves (4 Mi pixels, or 16 per entry), a hash map on huge, sparsely populated maps.
 template <class T>
 struct PixelTable {
-  size_t m;
+  size_t rows, m;  // m: columns (the row stride)
   T fill;
   bool dense;
   std::vector<T> flat;
   std::unordered_map<uint64_t, T> sparse;
-  PixelTable(uint16_t map_size, size_t n_entries, T fill_value) : m(map_size), fill(fill_value) {
-    const size_t n_pixels = m * m;
+  PixelTable(const MapShape &shape, size_t n_entries, T fill_value) : rows(shape.rows), m(shape.cols), fill(fill_value) {
+    const size_t n_pixels = rows * m;
     dense = n_pixels <= ((size_t)1 << 22) || n_pixels <= 16 * n_entries;
     if (dense) flat.assign(n_pixels, fill);
     else sparse.reserve(2 * n_entries);
   }
   void check(const Pos &p) const {
-    if (p.first >= m || p.second >= m) throw py::index_error("position outside the map");
+    if (p.first >= rows || p.second >= m) throw py::index_error("position outside the map");
   }
   T &at(const Pos &p) {  // created with the fill value if absent
     const size_t k = (size_t)p.first * m + p.second;
@@ -607,7 +638,7 @@ std::vector<size_t> unique_in_order(const std::vector<size_t> &idxs, size_t n) {
 // is recognised by the ranks of the two cells in from_idxs, no set of seen pairs is kept.
 std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &from_raw,
                                                      const std::vector<size_t> &to_raw,
-                                                     const std::vector<Pos> &positions, uint16_t map_size) {
+                                                     const std::vector<Pos> &positions, const MapShape &map_size) {
   const size_t n = positions.size();
   const std::vector<size_t> from_idxs = unique_in_order(from_raw, n), to_idxs = unique_in_order(to_raw, n);
   constexpr int64_t NONE = -1;
@@ -615,7 +646,7 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
   for (size_t r = 0; r < from_idxs.size(); r++) from_rank[from_idxs[r]] = (int64_t)r;
   for (size_t r = 0; r < to_idxs.size(); r++) to_rank[to_idxs[r]] = (int64_t)r;
   // pixel -> chain of ranks in to_idxs (ascending rank along the chain)
-  const size_t m = map_size;
+  const size_t m = map_size.cols;
   PixelTable<int64_t> head(map_size, to_idxs.size(), NONE);
   std::vector<int64_t> next(to_idxs.size(), NONE);
   for (size_t r = to_idxs.size(); r-- > 0;) {
@@ -641,7 +672,7 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
       size_t n_px = 0;
       pixels[n_px++] = pixel_key(p0.first, p0.second);
       for (const auto &q : moore(p0.first, p0.second, map_size)) pixels[n_px++] = pixel_key(q.first, q.second);
-      if (m < 3) {
+      if (m < 3 || map_size.rows < 3) {
         std::sort(pixels.begin(), pixels.begin() + n_px);
         n_px = (size_t)(std::unique(pixels.begin(), pixels.begin() + n_px) - pixels.begin());
       }
@@ -670,7 +701,7 @@ std::vector<std::pair<size_t, size_t>> get_neighbors(const std::vector<size_t> &
 // cells per pixel of a square map
 struct Occupancy {
   PixelTable<int32_t> count;
-  Occupancy(const std::vector<Pos> &positions, uint16_t map_size) : count(map_size, positions.size(), 0) {
+  Occupancy(const std::vector<Pos> &positions, const MapShape &map_size) : count(map_size, positions.size(), 0) {
     for (const auto &p : positions) {
       count.check(p);
       count.at(p)++;
@@ -683,7 +714,7 @@ struct Occupancy {
 // rust/world.rs:59-99: in the order of cell_idxs, every cell picks one free Moore pixel at random
 // (free of all current cells and of the children placed before it); children get indices n_cells..
 std::tuple<std::vector<size_t>, std::vector<size_t>, std::vector<Pos>> divide_cells_if_possible(
-    const std::vector<size_t> &cell_idxs, const std::vector<Pos> &positions, size_t n_cells, uint16_t map_size) {
+    const std::vector<size_t> &cell_idxs, const std::vector<Pos> &positions, size_t n_cells, const MapShape &map_size) {
   Occupancy occ(positions, map_size);
   SeqRng rng(next_seed(), 0);
   std::vector<size_t> parents, children;
@@ -709,7 +740,7 @@ std::tuple<std::vector<size_t>, std::vector<size_t>, std::vector<Pos>> divide_ce
 // random: free of the cells that do not move and of the moving cells' current pixels
 std::tuple<std::vector<Pos>, std::vector<size_t>> move_cells(const std::vector<size_t> &cell_idxs,
                                                              const std::vector<Pos> &positions,
-                                                             uint16_t map_size) {
+                                                             const MapShape &map_size) {
   Occupancy occ(positions, map_size);
   SeqRng rng(next_seed(), 0);
   std::vector<Pos> new_pos;
@@ -728,6 +759,21 @@ std::tuple<std::vector<Pos>, std::vector<size_t>> move_cells(const std::vector<s
     moved.push_back(idx);
   }
   return {new_pos, moved};
+}
+
+// `map_size` as the reference passes it (an int: a square torus) or (rows, cols[, wrap_rows]) for a row slab
+MapShape shape_from(const py::object &obj) {
+  const auto dim = [](long long v) {
+    if (v < 1 || v > 0xffff) throw py::value_error("map sizes must be in 1..65535");
+    return (uint16_t)v;
+  };
+  if (py::isinstance<py::int_>(obj)) {
+    const uint16_t m = dim(obj.cast<long long>());
+    return MapShape{m, m, true};
+  }
+  const auto seq = obj.cast<py::sequence>();
+  if (py::len(seq) != 2 && py::len(seq) != 3) throw py::value_error("map_size: int or (rows, cols[, wrap_rows])");
+  return MapShape{dim(seq[0].cast<long long>()), dim(seq[1].cast<long long>()), py::len(seq) == 3 ? seq[2].cast<bool>() : true};
 }
 
 // positions as a list of (x, y) pairs (the reference's interface) or as an (n, 2) integer array
@@ -948,21 +994,22 @@ PYBIND11_MODULE(_lib, m) {
         py::arg("signs"), py::arg("reacts"), py::arg("trnspts"), py::arg("effectors"), py::arg("molecules"));
   m.def("get_neighbors",
         [](const std::vector<size_t> &from_idxs, const std::vector<size_t> &to_idxs, const py::object &positions,
-           uint16_t map_size) {
+           const py::object &map_size) {
           const auto pos = positions_from(positions);
+          const MapShape shape = shape_from(map_size);
           py::gil_scoped_release release;
-          return get_neighbors(from_idxs, to_idxs, pos, map_size);
+          return get_neighbors(from_idxs, to_idxs, pos, shape);
         },
         py::arg("from_idxs"), py::arg("to_idxs"), py::arg("positions"), py::arg("map_size"));
   m.def("neighbor_recombinations",
-        [](const py::list &genomes, const std::vector<size_t> &cell_idxs, const py::object &positions, uint16_t map_size,
-           double p) {
+        [](const py::list &genomes, const std::vector<size_t> &cell_idxs, const py::object &positions,
+           const py::object &map_size, double p) {
           // World.recombinate_cells in one call (world.py:716-745): neighbour pairs among cell_idxs,
           // recombinations between their genomes; only the pairs that were hit come back, as
           // (genome a, genome b, a, b).  No list of pairs crosses the language boundary.
           const auto pos = positions_from(positions);
           if ((size_t)py::len(genomes) != pos.size()) throw py::value_error("one genome per position expected");
-          const auto pairs = get_neighbors(cell_idxs, cell_idxs, pos, map_size);
+          const auto pairs = get_neighbors(cell_idxs, cell_idxs, pos, shape_from(map_size));
           const auto hits = recombinations_indexed(genomes, pairs, p);
           std::vector<std::tuple<std::string, std::string, size_t, size_t>> out;
           out.reserve(hits.size());
@@ -972,17 +1019,19 @@ PYBIND11_MODULE(_lib, m) {
         py::arg("genomes"), py::arg("cell_idxs"), py::arg("positions"), py::arg("map_size"), py::arg("p"),
         "no counterpart in the reference");
   m.def("divide_cells_if_possible",
-        [](const std::vector<size_t> &cell_idxs, const py::object &positions, size_t n_cells, uint16_t map_size) {
+        [](const std::vector<size_t> &cell_idxs, const py::object &positions, size_t n_cells, const py::object &map_size) {
           const auto pos = positions_from(positions);
+          const MapShape shape = shape_from(map_size);
           py::gil_scoped_release release;
-          return divide_cells_if_possible(cell_idxs, pos, n_cells, map_size);
+          return divide_cells_if_possible(cell_idxs, pos, n_cells, shape);
         },
         py::arg("cell_idxs"), py::arg("positions"), py::arg("n_cells"), py::arg("map_size"));
   m.def("move_cells",
-        [](const std::vector<size_t> &cell_idxs, const py::object &positions, uint16_t map_size) {
+        [](const std::vector<size_t> &cell_idxs, const py::object &positions, const py::object &map_size) {
           const auto pos = positions_from(positions);
+          const MapShape shape = shape_from(map_size);
           py::gil_scoped_release release;
-          return move_cells(cell_idxs, pos, map_size);
+          return move_cells(cell_idxs, pos, shape);
         },
         py::arg("cell_idxs"), py::arg("positions"), py::arg("map_size"));
 }

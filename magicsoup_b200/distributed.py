@@ -105,6 +105,11 @@ class SlabWorld(World):
         if pending and self.peer_status():
             raise RuntimeError("an exchange over peer memory gave up waiting for a rank (see csrc/peer.cu)")
 
+    def _map_shape(self):
+        # the slab's rows end where other ranks begin: the Moore-neighbourhood searches of `_lib`
+        # (divide_cells, move_cells, get_neighbors, recombinate_cells) stay inside the slab; columns wrap
+        return (int(self.slab_rows), int(self.global_map_size[1]), self.world_size == 1)
+
     def _set_slabs(self, heights: list[int]):
         H = self.global_map_size[0]
         if len(heights) != self.world_size or any(int(h) < 1 for h in heights) or sum(heights) != H:

@@ -582,10 +582,12 @@ class World:
         """cell positions as an (n, 2) host array for the map searches of `_lib`"""
         return self.cell_positions.cpu().numpy()
 
-    def _square_size(self) -> int:
-        if not isinstance(self.map_size, int):
-            raise ValueError("neighbour, division and movement searches need a square map (map_size: int)")
-        return self.map_size
+    def _map_shape(self):
+        """the map as `_lib`'s searches take it: an int (square torus, the reference's maps) or (rows, cols, wrap_rows)"""
+        if isinstance(self.map_size, int):
+            return self.map_size
+        rows, cols = self.map_size
+        return (int(rows), int(cols), True)
 
     def get_neighbors(self, cell_idxs: list[int], nghbr_idxs: list[int] | None = None) -> list[tuple[int, int]]:
         """world.py:229-285: unique pairs (lower index first) of cells in each other's Moore neighbourhood"""
@@ -595,7 +597,7 @@ class World:
         to_idxs = list(set(cell_idxs)) if nghbr_idxs is None else list(set(nghbr_idxs))
         if len(to_idxs) == 0:
             return []
-        return _hostlib().get_neighbors(from_idxs, to_idxs, self._positions_array(), self._square_size())
+        return _hostlib().get_neighbors(from_idxs, to_idxs, self._positions_array(), self._map_shape())
 
     def spawn_cells(self, genomes: list[str]) -> list[int]:
         """world.py:287-341: new cells on random free pixels, each takes half of its pixel's molecules"""
@@ -634,7 +636,7 @@ class World:
         if len(cell_idxs) == 0:
             return []
         parents, children, child_pos = _hostlib().divide_cells_if_possible(
-            list(set(cell_idxs)), self._positions_array(), self.n_cells, self._square_size())
+            list(set(cell_idxs)), self._positions_array(), self.n_cells, self._map_shape())
         if len(children) == 0:
             return []
         pos = torch.tensor(child_pos, dtype=torch.int32, device=self.cell_positions.device)
@@ -658,7 +660,7 @@ class World:
             cell_idxs = list(range(self.n_cells))
         if len(cell_idxs) == 0:
             return
-        new_pos, moved = _hostlib().move_cells(sorted(set(cell_idxs)), self._positions_array(), self._square_size())
+        new_pos, moved = _hostlib().move_cells(sorted(set(cell_idxs)), self._positions_array(), self._map_shape())
         if len(moved) == 0:
             return
         old = self.cell_positions[moved].long()
@@ -701,7 +703,7 @@ class World:
             return
         if type(self).get_neighbors is World.get_neighbors and isinstance(self.cell_genomes, list):
             hits = _hostlib().neighbor_recombinations(self.cell_genomes, list(set(cell_idxs)), self._positions_array(),
-                                                     self._square_size(), p)
+                                                     self._map_shape(), p)
             changed = [pair for g0, g1, a, b in hits for pair in ((g0, a), (g1, b))]
         else:
             nghbrs = self.get_neighbors(cell_idxs=cell_idxs)

@@ -60,3 +60,16 @@ def test_slab_world_equals_one_gpu_under_lifecycle_churn(blocking):
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=dict(os.environ))
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "dist_stress ok" in res.stdout
+
+
+def test_genome_driven_loop_on_slabs():
+    """spawn / kill / divide / recombinate / mutate / move on every rank's own cells (tests/dist_genome_worker.py):
+    each step of all ranks together equals the CPU oracle on the gathered world, bookkeeping stays consistent"""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={min(n, 4)}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(ROOT / "tests" / "dist_genome_worker.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=str(ROOT), env=dict(os.environ))
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "dist_genome ok" in res.stdout

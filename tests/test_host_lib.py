@@ -335,3 +335,48 @@ def test_lazy_mutation_entry_points():
     lib().seed(78)
     got = lib().neighbor_recombinations(genomes, idxs, pos, size, 0.02)
     assert got == want and len(got) > 3
+
+
+def test_map_searches_on_a_row_slab():
+    """(rows, cols, wrap_rows=False): a row slab of a map split over several GPUs -- columns wrap,
+    the first and the last row end at another rank (magicsoup_b200/distributed.py)"""
+    rng = random.Random(9)
+    rows, cols = 7, 11
+    pixels = rng.sample([(x, y) for x in range(rows) for y in range(cols)], 40)
+    idxs = list(range(len(pixels)))
+
+    def near(a, b, wrap_rows):
+        dx = abs(a[0] - b[0])
+        if wrap_rows:
+            dx = min(dx, rows - dx)
+        dy = abs(a[1] - b[1])
+        return dx <= 1 and min(dy, cols - dy) <= 1
+
+    for wrap in (False, True):
+        got = lib().get_neighbors(idxs, idxs, pixels, (rows, cols, wrap))
+        want = {(i, j) for i in idxs for j in idxs if i < j and near(pixels[i], pixels[j], wrap)}
+        assert set(got) == want and len(got) == len(want)
+    assert set(lib().get_neighbors(idxs, idxs, pixels, (rows, cols))) == \
+        set(lib().get_neighbors(idxs, idxs, pixels, (rows, cols, True)))
+    # children and moves stay inside the slab and on free pixels
+    lib().seed(5)
+    parents, children, child_pos = lib().divide_cells_if_possible(idxs, pixels, len(pixels), (rows, cols, False))
+    assert children == list(range(len(pixels), len(pixels) + len(parents))) and len(parents) > 20
+    taken = set(pixels)
+    for par, pos in zip(parents, child_pos):
+        pos = tuple(pos)
+        assert 0 <= pos[0] < rows and 0 <= pos[1] < cols and pos not in taken and near(pixels[par], pos, False)
+        taken.add(pos)
+    new_pos, moved = lib().move_cells(idxs, pixels, (rows, cols, False))
+    now = list(pixels)
+    for i, pos in zip(moved, new_pos):
+        pos = tuple(pos)
+        assert 0 <= pos[0] < rows and near(pixels[i], pos, False)
+        now[i] = pos
+    assert len(set(now)) == len(now)
+    # a cell in a one-row slab can only go sideways
+    assert lib().divide_cells_if_possible([0], [(0, 0)], 1, (1, 3, False))[2] in ([(0, 1)], [(0, 2)])
+    with pytest.raises(ValueError):
+        lib().get_neighbors([0], [0], [(0, 0)], (0, 4))
+    with pytest.raises(IndexError):
+        lib().get_neighbors([0], [0], [(5, 0)], (4, 4, False))

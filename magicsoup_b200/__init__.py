@@ -1,7 +1,8 @@
 """
-magicsoup_b200: B200-native (sm_100a) implementation of magicsoup's per-step world
-math behind the reference's own `Kinetics` / `World` API:
-`Kinetics.integrate_signals`, `World.enzymatic_activity`, `World.diffuse_molecules`.
+magicsoup_b200: B200-native (sm_100a) implementation of magicsoup's per-step world math behind the
+reference's own `Kinetics` / `World` API (`Kinetics.integrate_signals`, `World.enzymatic_activity`,
+`World.diffuse_molecules`), with the genome side around it (`Genetics`, mutations, `_lib` in C++,
+`set_cell_params` as a kernel) and `distributed.SlabWorld` for several GPUs.
 """
 from magicsoup_b200.kinetics import Kinetics  # noqa: F401
 from magicsoup_b200.world import World, Molecule, Chemistry  # noqa: F401

@@ -1,24 +1,31 @@
 """
-`World` with the reference's step interface (mRcSchwering/magic-soup 1.0.5,
-python/magicsoup/world.py:36-1004) for the per-step world math:
+`World` with the reference's interface (mRcSchwering/magic-soup 1.0.5,
+python/magicsoup/world.py:36-1004).  The per-step world math runs as CUDA kernels:
 
   enzymatic_activity()        world.py:610-625   fused kinetics kernel + write-back
   diffuse_molecules()         world.py:627-665   tiled stencil, mass correction, permeation
-  degrade_molecules()         world.py:667-678
+  degrade_molecules()         world.py:667-678   one launch, or folded into the diffusion
   increment_cell_lifetimes()  world.py:680-687
-  kill_cells / divide_cells_at / add_cells_from_params   index-consistent bookkeeping of
-                              world.py:406-540 for the tensors the kernels read
+
+and the bookkeeping around it keeps every tensor the kernels read index-consistent:
+
+  spawn_cells / divide_cells / update_cells / kill_cells / move_cells / reposition_cells /
+  mutate_cells / recombinate_cells / get_neighbors          world.py:229-608, 689-745
+  add_cells_from_params / divide_cells_at                   the same with ready-made parameter
+                                                            tensors / caller-chosen pixels
+  save / from_file / save_state / load_state                world.py:747-878
+
+String and map searches run in `magicsoup_b200._lib` (C++, the interface of the reference's Rust
+extension), `Kinetics.set_cell_params` as one kernel.
 
 State attributes keep the reference's names, shapes and dtypes (world.py:192-204):
 cell_map (H,W) bool, cell_positions (c,2) i32, cell_lifetimes/cell_divisions (c,) i32,
 cell_molecules (c,m) f32, molecule_map (m,H,W) f32.  As in the reference,
 enzymatic_activity/diffuse_molecules update molecule_map in place and REBIND
-cell_molecules to a new tensor.
+cell_molecules to a new tensor.  cell_molecules, molecule_map and cell_positions are properties:
+reading one first finishes a step whose early-exit check is still pending (`_settle`).
 
-Genomes, translation and mutation (genetics.py, mutations.py, the Rust `_lib`) keep
-their host role in the reference and are not part of this package; cells enter through
-`add_cells_from_params` with ready parameter tensors.  No CPU fallback: the step methods
-raise without a CUDA device.
+No CPU fallback: the step methods raise without a CUDA device.
 """
 from __future__ import annotations
 

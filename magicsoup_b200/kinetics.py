@@ -12,14 +12,18 @@ Mirrored from the reference (same names, argument meaning, dtypes, error behavio
   unset_cell_params / copy_cell_params / remove_cell_params /
   increase_max_cells / increase_max_proteins            kinetics.py:627-723
 
-The parameter tensors are plain attributes that users and tests overwrite
-(`kinetics.N = tensor`), possibly with CPU tensors: every call reads the current
-attributes and normalises them (device, dtype, contiguity) at the boundary.
+  set_cell_params(cell_idxs, proteomes)                 kinetics.py:521-625, one kernel launch
+  token maps km_map / vmax_map / sign_map / hill_map / reaction_map / transport_map /
+  effector_map (kinetics.py:16-289; magicsoup_b200/tokens.py)
+
+The parameter tensors are attributes that users and tests overwrite (`kinetics.N = tensor`),
+possibly with CPU tensors: every call reads the current attributes and normalises them (device,
+dtype, contiguity) at the boundary.  Behind them sits a capacity store with a row map and the
+kernel's list cache (see "parameter store" below).
 
 There is no CPU fallback: the numeric methods raise without a CUDA device.
-`set_cell_params` / `get_proteome` (genome -> parameters, kinetics.py:462-625) are host
-side genetics and not part of this hot path; populations are installed with
-`set_cell_params_from_tensors`.
+`get_proteome` (parameters -> domain descriptions for the reference's `Cell` container,
+kinetics.py:462-519) is not part of this package; `_lib.get_proteome` has the Rust function's interface.
 """
 from __future__ import annotations
 
